@@ -1,0 +1,165 @@
+"""Generate tests/golden/*.npz by running the REFERENCE's own modules (imported by file path
+from /root/reference -- the package __init__ chain needs mamba_ssm/clip/h5py which are absent).
+
+Run in the build container only (the GPU box has no /root/reference):
+    python oracle/gen_golden.py
+The fixtures are committed; tests/test_oracle_golden.py pins oracle/lipvq_oracle.py to them and
+the -m gpu tests pin the CUDA path to the same files.
+"""
+from __future__ import annotations
+
+import importlib.util
+import os
+import sys
+
+import numpy as np
+import torch
+
+REF = os.environ.get("LIPVQ_REFERENCE", "/root/reference")
+HERE = os.path.dirname(os.path.abspath(__file__))
+OUT = os.path.join(os.path.dirname(HERE), "tests", "golden")
+
+
+def _load(name: str, rel: str):
+    spec = importlib.util.spec_from_file_location(name, os.path.join(REF, rel))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
+def _np(d):
+    return {k: (v.detach().cpu().numpy() if torch.is_tensor(v) else np.asarray(v)) for k, v in d.items()}
+
+
+def _save(name: str, **arrs):
+    os.makedirs(OUT, exist_ok=True)
+    path = os.path.join(OUT, name + ".npz")
+    np.savez_compressed(path, **_np(arrs))
+    print(f"wrote {path}  ({os.path.getsize(path) / 1024:.0f} KiB)")
+
+
+def _actions(n, f, seed=123):
+    g = torch.Generator().manual_seed(seed)
+    return torch.rand(n, f, generator=g) * 2 - 1
+
+
+def gen_t1(v5, tag, F_, D, K, N, steps):
+    torch.manual_seed(0)
+    model = v5.LLFQVAE_V4(F_, D, K)
+    x = _actions(N, F_)
+    sd0 = {k: v.clone() for k, v in model.state_dict().items()}
+    # forward pieces through the reference's own submodules
+    h = model.encoder(x)
+    z_e = model.to_latent(h)
+    z_q, idx = model.quantizer(z_e)
+    z_latent, loss = model(x)
+    model.zero_grad()
+    loss.backward()
+    grads = {"grad." + k: p.grad.clone() for k, p in model.named_parameters()}
+    # AdamW trajectory with the reference protocol (icl.py:1437-1441, 1466, 1520-1522)
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=1e-4)
+    losses = []
+    for _ in range(steps):
+        opt.zero_grad()
+        _, l = model(x)
+        l.backward()
+        opt.step()
+        losses.append(l.detach().clone())
+    sdT = {"final." + k: v.clone() for k, v in model.state_dict().items()}
+    _save(tag, x=x, z_e=z_e, indices=idx, z_latent=z_latent, loss=loss, traj_losses=torch.stack(losses),
+          **{"sd." + k: v for k, v in sd0.items()}, **grads, **sdT)
+
+
+def gen_t1_ema(v5, hq, tag, F_, D, K, N, steps):
+    """T1 body with the EMA quantizer of hq_vae.py:224-281 swapped in (train mode)."""
+    torch.manual_seed(0)
+    model = v5.LLFQVAE_V4(F_, D, K)
+    model.quantizer = hq.LFQQuantizerEMA(K, D)
+    model.train()
+    x = _actions(N, F_)
+    sd0 = {k: v.clone() for k, v in model.state_dict().items()}
+    opt = torch.optim.AdamW(model.parameters(), lr=1e-3, weight_decay=1e-4)
+    losses = []
+    for _ in range(steps):
+        opt.zero_grad()
+        _, l = model(x)
+        l.backward()
+        opt.step()
+        losses.append(l.detach().clone())
+    sdT = {"final." + k: v.clone() for k, v in model.state_dict().items()}
+    _save(tag, x=x, traj_losses=torch.stack(losses), **{"sd." + k: v for k, v in sd0.items()}, **sdT)
+
+
+def gen_quantizers(hq, tag, N, K, D):
+    torch.manual_seed(1)
+    z = torch.rand(N, D)
+    q = hq.LFQQuantizerEMA(K, D)
+    q.train()
+    pre = {k: v.clone() for k, v in q.state_dict().items()}
+    z_q, idx = q(z)
+    post = {k: v.clone() for k, v in q.state_dict().items()}
+    torch.manual_seed(2)
+    ql = hq.LFQQuantizerEMA_KMeans(K, D, dead_threshold=0)
+    ql.initialized = True  # k-means init is host-side sklearn: excluded
+    prel = {k: v.clone() for k, v in ql.state_dict().items()}
+    z_ql, idxl = ql(z)
+    postl = {k: v.clone() for k, v in ql.state_dict().items()}
+    _save(tag, z=z, z_q=z_q, indices=idx, **{"pre." + k: v for k, v in pre.items()},
+          **{"post." + k: v for k, v in post.items()}, lap_z_q=z_ql, lap_indices=idxl,
+          **{"lap_pre." + k: v for k, v in prel.items()}, **{"lap_post." + k: v for k, v in postl.items()})
+
+
+def gen_t4(bb, tag, F_, D, K, N):
+    torch.manual_seed(0)
+    model = bb.VQVAE(F_, D, num_embeddings=K)
+    x = _actions(N, F_)
+    sd0 = {k: v.clone() for k, v in model.state_dict().items()}
+    z_e = model.encoder(x)
+    d = (z_e.unsqueeze(1) - model.embedding.weight).pow(2).sum(-1)
+    idx = torch.argmin(d, dim=1)
+    z_latent, loss = model(x)
+    model.zero_grad()
+    loss.backward()
+    grads = {"grad." + k: p.grad.clone() for k, p in model.named_parameters()}
+    _save(tag, x=x, z_e=z_e, indices=idx, z_latent=z_latent, loss=loss,
+          **{"sd." + k: v for k, v in sd0.items()}, **grads)
+
+
+def gen_t2(hv, tag, A, E, Kz, Kq, stages, layers, B, T):
+    torch.manual_seed(0)
+    model = hv.HierarchicalVQVAE(A, embed_dim=E, num_subclusters=Kz, num_clusters=Kq, num_stages=stages,
+                                 num_layers_per_stage=layers, dropout=0.0, replace_threshold_z=0.0,
+                                 replace_threshold_q=0.0, kmeans_init=False)
+    model.codebooks_initialized.fill_(True)  # skip RNG/k-means init; constructor codebooks are used
+    g = torch.Generator().manual_seed(123)
+    actions = torch.rand(B, T, A, generator=g) * 2 - 1
+    sd0 = {k: v.clone() for k, v in model.state_dict().items()}
+    out = model(actions, training=True)
+    losses = model.compute_vqvae_loss(out, actions, lambda_rec=0.002)
+    model.zero_grad()
+    losses["vqvae_loss"].backward()
+    grads = {"grad." + k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}
+    post = {"post." + k: model.state_dict()[k].clone() for k in
+            ("codebook_z", "codebook_q", "cluster_size_z", "cluster_size_q", "embed_avg_z", "embed_avg_q")}
+    usage = model.get_codebook_usage()
+    _save(tag, actions=actions, **{"out." + k: v for k, v in out.items()},
+          **{"loss." + k: v for k, v in losses.items()}, **{"sd." + k: v for k, v in sd0.items()}, **grads, **post,
+          usage_z_used=usage["z_used"], usage_q_used=usage["q_used"])
+
+
+def main():
+    v5 = _load("ref_v5", "robomimic/models/vq_vae/backbone_lfqvae_v5.py")
+    hq = _load("ref_hq", "robomimic/models/vq_vae/hq_vae.py")
+    bb = _load("ref_bb", "robomimic/models/vq_vae/backbone.py")
+    hv = _load("ref_hv", "robomimic/algo/heirarchical_vqvae.py")
+    torch.set_num_threads(1)
+    gen_t1(v5, "t1_c1", 7, 64, 512, 64, steps=10)           # BASELINE C1 shape (rows reduced)
+    gen_t1(v5, "t1_real", 12, 208, 128, 80, steps=5)        # reference __main__ shape (backbone_lfqvae_v5.py:89-93)
+    gen_t1_ema(v5, hq, "t1_ema", 12, 64, 128, 256, steps=6)
+    gen_quantizers(hq, "quantizers", 256, 64, 32)
+    gen_t4(bb, "t4_classic", 7, 32, 128, 64)
+    gen_t2(hv, "t2_hvq", 7, 64, 64, 32, 2, 3, 4, 16)
+
+
+if __name__ == "__main__":
+    sys.exit(main())
