@@ -1,0 +1,210 @@
+/*
+ * lipvq.h -- C ABI of the B200-native LipVQ-VAE action-tokenizer kernels (liblipvq.so).
+ *
+ * This is the drop-in boundary underneath the reference's PyTorch module API.  The reference
+ * (Alishah-Naushad/Robot-Manipulation-VQ-VAE) has no FFI of its own: its "operator interface"
+ * for this path is the nn.Module ctor/forward/state_dict surface.  Every entry
+ * point below replaces a group of torch ops of the reference and cites the file:line it stands
+ * in for (paths relative to the reference checkout).  The Python shim that keeps the module API
+ * (robot-manipulation-vq-vae_b200/lipvq/) binds these symbols with ctypes; INTEGRATION.md shows
+ * the stub a reference maintainer would add.
+ *
+ * Conventions
+ *   - plain pointers + sizes; no torch / C++ types.  All pointers are DEVICE pointers unless
+ *     the name ends in _host.  Row-major, contiguous, fp32 unless stated.  Indices are int64
+ *     (what torch.argmin returns).
+ *   - every call is asynchronous on `stream` (a cudaStream_t passed as void*), performs no
+ *     allocation and no host synchronisation, and is CUDA-graph capturable.  Scratch memory is
+ *     supplied by the caller (see *_workspace_bytes).
+ *   - return value: LIPVQ_OK or an error code; lipvq_last_error() gives the message of the
+ *     last failing call on the calling thread.
+ *   - sm_100a only.  There is no CPU path in this library.
+ */
+#ifndef LIPVQ_H_
+#define LIPVQ_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LIPVQ_ABI_VERSION 1
+#define LIPVQ_API __attribute__((visibility("default")))
+
+enum {
+  LIPVQ_OK = 0,
+  LIPVQ_ERR_INVALID = 1, /* bad argument (shape, alignment, null pointer, workspace too small) */
+  LIPVQ_ERR_CUDA = 2,    /* a CUDA runtime/driver call or kernel launch failed */
+  LIPVQ_ERR_UNSUPPORTED = 3
+};
+
+/* nearest-code metric */
+enum {
+  LIPVQ_METRIC_L2 = 0,     /* argmin_k sqrt(sum_d (z-e)^2): LFQQuantizer, backbone_lfqvae_v5.py:39-46 */
+  LIPVQ_METRIC_L2SQ = 1,   /* argmin_k sum_d (z-e)^2 (no sqrt): VQVAE.quantize, backbone.py:57-63 */
+  LIPVQ_METRIC_DOT = 2     /* argmax_k <z,e> on caller-normalised rows: heirarchical_vqvae.py:441-449 */
+};
+
+/* search algorithm */
+enum {
+  LIPVQ_ALGO_AUTO = 0,
+  LIPVQ_ALGO_SIMT_F32 = 1, /* shared-memory staged fp32 FFMA tiles, warp-shuffle argmin */
+  LIPVQ_ALGO_TCGEN05 = 2   /* TMA-fed tcgen05/TMEM split-bf16 contraction, argmin in the TMEM epilogue */
+};
+
+/* activations understood by the fused linear kernels */
+enum {
+  LIPVQ_ACT_NONE = 0,
+  LIPVQ_ACT_RELU = 1,
+  LIPVQ_ACT_GELU = 2,    /* exact erf GELU (nn.GELU() default) */
+  LIPVQ_ACT_SIGMOID = 3
+};
+
+/* EMA codebook normalisation variants */
+enum {
+  LIPVQ_EMA_SIMPLE = 0,   /* codebook = sum / (size + eps)                      hq_vae.py:277-279 */
+  LIPVQ_EMA_LAPLACE = 1,  /* codebook = sum / ((size+eps)/(sum(size)+K*eps))    hq_vae.py:115-118 */
+  LIPVQ_EMA_NORMALIZE = 2 /* codebook = l2normalize(sum / (size + eps))         heirarchical_vqvae.py:533-541 */
+};
+
+LIPVQ_API int lipvq_abi_version(void);
+LIPVQ_API const char* lipvq_last_error(void);
+/* number of kernels this library has launched from the calling process since load (all threads) */
+LIPVQ_API uint64_t lipvq_launch_count(void);
+
+/* ---------------------------------------------------------------------------------------------
+ * K3  fused distance + argmin (nearest code).  Replaces the [N,K,D] broadcast, torch.norm and
+ * torch.argmin of LFQQuantizer.forward (backbone_lfqvae_v5.py:39-46; dup hq_vae.py:92-97,
+ * 247-255), the squared form of VQVAE.quantize (backbone.py:57-63) and the matmul+argmax of
+ * HierarchicalVQVAE._compute_similarities/quantize_* (heirarchical_vqvae.py:421-449).
+ *
+ * Never materialises [N,K].  Scores ||e||^2 - 2 z.e are produced by the chosen contraction
+ * (fp32 FFMA tiles, or split-bf16 tcgen05 MMAs accumulated in TMEM) with a per-row running
+ * top-2; rows whose two best scores are closer than a rigorous error bound of the contraction
+ * are re-scored by an exact fp32 direct-difference scan (sqrt applied for METRIC_L2, first-min
+ * tie rule), so indices equal the reference's except where the reference's own fp32 rounding
+ * decides (relative distance gap < 1e-6).
+ *
+ *   z [N,D], codebook [K,D] fp32; idx_out [N] int64; best_out [N] fp32 or NULL (exact winning
+ *   distance / squared distance / similarity, as the metric defines).
+ *   stats_out: NULL or 4 x int32 on device: {rows rescored exactly, 0, 0, 0}.
+ * --------------------------------------------------------------------------------------------- */
+LIPVQ_API size_t lipvq_nn_search_workspace_bytes(int64_t N, int D, int K, int metric, int algo);
+LIPVQ_API int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook, int K, int metric, int algo,
+                        int64_t* idx_out, float* best_out, int32_t* stats_out, void* workspace,
+                        size_t workspace_bytes, void* stream);
+/* which algorithm AUTO resolves to for a shape (host-side, no launch) */
+LIPVQ_API int lipvq_nn_search_pick_algo(int64_t N, int D, int K, int metric);
+
+/* row-wise F.normalize(x, dim=-1, eps=1e-12) (heirarchical_vqvae.py:441-445). y may alias x. */
+LIPVQ_API int lipvq_l2_normalize_rows_f32(const float* x, int64_t rows, int D, float* y, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K4  gather + straight-through + commitment/codebook loss.  Replaces codebook[indices],
+ * z + (q - z).detach(), the two mse_loss calls and z_q.clone().detach()
+ * (backbone_lfqvae_v5.py:47,74,80-81; backbone.py:66-74; heirarchical_vqvae.py:450-459).
+ *
+ *   z_q_out   [N,D]: codebook[idx] (bit-exact copy of the code rows)
+ *   z_st_out  [N,D] or NULL: z + (z_q - z) evaluated in fp32 exactly as the reference's STE
+ *   sqerr_sum (double*, 1 element, ACCUMULATED INTO): sum over N*D of (z_q - z)^2
+ * --------------------------------------------------------------------------------------------- */
+LIPVQ_API int lipvq_gather_ste_loss_fwd_f32(const float* z, const int64_t* idx, const float* codebook, int64_t N, int D, int K,
+                                  float* z_q_out, float* z_st_out, double* sqerr_sum, void* stream);
+
+/* backward of the two MSE terms + gather:
+ *   dz_out[n,:]  = w_commit * 2/(N*D) * (z - z_q) * gscale            (+ dzq_up[n,:] if ste != 0)
+ *   dcodebook[idx[n],:] += w_codebook * 2/(N*D) * (z_q - z) * gscale  (+ dzq_up[n,:] if ste == 0)
+ * gscale is read from device (*gscale_dev, the upstream d loss) or 1 if NULL.  dzq_up (gradient
+ * arriving at z_q / z_st from the decoder) may be NULL.  If sigmoid_out != NULL the result is
+ * multiplied by y(1-y) with y = sigmoid_out (= z), i.e. dz_out is the gradient at the Lipschitz
+ * layer's pre-activation (fuses torch.sigmoid's backward, backbone_lfqvae_v5.py:24). */
+LIPVQ_API int lipvq_gather_ste_loss_bwd_f32(const float* z, const float* z_q, const int64_t* idx, const float* dzq_up,
+                                  const float* gscale_dev, float w_commit, float w_codebook, int ste,
+                                  const float* sigmoid_out, int64_t N, int D, int K, float* dz_out,
+                                  float* dcodebook, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K5  EMA codebook statistics and update.  Replaces F.one_hot, .sum(0), one_hot^T @ z and the
+ * mul_/add_ EMA + normalise chain (hq_vae.py:103-118, 262-279; heirarchical_vqvae.py:498-541).
+ * counts [K] fp32 and sums [K,D] fp32 are ACCUMULATED INTO (zero them first; in data-parallel
+ * runs they are all-reduced between the two calls).
+ * --------------------------------------------------------------------------------------------- */
+LIPVQ_API int lipvq_ema_stats_f32(const float* z, const int64_t* idx, int64_t N, int D, int K, float* counts, float* sums,
+                        void* stream);
+/* size <- decay*size + (1-decay)*counts ; ema_sum <- decay*ema_sum + (1-decay)*sums ;
+ * codebook <- variant(ema_sum, size).  one_minus_decay is passed separately so the host can form
+ * it in double like the reference does (1 - self.decay).  scratch: >= 8 bytes device. */
+LIPVQ_API int lipvq_ema_apply_f32(const float* counts, const float* sums, int K, int D, float decay, float one_minus_decay,
+                        float eps, int variant, float* ema_size, float* ema_sum, float* codebook, void* scratch,
+                        void* stream);
+/* usage bookkeeping of LFQQuantizerEMA_KMeans (hq_vae.py:123-130):
+ * usage_counts += counts; usage_ma = .99*usage_ma + .01*(counts>0); entropy_ma (1 elem) EMA of
+ * -(p log(p+1e-8)).sum(), p = counts/(counts.sum()+1e-8). */
+LIPVQ_API int lipvq_usage_stats_f32(const float* counts, int K, float* usage_counts, float* usage_ma, float* entropy_ma,
+                          void* stream);
+/* codebook-health summary (heirarchical_vqvae.py:687-706): out[0]=#(size>0), out[1]=#(size<dead_thr)
+ * as int32 on device -- one D2H copy instead of ~8 .item() syncs. */
+LIPVQ_API int lipvq_codebook_usage_f32(const float* cluster_size, int K, float dead_thr, int32_t* out2, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * K1/K2/K7  fused linear layers (encoder / Lipschitz / decoder MLPs).
+ * Replaces nn.Linear+nn.GELU chains (backbone_lfqvae_v5.py:54-68, 71, 75-76), nn.Linear+ReLU
+ * (backbone.py:17-32), normalization()+LipschitzMLP.forward (backbone_lfqvae_v5.py:6-24).
+ *
+ * Activations are applied at the CONSUMER: a layer stores its pre-activation a = x W^T + b, the
+ * next layer applies act_in while loading it.  One HBM write + one read per intermediate and
+ * the backward pass has the pre-activations it needs without a second copy.
+ *
+ *   fwd:   Y[n,o] = act_out( sum_i act_in(X[n,i]) * W[o,i] + bias[o] )           X:[N,in] W:[out,in]
+ *   bwd_x: dX[n,i] = ( sum_o dY[n,o] * W[o,i] ) * act_in'(X[n,i])                 (gradient at X, the stored pre-activation)
+ *   bwd_w: dW[o,i] += sum_n dY[n,o] * act_in(X[n,i]) ;  db[o] += sum_n dY[n,o]    (ACCUMULATED INTO; db may be NULL)
+ * --------------------------------------------------------------------------------------------- */
+LIPVQ_API int lipvq_linear_fwd_f32(const float* X, int64_t N, int in_dim, int act_in, const float* W, const float* bias,
+                         int out_dim, int act_out, float* Y, void* stream);
+LIPVQ_API int lipvq_linear_bwd_x_f32(const float* dY, int64_t N, int out_dim, const float* W, int in_dim, const float* X,
+                           int act_in, float* dX, void* stream);
+LIPVQ_API int lipvq_linear_bwd_w_f32(const float* dY, int64_t N, int out_dim, const float* X, int in_dim, int act_in, float* dW,
+                           float* db, void* stream);
+
+/* dX = dY * act'(.) evaluated from the layer OUTPUT y (sigmoid: y(1-y); relu: [y>0]; none: 1).  For modules used
+ * stand-alone (LipschitzMLP as q_encoder, hq_vae.py:375) whose upstream gradient arrives at the activation output. */
+LIPVQ_API int lipvq_act_bwd_from_output_f32(const float* dY, const float* Y, int act, int64_t numel, float* dX, void* stream);
+
+/* L-inf Lipschitz weight clamp (normalization(), backbone_lfqvae_v5.py:6-12):
+ * scale[o] = min(1, softplus(ci[o]) / sum_i |W[o,i]|);  W_norm = W * scale.  */
+LIPVQ_API int lipvq_lipschitz_scale_fwd_f32(const float* W, const float* ci, int out_dim, int in_dim, float* scale,
+                                  float* W_norm, void* stream);
+/* given G = dL/dW_norm: dW += G*scale + [scale<1] * (-(sum_i G W) * softplus(ci)/l1^2) * sign(W);
+ * dci += [scale<1] * (sum_i G W)/l1 * sigmoid(ci).  (autograd of the expression above) */
+LIPVQ_API int lipvq_lipschitz_scale_bwd_f32(const float* G, const float* W, const float* ci, int out_dim, int in_dim, float* dW,
+                                  float* dci, void* stream);
+
+/* mean-squared error (F.mse_loss, reduction='mean'), fused with its gradient:
+ * sqerr_sum (double, accumulated into) += sum (y-t)^2 ; if dY != NULL: dY = 2/(numel) * (y - t) * gscale,
+ * and multiplied by act'(y) for act_out in {NONE, RELU} when the layer applied it in its epilogue. */
+LIPVQ_API int lipvq_mse_fwd_bwd_f32(const float* Y, const float* T, int64_t numel, const float* gscale_dev, int act_out,
+                          double* sqerr_sum, float* dY, void* stream);
+
+/* T1 loss tail (backbone_lfqvae_v5.py:79-83): losses_out[0..3] = {loss, recon, commit, codebook} with
+ * recon = sq[0]/n_recon, commit = codebook = sq[1]/n_lat, loss = recon + w_commit*commit + w_cb*codebook (fp32). */
+LIPVQ_API int lipvq_t1_loss_finalize(const double* sq2, double n_recon, double n_lat, float w_commit, float w_cb,
+                           float* losses_out4, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Optimiser: torch.optim.AdamW single step over one flat fp32 buffer (robomimic/algo/icl.py:1437-1441:
+ * AdamW(lr=1e-3, weight_decay=1e-4) on the tokenizer).  grad_scale multiplies g first (1/world_size
+ * after a sum all-reduce).  step is 1-based.
+ * --------------------------------------------------------------------------------------------- */
+LIPVQ_API int lipvq_adamw_step_f32(float* p, const float* g, float* m, float* v, int64_t n, int step, const int32_t* step_dev,
+                         float lr, float beta1, float beta2, float eps, float weight_decay, float grad_scale,
+                         void* stream);
+/* *ctr += delta (device-resident step counter so a captured CUDA graph can be replayed step after step);
+ * when step_dev != NULL above, the step number is read from it instead of `step`. */
+LIPVQ_API int lipvq_counter_add_i32(int32_t* ctr, int delta, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LIPVQ_H_ */

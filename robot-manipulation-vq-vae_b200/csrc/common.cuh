@@ -1,0 +1,98 @@
+// Shared helpers for liblipvq.so (sm_100a).  Error plumbing, launch accounting, small device utilities.
+#pragma once
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+
+#include "lipvq.h"
+
+namespace lipvq {
+
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+void count_launch(int n = 1);
+int sm_count();
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
+
+}  // namespace lipvq
+
+#define LIPVQ_REQUIRE(cond, ...)      \
+  do {                                \
+    if (!(cond)) {                    \
+      lipvq::set_error(__VA_ARGS__);  \
+      return LIPVQ_ERR_INVALID;       \
+    }                                 \
+  } while (0)
+
+#define LIPVQ_CUDA(expr)                                             \
+  do {                                                               \
+    cudaError_t _e = (expr);                                         \
+    if (_e != cudaSuccess) return lipvq::cuda_fail(_e, #expr);       \
+  } while (0)
+
+// after a <<<>>> launch: count it and surface launch-configuration errors
+#define LIPVQ_LAUNCHED(name)                                         \
+  do {                                                               \
+    lipvq::count_launch();                                           \
+    cudaError_t _e = cudaGetLastError();                             \
+    if (_e != cudaSuccess) return lipvq::cuda_fail(_e, name);        \
+  } while (0)
+
+namespace lipvq {
+
+__device__ __forceinline__ float act_apply(int act, float x) {
+  switch (act) {
+    case LIPVQ_ACT_RELU: return x > 0.f ? x : 0.f;
+    case LIPVQ_ACT_GELU: return 0.5f * x * (1.f + erff(x * 0.70710678118654752440f));
+    case LIPVQ_ACT_SIGMOID: return 1.f / (1.f + expf(-x));
+    default: return x;
+  }
+}
+
+// derivative of act at pre-activation x
+__device__ __forceinline__ float act_grad(int act, float x) {
+  switch (act) {
+    case LIPVQ_ACT_RELU: return x > 0.f ? 1.f : 0.f;
+    case LIPVQ_ACT_GELU: {
+      // d/dx [x Phi(x)] = Phi(x) + x phi(x)
+      const float cdf = 0.5f * (1.f + erff(x * 0.70710678118654752440f));
+      const float pdf = 0.39894228040143267794f * expf(-0.5f * x * x);
+      return cdf + x * pdf;
+    }
+    case LIPVQ_ACT_SIGMOID: {
+      const float y = 1.f / (1.f + expf(-x));
+      return y * (1.f - y);
+    }
+    default: return 1.f;
+  }
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum_d(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// block-wide sum of doubles -> one atomicAdd(double) by thread 0.  blockDim.x <= 1024.
+__device__ __forceinline__ void block_atomic_add_double(double v, double* dst) {
+  __shared__ double s_part[32];
+  v = warp_sum_d(v);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) s_part[w] = v;
+  __syncthreads();
+  if (w == 0) {
+    const int nw = (blockDim.x + 31) >> 5;
+    double t = lane < nw ? s_part[lane] : 0.0;
+    t = warp_sum_d(t);
+    if (lane == 0) atomicAdd(dst, t);
+  }
+}
+
+}  // namespace lipvq

@@ -1,0 +1,457 @@
+// K4 gather / straight-through / commitment loss, K5 EMA codebook statistics + update, K6 usage bookkeeping.
+// HBM-bound streaming kernels: one coalesced pass over z (float4 when the row pitch allows), code rows come from
+// L2 (the codebook is re-read by every token), results leave in one coalesced pass.
+//
+// Reference anchors: backbone_lfqvae_v5.py:47,74,80-81 (gather, detach-copy, two MSE terms); backbone.py:66-74
+// (STE); hq_vae.py:103-130,262-279 and heirarchical_vqvae.py:498-541 (EMA counts/sums/update);
+// heirarchical_vqvae.py:687-706 (usage summary).
+#include "common.cuh"
+
+namespace lipvq {
+namespace {
+
+// ---- K4 forward -------------------------------------------------------------------------------------------------
+// VEC: D % 4 == 0 and 16-byte aligned bases -> one float4 per lane-step.  A group of `lanes_per_row` lanes owns
+// a row; groups stride over rows (grid-stride), so a warp reads 32*16 contiguous bytes of z per step when D >= 128.
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+    gather_fwd_kernel(const float* __restrict__ z, const int64_t* __restrict__ idx, const float* __restrict__ cb,
+                      int64_t N, int D, int K, float* __restrict__ zq, float* __restrict__ zst,
+                      double* __restrict__ sqerr) {
+  constexpr int W = VEC ? 4 : 1;
+  const int64_t total = N * (int64_t)(D / W);  // work items: one vector (or scalar) element each
+  const int per_row = D / W;
+  double local = 0.0;
+  float part = 0.f;
+  int cnt = 0;
+  for (int64_t it = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; it < total; it += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = it / per_row;
+    const int c = (int)(it - row * per_row) * W;
+    int64_t k = __ldg(idx + row);
+    k = k < 0 ? 0 : (k >= K ? K - 1 : k);  // defensive clamp; indices come from our own search
+    if (VEC) {
+      const float4 zv = __ldg(reinterpret_cast<const float4*>(z + row * D + c));
+      const float4 qv = __ldg(reinterpret_cast<const float4*>(cb + k * D + c));
+      *reinterpret_cast<float4*>(zq + row * D + c) = qv;
+      const float dx = qv.x - zv.x, dy = qv.y - zv.y, dz = qv.z - zv.z, dw = qv.w - zv.w;
+      if (zst) {
+        // z + (z_q - z): same two roundings as the reference's STE expression (backbone.py:74)
+        float4 st;
+        st.x = __fadd_rn(zv.x, dx); st.y = __fadd_rn(zv.y, dy); st.z = __fadd_rn(zv.z, dz); st.w = __fadd_rn(zv.w, dw);
+        *reinterpret_cast<float4*>(zst + row * D + c) = st;
+      }
+      part = fmaf(dx, dx, part); part = fmaf(dy, dy, part); part = fmaf(dz, dz, part); part = fmaf(dw, dw, part);
+    } else {
+      const float zv = __ldg(z + row * D + c);
+      const float qv = __ldg(cb + k * D + c);
+      zq[row * D + c] = qv;
+      const float dx = qv - zv;
+      if (zst) zst[row * D + c] = __fadd_rn(zv, dx);
+      part = fmaf(dx, dx, part);
+    }
+    if (++cnt == 64) {  // flush the fp32 partial into the double accumulator before it loses bits
+      local += (double)part;
+      part = 0.f;
+      cnt = 0;
+    }
+  }
+  local += (double)part;
+  block_atomic_add_double(local, sqerr);
+}
+
+// ---- K4 backward ------------------------------------------------------------------------------------------------
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+    gather_bwd_kernel(const float* __restrict__ z, const float* __restrict__ zq, const int64_t* __restrict__ idx,
+                      const float* __restrict__ dzq_up, const float* __restrict__ gscale_dev, float w_commit,
+                      float w_codebook, int ste, const float* __restrict__ sig_out, int64_t N, int D, int K,
+                      float* __restrict__ dz, float* __restrict__ dcb) {
+  constexpr int W = VEC ? 4 : 1;
+  const int per_row = D / W;
+  const int64_t total = N * (int64_t)per_row;
+  const float g = gscale_dev ? __ldg(gscale_dev) : 1.f;
+  const float coef = (float)(2.0 / ((double)N * (double)D)) * g;
+  const float cz = w_commit * coef, cq = w_codebook * coef;
+  for (int64_t it = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; it < total; it += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = it / per_row;
+    const int c = (int)(it - row * per_row) * W;
+    int64_t k = __ldg(idx + row);
+    k = k < 0 ? 0 : (k >= K ? K - 1 : k);
+    const int64_t o = row * D + c;
+    if (VEC) {
+      const float4 zv = __ldg(reinterpret_cast<const float4*>(z + o));
+      const float4 qv = __ldg(reinterpret_cast<const float4*>(zq + o));
+      float4 up = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (dzq_up) up = __ldg(reinterpret_cast<const float4*>(dzq_up + o));
+      float4 gz, gq;
+      gz.x = cz * (zv.x - qv.x); gz.y = cz * (zv.y - qv.y); gz.z = cz * (zv.z - qv.z); gz.w = cz * (zv.w - qv.w);
+      gq.x = cq * (qv.x - zv.x); gq.y = cq * (qv.y - zv.y); gq.z = cq * (qv.z - zv.z); gq.w = cq * (qv.w - zv.w);
+      if (ste) { gz.x += up.x; gz.y += up.y; gz.z += up.z; gz.w += up.w; }
+      else     { gq.x += up.x; gq.y += up.y; gq.z += up.z; gq.w += up.w; }
+      if (sig_out) {
+        const float4 y = __ldg(reinterpret_cast<const float4*>(sig_out + o));
+        gz.x *= y.x * (1.f - y.x); gz.y *= y.y * (1.f - y.y); gz.z *= y.z * (1.f - y.z); gz.w *= y.w * (1.f - y.w);
+      }
+      if (dz) *reinterpret_cast<float4*>(dz + o) = gz;
+      if (dcb) atomicAdd(reinterpret_cast<float4*>(dcb + k * D + c), gq);  // red.global.add.v4.f32 (sm_90+)
+    } else {
+      const float zv = __ldg(z + o), qv = __ldg(zq + o);
+      const float up = dzq_up ? __ldg(dzq_up + o) : 0.f;
+      float gz = cz * (zv - qv), gq = cq * (qv - zv);
+      if (ste) gz += up; else gq += up;
+      if (sig_out) {
+        const float y = __ldg(sig_out + o);
+        gz *= y * (1.f - y);
+      }
+      if (dz) dz[o] = gz;
+      if (dcb) atomicAdd(dcb + k * D + c, gq);
+    }
+  }
+}
+
+// ---- K5 statistics ----------------------------------------------------------------------------------------------
+// Each warp walks a contiguous run of tokens.  Lanes span the latent dim; the running sum of the current code is
+// kept in registers and flushed with one (vector) atomic per element only when the code changes -- consecutive
+// action steps usually share a code, so real data flushes rarely; random data costs one red per token element.
+template <int VPL>  // float4 vectors per lane: D = 128*VPL at most
+__global__ void __launch_bounds__(256)
+    ema_stats_vec_kernel(const float* __restrict__ z, const int64_t* __restrict__ idx, int64_t N, int D, int K,
+                         int64_t rows_per_warp, float* __restrict__ counts, float* __restrict__ sums) {
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  const int64_t r0 = warp * rows_per_warp;
+  if (r0 >= N) return;
+  const int64_t r1 = (r0 + rows_per_warp < N) ? r0 + rows_per_warp : N;
+  float4 acc[VPL];
+#pragma unroll
+  for (int v = 0; v < VPL; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+  int64_t cur = -1;
+  float run = 0.f;
+  for (int64_t r = r0; r < r1; ++r) {
+    int64_t k = __ldg(idx + r);
+    k = k < 0 ? 0 : (k >= K ? K - 1 : k);
+    if (k != cur) {
+      if (cur >= 0) {
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+          const int c = (lane + 32 * v) * 4;
+          if (c < D) atomicAdd(reinterpret_cast<float4*>(sums + cur * D + c), acc[v]);
+          acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        if (lane == 0) atomicAdd(counts + cur, run);
+      }
+      cur = k;
+      run = 0.f;
+    }
+    run += 1.f;
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+      const int c = (lane + 32 * v) * 4;
+      if (c < D) {
+        const float4 zv = __ldg(reinterpret_cast<const float4*>(z + r * D + c));
+        acc[v].x += zv.x; acc[v].y += zv.y; acc[v].z += zv.z; acc[v].w += zv.w;
+      }
+    }
+  }
+  if (cur >= 0) {
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+      const int c = (lane + 32 * v) * 4;
+      if (c < D) atomicAdd(reinterpret_cast<float4*>(sums + cur * D + c), acc[v]);
+    }
+    if (lane == 0) atomicAdd(counts + cur, run);
+  }
+}
+
+// generic fallback (any D / alignment): one thread per element, plain scalar atomics
+__global__ void __launch_bounds__(256)
+    ema_stats_scalar_kernel(const float* __restrict__ z, const int64_t* __restrict__ idx, int64_t N, int D, int K,
+                            float* __restrict__ counts, float* __restrict__ sums) {
+  const int64_t total = N * (int64_t)D;
+  for (int64_t it = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; it < total; it += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = it / D;
+    const int c = (int)(it - row * D);
+    int64_t k = __ldg(idx + row);
+    k = k < 0 ? 0 : (k >= K ? K - 1 : k);
+    atomicAdd(sums + k * D + c, __ldg(z + it));
+    if (c == 0) atomicAdd(counts + k, 1.f);
+  }
+}
+
+// ---- K5 update --------------------------------------------------------------------------------------------------
+// pass 1: size <- decay*size + (1-decay)*counts ; total = sum(size) (Laplace variant needs it)
+__global__ void __launch_bounds__(256)
+    ema_size_kernel(const float* __restrict__ counts, int K, float decay, float omd, float* __restrict__ ema_size,
+                    double* __restrict__ total) {
+  double local = 0.0;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < K; k += gridDim.x * blockDim.x) {
+    const float s = fmaf(omd, counts[k], ema_size[k] * decay);  // mul_(decay).add_(x, alpha=1-decay)
+    ema_size[k] = s;
+    local += (double)s;
+  }
+  block_atomic_add_double(local, total);
+}
+
+// pass 2: one warp per code row
+__global__ void __launch_bounds__(256)
+    ema_codebook_kernel(const float* __restrict__ sums, int K, int D, float decay, float omd, float eps, int variant,
+                        const float* __restrict__ ema_size, const double* __restrict__ total,
+                        float* __restrict__ ema_sum, float* __restrict__ codebook) {
+  const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (k >= K) return;
+  const float size = ema_size[k];
+  float denom;
+  if (variant == LIPVQ_EMA_LAPLACE) {
+    const float n = (float)(*total);
+    denom = (size + eps) / (n + (float)K * eps);
+  } else {
+    denom = size + eps;
+  }
+  float* es = ema_sum + (size_t)k * D;
+  const float* sm = sums + (size_t)k * D;
+  float* cbk = codebook + (size_t)k * D;
+  float nrm = 0.f;
+  for (int d = lane; d < D; d += 32) {
+    const float e = fmaf(omd, sm[d], es[d] * decay);
+    es[d] = e;
+    const float c = e / denom;
+    cbk[d] = c;
+    nrm = fmaf(c, c, nrm);
+  }
+  if (variant == LIPVQ_EMA_NORMALIZE) {
+    nrm = warp_sum(nrm);
+    const float dn = fmaxf(sqrtf(nrm), 1e-12f);
+    __syncwarp();
+    for (int d = lane; d < D; d += 32) cbk[d] = cbk[d] / dn;
+  }
+}
+
+// ---- K6 ---------------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(1024)
+    usage_stats_kernel(const float* __restrict__ counts, int K, float* __restrict__ usage_counts,
+                       float* __restrict__ usage_ma, float* __restrict__ entropy_ma) {
+  __shared__ double s_red[32];
+  __shared__ double s_total;
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  double tot = 0.0;
+  for (int k = threadIdx.x; k < K; k += blockDim.x) tot += (double)counts[k];
+  tot = warp_sum_d(tot);
+  if (lane == 0) s_red[w] = tot;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += s_red[i];
+    s_total = t;
+  }
+  __syncthreads();
+  const float denom = (float)s_total + 1e-8f;
+  double ent = 0.0;
+  for (int k = threadIdx.x; k < K; k += blockDim.x) {
+    const float c = counts[k];
+    usage_counts[k] += c;
+    usage_ma[k] = 0.99f * usage_ma[k] + 0.01f * (c > 0.f ? 1.f : 0.f);
+    const float p = c / denom;
+    ent += (double)(p * logf(p + 1e-8f));
+  }
+  ent = warp_sum_d(ent);
+  __syncthreads();
+  if (lane == 0) s_red[w] = ent;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += s_red[i];
+    entropy_ma[0] = 0.99f * entropy_ma[0] + 0.01f * (float)(-t);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    codebook_usage_kernel(const float* __restrict__ size, int K, float dead_thr, int32_t* __restrict__ out2) {
+  int used = 0, dead = 0;
+  for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < K; k += gridDim.x * blockDim.x) {
+    const float s = size[k];
+    used += s > 0.f;
+    dead += s < dead_thr;
+  }
+  used = __reduce_add_sync(0xffffffffu, used);
+  dead = __reduce_add_sync(0xffffffffu, dead);
+  if ((threadIdx.x & 31) == 0) {
+    if (used) atomicAdd(out2 + 0, used);
+    if (dead) atomicAdd(out2 + 1, dead);
+  }
+}
+
+// ---- MSE (+ gradient) and the loss tail ---------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+    mse_kernel(const float* __restrict__ y, const float* __restrict__ t, int64_t n, const float* __restrict__ gscale_dev,
+               int act_out, double* __restrict__ sqerr, float* __restrict__ dy) {
+  const float g = gscale_dev ? __ldg(gscale_dev) : 1.f;
+  const float coef = (float)(2.0 / (double)n) * g;
+  double local = 0.0;
+  float part = 0.f;
+  int cnt = 0;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float yv = y[i];
+    const float d = yv - t[i];
+    part = fmaf(d, d, part);
+    if (dy) {
+      float gr = coef * d;
+      if (act_out == LIPVQ_ACT_RELU && !(yv > 0.f)) gr = 0.f;
+      dy[i] = gr;
+    }
+    if (++cnt == 64) { local += (double)part; part = 0.f; cnt = 0; }
+  }
+  local += (double)part;
+  block_atomic_add_double(local, sqerr);
+}
+
+__global__ void t1_loss_finalize_kernel(const double* __restrict__ sq2, double n_recon, double n_lat, float w_commit,
+                                        float w_cb, float* __restrict__ out4) {
+  const float recon = (float)(sq2[0] / n_recon);
+  const float q = (float)(sq2[1] / n_lat);
+  // loss = recon_loss + 0.25 * commitment_loss + 0.25 * codebook_loss, left to right (backbone_lfqvae_v5.py:83)
+  const float loss = __fadd_rn(__fadd_rn(recon, __fmul_rn(w_commit, q)), __fmul_rn(w_cb, q));
+  out4[0] = loss;
+  out4[1] = recon;
+  out4[2] = q;
+  out4[3] = q;
+}
+
+inline int stream_grid(int64_t work_items, int threads, int per_sm) {
+  const int64_t want = ceil_div64(work_items, threads);
+  const int64_t cap = (int64_t)sm_count() * per_sm;
+  return (int)(want < 1 ? 1 : (want < cap ? want : cap));
+}
+
+}  // namespace
+}  // namespace lipvq
+
+using namespace lipvq;
+
+extern "C" {
+
+int lipvq_gather_ste_loss_fwd_f32(const float* z, const int64_t* idx, const float* codebook, int64_t N, int D, int K,
+                                  float* z_q_out, float* z_st_out, double* sqerr_sum, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(N >= 0 && D > 0 && K > 0, "gather_fwd: bad shape");
+  if (N == 0) return LIPVQ_OK;
+  LIPVQ_REQUIRE(z && idx && codebook && z_q_out && sqerr_sum, "gather_fwd: null pointer");
+  const bool vec = (D % 4 == 0) && aligned16(z) && aligned16(codebook) && aligned16(z_q_out) &&
+                   (!z_st_out || aligned16(z_st_out));
+  const int64_t items = N * (int64_t)(vec ? D / 4 : D);
+  const int grid = stream_grid(items, 256, 8);
+  if (vec)
+    gather_fwd_kernel<true><<<grid, 256, 0, stream>>>(z, idx, codebook, N, D, K, z_q_out, z_st_out, sqerr_sum);
+  else
+    gather_fwd_kernel<false><<<grid, 256, 0, stream>>>(z, idx, codebook, N, D, K, z_q_out, z_st_out, sqerr_sum);
+  LIPVQ_LAUNCHED("gather_fwd_kernel");
+  return LIPVQ_OK;
+}
+
+int lipvq_gather_ste_loss_bwd_f32(const float* z, const float* z_q, const int64_t* idx, const float* dzq_up,
+                                  const float* gscale_dev, float w_commit, float w_codebook, int ste,
+                                  const float* sigmoid_out, int64_t N, int D, int K, float* dz_out,
+                                  float* dcodebook, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(N >= 0 && D > 0 && K > 0, "gather_bwd: bad shape");
+  if (N == 0) return LIPVQ_OK;
+  LIPVQ_REQUIRE(z && z_q && idx, "gather_bwd: null pointer");
+  const bool vec = (D % 4 == 0) && aligned16(z) && aligned16(z_q) && (!dzq_up || aligned16(dzq_up)) &&
+                   (!sigmoid_out || aligned16(sigmoid_out)) && (!dz_out || aligned16(dz_out)) &&
+                   (!dcodebook || aligned16(dcodebook));
+  const int64_t items = N * (int64_t)(vec ? D / 4 : D);
+  const int grid = stream_grid(items, 256, 8);
+  if (vec)
+    gather_bwd_kernel<true><<<grid, 256, 0, stream>>>(z, z_q, idx, dzq_up, gscale_dev, w_commit, w_codebook, ste,
+                                                      sigmoid_out, N, D, K, dz_out, dcodebook);
+  else
+    gather_bwd_kernel<false><<<grid, 256, 0, stream>>>(z, z_q, idx, dzq_up, gscale_dev, w_commit, w_codebook, ste,
+                                                       sigmoid_out, N, D, K, dz_out, dcodebook);
+  LIPVQ_LAUNCHED("gather_bwd_kernel");
+  return LIPVQ_OK;
+}
+
+int lipvq_ema_stats_f32(const float* z, const int64_t* idx, int64_t N, int D, int K, float* counts, float* sums,
+                        void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(N >= 0 && D > 0 && K > 0, "ema_stats: bad shape");
+  if (N == 0) return LIPVQ_OK;
+  LIPVQ_REQUIRE(z && idx && counts && sums, "ema_stats: null pointer");
+  const bool vec = (D % 4 == 0) && D <= 512 && aligned16(z) && aligned16(sums);
+  if (vec) {
+    // enough warps for ~8 per SM sub-partition, at least 8 rows each so run-length aggregation has a chance
+    int64_t rows_per_warp = ceil_div64(N, (int64_t)sm_count() * 32);
+    if (rows_per_warp < 8) rows_per_warp = 8;
+    const int64_t warps = ceil_div64(N, rows_per_warp);
+    const unsigned grid = (unsigned)ceil_div64(warps * 32, 256);
+    const int vpl = (D + 127) / 128;
+    if (vpl == 1)
+      ema_stats_vec_kernel<1><<<grid, 256, 0, stream>>>(z, idx, N, D, K, rows_per_warp, counts, sums);
+    else if (vpl == 2)
+      ema_stats_vec_kernel<2><<<grid, 256, 0, stream>>>(z, idx, N, D, K, rows_per_warp, counts, sums);
+    else
+      ema_stats_vec_kernel<4><<<grid, 256, 0, stream>>>(z, idx, N, D, K, rows_per_warp, counts, sums);
+  } else {
+    ema_stats_scalar_kernel<<<stream_grid(N * (int64_t)D, 256, 8), 256, 0, stream>>>(z, idx, N, D, K, counts, sums);
+  }
+  LIPVQ_LAUNCHED("ema_stats_kernel");
+  return LIPVQ_OK;
+}
+
+int lipvq_ema_apply_f32(const float* counts, const float* sums, int K, int D, float decay, float one_minus_decay,
+                        float eps, int variant, float* ema_size, float* ema_sum, float* codebook, void* scratch,
+                        void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(K > 0 && D > 0, "ema_apply: bad shape");
+  LIPVQ_REQUIRE(counts && sums && ema_size && ema_sum && codebook && scratch, "ema_apply: null pointer");
+  LIPVQ_REQUIRE(variant >= LIPVQ_EMA_SIMPLE && variant <= LIPVQ_EMA_NORMALIZE, "ema_apply: bad variant %d", variant);
+  LIPVQ_REQUIRE(((uintptr_t)scratch & 7u) == 0, "ema_apply: scratch must be 8-byte aligned");
+  double* total = (double*)scratch;
+  LIPVQ_CUDA(cudaMemsetAsync(total, 0, sizeof(double), stream));
+  ema_size_kernel<<<stream_grid(K, 256, 4), 256, 0, stream>>>(counts, K, decay, one_minus_decay, ema_size, total);
+  LIPVQ_LAUNCHED("ema_size_kernel");
+  ema_codebook_kernel<<<(unsigned)ceil_div64((int64_t)K * 32, 256), 256, 0, stream>>>(
+      sums, K, D, decay, one_minus_decay, eps, variant, ema_size, total, ema_sum, codebook);
+  LIPVQ_LAUNCHED("ema_codebook_kernel");
+  return LIPVQ_OK;
+}
+
+int lipvq_usage_stats_f32(const float* counts, int K, float* usage_counts, float* usage_ma, float* entropy_ma,
+                          void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(K > 0 && counts && usage_counts && usage_ma && entropy_ma, "usage_stats: bad argument");
+  usage_stats_kernel<<<1, 1024, 0, stream>>>(counts, K, usage_counts, usage_ma, entropy_ma);
+  LIPVQ_LAUNCHED("usage_stats_kernel");
+  return LIPVQ_OK;
+}
+
+int lipvq_codebook_usage_f32(const float* cluster_size, int K, float dead_thr, int32_t* out2, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(K > 0 && cluster_size && out2, "codebook_usage: bad argument");
+  LIPVQ_CUDA(cudaMemsetAsync(out2, 0, 2 * sizeof(int32_t), stream));
+  codebook_usage_kernel<<<stream_grid(K, 256, 2), 256, 0, stream>>>(cluster_size, K, dead_thr, out2);
+  LIPVQ_LAUNCHED("codebook_usage_kernel");
+  return LIPVQ_OK;
+}
+
+int lipvq_mse_fwd_bwd_f32(const float* Y, const float* T, int64_t numel, const float* gscale_dev, int act_out,
+                          double* sqerr_sum, float* dY, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(numel >= 0, "mse: bad numel");
+  if (numel == 0) return LIPVQ_OK;
+  LIPVQ_REQUIRE(Y && T && sqerr_sum, "mse: null pointer");
+  LIPVQ_REQUIRE(act_out == LIPVQ_ACT_NONE || act_out == LIPVQ_ACT_RELU, "mse: act_out must be NONE or RELU");
+  mse_kernel<<<stream_grid(numel, 256, 8), 256, 0, stream>>>(Y, T, numel, gscale_dev, act_out, sqerr_sum, dY);
+  LIPVQ_LAUNCHED("mse_kernel");
+  return LIPVQ_OK;
+}
+
+int lipvq_t1_loss_finalize(const double* sq2, double n_recon, double n_lat, float w_commit, float w_cb,
+                           float* losses_out4, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(sq2 && losses_out4 && n_recon > 0 && n_lat > 0, "t1_loss_finalize: bad argument");
+  t1_loss_finalize_kernel<<<1, 1, 0, stream>>>(sq2, n_recon, n_lat, w_commit, w_cb, losses_out4);
+  LIPVQ_LAUNCHED("t1_loss_finalize_kernel");
+  return LIPVQ_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,466 @@
+// K3: fused distance + argmin (nearest code) -- fp32 SIMT contraction, top-2 merge/flag, exact rescore.
+//
+// Replaces LFQQuantizer.forward's [N,K,D] broadcast + torch.norm + torch.argmin
+// (reference robomimic/models/vq_vae/backbone_lfqvae_v5.py:39-46; hq_vae.py:92-97,247-255),
+// VQVAE.quantize's squared form (backbone.py:57-63) and HierarchicalVQVAE's matmul+argmax
+// (robomimic/algo/heirarchical_vqvae.py:441-449).
+//
+// Pipeline (all on one stream, no host sync):
+//   1. code_sqnorm_kernel   ||e_k||^2 and max_k ||e_k||^2
+//   2. contraction          score[n,k] = ||e_k||^2 - 2 z_n.e_k, per-row running top-2 (never stored as [N,K])
+//                           -- search_simt_kernel (here) or the tcgen05 kernel (search_tc.cu)
+//   3. finalize_kernel      merge the code slices; if second-best - best > error bound the best is provably the
+//                           reference's winner, else the row is queued
+//   4. rescore_kernel       queued rows: exact fp32 direct-difference scan in the reference's domain
+//                           (sqrt for METRIC_L2, first-min tie rule)
+#include "search.cuh"
+
+namespace lipvq {
+namespace {
+
+constexpr int BM = 128;  // z rows per CTA
+constexpr int BN = 64;   // codes per tile
+constexpr int BK = 16;   // latent-dim chunk
+constexpr int PAD = 4;
+constexpr int NT = 256;
+constexpr int kTargetCtas = 2 * 148 * 2;  // two resident CTAs per SM, two waves
+
+__global__ void __launch_bounds__(256) code_sqnorm_kernel(const float* __restrict__ cb, int K, int D, int metric,
+                                                          float* __restrict__ enorm, SearchHdr* hdr) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= K) return;
+  const float* row = cb + (size_t)warp * D;
+  float s = 0.f;
+  for (int d = lane; d < D; d += 32) {
+    const float v = __ldg(row + d);
+    s = fmaf(v, v, s);
+  }
+  s = warp_sum(s);
+  if (lane == 0) {
+    enorm[warp] = (metric == LIPVQ_METRIC_DOT) ? 0.f : s;
+    atomicMax(&hdr->emax2_bits, __float_as_uint(s));
+  }
+}
+
+// global -> registers for a [ROWS x BK] tile of a row-major matrix whose reduction dim is contiguous.
+template <int ROWS>
+__device__ __forceinline__ void ldg_tile(const float* __restrict__ src, int64_t r0, int64_t rmax, int k0, int kmax,
+                                         int ld, bool vec, float4 (&v)[ROWS * BK / 4 / NT]) {
+#pragma unroll
+  for (int u = 0; u < ROWS * BK / 4 / NT; ++u) {
+    const int f = threadIdx.x + NT * u;
+    const int r = f >> 2, kq = f & 3;
+    const int64_t row = r0 + r;
+    const int k = k0 + 4 * kq;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (row < rmax && k < kmax) {
+      const float* p = src + row * (int64_t)ld + k;
+      if (vec) {
+        x = __ldg(reinterpret_cast<const float4*>(p));
+      } else {
+        x.x = __ldg(p);
+        if (k + 1 < kmax) x.y = __ldg(p + 1);
+        if (k + 2 < kmax) x.z = __ldg(p + 2);
+        if (k + 3 < kmax) x.w = __ldg(p + 3);
+      }
+    }
+    v[u] = x;
+  }
+}
+
+// registers -> smem, transposed to [k][row]
+template <int ROWS>
+__device__ __forceinline__ void sts_tile(float (*S)[ROWS + PAD], const float4 (&v)[ROWS * BK / 4 / NT]) {
+#pragma unroll
+  for (int u = 0; u < ROWS * BK / 4 / NT; ++u) {
+    const int f = threadIdx.x + NT * u;
+    const int r = f >> 2, kq = f & 3;
+    S[4 * kq + 0][r] = v[u].x;
+    S[4 * kq + 1][r] = v[u].y;
+    S[4 * kq + 2][r] = v[u].z;
+    S[4 * kq + 3][r] = v[u].w;
+  }
+}
+
+// score[n,k] = enorm[k] - 2 z_n.e_k on fp32 FFMA tiles; per-row running (best, second, argbest).
+// grid = (ceil(N/BM), ksplit).  Thread (ty,tx) owns rows {4ty+i, 64+4ty+i} x codes {4tx+j}.
+__global__ void __launch_bounds__(NT, 2)
+    search_simt_kernel(const float* __restrict__ z, int64_t N, int D, const float* __restrict__ cb, int K,
+                       const float* __restrict__ enorm, int codes_per_split, float* __restrict__ pbest,
+                       float* __restrict__ psecond, int* __restrict__ pidx, int vec) {
+  __shared__ __align__(16) float As[BK][BM + PAD];
+  __shared__ __align__(16) float Bs[BK][BN + PAD];
+  __shared__ float en_s[BN];
+
+  const int t = threadIdx.x, tx = t & 15, ty = t >> 4;
+  const int64_t m0 = (int64_t)blockIdx.x * BM;
+  const int kbeg = blockIdx.y * codes_per_split;
+  const int kend = min(K, kbeg + codes_per_split);
+
+  float best[8], second[8];
+  int bidx[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    best[i] = INFINITY;
+    second[i] = INFINITY;
+    bidx[i] = kbeg;
+  }
+
+  for (int kt = kbeg; kt < kend; kt += BN) {
+    float acc[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+    float4 ra[2], rb[1];
+    ldg_tile<BM>(z, m0, N, 0, D, D, vec != 0, ra);
+    ldg_tile<BN>(cb, kt, kend, 0, D, D, vec != 0, rb);
+
+    for (int d0 = 0; d0 < D; d0 += BK) {
+      __syncthreads();  // everyone is done with the previous chunk (and the previous tile's epilogue)
+      sts_tile<BM>(As, ra);
+      sts_tile<BN>(Bs, rb);
+      if (d0 == 0 && t < BN) en_s[t] = (kt + t < kend) ? __ldg(enorm + kt + t) : INFINITY;
+      __syncthreads();
+      if (d0 + BK < D) {
+        ldg_tile<BM>(z, m0, N, d0 + BK, D, D, vec != 0, ra);
+        ldg_tile<BN>(cb, kt, kend, d0 + BK, D, D, vec != 0, rb);
+      }
+#pragma unroll
+      for (int kk = 0; kk < BK; ++kk) {
+        const float4 a0 = *reinterpret_cast<const float4*>(&As[kk][4 * ty]);
+        const float4 a1 = *reinterpret_cast<const float4*>(&As[kk][64 + 4 * ty]);
+        const float4 b0 = *reinterpret_cast<const float4*>(&Bs[kk][4 * tx]);
+        const float a[8] = {a0.x, a0.y, a0.z, a0.w, a1.x, a1.y, a1.z, a1.w};
+        const float b[4] = {b0.x, b0.y, b0.z, b0.w};
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+          for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+      }
+    }
+
+    // epilogue of this code tile: fold the 4 scores of every row into its running top-2
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int col = 4 * tx + j;
+      const float en = en_s[col];  // +inf for codes past the slice end -> never selected
+      const int k = kt + col;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float s = fmaf(-2.f, acc[i][j], en);
+        const bool lt = s < best[i];
+        second[i] = lt ? best[i] : fminf(second[i], s);
+        bidx[i] = lt ? k : bidx[i];
+        best[i] = lt ? s : best[i];
+      }
+    }
+  }
+
+  // merge the 16 threads (tx) that share a row: lanes differ only in the low 4 bits
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+#pragma unroll
+    for (int o = 8; o > 0; o >>= 1) {
+      const float ob = __shfl_xor_sync(0xffffffffu, best[i], o);
+      const float os = __shfl_xor_sync(0xffffffffu, second[i], o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bidx[i], o);
+      const bool take = (ob < best[i]) || (ob == best[i] && oi < bidx[i]);
+      const float loser = take ? best[i] : ob;
+      second[i] = fminf(fminf(second[i], os), loser);
+      best[i] = take ? ob : best[i];
+      bidx[i] = take ? oi : bidx[i];
+    }
+  }
+  if (tx == 0) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int64_t row = m0 + (i < 4 ? 4 * ty + i : 64 + 4 * ty + (i - 4));
+      if (row < N) {
+        const int64_t o = (int64_t)blockIdx.y * N + row;
+        pbest[o] = best[i];
+        psecond[o] = second[i];
+        pidx[o] = bidx[i];
+      }
+    }
+  }
+}
+
+// One warp per row: merge code slices, decide whether the approximate winner is provably exact.
+__global__ void __launch_bounds__(256)
+    finalize_kernel(const float* __restrict__ z, int64_t N, int D, const float* __restrict__ cb, int metric,
+                    int ksplit, const float* __restrict__ pbest, const float* __restrict__ psecond,
+                    const int* __restrict__ pidx, float gamma, float gamma_ref, SearchHdr* hdr,
+                    int* __restrict__ work, int64_t* __restrict__ idx_out, float* __restrict__ best_out) {
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= N) return;
+
+  float b = INFINITY, s2 = INFINITY;
+  int bi = 0;
+  for (int s = 0; s < ksplit; ++s) {  // uniform across the warp
+    const float ob = pbest[(int64_t)s * N + row], os = psecond[(int64_t)s * N + row];
+    const int oi = pidx[(int64_t)s * N + row];
+    const bool take = (ob < b) || (ob == b && oi < bi) || s == 0;
+    const float loser = take ? b : ob;
+    s2 = fminf(fminf(s2, os), loser);
+    b = take ? ob : b;
+    bi = take ? oi : bi;
+  }
+
+  // ||z||^2 and the exact value of the candidate winner, lanes across the latent dim
+  const float* zr = z + row * (int64_t)D;
+  const float* er = cb + (int64_t)bi * D;
+  float zn2 = 0.f, ex = 0.f;
+  for (int d = lane; d < D; d += 32) {
+    const float zv = __ldg(zr + d), ev = __ldg(er + d);
+    zn2 = fmaf(zv, zv, zn2);
+    if (metric == LIPVQ_METRIC_DOT) {
+      ex = fmaf(zv, ev, ex);
+    } else {
+      const float df = zv - ev;
+      ex = fmaf(df, df, ex);
+    }
+  }
+  zn2 = warp_sum(zn2);
+  ex = warp_sum(ex);
+  if (lane != 0) return;
+
+  const float emax2 = __uint_as_float(hdr->emax2_bits);
+  const float zn = sqrtf(zn2), emax = sqrtf(emax2);
+  // both competitors' scores can be off by gamma * (||e||^2 + 2||z|| ||e||) each
+  const float margin_alg = 2.f * gamma * (emax2 + 2.f * zn * emax);
+  // the reference's own fp32 rounding of d^2 (or of the similarity): stay out of its noise too
+  const float ref_mag = (metric == LIPVQ_METRIC_DOT) ? 2.f * zn * emax : fmaxf(b + zn2, 0.f);
+  const float margin = fmaxf(margin_alg, gamma_ref * ref_mag);
+  if (s2 - b > margin) {
+    idx_out[row] = (int64_t)bi;
+    if (best_out) best_out[row] = (metric == LIPVQ_METRIC_L2) ? sqrtf(ex) : ex;
+  } else {
+    const int pos = atomicAdd(&hdr->flagged, 1);
+    work[pos] = (int)row;
+  }
+}
+
+// Exact scan for queued rows: one warp per row, lane l takes codes l, l+32, ... ; each code's distance is a
+// sequential fp32 direct-difference sum over d (the reference's expression, backbone_lfqvae_v5.py:41-45).
+__global__ void __launch_bounds__(128)
+    rescore_kernel(const float* __restrict__ z, int D, const float* __restrict__ cb, int K, int metric,
+                   const SearchHdr* __restrict__ hdr, const int* __restrict__ work, int64_t* __restrict__ idx_out,
+                   float* __restrict__ best_out, int32_t* __restrict__ stats_out, int vec) {
+  extern __shared__ __align__(16) float zs_all[];
+  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* zs = zs_all + (size_t)wib * D;
+  const int nflag = hdr->flagged;
+  if (stats_out && blockIdx.x == 0 && threadIdx.x == 0) stats_out[0] = nflag;
+  const int warps_total = gridDim.x * (blockDim.x >> 5);
+  for (int w = blockIdx.x * (blockDim.x >> 5) + wib; w < nflag; w += warps_total) {
+    const int64_t row = work[w];
+    const float* zr = z + row * (int64_t)D;
+    __syncwarp();
+    for (int d = lane; d < D; d += 32) zs[d] = __ldg(zr + d);
+    __syncwarp();
+    float bv = INFINITY;
+    int bk = 0x7fffffff;
+    for (int k = lane; k < K; k += 32) {
+      const float* er = cb + (int64_t)k * D;
+      float a = 0.f;
+      if (vec) {
+        for (int d = 0; d < D; d += 4) {
+          const float4 e4 = __ldg(reinterpret_cast<const float4*>(er + d));
+          const float4 z4 = *reinterpret_cast<const float4*>(zs + d);
+          if (metric == LIPVQ_METRIC_DOT) {
+            a = fmaf(z4.x, e4.x, a); a = fmaf(z4.y, e4.y, a); a = fmaf(z4.z, e4.z, a); a = fmaf(z4.w, e4.w, a);
+          } else {
+            float df;
+            df = z4.x - e4.x; a = fmaf(df, df, a);
+            df = z4.y - e4.y; a = fmaf(df, df, a);
+            df = z4.z - e4.z; a = fmaf(df, df, a);
+            df = z4.w - e4.w; a = fmaf(df, df, a);
+          }
+        }
+      } else {
+        for (int d = 0; d < D; ++d) {
+          const float ev = __ldg(er + d);
+          if (metric == LIPVQ_METRIC_DOT) {
+            a = fmaf(zs[d], ev, a);
+          } else {
+            const float df = zs[d] - ev;
+            a = fmaf(df, df, a);
+          }
+        }
+      }
+      const float val = (metric == LIPVQ_METRIC_L2) ? sqrtf(a) : (metric == LIPVQ_METRIC_DOT ? -a : a);
+      if (val < bv) {  // strict: earlier (lower) k wins ties within the lane
+        bv = val;
+        bk = k;
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int ok = __shfl_xor_sync(0xffffffffu, bk, o);
+      if (ov < bv || (ov == bv && ok < bk)) {
+        bv = ov;
+        bk = ok;
+      }
+    }
+    if (lane == 0) {
+      if (bk == 0x7fffffff) bk = 0;  // all-NaN row: torch would return the NaN's index; we return 0
+      idx_out[row] = (int64_t)bk;
+      if (best_out) best_out[row] = (metric == LIPVQ_METRIC_DOT) ? -bv : bv;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    l2_normalize_rows_kernel(const float* __restrict__ x, int64_t rows, int D, float* __restrict__ y) {
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const float* xr = x + row * (int64_t)D;
+  float s = 0.f;
+  for (int d = lane; d < D; d += 32) {
+    const float v = xr[d];
+    s = fmaf(v, v, s);
+  }
+  s = warp_sum(s);
+  const float denom = fmaxf(sqrtf(s), 1e-12f);  // F.normalize: x / max(||x||_2, eps)
+  float* yr = y + row * (int64_t)D;
+  for (int d = lane; d < D; d += 32) yr[d] = xr[d] / denom;
+}
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+}  // namespace
+
+SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo) {
+  (void)metric;
+  SearchPlan p{};
+  if (algo == LIPVQ_ALGO_AUTO) algo = lipvq_nn_search_pick_algo(N, D, K, metric);
+  p.algo = algo;
+  const int tile = (algo == LIPVQ_ALGO_TCGEN05) ? 128 : BN;
+  const int64_t row_tiles = ceil_div64(N > 0 ? N : 1, 128);
+  const int code_tiles = (K + tile - 1) / tile;
+  int ks = (int)ceil_div64(kTargetCtas, row_tiles);
+  if (ks > code_tiles) ks = code_tiles;
+  if (ks < 1) ks = 1;
+  const int tiles_per_split = (code_tiles + ks - 1) / ks;
+  p.codes_per_split = tiles_per_split * tile;
+  p.ksplit = (K + p.codes_per_split - 1) / p.codes_per_split;
+  p.Dp = (D + 63) / 64 * 64;
+  p.Np = ceil_div64(N > 0 ? N : 1, 128) * 128;
+  p.Kp = (K + 127) / 128 * 128;
+  size_t o = 0;
+  p.off_hdr = o;      o = align_up(o + sizeof(SearchHdr), 256);
+  p.off_enorm = o;    o = align_up(o + sizeof(float) * (size_t)p.Kp, 256);
+  p.off_pbest = o;    o = align_up(o + sizeof(float) * (size_t)p.ksplit * N, 256);
+  p.off_psecond = o;  o = align_up(o + sizeof(float) * (size_t)p.ksplit * N, 256);
+  p.off_pidx = o;     o = align_up(o + sizeof(int) * (size_t)p.ksplit * N, 256);
+  p.off_work = o;     o = align_up(o + sizeof(int) * (size_t)(N > 0 ? N : 1), 256);
+  if (algo == LIPVQ_ALGO_TCGEN05) {
+    const size_t zb = sizeof(uint16_t) * (size_t)p.Np * p.Dp, eb = sizeof(uint16_t) * (size_t)p.Kp * p.Dp;
+    p.off_zhi = o;  o = align_up(o + zb, 1024);
+    p.off_zlo = o;  o = align_up(o + zb, 1024);
+    p.off_ehi = o;  o = align_up(o + eb, 1024);
+    p.off_elo = o;  o = align_up(o + eb, 1024);
+  }
+  p.total = o;
+  return p;
+}
+
+}  // namespace lipvq
+
+using namespace lipvq;
+
+extern "C" {
+
+int lipvq_nn_search_pick_algo(int64_t N, int D, int K, int metric) {
+  (void)metric;
+  // The tensor path pays a bf16 split pass over z and the codebook and 128x128 tiles; it wins once there is
+  // enough contraction per row (profiles/ has the crossover).  Tiny problems stay on the FFMA kernel.
+  if (search_tc_supported(N, D, K) && (int64_t)N * K >= (int64_t)1 << 20) return LIPVQ_ALGO_TCGEN05;
+  return LIPVQ_ALGO_SIMT_F32;
+}
+
+size_t lipvq_nn_search_workspace_bytes(int64_t N, int D, int K, int metric, int algo) {
+  if (N < 0 || D <= 0 || K <= 0) return 0;
+  return make_search_plan(N, D, K, metric, algo).total;
+}
+
+int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook, int K, int metric, int algo,
+                        int64_t* idx_out, float* best_out, int32_t* stats_out, void* workspace,
+                        size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(N >= 0 && D > 0 && K > 0, "nn_search: bad shape N=%lld D=%d K=%d", (long long)N, D, K);
+  LIPVQ_REQUIRE(N < ((int64_t)1 << 31), "nn_search: N=%lld exceeds int32 row ids", (long long)N);
+  LIPVQ_REQUIRE(metric >= LIPVQ_METRIC_L2 && metric <= LIPVQ_METRIC_DOT, "nn_search: bad metric %d", metric);
+  LIPVQ_REQUIRE(algo >= LIPVQ_ALGO_AUTO && algo <= LIPVQ_ALGO_TCGEN05, "nn_search: bad algo %d", algo);
+  if (N == 0) {
+    if (stats_out) LIPVQ_CUDA(cudaMemsetAsync(stats_out, 0, 4 * sizeof(int32_t), stream));
+    return LIPVQ_OK;
+  }
+  LIPVQ_REQUIRE(z && codebook && idx_out && workspace, "nn_search: null pointer");
+  if (algo == LIPVQ_ALGO_TCGEN05)
+    LIPVQ_REQUIRE(search_tc_supported(N, D, K), "nn_search: tcgen05 path does not support N=%lld D=%d K=%d",
+                  (long long)N, D, K);
+  const SearchPlan plan = make_search_plan(N, D, K, metric, algo);
+  LIPVQ_REQUIRE(workspace_bytes >= plan.total, "nn_search: workspace %zu < required %zu", workspace_bytes, plan.total);
+  LIPVQ_REQUIRE(aligned16(workspace), "nn_search: workspace must be 16-byte aligned");
+
+  char* ws = (char*)workspace;
+  SearchHdr* hdr = (SearchHdr*)(ws + plan.off_hdr);
+  float* enorm = (float*)(ws + plan.off_enorm);
+  float* pbest = (float*)(ws + plan.off_pbest);
+  float* psecond = (float*)(ws + plan.off_psecond);
+  int* pidx = (int*)(ws + plan.off_pidx);
+  int* work = (int*)(ws + plan.off_work);
+
+  LIPVQ_CUDA(cudaMemsetAsync(hdr, 0, sizeof(SearchHdr), stream));
+  if (stats_out) LIPVQ_CUDA(cudaMemsetAsync(stats_out, 0, 4 * sizeof(int32_t), stream));
+
+  code_sqnorm_kernel<<<(unsigned)ceil_div64((int64_t)K * 32, 256), 256, 0, stream>>>(codebook, K, D, metric, enorm, hdr);
+  LIPVQ_LAUNCHED("code_sqnorm_kernel");
+
+  const int vec = (D % 4 == 0) && aligned16(z) && aligned16(codebook);
+  float gamma;
+  if (plan.algo == LIPVQ_ALGO_TCGEN05) {
+    const int rc = search_tc_launch(z, N, D, codebook, K, plan, ws, stream);
+    if (rc != LIPVQ_OK) return rc;
+    gamma = search_tc_gamma(D);
+  } else {
+    dim3 grid((unsigned)ceil_div64(N, BM), (unsigned)plan.ksplit);
+    search_simt_kernel<<<grid, NT, 0, stream>>>(z, N, D, codebook, K, enorm, plan.codes_per_split, pbest, psecond,
+                                                pidx, vec);
+    LIPVQ_LAUNCHED("search_simt_kernel");
+    // fp32 FMA chain of length D plus the separately rounded ||e||^2 and the final fma: (D+4) unit roundoffs
+    gamma = (float)(D + 4) * 5.9604645e-8f;
+  }
+  const float gamma_ref = 4.f * (float)(D + 4) * 5.9604645e-8f;
+
+  finalize_kernel<<<(unsigned)ceil_div64(N * 32, 256), 256, 0, stream>>>(z, N, D, codebook, metric, plan.ksplit, pbest,
+                                                                         psecond, pidx, gamma, gamma_ref, hdr, work,
+                                                                         idx_out, best_out);
+  LIPVQ_LAUNCHED("finalize_kernel");
+
+  const int rs_blocks = 2 * sm_count();
+  const size_t rs_smem = (size_t)4 * D * sizeof(float);
+  LIPVQ_REQUIRE(rs_smem <= 48 * 1024, "nn_search: D=%d too large for the rescore kernel", D);
+  rescore_kernel<<<rs_blocks, 128, rs_smem, stream>>>(z, D, codebook, K, metric, hdr, work, idx_out, best_out,
+                                                      stats_out, vec);
+  LIPVQ_LAUNCHED("rescore_kernel");
+  return LIPVQ_OK;
+}
+
+int lipvq_l2_normalize_rows_f32(const float* x, int64_t rows, int D, float* y, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(rows >= 0 && D > 0, "l2_normalize_rows: bad shape");
+  if (rows == 0) return LIPVQ_OK;
+  LIPVQ_REQUIRE(x && y, "l2_normalize_rows: null pointer");
+  l2_normalize_rows_kernel<<<(unsigned)ceil_div64(rows * 32, 256), 256, 0, stream>>>(x, rows, D, y);
+  LIPVQ_LAUNCHED("l2_normalize_rows_kernel");
+  return LIPVQ_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,216 @@
+"""Tensor-level wrappers over the C ABI: validate device/dtype/contiguity, hand raw pointers and the
+current CUDA stream to liblipvq.so.  PyTorch is used for device memory and streams only -- every
+arithmetic op here is a hand-written sm_100a kernel; nothing falls back to torch ops or the CPU.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _cabi as A
+
+lib = A.lib
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _chk(t: Optional[torch.Tensor], dtype, name: str, allow_none: bool = False) -> int:
+    if t is None:
+        if allow_none:
+            return 0
+        raise ValueError(f"{name} is required")
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor: lipvq has no CPU path")
+    if t.dtype != dtype:
+        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    if not t.is_contiguous():
+        raise ValueError(f"{name} must be contiguous")
+    return t.data_ptr()
+
+
+F32, I64, I32, F64 = torch.float32, torch.int64, torch.int32, torch.float64
+
+_ws_cache = {}
+
+
+def _workspace(nbytes: int, device) -> torch.Tensor:
+    """Grow-only byte workspace per (device, stream): stable addresses for CUDA-graph capture."""
+    key = (device.index, _stream())
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+def nn_search(z: torch.Tensor, codebook: torch.Tensor, metric: int = A.METRIC_L2, algo: int = A.ALGO_AUTO,
+              want_best: bool = False, want_stats: bool = False, out: Optional[torch.Tensor] = None,
+              workspace: Optional[torch.Tensor] = None):
+    """argmin_k dist(z_n, e_k) -> int64 [N] (+ exact winning value, + int32[4] stats)."""
+    N, D = z.shape
+    K, D2 = codebook.shape
+    if D != D2:
+        raise RuntimeError(f"shape mismatch: z has dim {D}, codebook {D2}")
+    zp, cp = _chk(z, F32, "z"), _chk(codebook, F32, "codebook")
+    idx = out if out is not None else torch.empty(N, dtype=I64, device=z.device)
+    best = torch.empty(N, dtype=F32, device=z.device) if want_best else None
+    stats = torch.empty(4, dtype=I32, device=z.device) if want_stats else None
+    need = lib.lipvq_nn_search_workspace_bytes(N, D, K, metric, algo)
+    ws = workspace if workspace is not None else _workspace(need, z.device)
+    if ws.numel() * ws.element_size() < need:
+        raise ValueError(f"workspace too small: {ws.numel() * ws.element_size()} < {need}")
+    A.check(lib.lipvq_nn_search_f32(zp, N, D, cp, K, metric, algo, _chk(idx, I64, "idx"),
+                                    _chk(best, F32, "best", True), _chk(stats, I32, "stats", True),
+                                    ws.data_ptr(), ws.numel() * ws.element_size(), _stream()), "nn_search")
+    res = (idx,)
+    if want_best:
+        res += (best,)
+    if want_stats:
+        res += (stats,)
+    return res[0] if len(res) == 1 else res
+
+
+def search_workspace_bytes(N: int, D: int, K: int, metric: int = A.METRIC_L2, algo: int = A.ALGO_AUTO) -> int:
+    return int(lib.lipvq_nn_search_workspace_bytes(N, D, K, metric, algo))
+
+
+def pick_algo(N: int, D: int, K: int, metric: int = A.METRIC_L2) -> int:
+    return int(lib.lipvq_nn_search_pick_algo(N, D, K, metric))
+
+
+def l2_normalize_rows(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    D = x.shape[-1]
+    rows = x.numel() // D
+    y = out if out is not None else torch.empty_like(x)
+    A.check(lib.lipvq_l2_normalize_rows_f32(_chk(x, F32, "x"), rows, D, _chk(y, F32, "y"), _stream()), "l2_normalize_rows")
+    return y
+
+
+def gather_fwd(z, idx, codebook, sqerr: torch.Tensor, z_q=None, z_st=None, want_ste=False):
+    N, D = z.shape
+    K = codebook.shape[0]
+    if z_q is None:
+        z_q = torch.empty_like(z)
+    if want_ste and z_st is None:
+        z_st = torch.empty_like(z)
+    A.check(lib.lipvq_gather_ste_loss_fwd_f32(_chk(z, F32, "z"), _chk(idx, I64, "idx"), _chk(codebook, F32, "codebook"),
+                                              N, D, K, _chk(z_q, F32, "z_q"), _chk(z_st, F32, "z_st", True),
+                                              _chk(sqerr, F64, "sqerr"), _stream()), "gather_fwd")
+    return z_q, z_st
+
+
+def gather_bwd(z, z_q, idx, dzq_up, gscale, w_commit: float, w_codebook: float, ste: bool, sigmoid_out, K: int,
+               dz_out, dcodebook):
+    N, D = z.shape
+    A.check(lib.lipvq_gather_ste_loss_bwd_f32(_chk(z, F32, "z"), _chk(z_q, F32, "z_q"), _chk(idx, I64, "idx"),
+                                              _chk(dzq_up, F32, "dzq_up", True), _chk(gscale, F32, "gscale", True),
+                                              w_commit, w_codebook, int(ste), _chk(sigmoid_out, F32, "sigmoid_out", True),
+                                              N, D, K, _chk(dz_out, F32, "dz_out", True),
+                                              _chk(dcodebook, F32, "dcodebook", True), _stream()), "gather_bwd")
+
+
+def ema_stats(z, idx, counts, sums):
+    N, D = z.shape
+    K = counts.numel()
+    A.check(lib.lipvq_ema_stats_f32(_chk(z, F32, "z"), _chk(idx, I64, "idx"), N, D, K, _chk(counts, F32, "counts"),
+                                    _chk(sums, F32, "sums"), _stream()), "ema_stats")
+
+
+def ema_apply(counts, sums, ema_size, ema_sum, codebook, decay: float, eps: float, variant: int, scratch):
+    K, D = ema_sum.shape
+    A.check(lib.lipvq_ema_apply_f32(_chk(counts, F32, "counts"), _chk(sums, F32, "sums"), K, D, decay, 1.0 - decay, eps,
+                                    variant, _chk(ema_size, F32, "ema_size"), _chk(ema_sum, F32, "ema_sum"),
+                                    _chk(codebook, F32, "codebook"), _chk(scratch, F64, "scratch"), _stream()), "ema_apply")
+
+
+def usage_stats(counts, usage_counts, usage_ma, entropy_ma):
+    A.check(lib.lipvq_usage_stats_f32(_chk(counts, F32, "counts"), counts.numel(), _chk(usage_counts, F32, "usage_counts"),
+                                      _chk(usage_ma, F32, "usage_ma"), _chk(entropy_ma, F32, "entropy_ma"), _stream()),
+            "usage_stats")
+
+
+def codebook_usage(cluster_size, dead_thr: float) -> torch.Tensor:
+    out = torch.empty(2, dtype=I32, device=cluster_size.device)
+    A.check(lib.lipvq_codebook_usage_f32(_chk(cluster_size, F32, "cluster_size"), cluster_size.numel(), dead_thr,
+                                         _chk(out, I32, "out"), _stream()), "codebook_usage")
+    return out
+
+
+def linear_fwd(x, act_in: int, W, bias, act_out: int, out=None):
+    in_dim = x.shape[-1]
+    N = x.numel() // in_dim
+    out_dim = W.shape[0]
+    if W.shape[1] != in_dim:
+        raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({N}x{in_dim} and {W.shape[1]}x{out_dim})")
+    y = out if out is not None else torch.empty(*x.shape[:-1], out_dim, dtype=F32, device=x.device)
+    A.check(lib.lipvq_linear_fwd_f32(_chk(x, F32, "x"), N, in_dim, act_in, _chk(W, F32, "W"), _chk(bias, F32, "bias", True),
+                                     out_dim, act_out, _chk(y, F32, "y"), _stream()), "linear_fwd")
+    return y
+
+
+def linear_bwd_x(dY, W, Xpre, act_in: int, out=None):
+    out_dim, in_dim = W.shape
+    N = dY.numel() // out_dim
+    dX = out if out is not None else torch.empty(*dY.shape[:-1], in_dim, dtype=F32, device=dY.device)
+    A.check(lib.lipvq_linear_bwd_x_f32(_chk(dY, F32, "dY"), N, out_dim, _chk(W, F32, "W"), in_dim,
+                                       _chk(Xpre, F32, "Xpre", act_in == A.ACT_NONE), act_in, _chk(dX, F32, "dX"),
+                                       _stream()), "linear_bwd_x")
+    return dX
+
+
+def linear_bwd_w(dY, X, act_in: int, dW, db):
+    """dW += dY^T act_in(X); db += colsum(dY).  dW/db are accumulated into."""
+    out_dim, in_dim = dW.shape
+    N = dY.numel() // out_dim
+    A.check(lib.lipvq_linear_bwd_w_f32(_chk(dY, F32, "dY"), N, out_dim, _chk(X, F32, "X"), in_dim, act_in,
+                                       _chk(dW, F32, "dW"), _chk(db, F32, "db", True), _stream()), "linear_bwd_w")
+
+
+def act_bwd_from_output(dY, Y, act: int, out=None):
+    dX = out if out is not None else torch.empty_like(dY)
+    A.check(lib.lipvq_act_bwd_from_output_f32(_chk(dY, F32, "dY"), _chk(Y, F32, "Y"), act, dY.numel(), _chk(dX, F32, "dX"),
+                                              _stream()), "act_bwd_from_output")
+    return dX
+
+
+def lipschitz_scale_fwd(W, ci, W_norm=None, scale=None):
+    out_dim, in_dim = W.shape
+    if W_norm is None:
+        W_norm = torch.empty_like(W)
+    A.check(lib.lipvq_lipschitz_scale_fwd_f32(_chk(W, F32, "W"), _chk(ci, F32, "ci"), out_dim, in_dim,
+                                              _chk(scale, F32, "scale", True), _chk(W_norm, F32, "W_norm"), _stream()),
+            "lipschitz_scale_fwd")
+    return W_norm
+
+
+def lipschitz_scale_bwd(G, W, ci, dW, dci):
+    out_dim, in_dim = W.shape
+    A.check(lib.lipvq_lipschitz_scale_bwd_f32(_chk(G, F32, "G"), _chk(W, F32, "W"), _chk(ci, F32, "ci"), out_dim, in_dim,
+                                              _chk(dW, F32, "dW"), _chk(dci, F32, "dci"), _stream()), "lipschitz_scale_bwd")
+
+
+def mse_fwd_bwd(y, target, sqerr, gscale=None, act_out: int = A.ACT_NONE, dY=None):
+    if y.shape != target.shape:
+        raise RuntimeError(f"mse: shape mismatch {tuple(y.shape)} vs {tuple(target.shape)}")
+    A.check(lib.lipvq_mse_fwd_bwd_f32(_chk(y, F32, "y"), _chk(target, F32, "target"), y.numel(),
+                                      _chk(gscale, F32, "gscale", True), act_out, _chk(sqerr, F64, "sqerr"),
+                                      _chk(dY, F32, "dY", True), _stream()), "mse_fwd_bwd")
+
+
+def t1_loss_finalize(sq2, n_recon: float, n_lat: float, w_commit: float, w_cb: float, out4):
+    A.check(lib.lipvq_t1_loss_finalize(_chk(sq2, F64, "sq2"), float(n_recon), float(n_lat), w_commit, w_cb,
+                                       _chk(out4, F32, "out4"), _stream()), "t1_loss_finalize")
+
+
+def adamw_step(p, g, m, v, step: int, step_dev=None, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-4,
+               grad_scale: float = 1.0):
+    A.check(lib.lipvq_adamw_step_f32(_chk(p, F32, "p"), _chk(g, F32, "g"), _chk(m, F32, "m"), _chk(v, F32, "v"), p.numel(),
+                                     int(step), _chk(step_dev, I32, "step_dev", True), lr, betas[0], betas[1], eps,
+                                     weight_decay, grad_scale, _stream()), "adamw_step")
+
+
+def counter_add(ctr, delta: int = 1):
+    A.check(lib.lipvq_counter_add_i32(_chk(ctr, I32, "ctr"), delta, _stream()), "counter_add")

@@ -1,0 +1,119 @@
+"""Kernel schedule of the LipVQ-VAE tokenizer (T1): forward, backward, EMA -- as launches of liblipvq.so.
+
+Follows LLFQVAE_V4.forward (reference robomimic/models/vq_vae/backbone_lfqvae_v5.py:70-84) and, with
+``ema``, LFQQuantizerEMA.forward (robomimic/models/vq_vae/hq_vae.py:240-281).  Gradient topology is
+the reference's: z_q = codebook[idx] WITHOUT straight-through, so the reconstruction loss trains the
+decoder and the selected code rows, and the encoder learns through the commitment term only.
+
+Used by both front-ends: the nn.Module / autograd path (modules.py) and the graph-captured trainer
+(trainer.py).  All buffers are caller-visible tensors; nothing here allocates when ``bufs`` is reused.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Dict, Optional
+
+import torch
+
+from . import _cabi as A
+from . import ops
+
+PARAM_SHAPES = lambda F, D, K, H=128: {  # state_dict order/names of LLFQVAE_V4 (backbone_lfqvae_v5.py:52-68)
+    "encoder.0.weight": (64, F), "encoder.0.bias": (64,),
+    "encoder.2.weight": (H, 64), "encoder.2.bias": (H,),
+    "to_latent.W": (D, H), "to_latent.b": (D,), "to_latent.ci": (D,),
+    "quantizer.codebook": (K, D),
+    "decoder.0.weight": (64, D), "decoder.0.bias": (64,),
+    "decoder.2.weight": (H, 64), "decoder.2.bias": (H,),
+    "to_output.weight": (F, H), "to_output.bias": (F,),
+}
+
+
+@dataclass
+class T1Buffers:
+    """Activations of one step.  Pre-activations are stored; consumers apply GELU while loading."""
+    N: int
+    F: int
+    D: int
+    K: int
+    H: int
+    device: torch.device
+    t: Dict[str, torch.Tensor] = field(default_factory=dict)
+
+    def __post_init__(self):
+        N, F, D, K, H, dev = self.N, self.F, self.D, self.K, self.H, self.device
+        e = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+        self.t = {
+            "Wn": e(D, H), "a1": e(N, 64), "a2": e(N, H), "z_e": e(N, D),
+            "idx": torch.empty(N, dtype=torch.int64, device=dev), "z_q": e(N, D),
+            "c1": e(N, 64), "c2": e(N, H), "x_recon": e(N, F),
+            "sq": torch.zeros(2, dtype=torch.float64, device=dev),   # [sum (x_recon-x)^2, sum (z_q-z_e)^2]
+            "losses": e(4),                                          # loss, recon, commit, codebook
+            "stats": torch.zeros(4, dtype=torch.int32, device=dev),
+            "ws": torch.empty(max(1, ops.search_workspace_bytes(N, D, K)), dtype=torch.uint8, device=dev),
+        }
+
+    def alloc_backward(self):
+        N, F, D, H, dev = self.N, self.F, self.D, self.H, self.device
+        e = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+        if "dxr" not in self.t:
+            self.t.update({"dxr": e(N, F), "dc2": e(N, H), "dc1": e(N, 64), "dzq": e(N, D), "dzpre": e(N, D),
+                           "da2": e(N, H), "da1": e(N, 64), "G": e(D, H),
+                           "scratch": torch.zeros(1, dtype=torch.float64, device=dev)})
+
+
+def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: int = A.ALGO_AUTO,
+            encode_only: bool = False) -> None:
+    """x [N,F] -> b.t[...]: z_e, idx, z_q, x_recon, losses.  ``encode_only`` stops after the search
+    (the bulk-tokenisation path: encode + VQ)."""
+    t = b.t
+    ops.lipschitz_scale_fwd(p["to_latent.W"], p["to_latent.ci"], t["Wn"])
+    ops.linear_fwd(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_NONE, out=t["a1"])
+    ops.linear_fwd(t["a1"], A.ACT_GELU, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_NONE, out=t["a2"])
+    ops.linear_fwd(t["a2"], A.ACT_GELU, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"])
+    ops.nn_search(t["z_e"], p["quantizer.codebook"], A.METRIC_L2, algo, out=t["idx"], workspace=t["ws"])
+    if encode_only:
+        return
+    t["sq"].zero_()
+    ops.gather_fwd(t["z_e"], t["idx"], p["quantizer.codebook"], t["sq"][1:], z_q=t["z_q"])
+    ops.linear_fwd(t["z_q"], A.ACT_NONE, p["decoder.0.weight"], p["decoder.0.bias"], A.ACT_NONE, out=t["c1"])
+    ops.linear_fwd(t["c1"], A.ACT_GELU, p["decoder.2.weight"], p["decoder.2.bias"], A.ACT_NONE, out=t["c2"])
+    ops.linear_fwd(t["c2"], A.ACT_GELU, p["to_output.weight"], p["to_output.bias"], A.ACT_NONE, out=t["x_recon"])
+    ops.mse_fwd_bwd(t["x_recon"], x, t["sq"][0:1])
+    ops.t1_loss_finalize(t["sq"], float(b.N) * b.F, float(b.N) * b.D, 0.25, 0.25, t["losses"])
+
+
+def backward(p: Dict[str, torch.Tensor], g: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers,
+             gscale: Optional[torch.Tensor] = None) -> None:
+    """Accumulates d loss / d param into ``g`` (same keys as ``p``; caller zeroes them).  ``gscale``:
+    optional 1-element device tensor multiplying the loss gradient (autograd's grad_output)."""
+    b.alloc_backward()
+    t = b.t
+    scratch = t["scratch"]
+    # d recon_loss / d x_recon (the forward pass already produced the loss value; sq is not reused)
+    ops.mse_fwd_bwd(t["x_recon"], x, scratch, gscale=gscale, dY=t["dxr"])
+    # decoder
+    ops.linear_bwd_w(t["dxr"], t["c2"], A.ACT_GELU, g["to_output.weight"], g["to_output.bias"])
+    ops.linear_bwd_x(t["dxr"], p["to_output.weight"], t["c2"], A.ACT_GELU, out=t["dc2"])
+    ops.linear_bwd_w(t["dc2"], t["c1"], A.ACT_GELU, g["decoder.2.weight"], g["decoder.2.bias"])
+    ops.linear_bwd_x(t["dc2"], p["decoder.2.weight"], t["c1"], A.ACT_GELU, out=t["dc1"])
+    ops.linear_bwd_w(t["dc1"], t["z_q"], A.ACT_NONE, g["decoder.0.weight"], g["decoder.0.bias"])
+    ops.linear_bwd_x(t["dc1"], p["decoder.0.weight"], None, A.ACT_NONE, out=t["dzq"])
+    # quantizer: codebook rows get recon grad + 0.25*codebook-loss grad; encoder gets 0.25*commitment grad,
+    # already multiplied by sigmoid'(.) so it is the gradient at the Lipschitz layer's pre-activation
+    ops.gather_bwd(t["z_e"], t["z_q"], t["idx"], t["dzq"], gscale, 0.25, 0.25, False, t["z_e"], b.K, t["dzpre"],
+                   g["quantizer.codebook"])
+    # Lipschitz layer: G = dL/dW_norm, then through min(1, softplus(ci)/||W_i||_1)
+    t["G"].zero_()
+    ops.linear_bwd_w(t["dzpre"], t["a2"], A.ACT_GELU, t["G"], g["to_latent.b"])
+    ops.lipschitz_scale_bwd(t["G"], p["to_latent.W"], p["to_latent.ci"], g["to_latent.W"], g["to_latent.ci"])
+    ops.linear_bwd_x(t["dzpre"], t["Wn"], t["a2"], A.ACT_GELU, out=t["da2"])
+    # encoder
+    ops.linear_bwd_w(t["da2"], t["a1"], A.ACT_GELU, g["encoder.2.weight"], g["encoder.2.bias"])
+    ops.linear_bwd_x(t["da2"], p["encoder.2.weight"], t["a1"], A.ACT_GELU, out=t["da1"])
+    ops.linear_bwd_w(t["da1"], x, A.ACT_NONE, g["encoder.0.weight"], g["encoder.0.bias"])
+
+
+def ema_stats(b: T1Buffers, counts: torch.Tensor, sums: torch.Tensor) -> None:
+    """counts[K] += bincount(idx); sums[K,D] += onehot^T z_e  (hq_vae.py:264-271)."""
+    ops.ema_stats(b.t["z_e"], b.t["idx"], counts, sums)

@@ -1,0 +1,174 @@
+"""Tokenizer training step as the reference's algo layer runs it, expressed as one launch sequence.
+
+Reference protocol (robomimic/algo/icl.py:1437-1441, 1466, 1520-1522): a dedicated
+``AdamW(vq_vae_model.parameters(), lr=1e-3, weight_decay=1e-4)``; per step zero_grad -> forward ->
+``_vq_vae_loss.backward()`` -> ``vq_optimizer.step()``; no gradient clipping on the tokenizer.
+With an EMA quantizer (LFQQuantizerEMA, robomimic/models/vq_vae/hq_vae.py:224-281) the codebook is
+overwritten from the EMA buffers each step and still takes its AdamW update, as the reference does.
+
+Layout in HBM: parameters, gradients and both Adam moments are single flat fp32 slabs (the module's
+nn.Parameters are re-pointed at views of the parameter slab, so ``state_dict`` keeps working).  The
+reduction slab is ``[grads | counts(K) | sums(K*D) | losses(4)]`` (parallel.SlabLayout) so a
+data-parallel step needs exactly ONE ``all_reduce(sum)`` (NCCL over NVLink); every rank then applies
+the identical EMA + AdamW update and replicas stay bit-identical.  The two halves of the step (before /
+after the reduction) are captured as CUDA graphs.
+"""
+from __future__ import annotations
+
+from typing import Dict, Optional
+
+import torch
+import torch.distributed as dist
+
+from . import _cabi as A
+from . import ops, t1
+from .modules import LFQQuantizerEMA, LLFQVAE_V4, _T1_KEYS
+from .parallel import SlabLayout, all_reduce_slab
+
+
+class TokenizerTrainer:
+    def __init__(self, model: LLFQVAE_V4, batch_tokens: int, lr: float = 1e-3, weight_decay: float = 1e-4,
+                 betas=(0.9, 0.999), eps: float = 1e-8, use_graph: bool = True,
+                 process_group: Optional[dist.ProcessGroup] = None, search_algo: int = A.ALGO_AUTO):
+        self.model = model
+        dev = next(model.parameters()).device
+        if dev.type != "cuda":
+            raise RuntimeError("TokenizerTrainer needs the model on a CUDA device (no CPU path)")
+        self.device = dev
+        self.N = int(batch_tokens)
+        F_, D, _, H = model._dims
+        K = model.quantizer.codebook.shape[0]
+        self.F, self.D, self.K, self.H = F_, D, K, H
+        self.ema = isinstance(model.quantizer, LFQQuantizerEMA)
+        self.lr, self.wd, self.betas, self.eps = lr, weight_decay, betas, eps
+        self.search_algo = search_algo
+        self.pg = process_group
+        self.world = dist.get_world_size(process_group) if dist.is_initialized() else 1
+
+        named = dict(model.named_parameters())
+        self.layout = SlabLayout(list(_T1_KEYS), [tuple(named[k].shape) for k in _T1_KEYS], K, D, self.ema)
+        L = self.layout
+        self.flat_p = torch.empty(L.P, dtype=torch.float32, device=dev)
+        self.red = torch.zeros(L.length, dtype=torch.float32, device=dev)
+        self.flat_g = self.red[:L.P]
+        self.flat_m = torch.zeros(L.P, dtype=torch.float32, device=dev)
+        self.flat_v = torch.zeros(L.P, dtype=torch.float32, device=dev)
+        self.p: Dict[str, torch.Tensor] = {}
+        self.g: Dict[str, torch.Tensor] = {}
+        with torch.no_grad():
+            for k in _T1_KEYS:
+                view = L.grad_view(self.flat_p, k)
+                view.copy_(named[k].detach())
+                named[k].data = view  # the module now lives in the slab
+                self.p[k] = view
+                self.g[k] = L.grad_view(self.red, k)
+        if self.ema:
+            self.counts, self.sums = L.counts(self.red), L.sums(self.red)
+        self.losses_red = L.losses(self.red)
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
+        self.scratch = torch.zeros(1, dtype=torch.float64, device=dev)
+        self.bufs = t1.T1Buffers(self.N, F_, D, K, H, dev)
+        self.bufs.alloc_backward()
+        self.x_static = torch.empty(self.N, F_, dtype=torch.float32, device=dev)
+        self.use_graph = use_graph
+        self._graph_a = None  # zero grads, forward, EMA statistics, backward
+        self._graph_b = None  # EMA apply + AdamW
+        self._graph_tok = None
+        self.steps_done = 0
+
+    # -- the launch sequence -------------------------------------------------------------------
+    def _phase_a(self):
+        self.red.zero_()
+        t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo)
+        if self.ema:
+            t1.ema_stats(self.bufs, self.counts, self.sums)
+        t1.backward(self.p, self.g, self.x_static, self.bufs)
+        self.losses_red.copy_(self.bufs.t["losses"])
+
+    def _phase_b(self):
+        if self.ema:
+            q = self.model.quantizer
+            ops.ema_apply(self.counts, self.sums, q.ema_cluster_size, q.ema_codebook, self.p["quantizer.codebook"],
+                          q.decay, q.epsilon, A.EMA_SIMPLE, self.scratch)
+        ops.counter_add(self.step_dev, 1)
+        ops.adamw_step(self.flat_p, self.flat_g, self.flat_m, self.flat_v, 0, self.step_dev, self.lr, self.betas,
+                       self.eps, self.wd, 1.0 / self.world)
+
+    def _snapshot(self):
+        st = [self.flat_p.clone(), self.flat_m.clone(), self.flat_v.clone(), self.step_dev.clone()]
+        if self.ema:
+            q = self.model.quantizer
+            st += [q.ema_cluster_size.clone(), q.ema_codebook.clone()]
+        return st
+
+    def _restore(self, st):
+        self.flat_p.copy_(st[0]); self.flat_m.copy_(st[1]); self.flat_v.copy_(st[2]); self.step_dev.copy_(st[3])
+        if self.ema:
+            q = self.model.quantizer
+            q.ema_cluster_size.copy_(st[4]); q.ema_codebook.copy_(st[5])
+
+    def _capture(self):
+        # one eager pass on a side stream first (lazy module loading, allocator), then capture both halves;
+        # the eager pass advanced the optimiser state, so put it back afterwards
+        st = self._snapshot()
+        s = torch.cuda.Stream(device=self.device)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            self._phase_a()
+            self._phase_b()
+        torch.cuda.current_stream().wait_stream(s)
+        ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(ga):
+            self._phase_a()
+        with torch.cuda.graph(gb):
+            self._phase_b()
+        self._restore(st)
+        self._graph_a, self._graph_b = ga, gb
+
+    def step(self, x: torch.Tensor) -> torch.Tensor:
+        """One optimisation step on x [N,F] (device tensor, or pinned host tensor -> async H2D).
+        Returns a VIEW of the 4 loss scalars (loss, recon, commitment, codebook; summed over ranks -- divide
+        by ``world``) that the next step overwrites."""
+        if tuple(x.shape) != tuple(self.x_static.shape):
+            raise RuntimeError(f"expected input of shape {tuple(self.x_static.shape)}, got {tuple(x.shape)}")
+        self.x_static.copy_(x, non_blocking=True)
+        if self.use_graph and self._graph_a is None:
+            self._capture()
+        if self.use_graph:
+            self._graph_a.replay()
+        else:
+            self._phase_a()
+        if self.world > 1:
+            all_reduce_slab(self.red, self.pg)
+        if self.use_graph:
+            self._graph_b.replay()
+        else:
+            self._phase_b()
+        self.steps_done += 1
+        return self.losses_red
+
+    @property
+    def indices(self) -> torch.Tensor:
+        return self.bufs.t["idx"]
+
+    @torch.no_grad()
+    def tokenize(self, x: torch.Tensor) -> torch.Tensor:
+        """encode + VQ only on x [N,F] (bulk tokenisation) -> int64 [N] (a buffer the next call overwrites)."""
+        if tuple(x.shape) != tuple(self.x_static.shape):
+            raise RuntimeError(f"expected input of shape {tuple(self.x_static.shape)}, got {tuple(x.shape)}")
+        self.x_static.copy_(x, non_blocking=True)
+        if not self.use_graph:
+            t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True)
+            return self.bufs.t["idx"]
+        if self._graph_tok is None:
+            s = torch.cuda.Stream(device=self.device)
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True)
+            torch.cuda.current_stream().wait_stream(s)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True)
+            self._graph_tok = g
+        self._graph_tok.replay()
+        return self.bufs.t["idx"]
