@@ -60,68 +60,115 @@ __global__ void __launch_bounds__(256)
 }
 
 // ---- K4 backward ------------------------------------------------------------------------------------------------
-template <bool VEC>
+// Sub-warp groups of G lanes own a row (lane gl holds float4 columns (gl + G*v)*4) and walk a contiguous run of rows.
+// The codebook-gradient contribution of consecutive rows that selected the same code is summed in registers and
+// flushed with one vector red per element when the code changes: consecutive action steps usually share a code, and
+// a collapsed codebook (every token on a handful of codes) would otherwise serialise N*D/4 atomics on a few lines.
+template <int G, int VPL>
 __global__ void __launch_bounds__(256)
-    gather_bwd_kernel(const float* __restrict__ z, const float* __restrict__ zq, const int64_t* __restrict__ idx,
-                      const float* __restrict__ dzq_up, const float* __restrict__ gscale_dev, float w_commit,
-                      float w_codebook, int ste, const float* __restrict__ sig_out, int64_t N, int D, int K,
-                      float* __restrict__ dz, float* __restrict__ dcb) {
-  constexpr int W = VEC ? 4 : 1;
-  const int per_row = D / W;
-  const int64_t total = N * (int64_t)per_row;
+    gather_bwd_runs_kernel(const float* __restrict__ z, const float* __restrict__ zq, const int64_t* __restrict__ idx,
+                           const float* __restrict__ dzq_up, const float* __restrict__ gscale_dev, float w_commit,
+                           float w_codebook, int ste, const float* __restrict__ sig_out, int64_t N, int D, int K,
+                           int64_t rows_per_group, float* __restrict__ dz, float* __restrict__ dcb) {
+  const int64_t gid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
+  const int gl = threadIdx.x % G;
+  const int64_t r0 = gid * rows_per_group;
+  if (r0 >= N) return;
+  const int64_t r1 = (r0 + rows_per_group < N) ? r0 + rows_per_group : N;
   const float g = gscale_dev ? __ldg(gscale_dev) : 1.f;
   const float coef = (float)(2.0 / ((double)N * (double)D)) * g;
   const float cz = w_commit * coef, cq = w_codebook * coef;
-  for (int64_t it = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; it < total; it += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t row = it / per_row;
-    const int c = (int)(it - row * per_row) * W;
-    int64_t k = __ldg(idx + row);
+  float4 acc[VPL];
+#pragma unroll
+  for (int v = 0; v < VPL; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+  int64_t cur = -1;
+  for (int64_t r = r0; r < r1; ++r) {
+    int64_t k = __ldg(idx + r);
     k = k < 0 ? 0 : (k >= K ? K - 1 : k);
-    const int64_t o = row * D + c;
-    if (VEC) {
-      const float4 zv = __ldg(reinterpret_cast<const float4*>(z + o));
-      const float4 qv = __ldg(reinterpret_cast<const float4*>(zq + o));
-      float4 up = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (dzq_up) up = __ldg(reinterpret_cast<const float4*>(dzq_up + o));
-      float4 gz, gq;
-      gz.x = cz * (zv.x - qv.x); gz.y = cz * (zv.y - qv.y); gz.z = cz * (zv.z - qv.z); gz.w = cz * (zv.w - qv.w);
-      gq.x = cq * (qv.x - zv.x); gq.y = cq * (qv.y - zv.y); gq.z = cq * (qv.z - zv.z); gq.w = cq * (qv.w - zv.w);
-      if (ste) { gz.x += up.x; gz.y += up.y; gz.z += up.z; gz.w += up.w; }
-      else     { gq.x += up.x; gq.y += up.y; gq.z += up.z; gq.w += up.w; }
-      if (sig_out) {
-        const float4 y = __ldg(reinterpret_cast<const float4*>(sig_out + o));
-        gz.x *= y.x * (1.f - y.x); gz.y *= y.y * (1.f - y.y); gz.z *= y.z * (1.f - y.z); gz.w *= y.w * (1.f - y.w);
+    if (k != cur) {
+      if (cur >= 0 && dcb) {
+#pragma unroll
+        for (int v = 0; v < VPL; ++v) {
+          const int c = (gl + G * v) * 4;
+          if (c < D) atomicAdd(reinterpret_cast<float4*>(dcb + cur * D + c), acc[v]);  // red.global.add.v4.f32
+          acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
       }
-      if (dz) *reinterpret_cast<float4*>(dz + o) = gz;
-      if (dcb) atomicAdd(reinterpret_cast<float4*>(dcb + k * D + c), gq);  // red.global.add.v4.f32 (sm_90+)
-    } else {
-      const float zv = __ldg(z + o), qv = __ldg(zq + o);
-      const float up = dzq_up ? __ldg(dzq_up + o) : 0.f;
-      float gz = cz * (zv - qv), gq = cq * (qv - zv);
-      if (ste) gz += up; else gq += up;
-      if (sig_out) {
-        const float y = __ldg(sig_out + o);
-        gz *= y * (1.f - y);
+      cur = k;
+    }
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+      const int c = (gl + G * v) * 4;
+      if (c < D) {
+        const int64_t o = r * D + c;
+        const float4 zv = __ldg(reinterpret_cast<const float4*>(z + o));
+        const float4 qv = __ldg(reinterpret_cast<const float4*>(zq + o));
+        float4 up = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (dzq_up) up = __ldg(reinterpret_cast<const float4*>(dzq_up + o));
+        float4 gz, gq;
+        gz.x = cz * (zv.x - qv.x); gz.y = cz * (zv.y - qv.y); gz.z = cz * (zv.z - qv.z); gz.w = cz * (zv.w - qv.w);
+        gq.x = cq * (qv.x - zv.x); gq.y = cq * (qv.y - zv.y); gq.z = cq * (qv.z - zv.z); gq.w = cq * (qv.w - zv.w);
+        if (ste) { gz.x += up.x; gz.y += up.y; gz.z += up.z; gz.w += up.w; }
+        else     { gq.x += up.x; gq.y += up.y; gq.z += up.z; gq.w += up.w; }
+        if (sig_out) {
+          const float4 y = __ldg(reinterpret_cast<const float4*>(sig_out + o));
+          gz.x *= y.x * (1.f - y.x); gz.y *= y.y * (1.f - y.y); gz.z *= y.z * (1.f - y.z); gz.w *= y.w * (1.f - y.w);
+        }
+        if (dz) *reinterpret_cast<float4*>(dz + o) = gz;
+        acc[v].x += gq.x; acc[v].y += gq.y; acc[v].z += gq.z; acc[v].w += gq.w;
       }
-      if (dz) dz[o] = gz;
-      if (dcb) atomicAdd(dcb + k * D + c, gq);
+    }
+  }
+  if (cur >= 0 && dcb) {
+#pragma unroll
+    for (int v = 0; v < VPL; ++v) {
+      const int c = (gl + G * v) * 4;
+      if (c < D) atomicAdd(reinterpret_cast<float4*>(dcb + cur * D + c), acc[v]);
     }
   }
 }
 
-// ---- K5 statistics ----------------------------------------------------------------------------------------------
-// Each warp walks a contiguous run of tokens.  Lanes span the latent dim; the running sum of the current code is
-// kept in registers and flushed with one (vector) atomic per element only when the code changes -- consecutive
-// action steps usually share a code, so real data flushes rarely; random data costs one red per token element.
-template <int VPL>  // float4 vectors per lane: D = 128*VPL at most
+// scalar fallback (D % 4 != 0 or unaligned bases)
 __global__ void __launch_bounds__(256)
-    ema_stats_vec_kernel(const float* __restrict__ z, const int64_t* __restrict__ idx, int64_t N, int D, int K,
-                         int64_t rows_per_warp, float* __restrict__ counts, float* __restrict__ sums) {
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  const int64_t r0 = warp * rows_per_warp;
+    gather_bwd_scalar_kernel(const float* __restrict__ z, const float* __restrict__ zq,
+                             const int64_t* __restrict__ idx, const float* __restrict__ dzq_up,
+                             const float* __restrict__ gscale_dev, float w_commit, float w_codebook, int ste,
+                             const float* __restrict__ sig_out, int64_t N, int D, int K, float* __restrict__ dz,
+                             float* __restrict__ dcb) {
+  const int64_t total = N * (int64_t)D;
+  const float g = gscale_dev ? __ldg(gscale_dev) : 1.f;
+  const float coef = (float)(2.0 / ((double)N * (double)D)) * g;
+  const float cz = w_commit * coef, cq = w_codebook * coef;
+  for (int64_t o = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; o < total; o += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t row = o / D;
+    const int c = (int)(o - row * D);
+    int64_t k = __ldg(idx + row);
+    k = k < 0 ? 0 : (k >= K ? K - 1 : k);
+    const float zv = __ldg(z + o), qv = __ldg(zq + o);
+    const float up = dzq_up ? __ldg(dzq_up + o) : 0.f;
+    float gz = cz * (zv - qv), gq = cq * (qv - zv);
+    if (ste) gz += up; else gq += up;
+    if (sig_out) {
+      const float y = __ldg(sig_out + o);
+      gz *= y * (1.f - y);
+    }
+    if (dz) dz[o] = gz;
+    if (dcb) atomicAdd(dcb + k * D + c, gq);
+  }
+}
+
+// ---- K5 statistics ----------------------------------------------------------------------------------------------
+// Same sub-warp-group walk as above: the running sum of the current code lives in registers and is flushed with one
+// vector red per element (and one red for the count) only when the code changes.
+template <int G, int VPL>
+__global__ void __launch_bounds__(256)
+    ema_stats_runs_kernel(const float* __restrict__ z, const int64_t* __restrict__ idx, int64_t N, int D, int K,
+                          int64_t rows_per_group, float* __restrict__ counts, float* __restrict__ sums) {
+  const int64_t gid = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) / G;
+  const int gl = threadIdx.x % G;
+  const int64_t r0 = gid * rows_per_group;
   if (r0 >= N) return;
-  const int64_t r1 = (r0 + rows_per_warp < N) ? r0 + rows_per_warp : N;
+  const int64_t r1 = (r0 + rows_per_group < N) ? r0 + rows_per_group : N;
   float4 acc[VPL];
 #pragma unroll
   for (int v = 0; v < VPL; ++v) acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -134,11 +181,11 @@ __global__ void __launch_bounds__(256)
       if (cur >= 0) {
 #pragma unroll
         for (int v = 0; v < VPL; ++v) {
-          const int c = (lane + 32 * v) * 4;
+          const int c = (gl + G * v) * 4;
           if (c < D) atomicAdd(reinterpret_cast<float4*>(sums + cur * D + c), acc[v]);
           acc[v] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        if (lane == 0) atomicAdd(counts + cur, run);
+        if (gl == 0) atomicAdd(counts + cur, run);
       }
       cur = k;
       run = 0.f;
@@ -146,7 +193,7 @@ __global__ void __launch_bounds__(256)
     run += 1.f;
 #pragma unroll
     for (int v = 0; v < VPL; ++v) {
-      const int c = (lane + 32 * v) * 4;
+      const int c = (gl + G * v) * 4;
       if (c < D) {
         const float4 zv = __ldg(reinterpret_cast<const float4*>(z + r * D + c));
         acc[v].x += zv.x; acc[v].y += zv.y; acc[v].z += zv.z; acc[v].w += zv.w;
@@ -156,11 +203,29 @@ __global__ void __launch_bounds__(256)
   if (cur >= 0) {
 #pragma unroll
     for (int v = 0; v < VPL; ++v) {
-      const int c = (lane + 32 * v) * 4;
+      const int c = (gl + G * v) * 4;
       if (c < D) atomicAdd(reinterpret_cast<float4*>(sums + cur * D + c), acc[v]);
     }
-    if (lane == 0) atomicAdd(counts + cur, run);
+    if (gl == 0) atomicAdd(counts + cur, run);
   }
+}
+
+// Picks the group width for a row of D/4 float4 vectors and the rows each group walks; calls f.template
+// operator()<G, VPL>(grid, rows_per_group).
+struct RunsPlan { int G, VPL; int64_t rows_per_group; unsigned grid; };
+inline RunsPlan plan_runs(int64_t N, int D) {
+  const int nvec = D / 4;
+  RunsPlan p;
+  p.G = nvec <= 8 ? 8 : (nvec <= 16 ? 16 : 32);
+  p.VPL = (nvec + p.G - 1) / p.G;
+  if (p.VPL == 3) p.VPL = 4;
+  const int64_t resident_groups = (int64_t)sm_count() * 2048 / p.G;
+  int64_t rpg = ceil_div64(N, resident_groups);
+  if (rpg < 8) rpg = 8;  // at least 8 consecutive rows so run-length aggregation has something to merge
+  p.rows_per_group = rpg;
+  const int64_t groups = ceil_div64(N, rpg);
+  p.grid = (unsigned)ceil_div64(groups * p.G, 256);
+  return p;
 }
 
 // generic fallback (any D / alignment): one thread per element, plain scalar atomics
@@ -358,14 +423,22 @@ int lipvq_gather_ste_loss_bwd_f32(const float* z, const float* z_q, const int64_
   const bool vec = (D % 4 == 0) && aligned16(z) && aligned16(z_q) && (!dzq_up || aligned16(dzq_up)) &&
                    (!sigmoid_out || aligned16(sigmoid_out)) && (!dz_out || aligned16(dz_out)) &&
                    (!dcodebook || aligned16(dcodebook));
-  const int64_t items = N * (int64_t)(vec ? D / 4 : D);
-  const int grid = stream_grid(items, 256, 8);
-  if (vec)
-    gather_bwd_kernel<true><<<grid, 256, 0, stream>>>(z, z_q, idx, dzq_up, gscale_dev, w_commit, w_codebook, ste,
-                                                      sigmoid_out, N, D, K, dz_out, dcodebook);
-  else
-    gather_bwd_kernel<false><<<grid, 256, 0, stream>>>(z, z_q, idx, dzq_up, gscale_dev, w_commit, w_codebook, ste,
-                                                       sigmoid_out, N, D, K, dz_out, dcodebook);
+  if (vec && D <= 512) {
+    const RunsPlan rp = plan_runs(N, D);
+#define LIPVQ_GB(G_, V_)                                                                                          \
+  gather_bwd_runs_kernel<G_, V_><<<rp.grid, 256, 0, stream>>>(z, z_q, idx, dzq_up, gscale_dev, w_commit, w_codebook, \
+                                                              ste, sigmoid_out, N, D, K, rp.rows_per_group, dz_out,  \
+                                                              dcodebook)
+    if (rp.G == 8) LIPVQ_GB(8, 1);
+    else if (rp.G == 16) LIPVQ_GB(16, 1);
+    else if (rp.VPL == 1) LIPVQ_GB(32, 1);
+    else if (rp.VPL == 2) LIPVQ_GB(32, 2);
+    else LIPVQ_GB(32, 4);
+#undef LIPVQ_GB
+  } else {
+    gather_bwd_scalar_kernel<<<stream_grid(N * (int64_t)D, 256, 8), 256, 0, stream>>>(
+        z, z_q, idx, dzq_up, gscale_dev, w_commit, w_codebook, ste, sigmoid_out, N, D, K, dz_out, dcodebook);
+  }
   LIPVQ_LAUNCHED("gather_bwd_kernel");
   return LIPVQ_OK;
 }
@@ -378,18 +451,15 @@ int lipvq_ema_stats_f32(const float* z, const int64_t* idx, int64_t N, int D, in
   LIPVQ_REQUIRE(z && idx && counts && sums, "ema_stats: null pointer");
   const bool vec = (D % 4 == 0) && D <= 512 && aligned16(z) && aligned16(sums);
   if (vec) {
-    // enough warps for ~8 per SM sub-partition, at least 8 rows each so run-length aggregation has a chance
-    int64_t rows_per_warp = ceil_div64(N, (int64_t)sm_count() * 32);
-    if (rows_per_warp < 8) rows_per_warp = 8;
-    const int64_t warps = ceil_div64(N, rows_per_warp);
-    const unsigned grid = (unsigned)ceil_div64(warps * 32, 256);
-    const int vpl = (D + 127) / 128;
-    if (vpl == 1)
-      ema_stats_vec_kernel<1><<<grid, 256, 0, stream>>>(z, idx, N, D, K, rows_per_warp, counts, sums);
-    else if (vpl == 2)
-      ema_stats_vec_kernel<2><<<grid, 256, 0, stream>>>(z, idx, N, D, K, rows_per_warp, counts, sums);
-    else
-      ema_stats_vec_kernel<4><<<grid, 256, 0, stream>>>(z, idx, N, D, K, rows_per_warp, counts, sums);
+    const RunsPlan rp = plan_runs(N, D);
+#define LIPVQ_ES(G_, V_) \
+  ema_stats_runs_kernel<G_, V_><<<rp.grid, 256, 0, stream>>>(z, idx, N, D, K, rp.rows_per_group, counts, sums)
+    if (rp.G == 8) LIPVQ_ES(8, 1);
+    else if (rp.G == 16) LIPVQ_ES(16, 1);
+    else if (rp.VPL == 1) LIPVQ_ES(32, 1);
+    else if (rp.VPL == 2) LIPVQ_ES(32, 2);
+    else LIPVQ_ES(32, 4);
+#undef LIPVQ_ES
   } else {
     ema_stats_scalar_kernel<<<stream_grid(N * (int64_t)D, 256, 8), 256, 0, stream>>>(z, idx, N, D, K, counts, sums);
   }

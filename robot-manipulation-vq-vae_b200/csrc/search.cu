@@ -228,9 +228,14 @@ __global__ void __launch_bounds__(256)
   if (lane != 0) return;
 
   const float emax2 = __uint_as_float(hdr->emax2_bits);
-  const float zn = sqrtf(zn2), emax = sqrtf(emax2);
+  const float zn = sqrtf(zn2);
+  float emax = sqrtf(emax2);
+  // Only codes that can still beat the candidate matter, and by the triangle inequality those satisfy
+  // ||e_k|| <= ||z|| + d_k <= ||z|| + d_best.  This keeps the bound tight when some codes are huge (an EMA codebook
+  // divides by ~eps for codes that were never hit, hq_vae.py:277-279), which a global max-norm bound would not.
+  if (metric != LIPVQ_METRIC_DOT) emax = fminf(emax, zn + 1.02f * sqrtf(fmaxf(b + zn2, 0.f)) + 1e-30f);
   // both competitors' scores can be off by gamma * (||e||^2 + 2||z|| ||e||) each
-  const float margin_alg = 2.f * gamma * (emax2 + 2.f * zn * emax);
+  const float margin_alg = 2.f * gamma * (emax * emax + 2.f * zn * emax);
   // the reference's own fp32 rounding of d^2 (or of the similarity): stay out of its noise too
   const float ref_mag = (metric == LIPVQ_METRIC_DOT) ? 2.f * zn * emax : fmaxf(b + zn2, 0.f);
   const float margin = fmaxf(margin_alg, gamma_ref * ref_mag);

@@ -119,8 +119,11 @@ def test_t1_training_step_at_baseline_batch():
     assert abs(l0[0].item() - ref["loss"].item()) <= 1e-4 * abs(ref["loss"].item())
     sd = m.state_dict()
     assert abs(sd["quantizer.ema_cluster_size"].sum().item() - 0.01 * N) <= 1e-3 * 0.01 * N
-    for k in ("encoder.2.weight", "to_latent.W", "to_latent.ci", "decoder.0.weight", "to_output.bias"):
-        assert torch.allclose(sd[k].cpu(), p0[k], rtol=1e-3, atol=1e-5), k
+    # gradients of this step are still in the trainer's reduction slab (AdamW's first update is ~lr*sign(g), so
+    # comparing post-step weights would amplify fp32 noise on near-zero gradients; compare the gradients themselves)
+    for k in ("encoder.0.weight", "encoder.2.weight", "to_latent.W", "to_latent.ci", "decoder.0.weight", "to_output.bias"):
+        gr = ref["grads"][k]
+        assert torch.allclose(tr.g[k].cpu(), gr, rtol=1e-3, atol=1e-3 * gr.abs().max().item()), k
     losses = [l0[0].item()] + [tr.step(x.to(DEV))[0].item() for _ in range(5)]
     assert losses[-1] < losses[0]
     toks = tr.tokenize(x.to(DEV))
