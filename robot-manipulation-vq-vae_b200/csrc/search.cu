@@ -13,6 +13,8 @@
 //                           reference's winner, else the row is queued
 //   4. rescore_kernel       queued rows: exact fp32 direct-difference scan in the reference's domain
 //                           (sqrt for METRIC_L2, first-min tie rule)
+#include <cstdlib>
+
 #include "search.cuh"
 
 namespace lipvq {
@@ -191,7 +193,7 @@ __global__ void __launch_bounds__(NT, 2)
 __global__ void __launch_bounds__(256)
     finalize_kernel(const float* __restrict__ z, int64_t N, int D, const float* __restrict__ cb, int metric,
                     int ksplit, const float* __restrict__ pbest, const float* __restrict__ psecond,
-                    const int* __restrict__ pidx, float gamma, float gamma_ref, SearchHdr* hdr,
+                    const int* __restrict__ pidx, float gamma_en, float gamma_dot, float gamma_ref, SearchHdr* hdr,
                     int* __restrict__ work, int64_t* __restrict__ idx_out, float* __restrict__ best_out) {
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
@@ -234,8 +236,8 @@ __global__ void __launch_bounds__(256)
   // ||e_k|| <= ||z|| + d_k <= ||z|| + d_best.  This keeps the bound tight when some codes are huge (an EMA codebook
   // divides by ~eps for codes that were never hit, hq_vae.py:277-279), which a global max-norm bound would not.
   if (metric != LIPVQ_METRIC_DOT) emax = fminf(emax, zn + 1.02f * sqrtf(fmaxf(b + zn2, 0.f)) + 1e-30f);
-  // both competitors' scores can be off by gamma * (||e||^2 + 2||z|| ||e||) each
-  const float margin_alg = 2.f * gamma * (emax * emax + 2.f * zn * emax);
+  // both competitors' scores can be off by gamma_en*||e||^2 (the separately rounded norm) + gamma_dot*2||z|| ||e|| each
+  const float margin_alg = 2.f * (gamma_en * emax * emax + gamma_dot * 2.f * zn * emax);
   // the reference's own fp32 rounding of d^2 (or of the similarity): stay out of its noise too
   const float ref_mag = (metric == LIPVQ_METRIC_DOT) ? 2.f * zn * emax : fmaxf(b + zn2, 0.f);
   const float margin = fmaxf(margin_alg, gamma_ref * ref_mag);
@@ -345,18 +347,26 @@ SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo) {
   SearchPlan p{};
   if (algo == LIPVQ_ALGO_AUTO) algo = lipvq_nn_search_pick_algo(N, D, K, metric);
   p.algo = algo;
-  const int tile = (algo == LIPVQ_ALGO_TCGEN05) ? 128 : BN;
-  const int64_t row_tiles = ceil_div64(N > 0 ? N : 1, 128);
-  const int code_tiles = (K + tile - 1) / tile;
-  int ks = (int)ceil_div64(kTargetCtas, row_tiles);
-  if (ks > code_tiles) ks = code_tiles;
-  if (ks < 1) ks = 1;
-  const int tiles_per_split = (code_tiles + ks - 1) / ks;
-  p.codes_per_split = tiles_per_split * tile;
-  p.ksplit = (K + p.codes_per_split - 1) / p.codes_per_split;
-  p.Dp = (D + 63) / 64 * 64;
   p.Np = ceil_div64(N > 0 ? N : 1, 128) * 128;
-  p.Kp = (K + 127) / 128 * 128;
+  if (algo == LIPVQ_ALGO_TCGEN05) {
+    int codes_res, S, Dp;
+    search_tc_plan(N, D, K, &codes_res, &S, &Dp);
+    p.codes_per_split = codes_res;
+    p.ksplit = S;
+    p.Dp = Dp;
+    p.Kp = S * codes_res;
+  } else {
+    const int64_t row_tiles = ceil_div64(N > 0 ? N : 1, BM);
+    const int code_tiles = (K + BN - 1) / BN;
+    int ks = (int)ceil_div64(kTargetCtas, row_tiles);
+    if (ks > code_tiles) ks = code_tiles;
+    if (ks < 1) ks = 1;
+    const int tiles_per_split = (code_tiles + ks - 1) / ks;
+    p.codes_per_split = tiles_per_split * BN;
+    p.ksplit = (K + p.codes_per_split - 1) / p.codes_per_split;
+    p.Dp = (D + 63) / 64 * 64;
+    p.Kp = (K + 127) / 128 * 128;
+  }
   size_t o = 0;
   p.off_hdr = o;      o = align_up(o + sizeof(SearchHdr), 256);
   p.off_enorm = o;    o = align_up(o + sizeof(float) * (size_t)p.Kp, 256);
@@ -383,6 +393,11 @@ extern "C" {
 
 int lipvq_nn_search_pick_algo(int64_t N, int D, int K, int metric) {
   (void)metric;
+  // LIPVQ_SEARCH_ALGO=simt|tc overrides the heuristic (A/B runs in bench.py and the profiling scripts)
+  if (const char* f = getenv("LIPVQ_SEARCH_ALGO")) {
+    if (f[0] == 's') return LIPVQ_ALGO_SIMT_F32;
+    if (f[0] == 't' && search_tc_supported(N, D, K)) return LIPVQ_ALGO_TCGEN05;
+  }
   // The tensor path pays a bf16 split pass over z and the codebook and 128x128 tiles; it wins once there is
   // enough contraction per row (profiles/ has the crossover).  Tiny problems stay on the FFMA kernel.
   if (search_tc_supported(N, D, K) && (int64_t)N * K >= (int64_t)1 << 20) return LIPVQ_ALGO_TCGEN05;
@@ -429,6 +444,7 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
   LIPVQ_LAUNCHED("code_sqnorm_kernel");
 
   const int vec = (D % 4 == 0) && aligned16(z) && aligned16(codebook);
+  const float gamma_en = (float)(D + 4) * 5.9604645e-8f;  // fp32 FMA chain of ||e||^2 plus the final add
   float gamma;
   if (plan.algo == LIPVQ_ALGO_TCGEN05) {
     const int rc = search_tc_launch(z, N, D, codebook, K, plan, ws, stream);
@@ -445,7 +461,7 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
   const float gamma_ref = 4.f * (float)(D + 4) * 5.9604645e-8f;
 
   finalize_kernel<<<(unsigned)ceil_div64(N * 32, 256), 256, 0, stream>>>(z, N, D, codebook, metric, plan.ksplit, pbest,
-                                                                         psecond, pidx, gamma, gamma_ref, hdr, work,
+                                                                         psecond, pidx, gamma_en, gamma, gamma_ref, hdr, work,
                                                                          idx_out, best_out);
   LIPVQ_LAUNCHED("finalize_kernel");
 

@@ -30,7 +30,9 @@ SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo);
 bool search_tc_supported(int64_t N, int D, int K);
 int search_tc_launch(const float* z, int64_t N, int D, const float* cb, int K, const SearchPlan& plan, char* ws,
                      cudaStream_t stream);
-// rigorous bound factor of the tcgen05 split-bf16 score error (see search_tc.cu)
+// rigorous bound factor of the tcgen05 split-bf16 dot-product error (see search_tc.cu)
 float search_tc_gamma(int D);
+// resident-slice geometry of the tensor path for a shape: codes per slice, number of slices, padded latent dim
+void search_tc_plan(int64_t N, int D, int K, int* codes_res, int* S, int* Dp);
 
 }  // namespace lipvq

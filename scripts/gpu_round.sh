@@ -1,16 +1,19 @@
 #!/bin/bash
-# One gpurun call: GPU parity tests, smoke, a short bench, then the ncu launch list and one full capture of the search
-# kernel (each ncu run directly after the same command exited 0 without ncu).  Logs land in gpurun_out/.
+# One gpurun call: GPU parity tests (the tcgen05 tests first, in their own process, so a fault there cannot poison the
+# rest), smoke, bench, then the ncu launch list and one full capture of the search kernel (each ncu run directly after
+# the same command exited 0 without ncu).  Logs land in gpurun_out/.   usage: gpu_round.sh [noncu]
 set -u
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
-timeout 900 python -m pytest tests -q -m gpu -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1
+timeout 600 python -m pytest tests/test_gpu_search_tc.py -q -m gpu -p no:cacheprovider -x > gpurun_out/pytest_tc.log 2>&1
+TC=$?; echo "pytest tc exit $TC" >> gpurun_out/pytest_tc.log; tail -n 25 gpurun_out/pytest_tc.log
+if [ $TC -ne 0 ]; then export LIPVQ_SEARCH_ALGO=simt; echo "tcgen05 tests failed: rest of the round runs with LIPVQ_SEARCH_ALGO=simt"; fi
+timeout 900 python -m pytest tests -q -m gpu -p no:cacheprovider --deselect tests/test_gpu_search_tc.py > gpurun_out/pytest_gpu.log 2>&1
 echo "pytest exit $?" >> gpurun_out/pytest_gpu.log
-tail -n 30 gpurun_out/pytest_gpu.log
+tail -n 15 gpurun_out/pytest_gpu.log
 timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke exit $?"; tail -n 3 gpurun_out/smoke.log
 timeout 600 python bench.py --steps 30 --warmup 5 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"
 cat gpurun_out/bench.json; tail -n 5 gpurun_out/bench.err
-timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2>&1; cat gpurun_out/bench_ref.json
 if [ "${1:-}" != "noncu" ]; then
   timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
@@ -21,4 +24,4 @@ if [ "${1:-}" != "noncu" ]; then
       -f -o gpurun_out/prof_search python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
   echo "ncu full exit $?"
 fi
-ls -la gpurun_out
+ls -la gpurun_out | head -30

@@ -1,0 +1,82 @@
+"""-m gpu: the tcgen05/TMEM/TMA nearest-code contraction (LIPVQ_ALGO_TCGEN05) against the CPU oracle and against the
+fp32 FFMA path, over the geometry corners of the resident-slice scheduler (1 or 2 code tiles per slice, several
+latent-dim chunks, several slices, ragged N / K / D)."""
+import math
+
+import pytest
+import torch
+
+import lipvq_oracle as O
+from test_gpu_kernels import DEV, _rand_case, assert_indices
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("N,K,D", [
+    (4096, 512, 64),      # BASELINE C1: one slice or two, D = one swizzle atom
+    (128, 256, 64),       # single row block
+    (1000, 77, 12),       # ragged everything: D padded 12 -> 64, K padded, N padded
+    (5000, 4096, 64),     # many slices
+    (2048, 1024, 128),    # two latent chunks per row block
+    (300, 130, 256),      # four chunks, MMA N = 128
+    (80, 1024, 208),      # the reference's real shape (backbone_lfqvae_v5.py:89-93)
+    (700, 100, 512),      # HVQ embed dim: MMA N = 64, eight chunks
+])
+def test_tc_search_l2_vs_oracle(N, K, D):
+    import lipvq as L
+    z, cb = _rand_case(N, K, D, 900 + N + K + D)
+    ref = O.nearest_code_l2(z, cb)
+    idx, best, stats = L.ops.nn_search(z.to(DEV), cb.to(DEV), L.METRIC_L2, L.ALGO_TCGEN05, want_best=True, want_stats=True)
+    torch.cuda.synchronize()
+    assert_indices(z, cb, idx, ref)
+    assert torch.allclose(best.cpu(), torch.norm(z - cb[ref], dim=-1), rtol=1e-5, atol=1e-7)
+    # the split-bf16 contraction must leave only a small ambiguous set for the exact rescore
+    assert int(stats[0]) <= max(8, 0.05 * N), f"{int(stats[0])} of {N} rows went through the exact rescore"
+
+
+def test_tc_matches_simt_path_and_other_metrics():
+    import lipvq as L
+    z, cb = _rand_case(3000, 700, 64, 42)
+    zd, cd = z.to(DEV), cb.to(DEV)
+    a = L.ops.nn_search(zd, cd, L.METRIC_L2, L.ALGO_TCGEN05)
+    b = L.ops.nn_search(zd, cd, L.METRIC_L2, L.ALGO_SIMT_F32)
+    assert_indices(z, cb, a, b.cpu())
+    ref = O.nearest_code_l2(z, cb * 0.01, squared=True)
+    idx = L.ops.nn_search(zd, (cb * 0.01).to(DEV), L.METRIC_L2SQ, L.ALGO_TCGEN05)
+    assert_indices(z, cb * 0.01, idx, ref, max_near_tie_frac=0.05)
+    zn = torch.nn.functional.normalize(torch.randn(1500, 64), dim=-1)
+    cn = torch.nn.functional.normalize(torch.randn(257, 64), dim=-1)
+    ref = torch.argmax(zn @ cn.t(), dim=1)
+    idx = L.ops.nn_search(zn.to(DEV), cn.to(DEV), L.METRIC_DOT, L.ALGO_TCGEN05)
+    assert_indices(zn, cn, idx, ref, metric="dot")
+
+
+def test_tc_huge_norm_codes_and_duplicates():
+    """EMA codebooks hold never-hit codes divided by ~eps (hq_vae.py:277-279): norms ~1e5 must not disturb the search,
+    and exact duplicate codes must resolve to the lowest index through the exact path."""
+    import lipvq as L
+    z, cb = _rand_case(2048, 512, 64, 77)
+    cb[100:200] = torch.randn(100, 64) * 1e5
+    cb[300] = cb[7]
+    z[:64] = cb[7] + 1e-3
+    ref = O.nearest_code_l2(z, cb)
+    idx, stats = L.ops.nn_search(z.to(DEV), cb.to(DEV), L.METRIC_L2, L.ALGO_TCGEN05, want_stats=True)
+    assert_indices(z, cb, idx, ref)
+    assert (idx[:64] == 7).all()
+    assert int(stats[0]) < 0.2 * 2048
+
+
+def test_tc_full_size_c3_shapes():
+    """BASELINE C3 sizes with N = 65536: subsampled oracle check + determinism + optimality against random codes."""
+    import lipvq as L
+    for K, D, nsub in ((512, 64, 4096), (4096, 64, 1024), (512, 256, 1024)):
+        z, cb = _rand_case(65536, K, D, 5 + K + D)
+        zd, cd = z.to(DEV), cb.to(DEV)
+        idx, best = L.ops.nn_search(zd, cd, L.METRIC_L2, L.ALGO_TCGEN05, want_best=True)
+        idx2 = L.ops.nn_search(zd, cd, L.METRIC_L2, L.ALGO_TCGEN05)
+        assert torch.equal(idx, idx2)
+        rows = torch.randperm(65536, generator=torch.Generator().manual_seed(0))[:nsub]
+        assert_indices(z[rows], cb, idx.cpu()[rows], O.nearest_code_l2(z[rows], cb))
+        rk = torch.randint(0, K, (65536, 4), generator=torch.Generator().manual_seed(1))
+        d_rand = (z[:, None, :] - cb[rk]).norm(dim=-1)
+        assert (best.cpu()[:, None] <= d_rand * (1 + 1e-6)).all()
