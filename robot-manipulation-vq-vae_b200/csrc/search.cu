@@ -27,14 +27,44 @@ constexpr int PAD = 4;
 constexpr int NT = 256;
 constexpr int kTargetCtas = 2 * 148 * 2;  // two resident CTAs per SM, two waves
 
+// Centre of the data cloud: mu = mean of up to 64 evenly spaced rows of z (zero for the dot metric).  Distances are
+// translation invariant, but the expanded form ||e||^2 - 2 z.e loses |z||e|*eps of absolute accuracy; when z and the
+// live codes sit in a tight cluster away from the origin (sigmoid latents around 0.5, an EMA codebook tracking them)
+// that would push almost every row into the exact rescore.  Subtracting a nearby point from both sides first makes
+// the error scale with the spread of the cloud instead.  Any mu is valid; it only affects how tight the bound is.
+__global__ void __launch_bounds__(256) center_kernel(const float* __restrict__ z, int64_t N, int D, int metric,
+                                                     float* __restrict__ mu, SearchHdr* hdr) {
+  __shared__ float s_part[8];
+  const int R = (int)(N < 64 ? N : 64);
+  const int64_t stride = N / R;
+  float nrm = 0.f;
+  for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float s = 0.f;
+    if (metric != LIPVQ_METRIC_DOT)
+      for (int i = 0; i < R; ++i) s += __ldg(z + (int64_t)i * stride * D + d);
+    const float m = s / (float)R;
+    mu[d] = m;
+    nrm = fmaf(m, m, nrm);
+  }
+  nrm = warp_sum(nrm);
+  if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = nrm;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += s_part[i];
+    hdr->mu_norm = sqrtf(t);
+  }
+}
+
 __global__ void __launch_bounds__(256) code_sqnorm_kernel(const float* __restrict__ cb, int K, int D, int metric,
-                                                          float* __restrict__ enorm, SearchHdr* hdr) {
+                                                          const float* __restrict__ mu, float* __restrict__ enorm,
+                                                          SearchHdr* hdr) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (warp >= K) return;
   const float* row = cb + (size_t)warp * D;
   float s = 0.f;
   for (int d = lane; d < D; d += 32) {
-    const float v = __ldg(row + d);
+    const float v = __ldg(row + d) - mu[d];
     s = fmaf(v, v, s);
   }
   s = warp_sum(s);
@@ -46,8 +76,9 @@ __global__ void __launch_bounds__(256) code_sqnorm_kernel(const float* __restric
 
 // global -> registers for a [ROWS x BK] tile of a row-major matrix whose reduction dim is contiguous.
 template <int ROWS>
-__device__ __forceinline__ void ldg_tile(const float* __restrict__ src, int64_t r0, int64_t rmax, int k0, int kmax,
-                                         int ld, bool vec, float4 (&v)[ROWS * BK / 4 / NT]) {
+__device__ __forceinline__ void ldg_tile(const float* __restrict__ src, const float* __restrict__ mu, int64_t r0,
+                                         int64_t rmax, int k0, int kmax, int ld, bool vec,
+                                         float4 (&v)[ROWS * BK / 4 / NT]) {
 #pragma unroll
   for (int u = 0; u < ROWS * BK / 4 / NT; ++u) {
     const int f = threadIdx.x + NT * u;
@@ -59,11 +90,13 @@ __device__ __forceinline__ void ldg_tile(const float* __restrict__ src, int64_t 
       const float* p = src + row * (int64_t)ld + k;
       if (vec) {
         x = __ldg(reinterpret_cast<const float4*>(p));
+        const float4 m = *reinterpret_cast<const float4*>(mu + k);
+        x.x -= m.x; x.y -= m.y; x.z -= m.z; x.w -= m.w;
       } else {
-        x.x = __ldg(p);
-        if (k + 1 < kmax) x.y = __ldg(p + 1);
-        if (k + 2 < kmax) x.z = __ldg(p + 2);
-        if (k + 3 < kmax) x.w = __ldg(p + 3);
+        x.x = __ldg(p) - mu[k];
+        if (k + 1 < kmax) x.y = __ldg(p + 1) - mu[k + 1];
+        if (k + 2 < kmax) x.z = __ldg(p + 2) - mu[k + 2];
+        if (k + 3 < kmax) x.w = __ldg(p + 3) - mu[k + 3];
       }
     }
     v[u] = x;
@@ -88,7 +121,7 @@ __device__ __forceinline__ void sts_tile(float (*S)[ROWS + PAD], const float4 (&
 // grid = (ceil(N/BM), ksplit).  Thread (ty,tx) owns rows {4ty+i, 64+4ty+i} x codes {4tx+j}.
 __global__ void __launch_bounds__(NT, 2)
     search_simt_kernel(const float* __restrict__ z, int64_t N, int D, const float* __restrict__ cb, int K,
-                       const float* __restrict__ enorm, int codes_per_split, float* __restrict__ pbest,
+                       const float* __restrict__ mu, const float* __restrict__ enorm, int codes_per_split, float* __restrict__ pbest,
                        float* __restrict__ psecond, int* __restrict__ pidx, int vec) {
   __shared__ __align__(16) float As[BK][BM + PAD];
   __shared__ __align__(16) float Bs[BK][BN + PAD];
@@ -116,8 +149,8 @@ __global__ void __launch_bounds__(NT, 2)
       for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
 
     float4 ra[2], rb[1];
-    ldg_tile<BM>(z, m0, N, 0, D, D, vec != 0, ra);
-    ldg_tile<BN>(cb, kt, kend, 0, D, D, vec != 0, rb);
+    ldg_tile<BM>(z, mu, m0, N, 0, D, D, vec != 0, ra);
+    ldg_tile<BN>(cb, mu, kt, kend, 0, D, D, vec != 0, rb);
 
     for (int d0 = 0; d0 < D; d0 += BK) {
       __syncthreads();  // everyone is done with the previous chunk (and the previous tile's epilogue)
@@ -126,8 +159,8 @@ __global__ void __launch_bounds__(NT, 2)
       if (d0 == 0 && t < BN) en_s[t] = (kt + t < kend) ? __ldg(enorm + kt + t) : INFINITY;
       __syncthreads();
       if (d0 + BK < D) {
-        ldg_tile<BM>(z, m0, N, d0 + BK, D, D, vec != 0, ra);
-        ldg_tile<BN>(cb, kt, kend, d0 + BK, D, D, vec != 0, rb);
+        ldg_tile<BM>(z, mu, m0, N, d0 + BK, D, D, vec != 0, ra);
+        ldg_tile<BN>(cb, mu, kt, kend, d0 + BK, D, D, vec != 0, rb);
       }
 #pragma unroll
       for (int kk = 0; kk < BK; ++kk) {
@@ -191,8 +224,8 @@ __global__ void __launch_bounds__(NT, 2)
 
 // One warp per row: merge code slices, decide whether the approximate winner is provably exact.
 __global__ void __launch_bounds__(256)
-    finalize_kernel(const float* __restrict__ z, int64_t N, int D, const float* __restrict__ cb, int metric,
-                    int ksplit, const float* __restrict__ pbest, const float* __restrict__ psecond,
+    finalize_kernel(const float* __restrict__ z, int64_t N, int D, const float* __restrict__ cb,
+                    const float* __restrict__ mu, int metric, int ksplit, const float* __restrict__ pbest, const float* __restrict__ psecond,
                     const int* __restrict__ pidx, float gamma_en, float gamma_dot, float gamma_ref, SearchHdr* hdr,
                     int* __restrict__ work, int64_t* __restrict__ idx_out, float* __restrict__ best_out) {
   const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -214,10 +247,12 @@ __global__ void __launch_bounds__(256)
   // ||z||^2 and the exact value of the candidate winner, lanes across the latent dim
   const float* zr = z + row * (int64_t)D;
   const float* er = cb + (int64_t)bi * D;
-  float zn2 = 0.f, ex = 0.f;
+  float zn2 = 0.f, ex = 0.f, zo2 = 0.f;  // zn2: centred ||z - mu||^2 (what the contraction saw); zo2: ||z||^2
   for (int d = lane; d < D; d += 32) {
     const float zv = __ldg(zr + d), ev = __ldg(er + d);
-    zn2 = fmaf(zv, zv, zn2);
+    const float zc = zv - mu[d];
+    zn2 = fmaf(zc, zc, zn2);
+    zo2 = fmaf(zv, zv, zo2);
     if (metric == LIPVQ_METRIC_DOT) {
       ex = fmaf(zv, ev, ex);
     } else {
@@ -226,6 +261,7 @@ __global__ void __launch_bounds__(256)
     }
   }
   zn2 = warp_sum(zn2);
+  zo2 = warp_sum(zo2);
   ex = warp_sum(ex);
   if (lane != 0) return;
 
@@ -240,7 +276,12 @@ __global__ void __launch_bounds__(256)
   const float margin_alg = 2.f * (gamma_en * emax * emax + gamma_dot * 2.f * zn * emax);
   // the reference's own fp32 rounding of d^2 (or of the similarity): stay out of its noise too
   const float ref_mag = (metric == LIPVQ_METRIC_DOT) ? 2.f * zn * emax : fmaxf(b + zn2, 0.f);
-  const float margin = fmaxf(margin_alg, gamma_ref * ref_mag);
+  // rounding of the subtraction of mu itself: each vector moves by at most eps*(|x| + |mu|), which perturbs d^2 by
+  // 2 d delta + delta^2 per competitor
+  const float dhat = sqrtf(fmaxf(b + zn2, 0.f));
+  const float delta = 5.9604645e-8f * (sqrtf(zo2) + emax + 3.f * hdr->mu_norm);
+  const float margin_c = (metric == LIPVQ_METRIC_DOT) ? 0.f : 2.f * (2.f * dhat * delta + delta * delta);
+  const float margin = fmaxf(margin_alg + margin_c, gamma_ref * ref_mag);
   if (s2 - b > margin) {
     idx_out[row] = (int64_t)bi;
     if (best_out) best_out[row] = (metric == LIPVQ_METRIC_L2) ? sqrtf(ex) : ex;
@@ -369,6 +410,7 @@ SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo) {
   }
   size_t o = 0;
   p.off_hdr = o;      o = align_up(o + sizeof(SearchHdr), 256);
+  p.off_mu = o;       o = align_up(o + sizeof(float) * (size_t)((D + 63) / 64 * 64), 256);
   p.off_enorm = o;    o = align_up(o + sizeof(float) * (size_t)p.Kp, 256);
   p.off_pbest = o;    o = align_up(o + sizeof(float) * (size_t)p.ksplit * N, 256);
   p.off_psecond = o;  o = align_up(o + sizeof(float) * (size_t)p.ksplit * N, 256);
@@ -440,19 +482,23 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
   LIPVQ_CUDA(cudaMemsetAsync(hdr, 0, sizeof(SearchHdr), stream));
   if (stats_out) LIPVQ_CUDA(cudaMemsetAsync(stats_out, 0, 4 * sizeof(int32_t), stream));
 
-  code_sqnorm_kernel<<<(unsigned)ceil_div64((int64_t)K * 32, 256), 256, 0, stream>>>(codebook, K, D, metric, enorm, hdr);
+  float* mu = (float*)(ws + plan.off_mu);
+  center_kernel<<<1, 256, 0, stream>>>(z, N, D, metric, mu, hdr);
+  LIPVQ_LAUNCHED("center_kernel");
+  code_sqnorm_kernel<<<(unsigned)ceil_div64((int64_t)K * 32, 256), 256, 0, stream>>>(codebook, K, D, metric, mu, enorm,
+                                                                                     hdr);
   LIPVQ_LAUNCHED("code_sqnorm_kernel");
 
   const int vec = (D % 4 == 0) && aligned16(z) && aligned16(codebook);
   const float gamma_en = (float)(D + 4) * 5.9604645e-8f;  // fp32 FMA chain of ||e||^2 plus the final add
   float gamma;
   if (plan.algo == LIPVQ_ALGO_TCGEN05) {
-    const int rc = search_tc_launch(z, N, D, codebook, K, plan, ws, stream);
+    const int rc = search_tc_launch(z, N, D, codebook, K, mu, plan, ws, stream);
     if (rc != LIPVQ_OK) return rc;
     gamma = search_tc_gamma(D);
   } else {
     dim3 grid((unsigned)ceil_div64(N, BM), (unsigned)plan.ksplit);
-    search_simt_kernel<<<grid, NT, 0, stream>>>(z, N, D, codebook, K, enorm, plan.codes_per_split, pbest, psecond,
+    search_simt_kernel<<<grid, NT, 0, stream>>>(z, N, D, codebook, K, mu, enorm, plan.codes_per_split, pbest, psecond,
                                                 pidx, vec);
     LIPVQ_LAUNCHED("search_simt_kernel");
     // fp32 FMA chain of length D plus the separately rounded ||e||^2 and the final fma: (D+4) unit roundoffs
@@ -460,7 +506,7 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
   }
   const float gamma_ref = 4.f * (float)(D + 4) * 5.9604645e-8f;
 
-  finalize_kernel<<<(unsigned)ceil_div64(N * 32, 256), 256, 0, stream>>>(z, N, D, codebook, metric, plan.ksplit, pbest,
+  finalize_kernel<<<(unsigned)ceil_div64(N * 32, 256), 256, 0, stream>>>(z, N, D, codebook, mu, metric, plan.ksplit, pbest,
                                                                          psecond, pidx, gamma_en, gamma, gamma_ref, hdr, work,
                                                                          idx_out, best_out);
   LIPVQ_LAUNCHED("finalize_kernel");

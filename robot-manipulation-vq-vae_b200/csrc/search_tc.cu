@@ -149,8 +149,8 @@ __device__ __forceinline__ uint32_t umma_idesc_bf16(int M, int N) {
 // ---- bf16 hi/lo split (+ row norms) -----------------------------------------------------------------------------
 // out_hi/out_lo [rows_p][Dp] bf16, zero padded.  scale = 1 for z, -2 for the codebook.  One thread per 8 elements.
 __global__ void __launch_bounds__(256)
-    split_bf16_kernel(const float* __restrict__ x, int64_t rows, int D, int64_t rows_p, int Dp, float scale,
-                      __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo) {
+    split_bf16_kernel(const float* __restrict__ x, const float* __restrict__ mu, int64_t rows, int D, int64_t rows_p,
+                      int Dp, float scale, __nv_bfloat16* __restrict__ hi, __nv_bfloat16* __restrict__ lo) {
   const int per_row = Dp / 8;
   const int64_t total = rows_p * per_row;
   for (int64_t it = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; it < total; it += (int64_t)gridDim.x * blockDim.x) {
@@ -165,10 +165,12 @@ __global__ void __launch_bounds__(256)
         const float4 a = __ldg(reinterpret_cast<const float4*>(p));
         const float4 b = __ldg(reinterpret_cast<const float4*>(p + 4));
         v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[j] -= mu[c + j];
       } else {
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          if (c + j < D) v[j] = __ldg(p + j);
+          if (c + j < D) v[j] = __ldg(p + j) - mu[c + j];
       }
     }
     __align__(16) __nv_bfloat16 h[8], l[8];
@@ -428,8 +430,8 @@ void search_tc_plan(int64_t N, int D, int K, int* codes_res, int* S, int* Dp) {
   *Dp = g.Dp;
 }
 
-int search_tc_launch(const float* z, int64_t N, int D, const float* cb, int K, const SearchPlan& plan, char* ws,
-                     cudaStream_t stream) {
+int search_tc_launch(const float* z, int64_t N, int D, const float* cb, int K, const float* mu, const SearchPlan& plan,
+                     char* ws, cudaStream_t stream) {
   const TcGeom g = tc_geom(N, D, K);
   if (plan.ksplit != g.S || plan.codes_per_split != g.codes_res || plan.Dp != g.Dp) {
     set_error("search_tc: plan/geometry mismatch");
@@ -447,12 +449,12 @@ int search_tc_launch(const float* z, int64_t N, int D, const float* cb, int K, c
     int64_t blocks = ceil_div64(items, 256);
     const int64_t cap = (int64_t)sm_count() * 16;
     if (blocks > cap) blocks = cap;
-    split_bf16_kernel<<<(unsigned)blocks, 256, 0, stream>>>(z, N, D, Np, g.Dp, 1.f, zhi, zlo);
+    split_bf16_kernel<<<(unsigned)blocks, 256, 0, stream>>>(z, mu, N, D, Np, g.Dp, 1.f, zhi, zlo);
     LIPVQ_LAUNCHED("split_bf16_kernel(z)");
     const int64_t items_e = (int64_t)Kp * (g.Dp / 8);
     blocks = ceil_div64(items_e, 256);
     if (blocks > cap) blocks = cap;
-    split_bf16_kernel<<<(unsigned)blocks, 256, 0, stream>>>(cb, K, D, Kp, g.Dp, -2.f, ehi, elo);
+    split_bf16_kernel<<<(unsigned)blocks, 256, 0, stream>>>(cb, mu, K, D, Kp, g.Dp, -2.f, ehi, elo);
     LIPVQ_LAUNCHED("split_bf16_kernel(codebook)");
   }
 

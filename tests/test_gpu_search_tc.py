@@ -80,3 +80,22 @@ def test_tc_full_size_c3_shapes():
         rk = torch.randint(0, K, (65536, 4), generator=torch.Generator().manual_seed(1))
         d_rand = (z[:, None, :] - cb[rk]).norm(dim=-1)
         assert (best.cpu()[:, None] <= d_rand * (1 + 1e-6)).all()
+
+
+@pytest.mark.parametrize("algo", ["simt", "tc"])
+def test_clustered_latents_stay_on_fast_path(algo):
+    """Sigmoid latents of a fresh LipschitzMLP sit in a tight cluster around 0.5 and an EMA codebook tracks them with a
+    few live codes while dead codes blow up to ~1e5 (hq_vae.py:277-279).  Centring keeps the expanded-form error
+    proportional to the cluster's spread, so such rows must not all fall into the exact rescore."""
+    import lipvq as L
+    g = torch.Generator().manual_seed(3)
+    N, K, D = 8192, 512, 64
+    z = 0.5 + 0.01 * torch.randn(N, D, generator=g)
+    cb = torch.randn(K, D, generator=g) * 1e5
+    live = torch.randperm(K, generator=g)[:12]
+    cb[live] = 0.5 + 0.01 * torch.randn(12, D, generator=g)
+    ref = O.nearest_code_l2(z, cb)
+    a = L.ALGO_SIMT_F32 if algo == "simt" else L.ALGO_TCGEN05
+    idx, stats = L.ops.nn_search(z.to(DEV), cb.to(DEV), L.METRIC_L2, a, want_stats=True)
+    assert_indices(z, cb, idx, ref)
+    assert int(stats[0]) < 0.05 * N, f"{int(stats[0])} of {N} rows rescored"
