@@ -27,7 +27,7 @@ constexpr int PAD = 4;
 constexpr int NT = 256;
 constexpr int kTargetCtas = 2 * 148 * 2;  // two resident CTAs per SM, two waves
 
-// Centre of the data cloud: mu = mean of up to 64 evenly spaced rows of z (zero for the dot metric).  Distances are
+// Centre of the data cloud: mu = mean of up to 32 evenly spaced rows of z (zero for the dot metric).  Distances are
 // translation invariant, but the expanded form ||e||^2 - 2 z.e loses |z||e|*eps of absolute accuracy; when z and the
 // live codes sit in a tight cluster away from the origin (sigmoid latents around 0.5, an EMA codebook tracking them)
 // that would push almost every row into the exact rescore.  Subtracting a nearby point from both sides first makes
@@ -35,13 +35,18 @@ constexpr int kTargetCtas = 2 * 148 * 2;  // two resident CTAs per SM, two waves
 __global__ void __launch_bounds__(256) center_kernel(const float* __restrict__ z, int64_t N, int D, int metric,
                                                      float* __restrict__ mu, SearchHdr* hdr) {
   __shared__ float s_part[8];
-  const int R = (int)(N < 64 ? N : 64);
+  constexpr int RMAX = 32;
+  const int R = (int)(N < RMAX ? N : RMAX);
   const int64_t stride = N / R;
   float nrm = 0.f;
   for (int d = threadIdx.x; d < D; d += blockDim.x) {
+    float v[RMAX];
+#pragma unroll
+    for (int i = 0; i < RMAX; ++i)  // independent loads, all in flight together
+      v[i] = (metric != LIPVQ_METRIC_DOT && i < R) ? __ldg(z + (int64_t)i * stride * D + d) : 0.f;
     float s = 0.f;
-    if (metric != LIPVQ_METRIC_DOT)
-      for (int i = 0; i < R; ++i) s += __ldg(z + (int64_t)i * stride * D + d);
+#pragma unroll
+    for (int i = 0; i < RMAX; ++i) s += v[i];
     const float m = s / (float)R;
     mu[d] = m;
     nrm = fmaf(m, m, nrm);

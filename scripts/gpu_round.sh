@@ -5,7 +5,7 @@
 set -u
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/smi.txt 2>&1
-timeout 600 python -m pytest tests/test_gpu_search_tc.py -q -m gpu -p no:cacheprovider -x > gpurun_out/pytest_tc.log 2>&1
+timeout 600 python -m pytest tests/test_gpu_search_tc.py -q -m gpu -p no:cacheprovider > gpurun_out/pytest_tc.log 2>&1
 TC=$?; echo "pytest tc exit $TC" >> gpurun_out/pytest_tc.log; tail -n 25 gpurun_out/pytest_tc.log
 if [ $TC -ne 0 ]; then export LIPVQ_SEARCH_ALGO=simt; echo "tcgen05 tests failed: rest of the round runs with LIPVQ_SEARCH_ALGO=simt"; fi
 timeout 900 python -m pytest tests -q -m gpu -p no:cacheprovider --deselect tests/test_gpu_search_tc.py > gpurun_out/pytest_gpu.log 2>&1
