@@ -181,6 +181,41 @@ LIPVQ_API int lipvq_lipschitz_scale_fwd_f32(const float* W, const float* ci, int
 LIPVQ_API int lipvq_lipschitz_scale_bwd_f32(const float* G, const float* W, const float* ci, int out_dim, int in_dim, float* dW,
                                   float* dci, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * K8  MS-TCN layers of the hierarchical tokenizer.  Replaces DilatedTemporalConvLayer.forward
+ * (heirarchical_vqvae.py:39-57: Conv1d(E,E,3,dilation=d,padding=d) -> ReLU -> Dropout -> + x), the
+ * [B,T,E]<->[B,E,T] transposes of ActionEncoder/ActionDecoder (:147-158, 202-210) and nn.LayerNorm(E) (:137,159).
+ *
+ * Activations are token-major [N = B*T, E]; time index of row n is n % T.  Taps that can only read padding
+ * (dilation >= T) are skipped.  E % 4 == 0 and Ei == Eo (the reference never builds the 1x1 residual conv).
+ *   pack:   W [Eo][Ei][3] (nn.Conv1d layout) -> Wf [Eo][3][Ei] and/or Wb [3][Eo][Ei]
+ *   fwd:    OUT[n,o] = keep ? relu(pre)/(1-p) : 0  + X[n,o];  mask[n,o] = keep (uint8);  keep = pre>0 && not dropped
+ *           (dropout: counter-based hash of (seed, element index); p = 0 in eval)
+ *   bwd_x:  dX = dOUT + conv^T(dOUT * mask /(1-p))
+ *   bwd_w:  dWf [Eo][3][Ei] += ... ; db[o] += sum_n dOUT*mask/(1-p)   (ACCUMULATED INTO)
+ *   unpack: dW [Eo][Ei][3] += dWf
+ * --------------------------------------------------------------------------------------------- */
+LIPVQ_API int lipvq_conv_pack_weights_f32(const float* W, int Eo, int Ei, float* Wf, float* Wb, void* stream);
+LIPVQ_API int lipvq_conv_unpack_grad_f32(const float* dWf, int Eo, int Ei, float* dW, void* stream);
+LIPVQ_API int lipvq_dilated_conv_fwd_f32(const float* X, int64_t N, int T, int Ei, const float* Wf, const float* bias, int Eo,
+                               int dilation, float drop_p, uint32_t seed, float* OUT, uint8_t* mask, void* stream);
+LIPVQ_API int lipvq_dilated_conv_bwd_x_f32(const float* dOUT, const uint8_t* mask, int64_t N, int T, int Eo, const float* Wb,
+                                 int Ei, int dilation, float drop_p, float* dX, void* stream);
+LIPVQ_API int lipvq_dilated_conv_bwd_w_f32(const float* dOUT, const uint8_t* mask, const float* X, int64_t N, int T, int Eo,
+                                 int Ei, int dilation, float drop_p, float* dWf, float* db, void* stream);
+/* nn.LayerNorm over the last dim (biased variance, eps inside the sqrt); mean/rstd [rows] are kept for backward.
+ * bwd: dw/db ACCUMULATED INTO (may be NULL). */
+LIPVQ_API int lipvq_layernorm_fwd_f32(const float* X, int64_t rows, int E, const float* w, const float* b, float eps, float* Y,
+                            float* mean, float* rstd, void* stream);
+LIPVQ_API int lipvq_layernorm_bwd_f32(const float* dY, const float* X, const float* mean, const float* rstd, const float* w,
+                            int64_t rows, int E, float* dX, float* dw, float* db, void* stream);
+/* backward of F.normalize(x, dim=-1): dx = (dy - y (y.dy)) / max(||x||, 1e-12), y = x/max(||x||,1e-12)
+ * (cosine quantisation and the normalised commitment losses, heirarchical_vqvae.py:441-459, 652-667) */
+LIPVQ_API int lipvq_l2_normalize_rows_bwd_f32(const float* x, const float* dy, int64_t rows, int D, float* dx, void* stream);
+
+/* y = a*x + b (one fma per element; y may alias x).  `distances = 1.0 - sims` of heirarchical_vqvae.py:461,494. */
+LIPVQ_API int lipvq_affine_f32(const float* x, float a, float b, int64_t numel, float* y, void* stream);
+
 /* mean-squared error (F.mse_loss, reduction='mean'), fused with its gradient:
  * sqerr_sum (double, accumulated into) += sum (y-t)^2 ; if dY != NULL: dY = 2/(numel) * (y - t) * gscale,
  * and multiplied by act'(y) for act_out in {NONE, RELU} when the layer applied it in its epilogue. */

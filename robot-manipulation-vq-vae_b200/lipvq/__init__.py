@@ -7,5 +7,10 @@ from ._cabi import (ACT_GELU, ACT_NONE, ACT_RELU, ACT_SIGMOID, ALGO_AUTO, ALGO_S
                     EMA_NORMALIZE, EMA_SIMPLE, METRIC_DOT, METRIC_L2, METRIC_L2SQ, launch_count)
 from . import ops
 from .modules import LFQQuantizer, LFQQuantizerEMA, LipschitzMLP, LLFQVAE_V4
+from .classic import VQVAE
+from .hvq import (ActionDecoder, ActionEncoder, DilatedTemporalConvLayer, HierarchicalVQVAE, MSTCNStage)
+from .hq import HierarchicalLFQHVQVAE, LFQQuantizerEMA_KMeans
 
-__all__ = ["ops", "LLFQVAE_V4", "LipschitzMLP", "LFQQuantizer", "LFQQuantizerEMA", "launch_count"]
+__all__ = ["ops", "LLFQVAE_V4", "LipschitzMLP", "LFQQuantizer", "LFQQuantizerEMA", "LFQQuantizerEMA_KMeans",
+           "HierarchicalLFQHVQVAE", "VQVAE", "HierarchicalVQVAE", "ActionEncoder", "ActionDecoder", "MSTCNStage",
+           "DilatedTemporalConvLayer", "launch_count"]

@@ -44,6 +44,15 @@ SIGNATURES = {
     "lipvq_act_bwd_from_output_f32": (_i, [_p, _p, _i, _i64, _p, _p]),
     "lipvq_lipschitz_scale_fwd_f32": (_i, [_p, _p, _i, _i, _p, _p, _p]),
     "lipvq_lipschitz_scale_bwd_f32": (_i, [_p, _p, _p, _i, _i, _p, _p, _p]),
+    "lipvq_conv_pack_weights_f32": (_i, [_p, _i, _i, _p, _p, _p]),
+    "lipvq_conv_unpack_grad_f32": (_i, [_p, _i, _i, _p, _p]),
+    "lipvq_dilated_conv_fwd_f32": (_i, [_p, _i64, _i, _i, _p, _p, _i, _i, _f, C.c_uint32, _p, _p, _p]),
+    "lipvq_dilated_conv_bwd_x_f32": (_i, [_p, _p, _i64, _i, _i, _p, _i, _i, _f, _p, _p]),
+    "lipvq_dilated_conv_bwd_w_f32": (_i, [_p, _p, _p, _i64, _i, _i, _i, _i, _f, _p, _p, _p]),
+    "lipvq_layernorm_fwd_f32": (_i, [_p, _i64, _i, _p, _p, _f, _p, _p, _p, _p]),
+    "lipvq_layernorm_bwd_f32": (_i, [_p, _p, _p, _p, _p, _i64, _i, _p, _p, _p, _p]),
+    "lipvq_l2_normalize_rows_bwd_f32": (_i, [_p, _p, _i64, _i, _p, _p]),
+    "lipvq_affine_f32": (_i, [_p, _f, _f, _i64, _p, _p]),
     "lipvq_mse_fwd_bwd_f32": (_i, [_p, _p, _i64, _p, _i, _p, _p, _p]),
     "lipvq_t1_loss_finalize": (_i, [_p, _d, _d, _f, _f, _p, _p]),
     "lipvq_adamw_step_f32": (_i, [_p, _p, _p, _p, _i64, _i, _p, _f, _f, _f, _f, _f, _f, _p]),

@@ -38,12 +38,12 @@ def _f32c(x: torch.Tensor) -> torch.Tensor:
 # ----------------------------------------------------------------------------------------------
 class _LipschitzFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, W, b, ci):
+    def forward(ctx, x, W, b, ci, act_in=A.ACT_NONE):
         x2 = _f32c(x).reshape(-1, x.shape[-1])
         Wn = ops.lipschitz_scale_fwd(W.detach().contiguous(), ci.detach().contiguous())
-        y = ops.linear_fwd(x2, A.ACT_NONE, Wn, b.detach().contiguous(), A.ACT_SIGMOID)
+        y = ops.linear_fwd(x2, act_in, Wn, b.detach().contiguous(), A.ACT_SIGMOID)
         ctx.save_for_backward(x2, W, ci, Wn, y)
-        ctx.xshape = x.shape
+        ctx.xshape, ctx.act_in = x.shape, act_in
         return y.reshape(*x.shape[:-1], W.shape[0])
 
     @staticmethod
@@ -53,14 +53,14 @@ class _LipschitzFn(torch.autograd.Function):
         dpre = ops.act_bwd_from_output(dy2, y, A.ACT_SIGMOID)
         G = torch.zeros_like(W)
         db = torch.zeros(W.shape[0], dtype=torch.float32, device=W.device)
-        ops.linear_bwd_w(dpre, x2, A.ACT_NONE, G, db)
+        ops.linear_bwd_w(dpre, x2, ctx.act_in, G, db)
         dW = torch.zeros_like(W)
         dci = torch.zeros_like(ci)
         ops.lipschitz_scale_bwd(G, W.detach().contiguous(), ci.detach().contiguous(), dW, dci)
         dx = None
         if ctx.needs_input_grad[0]:
-            dx = ops.linear_bwd_x(dpre, Wn, None, A.ACT_NONE).reshape(ctx.xshape)
-        return dx, dW, db, dci
+            dx = ops.linear_bwd_x(dpre, Wn, x2 if ctx.act_in != A.ACT_NONE else None, ctx.act_in).reshape(ctx.xshape)
+        return dx, dW, db, dci, None
 
 
 class LipschitzMLP(nn.Module):

@@ -214,3 +214,89 @@ def adamw_step(p, g, m, v, step: int, step_dev=None, lr=1e-3, betas=(0.9, 0.999)
 
 def counter_add(ctr, delta: int = 1):
     A.check(lib.lipvq_counter_add_i32(_chk(ctr, I32, "ctr"), delta, _stream()), "counter_add")
+
+
+# ---- K8: MS-TCN layers, LayerNorm, normalize backward -------------------------------------------------
+U8 = torch.uint8
+
+
+def conv_pack_weights(W, want_fwd=True, want_bwd=True):
+    """W [Eo,Ei,3] -> (Wf [Eo,3,Ei] | None, Wb [3,Eo,Ei] | None)"""
+    Eo, Ei, k = W.shape
+    if k != 3:
+        raise RuntimeError(f"dilated conv kernels support kernel_size 3, got {k}")
+    Wf = torch.empty(Eo, 3, Ei, dtype=F32, device=W.device) if want_fwd else None
+    Wb = torch.empty(3, Eo, Ei, dtype=F32, device=W.device) if want_bwd else None
+    A.check(lib.lipvq_conv_pack_weights_f32(_chk(W, F32, "W"), Eo, Ei, _chk(Wf, F32, "Wf", True), _chk(Wb, F32, "Wb", True),
+                                            _stream()), "conv_pack_weights")
+    return Wf, Wb
+
+
+def conv_unpack_grad(dWf, dW):
+    Eo, Ei, _ = dW.shape
+    A.check(lib.lipvq_conv_unpack_grad_f32(_chk(dWf, F32, "dWf"), Eo, Ei, _chk(dW, F32, "dW"), _stream()), "conv_unpack_grad")
+
+
+def dilated_conv_fwd(x, T: int, Wf, bias, dilation: int, drop_p: float = 0.0, seed: int = 0):
+    """x [N,E] token-major (row n has time index n % T) -> (out [N,E], keep-mask uint8 [N,E])"""
+    N, Ei = x.shape
+    Eo = Wf.shape[0]
+    out = torch.empty(N, Eo, dtype=F32, device=x.device)
+    mask = torch.empty(N, Eo, dtype=U8, device=x.device)
+    A.check(lib.lipvq_dilated_conv_fwd_f32(_chk(x, F32, "x"), N, T, Ei, _chk(Wf, F32, "Wf"), _chk(bias, F32, "bias"), Eo,
+                                           dilation, drop_p, seed & 0xFFFFFFFF, _chk(out, F32, "out"), _chk(mask, U8, "mask"),
+                                           _stream()), "dilated_conv_fwd")
+    return out, mask
+
+
+def dilated_conv_bwd_x(dout, mask, T: int, Wb, dilation: int, drop_p: float = 0.0):
+    N, Eo = dout.shape
+    Ei = Wb.shape[2]
+    dx = torch.empty(N, Ei, dtype=F32, device=dout.device)
+    A.check(lib.lipvq_dilated_conv_bwd_x_f32(_chk(dout, F32, "dout"), _chk(mask, U8, "mask"), N, T, Eo, _chk(Wb, F32, "Wb"),
+                                             Ei, dilation, drop_p, _chk(dx, F32, "dx"), _stream()), "dilated_conv_bwd_x")
+    return dx
+
+
+def dilated_conv_bwd_w(dout, mask, x, T: int, dilation: int, dWf, db, drop_p: float = 0.0):
+    N, Eo = dout.shape
+    Ei = x.shape[1]
+    A.check(lib.lipvq_dilated_conv_bwd_w_f32(_chk(dout, F32, "dout"), _chk(mask, U8, "mask"), _chk(x, F32, "x"), N, T, Eo, Ei,
+                                             dilation, drop_p, _chk(dWf, F32, "dWf"), _chk(db, F32, "db", True), _stream()),
+            "dilated_conv_bwd_w")
+
+
+def layernorm_fwd(x, w, b, eps: float):
+    E = x.shape[-1]
+    rows = x.numel() // E
+    y = torch.empty_like(x)
+    mean = torch.empty(rows, dtype=F32, device=x.device)
+    rstd = torch.empty(rows, dtype=F32, device=x.device)
+    A.check(lib.lipvq_layernorm_fwd_f32(_chk(x, F32, "x"), rows, E, _chk(w, F32, "w"), _chk(b, F32, "b"), eps,
+                                        _chk(y, F32, "y"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd"), _stream()),
+            "layernorm_fwd")
+    return y, mean, rstd
+
+
+def layernorm_bwd(dy, x, mean, rstd, w, dw, db):
+    E = x.shape[-1]
+    rows = x.numel() // E
+    dx = torch.empty_like(x)
+    A.check(lib.lipvq_layernorm_bwd_f32(_chk(dy, F32, "dy"), _chk(x, F32, "x"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd"),
+                                        _chk(w, F32, "w"), rows, E, _chk(dx, F32, "dx"), _chk(dw, F32, "dw", True),
+                                        _chk(db, F32, "db", True), _stream()), "layernorm_bwd")
+    return dx
+
+
+def l2_normalize_rows_bwd(x, dy):
+    D = x.shape[-1]
+    dx = torch.empty_like(x)
+    A.check(lib.lipvq_l2_normalize_rows_bwd_f32(_chk(x, F32, "x"), _chk(dy, F32, "dy"), x.numel() // D, D, _chk(dx, F32, "dx"),
+                                                _stream()), "l2_normalize_rows_bwd")
+    return dx
+
+
+def affine(x, a: float, b: float, out=None):
+    y = out if out is not None else torch.empty_like(x)
+    A.check(lib.lipvq_affine_f32(_chk(x, F32, "x"), a, b, x.numel(), _chk(y, F32, "y"), _stream()), "affine")
+    return y
