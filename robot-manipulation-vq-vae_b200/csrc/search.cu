@@ -8,7 +8,7 @@
 // Pipeline (all on one stream, no host sync):
 //   1. code_sqnorm_kernel   ||e_k||^2 and max_k ||e_k||^2
 //   2. contraction          score[n,k] = ||e_k||^2 - 2 z_n.e_k, per-row running top-2 (never stored as [N,K])
-//                           -- search_simt_kernel (here) or the tcgen05 kernel (search_tc.cu)
+//                           -- search_simt_kernel (here); the tcgen05 path is search_fused.cu
 //   3. finalize_kernel      merge the code slices; if second-best - best > error bound the best is provably the
 //                           reference's winner, else the row is queued
 //   4. rescore_kernel       queued rows: exact fp32 direct-difference scan in the reference's domain
@@ -296,58 +296,88 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// Exact scan for queued rows: one warp per row, lane l takes codes l, l+32, ... ; each code's distance is a
-// sequential fp32 direct-difference sum over d (the reference's expression, backbone_lfqvae_v5.py:41-45).
-__global__ void __launch_bounds__(128)
+// Exact scan for queued rows: one CTA (8 warps) per row, grid-stride over the queue.  A group of LPC lanes owns one
+// code at a time and walks its row with coalesced float4 loads; each code's fp32 direct-difference sum (the reference's
+// expression, backbone_lfqvae_v5.py:41-45) is reduced over the group in a fixed butterfly order, so the result is
+// deterministic.  Winner = smallest value, lowest index on exact ties (torch.argmin's first-min rule).
+__global__ void __launch_bounds__(256)
     rescore_kernel(const float* __restrict__ z, int D, const float* __restrict__ cb, int K, int metric,
-                   const SearchHdr* __restrict__ hdr, const int* __restrict__ work, int64_t* __restrict__ idx_out,
-                   float* __restrict__ best_out, int32_t* __restrict__ stats_out, int vec) {
-  extern __shared__ __align__(16) float zs_all[];
-  const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* zs = zs_all + (size_t)wib * D;
-  const int nflag = hdr->flagged;
-  if (stats_out && blockIdx.x == 0 && threadIdx.x == 0) stats_out[0] = nflag;
-  const int warps_total = gridDim.x * (blockDim.x >> 5);
-  for (int w = blockIdx.x * (blockDim.x >> 5) + wib; w < nflag; w += warps_total) {
+                   const int* __restrict__ count, const int* __restrict__ first_count, const int* __restrict__ work,
+                   int64_t* __restrict__ idx_out, float* __restrict__ best_out, int32_t* __restrict__ stats_out, int vec,
+                   int lpc) {
+  extern __shared__ __align__(16) float zs[];
+  __shared__ float s_bv[8];
+  __shared__ int s_bk[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nflag = *count;
+  if (stats_out && blockIdx.x == 0 && threadIdx.x == 0) {
+    stats_out[0] = nflag;         // rows decided by the exact scan
+    stats_out[1] = *first_count;  // rows the first (fastest) level could not certify
+  }
+  const int sub = lane & (lpc - 1), grp = lane / lpc, groups = 32 / lpc;
+  for (int w = blockIdx.x; w < nflag; w += gridDim.x) {
     const int64_t row = work[w];
     const float* zr = z + row * (int64_t)D;
-    __syncwarp();
-    for (int d = lane; d < D; d += 32) zs[d] = __ldg(zr + d);
-    __syncwarp();
+    __syncthreads();  // previous row fully consumed
+    for (int d = threadIdx.x; d < D; d += blockDim.x) zs[d] = __ldg(zr + d);
+    __syncthreads();
     float bv = INFINITY;
     int bk = 0x7fffffff;
-    for (int k = lane; k < K; k += 32) {
-      const float* er = cb + (int64_t)k * D;
-      float a = 0.f;
+    // four codes per group and iteration, independent accumulators: the loads of all four are in flight together
+    for (int k0 = warp * groups; k0 < K; k0 += 8 * groups * 4) {
+      float a[4] = {0.f, 0.f, 0.f, 0.f};
       if (vec) {
-        for (int d = 0; d < D; d += 4) {
-          const float4 e4 = __ldg(reinterpret_cast<const float4*>(er + d));
+        for (int d = 4 * sub; d < D; d += 4 * lpc) {
+          float4 e4[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int k = k0 + grp + u * 8 * groups;
+            e4[u] = (k < K) ? __ldg(reinterpret_cast<const float4*>(cb + (int64_t)k * D + d)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
           const float4 z4 = *reinterpret_cast<const float4*>(zs + d);
-          if (metric == LIPVQ_METRIC_DOT) {
-            a = fmaf(z4.x, e4.x, a); a = fmaf(z4.y, e4.y, a); a = fmaf(z4.z, e4.z, a); a = fmaf(z4.w, e4.w, a);
-          } else {
-            float df;
-            df = z4.x - e4.x; a = fmaf(df, df, a);
-            df = z4.y - e4.y; a = fmaf(df, df, a);
-            df = z4.z - e4.z; a = fmaf(df, df, a);
-            df = z4.w - e4.w; a = fmaf(df, df, a);
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (metric == LIPVQ_METRIC_DOT) {
+              a[u] = fmaf(z4.x, e4[u].x, a[u]); a[u] = fmaf(z4.y, e4[u].y, a[u]);
+              a[u] = fmaf(z4.z, e4[u].z, a[u]); a[u] = fmaf(z4.w, e4[u].w, a[u]);
+            } else {
+              float df;
+              df = z4.x - e4[u].x; a[u] = fmaf(df, df, a[u]);
+              df = z4.y - e4[u].y; a[u] = fmaf(df, df, a[u]);
+              df = z4.z - e4[u].z; a[u] = fmaf(df, df, a[u]);
+              df = z4.w - e4[u].w; a[u] = fmaf(df, df, a[u]);
+            }
           }
         }
       } else {
-        for (int d = 0; d < D; ++d) {
-          const float ev = __ldg(er + d);
-          if (metric == LIPVQ_METRIC_DOT) {
-            a = fmaf(zs[d], ev, a);
-          } else {
-            const float df = zs[d] - ev;
-            a = fmaf(df, df, a);
+        for (int d = sub; d < D; d += lpc) {
+          float ev[4];
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            const int k = k0 + grp + u * 8 * groups;
+            ev[u] = (k < K) ? __ldg(cb + (int64_t)k * D + d) : 0.f;
+          }
+#pragma unroll
+          for (int u = 0; u < 4; ++u) {
+            if (metric == LIPVQ_METRIC_DOT) {
+              a[u] = fmaf(zs[d], ev[u], a[u]);
+            } else {
+              const float df = zs[d] - ev[u];
+              a[u] = fmaf(df, df, a[u]);
+            }
           }
         }
       }
-      const float val = (metric == LIPVQ_METRIC_L2) ? sqrtf(a) : (metric == LIPVQ_METRIC_DOT ? -a : a);
-      if (val < bv) {  // strict: earlier (lower) k wins ties within the lane
-        bv = val;
-        bk = k;
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {  // ascending k within the group, so a strict < keeps the lowest index on ties
+        const int k = k0 + grp + u * 8 * groups;
+        float av = a[u];
+        for (int o = lpc >> 1; o > 0; o >>= 1) av += __shfl_xor_sync(0xffffffffu, av, o);
+        const float val = (metric == LIPVQ_METRIC_L2) ? sqrtf(av) : (metric == LIPVQ_METRIC_DOT ? -av : av);
+        if (k < K && val < bv) {
+          bv = val;
+          bk = k;
+        }
       }
     }
 #pragma unroll
@@ -360,6 +390,16 @@ __global__ void __launch_bounds__(128)
       }
     }
     if (lane == 0) {
+      s_bv[warp] = bv;
+      s_bk[warp] = bk;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      for (int i = 1; i < 8; ++i)
+        if (s_bv[i] < bv || (s_bv[i] == bv && s_bk[i] < bk)) {
+          bv = s_bv[i];
+          bk = s_bk[i];
+        }
       if (bk == 0x7fffffff) bk = 0;  // all-NaN row: torch would return the NaN's index; we return 0
       idx_out[row] = (int64_t)bk;
       if (best_out) best_out[row] = (metric == LIPVQ_METRIC_DOT) ? -bv : bv;
@@ -395,12 +435,12 @@ SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo) {
   p.algo = algo;
   p.Np = ceil_div64(N > 0 ? N : 1, 128) * 128;
   if (algo == LIPVQ_ALGO_TCGEN05) {
-    int codes_res, S, Dp;
-    search_tc_plan(N, D, K, &codes_res, &S, &Dp);
-    p.codes_per_split = codes_res;
-    p.ksplit = S;
+    int Kp, Dp;
+    search_fused_plan(D, K, &Kp, &Dp);
+    p.codes_per_split = Kp;
+    p.ksplit = 0;  // the fused kernel keeps the running top-2 in registers: no per-slice partials
     p.Dp = Dp;
-    p.Kp = S * codes_res;
+    p.Kp = Kp;
   } else {
     const int64_t row_tiles = ceil_div64(N > 0 ? N : 1, BM);
     const int code_tiles = (K + BN - 1) / BN;
@@ -415,16 +455,15 @@ SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo) {
   }
   size_t o = 0;
   p.off_hdr = o;      o = align_up(o + sizeof(SearchHdr), 256);
-  p.off_mu = o;       o = align_up(o + sizeof(float) * (size_t)((D + 63) / 64 * 64), 256);
+  p.off_mu = o;       o = align_up(o + sizeof(float) * 512, 256);
   p.off_enorm = o;    o = align_up(o + sizeof(float) * (size_t)p.Kp, 256);
   p.off_pbest = o;    o = align_up(o + sizeof(float) * (size_t)p.ksplit * N, 256);
   p.off_psecond = o;  o = align_up(o + sizeof(float) * (size_t)p.ksplit * N, 256);
   p.off_pidx = o;     o = align_up(o + sizeof(int) * (size_t)p.ksplit * N, 256);
   p.off_work = o;     o = align_up(o + sizeof(int) * (size_t)(N > 0 ? N : 1), 256);
   if (algo == LIPVQ_ALGO_TCGEN05) {
-    const size_t zb = sizeof(uint16_t) * (size_t)p.Np * p.Dp, eb = sizeof(uint16_t) * (size_t)p.Kp * p.Dp;
-    p.off_zhi = o;  o = align_up(o + zb, 1024);
-    p.off_zlo = o;  o = align_up(o + zb, 1024);
+    const size_t eb = sizeof(uint16_t) * (size_t)p.Kp * p.Dp;
+    p.off_work2 = o; o = align_up(o + sizeof(int) * (size_t)(N > 0 ? N : 1), 256);
     p.off_ehi = o;  o = align_up(o + eb, 1024);
     p.off_elo = o;  o = align_up(o + eb, 1024);
   }
@@ -443,11 +482,11 @@ int lipvq_nn_search_pick_algo(int64_t N, int D, int K, int metric) {
   // LIPVQ_SEARCH_ALGO=simt|tc overrides the heuristic (A/B runs in bench.py and the profiling scripts)
   if (const char* f = getenv("LIPVQ_SEARCH_ALGO")) {
     if (f[0] == 's') return LIPVQ_ALGO_SIMT_F32;
-    if (f[0] == 't' && search_tc_supported(N, D, K)) return LIPVQ_ALGO_TCGEN05;
+    if (f[0] == 't' && search_fused_supported(N, D, K)) return LIPVQ_ALGO_TCGEN05;
   }
   // The tensor path pays a bf16 split pass over z and the codebook and 128x128 tiles; it wins once there is
   // enough contraction per row (profiles/ has the crossover).  Tiny problems stay on the FFMA kernel.
-  if (search_tc_supported(N, D, K) && (int64_t)N * K >= (int64_t)1 << 20) return LIPVQ_ALGO_TCGEN05;
+  if (search_fused_supported(N, D, K) && (int64_t)N * K >= (int64_t)1 << 20) return LIPVQ_ALGO_TCGEN05;
   return LIPVQ_ALGO_SIMT_F32;
 }
 
@@ -470,7 +509,7 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
   }
   LIPVQ_REQUIRE(z && codebook && idx_out && workspace, "nn_search: null pointer");
   if (algo == LIPVQ_ALGO_TCGEN05)
-    LIPVQ_REQUIRE(search_tc_supported(N, D, K), "nn_search: tcgen05 path does not support N=%lld D=%d K=%d",
+    LIPVQ_REQUIRE(search_fused_supported(N, D, K), "nn_search: tcgen05 path does not support N=%lld D=%d K=%d",
                   (long long)N, D, K);
   const SearchPlan plan = make_search_plan(N, D, K, metric, algo);
   LIPVQ_REQUIRE(workspace_bytes >= plan.total, "nn_search: workspace %zu < required %zu", workspace_bytes, plan.total);
@@ -488,39 +527,47 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
   if (stats_out) LIPVQ_CUDA(cudaMemsetAsync(stats_out, 0, 4 * sizeof(int32_t), stream));
 
   float* mu = (float*)(ws + plan.off_mu);
+  const int vec = (D % 4 == 0) && aligned16(z) && aligned16(codebook);
+  const int rs_blocks = 4 * sm_count();
+  const size_t rs_smem = (size_t)D * sizeof(float);
+  int lpc = 1;  // lanes per code: enough to cover the row with one float4 (or one float) each, at most a warp
+  while (lpc < 32 && lpc * (vec ? 4 : 1) < D) lpc <<= 1;
+  LIPVQ_REQUIRE(rs_smem <= 48 * 1024, "nn_search: D=%d too large for the rescore kernel", D);
+
+  if (plan.algo == LIPVQ_ALGO_TCGEN05) {
+    // prep + fp16 pass + 3-term pass (search_fused.cu); whatever is still queued gets the exact scan
+    const int* queue = nullptr;
+    const int* count = nullptr;
+    const int rc = search_fused_launch(z, N, D, codebook, K, metric, plan, ws, idx_out, stream, &queue, &count);
+    if (rc != LIPVQ_OK) return rc;
+    rescore_kernel<<<rs_blocks, 256, rs_smem, stream>>>(z, D, codebook, K, metric, count, &hdr->flagged, queue, idx_out,
+                                                        nullptr, stats_out, vec, lpc);
+    LIPVQ_LAUNCHED("rescore_kernel");
+    if (best_out) return search_best_values(z, N, D, codebook, metric, idx_out, best_out, stream);
+    return LIPVQ_OK;
+  }
+
   center_kernel<<<1, 256, 0, stream>>>(z, N, D, metric, mu, hdr);
   LIPVQ_LAUNCHED("center_kernel");
   code_sqnorm_kernel<<<(unsigned)ceil_div64((int64_t)K * 32, 256), 256, 0, stream>>>(codebook, K, D, metric, mu, enorm,
                                                                                      hdr);
   LIPVQ_LAUNCHED("code_sqnorm_kernel");
 
-  const int vec = (D % 4 == 0) && aligned16(z) && aligned16(codebook);
   const float gamma_en = (float)(D + 4) * 5.9604645e-8f;  // fp32 FMA chain of ||e||^2 plus the final add
-  float gamma;
-  if (plan.algo == LIPVQ_ALGO_TCGEN05) {
-    const int rc = search_tc_launch(z, N, D, codebook, K, mu, plan, ws, stream);
-    if (rc != LIPVQ_OK) return rc;
-    gamma = search_tc_gamma(D);
-  } else {
-    dim3 grid((unsigned)ceil_div64(N, BM), (unsigned)plan.ksplit);
-    search_simt_kernel<<<grid, NT, 0, stream>>>(z, N, D, codebook, K, mu, enorm, plan.codes_per_split, pbest, psecond,
-                                                pidx, vec);
-    LIPVQ_LAUNCHED("search_simt_kernel");
-    // fp32 FMA chain of length D plus the separately rounded ||e||^2 and the final fma: (D+4) unit roundoffs
-    gamma = (float)(D + 4) * 5.9604645e-8f;
-  }
+  dim3 grid((unsigned)ceil_div64(N, BM), (unsigned)plan.ksplit);
+  search_simt_kernel<<<grid, NT, 0, stream>>>(z, N, D, codebook, K, mu, enorm, plan.codes_per_split, pbest, psecond, pidx,
+                                              vec);
+  LIPVQ_LAUNCHED("search_simt_kernel");
+  // fp32 FMA chain of length D plus the separately rounded ||e||^2 and the final fma: (D+4) unit roundoffs
+  const float gamma = (float)(D + 4) * 5.9604645e-8f;
   const float gamma_ref = 4.f * (float)(D + 4) * 5.9604645e-8f;
 
   finalize_kernel<<<(unsigned)ceil_div64(N * 32, 256), 256, 0, stream>>>(z, N, D, codebook, mu, metric, plan.ksplit, pbest,
                                                                          psecond, pidx, gamma_en, gamma, gamma_ref, hdr, work,
                                                                          idx_out, best_out);
   LIPVQ_LAUNCHED("finalize_kernel");
-
-  const int rs_blocks = 2 * sm_count();
-  const size_t rs_smem = (size_t)4 * D * sizeof(float);
-  LIPVQ_REQUIRE(rs_smem <= 48 * 1024, "nn_search: D=%d too large for the rescore kernel", D);
-  rescore_kernel<<<rs_blocks, 128, rs_smem, stream>>>(z, D, codebook, K, metric, hdr, work, idx_out, best_out,
-                                                      stats_out, vec);
+  rescore_kernel<<<rs_blocks, 256, rs_smem, stream>>>(z, D, codebook, K, metric, &hdr->flagged, &hdr->flagged, work,
+                                                      idx_out, best_out, stats_out, vec, lpc);
   LIPVQ_LAUNCHED("rescore_kernel");
   return LIPVQ_OK;
 }

@@ -9,32 +9,35 @@ struct SearchHdr {
   unsigned emax2_bits;  // max_k ||e_k||^2 as float bits (atomicMax on non-negative floats)
   int flagged;          // rows whose top-2 gap is inside the error bound -> exact rescore
   float mu_norm;        // ||mu||, mu = the centre subtracted from z and the codes before the contraction
-  int pad[13];
+  unsigned excl_inv_bits;  // fused path: max over codes excluded from the fp16 contraction of 1/||e_k-mu|| (0 = none)
+  int flagged2;         // fused path: rows the 3-term pass could not certify either -> exact rescore
+  int pad[11];
 };
 
 struct SearchPlan {
   int algo;             // resolved LIPVQ_ALGO_*
   int ksplit;           // code range is cut in ksplit slices (grid.y) so small N still fills the SMs
   int codes_per_split;  // multiple of the code tile
-  int Dp;               // tcgen05 path: D padded to a multiple of 64 (one 128-byte swizzle atom of bf16)
-  int64_t Np;           // tcgen05 path: N padded to a multiple of 128
+  int Dp;               // tcgen05 path: D padded to a multiple of 64 (one 128-byte swizzle atom of fp16)
+  int64_t Np;           // N padded to a multiple of 128
   int Kp;               // tcgen05 path: K padded to a multiple of the code tile
   size_t off_mu;        // centre mu[D] (fp32)
   size_t off_hdr, off_enorm, off_pbest, off_psecond, off_pidx, off_work;
-  size_t off_zhi, off_zlo, off_ehi, off_elo;  // tcgen05 path: bf16 hi/lo splits
+  size_t off_work2;                  // tcgen05 path: second-level queue
+  size_t off_ehi, off_elo;           // tcgen05 path: fp16 hi/lo of -2(e-mu), [Kp][Dp]
   size_t total;
 };
 
 SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo);
 
-// tcgen05 contraction (search_tc.cu): fills pbest/psecond/pidx [ksplit][N] exactly like the SIMT kernel.
-// Returns LIPVQ_ERR_UNSUPPORTED when the shape is outside what the tensor path handles.
-bool search_tc_supported(int64_t N, int D, int K);
-int search_tc_launch(const float* z, int64_t N, int D, const float* cb, int K, const float* mu, const SearchPlan& plan,
-                     char* ws, cudaStream_t stream);
-// rigorous bound factor of the tcgen05 split-bf16 dot-product error (see search_tc.cu)
-float search_tc_gamma(int D);
-// resident-slice geometry of the tensor path for a shape: codes per slice, number of slices, padded latent dim
-void search_tc_plan(int64_t N, int D, int K, int* codes_res, int* S, int* Dp);
+// Fused tcgen05 search (search_fused.cu): codebook prep, fp16 pass over all rows, 3-term pass over the queued rows.
+// Writes idx_out for every certified row; *final_queue / *final_count name the rows left for the exact scan.
+bool search_fused_supported(int64_t N, int D, int K);
+void search_fused_plan(int D, int K, int* Kp, int* Dp);
+int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, const SearchPlan& plan,
+                        char* ws, int64_t* idx_out, cudaStream_t stream, const int** final_queue,
+                        const int** final_count);
+int search_best_values(const float* z, int64_t N, int D, const float* cb, int metric, const int64_t* idx, float* best_out,
+                       cudaStream_t stream);
 
 }  // namespace lipvq

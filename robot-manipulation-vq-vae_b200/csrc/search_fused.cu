@@ -1,0 +1,967 @@
+// K3, second generation: ONE fused tcgen05 kernel for the nearest-code search.
+//
+//   fp32 z rows --(converter warps: centre, fp16 [hi|lo], 128B-swizzled smem)--> A operand (resident per row block)
+//   fp16 codes  --(TMA ring, or resident when the whole codebook fits the ring)--> B operand
+//   tcgen05.mma kind::f16 accumulates -2 z.e ON TOP OF ||e||^2 that the epilogue pre-stored in TMEM (tcgen05.st), so
+//   the accumulator already holds the score ||e_k-mu||^2 - 2 (z_n-mu).(e_k-mu) and the epilogue spends no add on it
+//   8 epilogue warps: tcgen05.ld, running top-2 + argmin per row over ALL code tiles (no [S][N] partials), then the
+//   certified-winner test and the final int64 index / the re-score queue, all in the same kernel.
+//
+// Precision ladder (every level is rigorous; a row only leaves a level with a proven winner):
+//   pass 1  TERMS=1: one fp16 MMA chain (unit roundoff 2^-11 per operand) over every row
+//   pass 2  TERMS=3: hi*hi + hi*lo + lo*hi fp16 chains (~2^-21) over the rows pass 1 could not certify, gathered
+//           through the work queue (row count read from device memory, same kernel, no host sync)
+//   pass 3  exact fp32 direct-difference scan (rescore_kernel, search.cu) for true near-ties
+//
+// Reference op replaced: the [N,K,D] broadcast + norm + argmin of LFQQuantizer.forward
+// (robomimic/models/vq_vae/backbone_lfqvae_v5.py:39-46) and the variants listed in search.cu.
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "search.cuh"
+
+namespace lipvq {
+namespace {
+
+constexpr int kBM = 128;     // z rows per block (UMMA_M, cta_group::1)
+constexpr int kChunk = 64;   // latent elements per smem tile row: 64 fp16 = one 128-byte swizzle atom
+constexpr int kEpiWarps = 8, kCvtWarps = 4;
+constexpr int kWarpMma = kEpiWarps + kCvtWarps, kWarpTma = kWarpMma + 1;
+constexpr int kThreads = 32 * (kWarpTma + 1);  // 448 threads: the register file is allocated per 4 warps, so 128 registers each
+constexpr int kZStage = kBM * kChunk * 4;     // one staged (row block, chunk): [128][64] fp32 = 32 KB
+constexpr int kStatSlots = 4;
+constexpr float kF16Safe = 3.0e4f;  // |x| below this survives the -2 scaling and fp16 conversion without overflow
+
+struct FusedParams {
+  const float* z;
+  const int* row_list;    // pass 2: rows to process (work queue of pass 1); nullptr = rows 0..N-1
+  const int* n_rows_ptr;  // pass 2: device-side row count
+  int64_t N;
+  int D, K, NC, BN, T;    // NC = Dp/64 chunks, BN = MMA N, T = Kp/BN code tiles
+  int stages, resident, nbufA;
+  int zstages;            // > 0: z arrives through a bulk-copy ring of fp32 [128][64] tiles; 0: converters load global
+  int metric;
+  const float* mu;
+  const float* enorm;     // [Kp]: ||e_k - mu||^2, +inf for padding / excluded codes
+  SearchHdr* hdr;
+  int* queue_out;         // rows that could not be certified at this precision
+  int* queue_count;
+  int64_t* idx_out;
+  float gamma_en, gamma_dot, gamma_ref;
+  float neg_zero, pos_zero;  // -0.0f / +0.0f the compiler cannot see through (see top2_update)
+};
+
+// ---- PTX wrappers -------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Bounded wait: a protocol bug must fault (trap) instead of hanging the GPU.  try_wait carries a suspend-time hint so a
+// waiting thread sleeps in hardware instead of spinning: the single-thread producer / MMA roles wait for most of the
+// kernel, and a hot spin loop there takes issue slots and ALU cycles from the epilogue warps on the same scheduler.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done, iters = 0;
+  long long t0 = 0;
+  do {
+    asm volatile(
+        "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n selp.u32 %0, 1, 0, p;\n}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity), "r"(20000u)
+        : "memory");
+    if (!done && (++iters & 1023u) == 0) {
+      if (t0 == 0) t0 = clock64();
+      else if (clock64() - t0 > 4000000000LL) __trap();
+    }
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(bar)
+               : "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc) {
+  // always accumulates: the epilogue pre-stored ||e||^2 in the accumulator
+  asm volatile(
+      "{\n .reg .pred p;\n setp.ne.b32 p, 1, 0;\n tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}" ::"r"(d_tmem),
+      "l"(adesc), "l"(bdesc), "r"(idesc)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+        "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]),
+        "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]),
+        "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// wait::ld that also "touches" the destination registers, so no use of them can be scheduled above the wait
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[32]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;"
+               : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]),
+                 "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]),
+                 "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]),
+                 "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
+}
+// 32 lanes x 8 columns: every lane of the warp stores the same 8 column values (the tile's ||e||^2 slice)
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const float4& a, const float4& b) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"r"(taddr),
+               "r"(__float_as_uint(a.x)), "r"(__float_as_uint(a.y)), "r"(__float_as_uint(a.z)), "r"(__float_as_uint(a.w)),
+               "r"(__float_as_uint(b.x)), "r"(__float_as_uint(b.y)), "r"(__float_as_uint(b.z)), "r"(__float_as_uint(b.w))
+               : "memory");
+}
+// 32 lanes x 32 columns from 32 registers (same values in every lane)
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};" ::"r"(taddr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+      "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]), "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]),
+      "r"(v[21]), "r"(v[22]), "r"(v[23]), "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]),
+      "r"(v[31])
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};" ::"r"(taddr),
+      "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+      "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+}
+__device__ __forceinline__ void lds128(uint32_t addr, uint32_t& a, uint32_t& b, uint32_t& c, uint32_t& d) {
+  asm volatile("ld.shared.v4.b32 {%0,%1,%2,%3}, [%4];" : "=r"(a), "=r"(b), "=r"(c), "=r"(d) : "r"(addr) : "memory");
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const float4& v) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// Running top-2 + argmin update for one score.  FMNMX / FSETP / SEL all issue on the half-rate ALU pipe, which is what
+// bounds this kernel once D <= 128; here only the compare and the rare-path min stay there (2 ALU ops per score) and
+// the three conditional moves are written as predicated FADD/FFMA with an opaque -0.0 / +0.0 operand (x + -0.0 == x
+// and s * 0 + e == e exactly for finite s), which ptxas keeps as predicated FMA-pipe instructions instead of SELs.
+__device__ __forceinline__ void top2_update(float& best, float& second, float& idxf, float s, float e, float nz, float pz) {
+  asm("{\n .reg .pred p;\n setp.lt.f32 p, %3, %0;\n @p add.f32 %1, %0, %5;\n @!p min.f32 %1, %1, %3;\n"
+      " @p add.f32 %0, %3, %5;\n @p fma.rn.f32 %2, %3, %6, %4;\n}"
+      : "+f"(best), "+f"(second), "+f"(idxf)
+      : "f"(s), "f"(e), "f"(nz), "f"(pz));
+}
+
+// UMMA shared-memory descriptor, K-major, SWIZZLE_128B, tile rows of 128 bytes (64 fp16), 8-row atoms 1024 B apart
+// (UMMA::SmemDescriptor: start>>4 [0,14), LBO>>4 [16,30) = 1, SBO>>4 [32,46) = 64, version [46,48) = 1, layout [61,64) = 2).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// Instruction descriptor: D = f32 (bit 4), A = B = f16 (format 0 at bits 7 and 10), both K-major, N>>3 at [17,23), M>>4 at [24,29)
+__device__ __forceinline__ uint32_t umma_idesc_f16(int M, int N) {
+  return (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ---- codebook preparation: centre, ||e-mu||^2, fp16 [hi|lo] of -2(e-mu) -------------------------------------------
+// One launch: every CTA recomputes mu (mean of <= 32 sampled z rows, 8-32 KB of reads) so no second kernel or grid
+// sync is needed; CTA 0 publishes mu and ||mu||.  One warp per code row, grid-stride.  Codes whose centred entries do
+// not fit fp16 (EMA rows divided by ~eps, hq_vae.py:277-279) are EXCLUDED from the contraction (zeros, norm = +inf)
+// and the smallest excluded ||e-mu|| is recorded: the epilogue proves per row that no excluded code can win, else the
+// row takes the exact path.
+__global__ void __launch_bounds__(256)
+    fused_prep_kernel(const float* __restrict__ z, int64_t N, int D, const float* __restrict__ cb, int K, int Kp, int Dp,
+                      int metric, float* __restrict__ mu_g, float* __restrict__ enorm, __half* __restrict__ ehi,
+                      __half* __restrict__ elo, SearchHdr* hdr) {
+  __shared__ float mu_s[512];
+  __shared__ float s_part[8];
+  constexpr int RMAX = 32;
+  const int R = (int)(N < RMAX ? N : RMAX);
+  const int64_t stride = N / R;
+  float nrm = 0.f;
+  for (int d = threadIdx.x; d < Dp; d += blockDim.x) {
+    float m = 0.f;
+    if (d < D && metric != LIPVQ_METRIC_DOT) {
+      float v[RMAX];
+#pragma unroll
+      for (int i = 0; i < RMAX; ++i) v[i] = (i < R) ? __ldg(z + (int64_t)i * stride * D + d) : 0.f;
+      float s = 0.f;
+#pragma unroll
+      for (int i = 0; i < RMAX; ++i) s += v[i];
+      m = s / (float)R;
+    }
+    mu_s[d] = m;
+    nrm = fmaf(m, m, nrm);
+  }
+  if (blockIdx.x == 0) {
+    nrm = warp_sum(nrm);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = nrm;
+  }
+  __syncthreads();
+  if (blockIdx.x == 0) {
+    for (int d = threadIdx.x; d < Dp; d += blockDim.x) mu_g[d] = mu_s[d];
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+      for (int i = 0; i < 8; ++i) t += s_part[i];
+      hdr->mu_norm = sqrtf(t);
+    }
+  }
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per_lane = Dp / 32;  // 2 .. 16
+  for (int k = blockIdx.x * 8 + warp; k < Kp; k += gridDim.x * 8) {
+    float c[16];
+    float s = 0.f, amax = 0.f;
+    bool finite = true;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      c[i] = 0.f;
+      const int d = lane + 32 * i;
+      if (i < per_lane && k < K && d < D) {
+        const float v = __ldg(cb + (size_t)k * D + d) - mu_s[d];
+        c[i] = v;
+        s = fmaf(v, v, s);
+        amax = fmaxf(amax, fabsf(v));
+        finite = finite && (fabsf(v) <= 3.0e38f);  // false for inf and NaN
+      }
+    }
+    s = warp_sum(s);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
+    finite = __all_sync(0xffffffffu, finite);
+    const bool valid = k < K;
+    const bool excluded = valid && (!finite || amax >= kF16Safe);
+    if (lane == 0) {
+      if (valid && !excluded) {
+        enorm[k] = (metric == LIPVQ_METRIC_DOT) ? 0.f : s;
+        atomicMax(&hdr->emax2_bits, __float_as_uint(s));
+      } else {
+        enorm[k] = INFINITY;
+        if (excluded) {
+          const float inv = (finite && s < 3.0e38f) ? rsqrtf(s) * 1.0001f : 0.f;  // 1/||e-mu|| rounded up
+          atomicMax(&hdr->excl_inv_bits, __float_as_uint(inv));
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int d = lane + 32 * i;
+      if (i < per_lane) {
+        const float v = (valid && !excluded) ? -2.f * c[i] : 0.f;  // exact scaling
+        const __half h = __float2half_rn(v);
+        const __half l = __float2half_rn(v - __half2float(h));
+        ehi[(size_t)k * Dp + d] = h;
+        elo[(size_t)k * Dp + d] = l;
+      }
+    }
+  }
+}
+
+// ---- the fused kernel ---------------------------------------------------------------------------------------------
+// Warp roles (448 threads, one CTA per SM):
+//   0-7   epilogue: warp w owns TMEM lanes 32*(w&3).. (= rows) and the column half (w>>2) of every code tile
+//   8-11  converters: global fp32 z rows -> centred fp16 [hi|lo] -> swizzled A tiles (+ per-row ||z-mu||^2, ||z||^2)
+//   12    TMEM allocation + single-thread tcgen05.mma issue
+//   13    TMA producer for the code tiles
+struct RowBest {
+  float best, second;
+  int idx;
+};
+
+template <int TERMS>
+__global__ void __launch_bounds__(kThreads, 1)
+    search_fused_kernel(const __grid_constant__ CUtensorMap tm_ehi, const __grid_constant__ CUtensorMap tm_elo,
+                        const __grid_constant__ CUtensorMap tm_z, const FusedParams p) {
+  constexpr int TA = (TERMS == 1) ? 1 : 2;  // operand copies held in smem (hi, or hi + lo)
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int a_tile = kBM * kChunk * 2;              // 16 KB: [128 x 64] fp16
+  const int a_bytes = TA * p.NC * a_tile;           // one row block: [term][chunk]
+  const int b_tile = p.BN * kChunk * 2;             // [BN x 64] fp16
+  const int b_stage = TA * b_tile;                  // one (code tile, chunk): [term]
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + p.nbufA * a_bytes;
+  uint8_t* sZ = sB + p.stages * b_stage;                                            // [zstages][128][64] fp32
+  float2* rowstat = reinterpret_cast<float2*>(sZ + p.zstages * kZStage);            // [kStatSlots][128]
+  RowBest* xchg = reinterpret_cast<RowBest*>(rowstat + kStatSlots * kBM);           // [2][128]
+  float* mu_s = reinterpret_cast<float*>(xchg + 2 * kBM);                           // [512]
+  float* en_scr = mu_s + 512;                                                       // [8 epilogue warps][256]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(en_scr + kEpiWarps * 256);
+  const uint32_t bar_a_full = smem_u32(bars + 0), bar_a_empty = smem_u32(bars + 2);
+  const uint32_t bar_acc_full = smem_u32(bars + 4), bar_acc_empty = smem_u32(bars + 6);
+  const uint32_t bar_b_full = smem_u32(bars + 8), bar_b_empty = smem_u32(bars + 16);  // [<= 8] each
+  const uint32_t bar_z_full = smem_u32(bars + 24), bar_z_empty = smem_u32(bars + 28);  // [<= 4] each
+  const uint32_t bar_x_full = smem_u32(bars + 32), bar_x_empty = smem_u32(bars + 34);  // [2] each: partial hand-over
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 36);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t tmem_cols = 2u * (uint32_t)p.BN;  // 256 or 512
+
+  int64_t n_rows = p.N;
+  if (p.n_rows_ptr) {
+    const int64_t q = (int64_t)*p.n_rows_ptr;
+    n_rows = q < p.N ? q : p.N;
+  }
+  const int row_blocks = (int)((n_rows + kBM - 1) / kBM);
+  const int nblk = ((int)blockIdx.x < row_blocks) ? (row_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  const int total_tiles = nblk * p.T;
+  if (nblk == 0) return;  // uniform per CTA: nothing allocated yet (the usual case for most CTAs of the 3-term pass)
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_a_full + 8 * s, kCvtWarps);
+      mbar_init(bar_a_empty + 8 * s, 1);
+      mbar_init(bar_acc_full + 8 * s, 1);
+      mbar_init(bar_acc_empty + 8 * s, kEpiWarps / 2);
+      mbar_init(bar_x_full + 8 * s, kEpiWarps / 2);
+      mbar_init(bar_x_empty + 8 * s, kEpiWarps / 2);
+    }
+    for (int s = 0; s < 8; ++s) {
+      mbar_init(bar_b_full + 8 * s, 1);
+      mbar_init(bar_b_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < 4; ++s) {
+      mbar_init(bar_z_full + 8 * s, 1);
+      mbar_init(bar_z_empty + 8 * s, kCvtWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kWarpMma) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(tmem_cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == kWarpTma) {
+    // ===== TMA producer: code tiles =====
+    if (lane == 0 && nblk > 0) {
+      if (p.resident) {
+        for (int j = 0; j < p.T; ++j)
+          for (int c = 0; c < p.NC; ++c) {
+            const int st = j * p.NC + c;
+            mbar_expect_tx(bar_b_full + 8 * st, (uint32_t)b_stage);
+            const uint32_t dst = smem_u32(sB + st * b_stage);
+            tma_load_2d(dst, &tm_ehi, bar_b_full + 8 * st, c * kChunk, j * p.BN);
+            if (TERMS == 3) tma_load_2d(dst + b_tile, &tm_elo, bar_b_full + 8 * st, c * kChunk, j * p.BN);
+          }
+      } else {
+        uint32_t sidx = 0;
+        for (int i = 0; i < nblk; ++i)
+          for (int j = 0; j < p.T; ++j)
+            for (int c = 0; c < p.NC; ++c, ++sidx) {
+              const uint32_t st = sidx % (uint32_t)p.stages, par = (sidx / (uint32_t)p.stages) & 1;
+              mbar_wait(bar_b_empty + 8 * st, par ^ 1);
+              mbar_expect_tx(bar_b_full + 8 * st, (uint32_t)b_stage);
+              const uint32_t dst = smem_u32(sB + st * b_stage);
+              tma_load_2d(dst, &tm_ehi, bar_b_full + 8 * st, c * kChunk, j * p.BN);
+              if (TERMS == 3) tma_load_2d(dst + b_tile, &tm_elo, bar_b_full + 8 * st, c * kChunk, j * p.BN);
+            }
+      }
+    }
+  } else if (warp == kWarpMma) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc_f16(kBM, p.BN);
+      uint32_t sidx = 0, t = 0;
+      for (int i = 0; i < nblk; ++i) {
+        const int buf = i % p.nbufA;
+        mbar_wait(bar_a_full + 8 * buf, (uint32_t)(i / p.nbufA) & 1);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(sA + buf * a_bytes);
+        for (int j = 0; j < p.T; ++j, ++t) {
+          const uint32_t ab = t & 1;
+          mbar_wait(bar_acc_empty + 8 * ab, (t >> 1) & 1);  // epilogue drained it and stored this tile's ||e||^2
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + ab * (uint32_t)p.BN;
+          for (int c = 0; c < p.NC; ++c, ++sidx) {
+            uint32_t st, par;
+            if (p.resident) {
+              st = (uint32_t)(j * p.NC + c);
+              par = 0;
+            } else {
+              st = sidx % (uint32_t)p.stages;
+              par = (sidx / (uint32_t)p.stages) & 1;
+            }
+            mbar_wait(bar_b_full + 8 * st, par);
+            tc_fence_after();
+            const uint32_t a_hi = a_base + (uint32_t)(c * a_tile), a_lo = a_hi + (uint32_t)(p.NC * a_tile);
+            const uint32_t b_hi = smem_u32(sB + st * b_stage), b_lo = b_hi + (uint32_t)b_tile;
+#pragma unroll
+            for (int combo = 0; combo < TERMS; ++combo) {
+              const uint32_t aa = (combo == 2) ? a_lo : a_hi;
+              const uint32_t bb = (combo == 1) ? b_lo : b_hi;
+#pragma unroll
+              for (int k = 0; k < kChunk / 16; ++k)
+                umma_f16(d_tmem, umma_desc_sw128(aa + 32 * k), umma_desc_sw128(bb + 32 * k), idesc);
+            }
+            if (!p.resident) umma_commit(bar_b_empty + 8 * st);
+          }
+          umma_commit(bar_acc_full + 8 * ab);
+        }
+        umma_commit(bar_a_empty + 8 * buf);  // z block free once every MMA of this row block has retired
+      }
+    }
+  } else if (warp >= kEpiWarps) {
+    // ===== converters: fp32 z rows -> centred fp16 A tiles =====
+    const int tc = (int)threadIdx.x - kEpiWarps * 32;  // 0..127
+    const int ch = tc & 7, r0 = tc >> 3;               // 16-byte chunk within the 128-byte tile row; rows r0 + 16u
+    for (int d = tc; d < p.NC * kChunk; d += kCvtWarps * 32) mu_s[d] = __ldg(p.mu + d);
+    asm volatile("bar.sync 2, 128;" ::: "memory");
+    const bool fast = (p.D % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.z) & 15) == 0);
+    // staged mode (dense rows only): converter thread 0 also feeds the fp32 staging ring with 2-D tensor copies of
+    // [128 x 64] boxes (out-of-range rows / columns arrive as zeros); unit = (row block, chunk)
+    const int total_units = nblk * p.NC;
+    auto z_issue = [&](int unit) {
+      const int i2 = unit / p.NC, c2 = unit - i2 * p.NC;
+      const uint32_t st = (uint32_t)unit % (uint32_t)p.zstages;
+      const int64_t l0 = ((int64_t)blockIdx.x + (int64_t)i2 * gridDim.x) * kBM;
+      mbar_expect_tx(bar_z_full + 8 * st, (uint32_t)kZStage);
+      tma_load_2d(smem_u32(sZ + st * kZStage), &tm_z, bar_z_full + 8 * st, c2 * kChunk, (int)l0);
+    };
+    if (p.zstages > 0 && tc == 0)
+      for (int u = 0; u < p.zstages && u < total_units; ++u) z_issue(u);
+    for (int i = 0; i < nblk; ++i) {
+      const int buf = i % p.nbufA;
+      const int64_t rb = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+      int64_t grow[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int64_t lrow = rb * kBM + r0 + 16 * u;
+        grow[u] = -1;
+        if (lrow < n_rows) grow[u] = p.row_list ? (int64_t)__ldg(p.row_list + lrow) : lrow;
+      }
+      float zn2[8], zo2[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) zn2[u] = zo2[u] = 0.f;
+      mbar_wait(bar_a_empty + 8 * buf, ((uint32_t)(i / p.nbufA) & 1) ^ 1);
+      uint8_t* a_buf = sA + buf * a_bytes;
+      for (int c = 0; c < p.NC; ++c) {
+        const int col = c * kChunk + ch * 8;
+        float4 va[8], vb[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          va[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          vb[u] = va[u];
+        }
+        if (p.zstages > 0) {  // staged: the tile sits in shared memory as dense [128][64] fp32
+          const uint32_t unit = (uint32_t)(i * p.NC + c);
+          const uint32_t st = unit % (uint32_t)p.zstages, par = (unit / (uint32_t)p.zstages) & 1;
+          mbar_wait(bar_z_full + 8 * st, par);
+          const float* zt = reinterpret_cast<const float*>(sZ + st * kZStage) + ch * 8;
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            if (grow[u] >= 0 && col < p.D) {
+              const float4* src = reinterpret_cast<const float4*>(zt + (r0 + 16 * u) * kChunk);
+              va[u] = src[0];
+              if (col + 4 < p.D) vb[u] = src[1];  // D % 4 == 0 on this path: an item is 8 or 4 valid columns
+            }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_z_empty + 8 * st);
+          if (tc == 0 && (int)unit + p.zstages < total_units) {  // refill this slot once all four warps have read it
+            mbar_wait(bar_z_empty + 8 * st, par);
+            z_issue((int)unit + p.zstages);
+          }
+        } else if (fast) {  // D % 8 == 0, 16-byte aligned rows: sixteen independent 128-bit loads in flight per thread
+          if (col < p.D) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u)
+              if (grow[u] >= 0) {
+                const float4* src = reinterpret_cast<const float4*>(p.z + grow[u] * (int64_t)p.D + col);
+                va[u] = __ldg(src);
+                vb[u] = __ldg(src + 1);
+              }
+          }
+        } else {
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            if (grow[u] >= 0 && col < p.D) {
+              const float* src = p.z + grow[u] * (int64_t)p.D + col;
+              float t[8];
+#pragma unroll
+              for (int e = 0; e < 8; ++e) t[e] = (col + e < p.D) ? __ldg(src + e) : 0.f;
+              va[u] = make_float4(t[0], t[1], t[2], t[3]);
+              vb[u] = make_float4(t[4], t[5], t[6], t[7]);
+            }
+        }
+        const float4 m0 = *reinterpret_cast<const float4*>(mu_s + col);
+        const float4 m1 = *reinterpret_cast<const float4*>(mu_s + col + 4);
+        const float mu8[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+          const float x[8] = {va[u].x, va[u].y, va[u].z, va[u].w, vb[u].x, vb[u].y, vb[u].z, vb[u].w};
+          uint32_t hh[4], ll[4];  // packed fp16 pairs, kept in registers
+          float amax = 0.f;
+#pragma unroll
+          for (int e = 0; e < 8; e += 2) {
+            const float za = x[e] - mu8[e], zb = x[e + 1] - mu8[e + 1];  // padded columns: 0 - 0
+            zo2[u] = fmaf(x[e], x[e], zo2[u]);
+            zo2[u] = fmaf(x[e + 1], x[e + 1], zo2[u]);
+            zn2[u] = fmaf(za, za, zn2[u]);
+            zn2[u] = fmaf(zb, zb, zn2[u]);
+            amax = fmaxf(amax, fmaxf(fabsf(za), fabsf(zb)));
+            const __half2 hp = __floats2half2_rn(za, zb);
+            hh[e >> 1] = *reinterpret_cast<const uint32_t*>(&hp);
+            if (TERMS == 3) {
+              const float2 back = __half22float2(hp);
+              const __half2 lp = __floats2half2_rn(za - back.x, zb - back.y);
+              ll[e >> 1] = *reinterpret_cast<const uint32_t*>(&lp);
+            }
+          }
+          if (!(amax < 6.0e4f)) zn2[u] = INFINITY;  // does not fit fp16 (or NaN): the row takes the exact path
+          const int r = r0 + 16 * u;
+          const uint32_t off = (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
+          *reinterpret_cast<uint4*>(a_buf + c * a_tile + off) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+          if (TERMS == 3)
+            *reinterpret_cast<uint4*>(a_buf + (p.NC + c) * a_tile + off) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+        }
+      }
+      float2* stat = rowstat + (i % kStatSlots) * kBM;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+#pragma unroll
+        for (int o = 1; o < 8; o <<= 1) {
+          zn2[u] += __shfl_xor_sync(0xffffffffu, zn2[u], o);
+          zo2[u] += __shfl_xor_sync(0xffffffffu, zo2[u], o);
+        }
+        if (ch == 0) stat[r0 + 16 * u] = make_float2(zn2[u], zo2[u]);
+      }
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to the MMA
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_a_full + 8 * buf);
+    }
+  } else {
+    // ===== epilogue warps 0-7: two groups of four; group g owns accumulator buffer g and drains every second tile =====
+    // The groups run half a tile out of phase, so one folds scores while the other waits for its accumulator, loads
+    // TMEM or refills the buffer with the next ||e||^2 -- the fold is issue-bound and this keeps the schedulers fed.
+    // TMEM lane = row; a warp walks all BN columns of its tiles.  For each row block the group that drains the block's
+    // last tile merges the other group's partial top-2 (handed over through shared memory) and certifies the row.
+    const int q = warp & 3, g = warp >> 2;
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+    const float emax2 = __uint_as_float(p.hdr->emax2_bits);
+    const float excl_inv = __uint_as_float(p.hdr->excl_inv_bits);
+    const float mu_norm = p.hdr->mu_norm;
+    const uint32_t scr = smem_u32(en_scr + warp * 256);
+    const uint32_t tbuf = tmem_base + (uint32_t)g * (uint32_t)p.BN + lane_off;
+
+    // ||e||^2 of code tile j: coalesced float4 loads (BN <= 256 values = two per lane), issued early so the latency hides
+    // behind the tile being drained ...
+    auto en_prefetch = [&](int j, float4& r0, float4& r1) {
+      const float4* src = reinterpret_cast<const float4*>(p.enorm + (size_t)j * p.BN);
+      r0 = __ldg(src + lane);
+      r1 = (p.BN > 128) ? __ldg(src + 32 + lane) : make_float4(0.f, 0.f, 0.f, 0.f);
+    };
+    // ... broadcast through this warp's scratch row and stored into the accumulator buffer for all 32 lanes (rows);
+    // then the buffer is released to the MMA warp
+    auto en_store = [&](const float4& r0, const float4& r1) {
+      __syncwarp();
+      sts128(scr + 16 * lane, r0);
+      if (p.BN > 128) sts128(scr + 512 + 16 * lane, r1);
+      __syncwarp();
+      for (int cc = 0; cc < p.BN; cc += 16) {
+        uint32_t v[16];
+#pragma unroll
+        for (int e = 0; e < 16; e += 4) lds128(scr + 4 * (cc + e), v[e], v[e + 1], v[e + 2], v[e + 3]);  // broadcast reads
+        tmem_st16(tbuf + cc, v);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_acc_empty + 8 * g);
+    };
+    if (g < total_tiles) {
+      float4 e0, e1;
+      en_prefetch(g % p.T, e0, e1);
+      en_store(e0, e1);
+    }
+
+    // four independent chains (columns mod 4) so consecutive updates do not wait on each other
+    float cb_[4], cs_[4], ci_[4];  // per chain: best, second, column (as float) within the chunk that set best
+    int cbase[4];                  // ... and the first code of that chunk
+    auto reset = [&]() {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        cb_[u] = INFINITY;
+        cs_[u] = INFINITY;
+        ci_[u] = 0.f;
+        cbase[u] = 0;
+      }
+    };
+    reset();
+    for (int t = g; t < total_tiles; t += 2) {
+      const int i = t / p.T, j = t - i * p.T;
+      const bool more = t + 2 < total_tiles;
+      float4 en0 = make_float4(0.f, 0.f, 0.f, 0.f), en1 = en0;
+      if (more) en_prefetch((t + 2) % p.T, en0, en1);
+      float2 st = make_float2(0.f, 0.f);
+      mbar_wait(bar_acc_full + 8 * g, (uint32_t)(t >> 1) & 1);
+      tc_fence_after();
+      auto fold = [&](const uint32_t (&v)[32], int kb) {
+        float prev[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) prev[u] = cb_[u];
+#pragma unroll
+        for (int e = 0; e < 32; e += 4)
+#pragma unroll
+          for (int u = 0; u < 4; ++u)
+            top2_update(cb_[u], cs_[u], ci_[u], __uint_as_float(v[e + u]), (float)(e + u), p.neg_zero, p.pos_zero);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) cbase[u] = cb_[u] < prev[u] ? kb : cbase[u];
+      };
+      const int kb0 = j * p.BN;
+      for (int c0 = 0; c0 < p.BN; c0 += 32) {
+        uint32_t v[32];
+        tmem_ld32(tbuf + c0, v);
+        tmem_ld_wait(v);
+        if (c0 + 32 >= p.BN) {
+          // last load of this buffer has landed: hand it back to the MMA warp before folding the chunk.
+          // (the converter may recycle the stat slot only after MMAs that need this release: read it first)
+          if (j == p.T - 1) st = rowstat[(i % kStatSlots) * kBM + q * 32 + lane];
+          if (more) en_store(en0, en1);
+        }
+        fold(v, kb0 + c0);
+      }
+      const bool last_of_block = (j == p.T - 1);
+      const bool leaves_block = last_of_block || (j + 2 >= p.T);  // this group's next tile belongs to another row block
+      if (!leaves_block) continue;
+
+      float best = cb_[0], second = cs_[0];
+      int bidx = cbase[0] + __float2int_rn(ci_[0]);
+#pragma unroll
+      for (int u = 1; u < 4; ++u) {
+        const bool take = cb_[u] < best;
+        second = fminf(fminf(second, cs_[u]), take ? best : cb_[u]);
+        bidx = take ? cbase[u] + __float2int_rn(ci_[u]) : bidx;
+        best = take ? cb_[u] : best;
+      }
+      reset();
+      RowBest* xs = xchg + (i & 1) * kBM + q * 32 + lane;
+      const uint32_t xpar = (uint32_t)(i >> 1) & 1;
+      if (!last_of_block) {
+        // hand this group's partial result for the block to the group that drains its last tile
+        mbar_wait(bar_x_empty + 8 * (i & 1), xpar ^ 1);
+        xs->best = best;
+        xs->second = second;
+        xs->idx = bidx;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_x_full + 8 * (i & 1));
+        continue;
+      }
+      if (p.T > 1) {
+        mbar_wait(bar_x_full + 8 * (i & 1), xpar);
+        const float ob = xs->best, os = xs->second;
+        const int oi = xs->idx;
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_x_empty + 8 * (i & 1));
+        const bool take = ob < best;
+        const float loser = take ? best : ob;
+        second = fminf(fminf(second, os), loser);
+        bidx = take ? oi : bidx;
+        best = take ? ob : best;
+      }
+      const int64_t rb = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+      const int64_t lrow = rb * kBM + q * 32 + lane;
+      if (lrow < n_rows) {
+        const int64_t row = p.row_list ? (int64_t)p.row_list[lrow] : lrow;
+        const float zn2 = st.x, zo2 = st.y;
+        const float zn = sqrtf(zn2);
+        const float dhat = sqrtf(fmaxf(best + zn2, 0.f));  // ~ distance to the candidate
+        float emax = sqrtf(emax2);
+        // only codes that can still beat the candidate matter: ||e-mu|| <= ||z-mu|| + d_best (triangle inequality)
+        if (p.metric != LIPVQ_METRIC_DOT) emax = fminf(emax, zn + 1.02f * dhat + 1e-30f);
+        // fp16 subnormal spacing: absolute 2^-25 per element on either operand
+        const float sub = 2.9802322e-8f * sqrtf((float)(p.NC * kChunk)) * (zn + 2.f * emax);
+        const float margin_alg = 2.f * (p.gamma_en * emax * emax + p.gamma_dot * 2.f * zn * emax + sub);
+        const float ref_mag = (p.metric == LIPVQ_METRIC_DOT) ? 2.f * zn * emax : fmaxf(best + zn2, 0.f);
+        const float delta = 5.9604645e-8f * (sqrtf(zo2) + emax + 3.f * mu_norm);
+        const float margin_c = (p.metric == LIPVQ_METRIC_DOT) ? 0.f : 2.f * (2.f * dhat * delta + delta * delta);
+        const float margin = fmaxf(margin_alg + margin_c, p.gamma_ref * ref_mag);
+        // excluded (non-fp16-representable) codes: ||e-mu|| >= 1/excl_inv must exceed ||z-mu|| + d_best
+        bool ok = second - best > margin;
+        if (excl_inv > 0.f) ok = ok && (p.metric != LIPVQ_METRIC_DOT) && ((zn + 1.02f * dhat) * excl_inv < 0.999f);
+        if (ok) {
+          p.idx_out[row] = (int64_t)bidx;
+        } else {
+          const int pos = atomicAdd(p.queue_count, 1);
+          p.queue_out[pos] = (int)row;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == kWarpMma) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
+  }
+}
+
+// exact winning value for the optional best_out: one warp per row
+__global__ void __launch_bounds__(256)
+    best_value_kernel(const float* __restrict__ z, int64_t N, int D, const float* __restrict__ cb, int metric,
+                      const int64_t* __restrict__ idx, float* __restrict__ best_out) {
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (row >= N) return;
+  const float* zr = z + row * (int64_t)D;
+  const float* er = cb + idx[row] * (int64_t)D;
+  float ex = 0.f;
+  for (int d = lane; d < D; d += 32) {
+    const float zv = __ldg(zr + d), ev = __ldg(er + d);
+    if (metric == LIPVQ_METRIC_DOT) {
+      ex = fmaf(zv, ev, ex);
+    } else {
+      const float df = zv - ev;
+      ex = fmaf(df, df, ex);
+    }
+  }
+  ex = warp_sum(ex);
+  if (lane == 0) best_out[row] = (metric == LIPVQ_METRIC_L2) ? sqrtf(ex) : ex;
+}
+
+// ---- host side ------------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* ptr = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  return fn;
+}
+
+// [rows][Dp] fp16 row-major, box = [64 elements x box_rows], 128-byte swizzle
+int make_map(CUtensorMap* tm, void* base, int64_t rows, int Dp, int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable");
+    return LIPVQ_ERR_CUDA;
+  }
+  const cuuint64_t gdim[2] = {(cuuint64_t)Dp, (cuuint64_t)rows};
+  const cuuint64_t gstride[1] = {(cuuint64_t)Dp * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)kChunk, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, base, gdim, gstride, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with %d (rows=%lld Dp=%d box_rows=%d)", (int)r, (long long)rows, Dp, box_rows);
+    return LIPVQ_ERR_CUDA;
+  }
+  return LIPVQ_OK;
+}
+
+// fp32 z [N][D] row-major, box = [64 columns x 128 rows], no swizzle: lands as the dense staging tile
+int make_z_map(CUtensorMap* tm, const float* z, int64_t N, int D) {
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) {
+    set_error("cuTensorMapEncodeTiled entry point unavailable");
+    return LIPVQ_ERR_CUDA;
+  }
+  const cuuint64_t gdim[2] = {(cuuint64_t)D, (cuuint64_t)N};
+  const cuuint64_t gstride[1] = {(cuuint64_t)D * 4};
+  const cuuint32_t box[2] = {(cuuint32_t)kChunk, (cuuint32_t)kBM};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(z), gdim, gstride, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled(z) failed with %d (N=%lld D=%d)", (int)r, (long long)N, D);
+    return LIPVQ_ERR_CUDA;
+  }
+  return LIPVQ_OK;
+}
+
+constexpr int kMiscBytes = kStatSlots * kBM * 8 + 2 * kBM * 12 + 512 * 4 + kEpiWarps * 256 * 4 + 320;  // rowstat, xchg, mu, barriers
+constexpr int kSmemBudget = 227 * 1024 - 1024 /*alignment*/ - kMiscBytes;
+
+struct FusedGeom {
+  int Dp, NC, Kp, BN, T, stages, resident, nbufA, zstages;
+  size_t smem;
+  bool ok;
+};
+
+// terms = 1 or 3.  Kp is fixed by the caller (multiple of 256, or 128 for tiny codebooks) so both passes share one
+// prepared codebook.  staged = z rows can be bulk-copied (D % 4 == 0, 16-byte aligned base).
+// Shared memory is split between A buffers (one or two row blocks of fp16 z), the code-tile ring (resident when the
+// whole codebook fits) and the fp32 z staging ring; options are tried in order of preference.
+FusedGeom fused_geom(int D, int Kp, int terms, bool staged) {
+  FusedGeom g{};
+  g.Dp = (D + kChunk - 1) / kChunk * kChunk;
+  g.NC = g.Dp / kChunk;
+  g.Kp = Kp;
+  const int TA = terms == 1 ? 1 : 2;
+  const int a_bytes = TA * g.NC * kBM * kChunk * 2;
+  g.ok = false;
+  static const int opts[6][2] = {{2, 3}, {2, 2}, {1, 2}, {2, 1}, {1, 1}, {1, 0}};  // (A buffers, z stages)
+  for (int bn = (Kp % 256 == 0) ? 256 : 128; bn >= 128 && !g.ok; bn -= 128) {
+    const int b_stage = TA * bn * kChunk * 2;
+    const int tiles = (Kp / bn) * g.NC;  // (code tile, chunk) pairs per row block
+    for (int o = 0; o < 6 && !g.ok; ++o) {
+      const int nbuf = opts[o][0];
+      const int zs = staged ? opts[o][1] : 0;
+      if (staged && zs == 0) continue;
+      if (!staged && o != 0 && o != 4) continue;  // direct loads: only the A-buffer count matters
+      const int rem = kSmemBudget - nbuf * a_bytes - zs * kZStage;
+      if (rem < b_stage) continue;
+      int st = rem / b_stage;
+      if (st > 8) st = 8;
+      const int need = tiles < 3 ? tiles : (o < 4 ? 3 : 2);
+      if (st < need) continue;
+      g.BN = bn;
+      g.T = Kp / bn;
+      g.resident = tiles <= st ? 1 : 0;
+      g.stages = g.resident ? tiles : st;
+      g.nbufA = nbuf;
+      g.zstages = zs;
+      g.smem = 1024 + (size_t)nbuf * a_bytes + (size_t)g.stages * b_stage + (size_t)zs * kZStage + kMiscBytes;
+      g.ok = true;
+    }
+  }
+  return g;
+}
+
+inline int fused_kp(int K) { return K <= 128 ? 128 : (K + 255) / 256 * 256; }
+
+}  // namespace
+
+bool search_fused_supported(int64_t N, int D, int K) {
+  if (N < 1 || K < 1 || D < 1 || D > 512) return false;
+  return fused_geom(D, fused_kp(K), 1, false).ok;
+}
+
+void search_fused_plan(int D, int K, int* Kp, int* Dp) {
+  *Kp = fused_kp(K);
+  *Dp = (D + kChunk - 1) / kChunk * kChunk;
+}
+
+// prep -> pass 1 (fp16, all rows) -> pass 2 (3-term fp16 split, rows pass 1 queued) ; leaves the rows that still need
+// the exact scan in *final_queue / *final_count (device pointers inside the workspace).
+int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, const SearchPlan& plan,
+                        char* ws, int64_t* idx_out, cudaStream_t stream, const int** final_queue,
+                        const int** final_count) {
+  const int Kp = fused_kp(K);
+  const bool staged = (D % 4 == 0) && aligned16(z);
+  FusedGeom g1 = fused_geom(D, Kp, 1, staged);
+  FusedGeom g3 = fused_geom(D, Kp, 3, false);  // gathered rows: the converters load them from global
+  if (!g1.ok) g1 = fused_geom(D, Kp, 1, false);  // no room for the staging ring: converters load from global
+  if (!g1.ok || plan.Kp != Kp || plan.Dp != g1.Dp) {
+    set_error("search_fused: plan/geometry mismatch");
+    return LIPVQ_ERR_INVALID;
+  }
+  SearchHdr* hdr = (SearchHdr*)(ws + plan.off_hdr);
+  float* mu = (float*)(ws + plan.off_mu);
+  float* enorm = (float*)(ws + plan.off_enorm);
+  __half* ehi = (__half*)(ws + plan.off_ehi);
+  __half* elo = (__half*)(ws + plan.off_elo);
+  int* work = (int*)(ws + plan.off_work);
+  int* work2 = (int*)(ws + plan.off_work2);
+  const int sms = sm_count();
+
+  {
+    int blocks = (Kp + 7) / 8;
+    if (blocks > sms) blocks = sms;
+    fused_prep_kernel<<<blocks, 256, 0, stream>>>(z, N, D, cb, K, Kp, g1.Dp, metric, mu, enorm, ehi, elo, hdr);
+    LIPVQ_LAUNCHED("fused_prep_kernel");
+  }
+
+  static size_t smem_set1 = 0, smem_set3 = 0;
+  const int row_blocks = (int)ceil_div64(N, kBM);
+  const float u22 = 2.3841858e-7f;  // 2^-22: bound used per accumulation step of the tensor core (truncating adder)
+  const float gamma_ref = 4.f * (float)(D + 4) * 5.9604645e-8f;
+
+  FusedParams p{};
+  p.z = z; p.N = N; p.D = D; p.K = K; p.metric = metric;
+  p.mu = mu; p.enorm = enorm; p.hdr = hdr; p.idx_out = idx_out;
+  p.gamma_ref = gamma_ref;
+  p.neg_zero = -0.0f;
+  p.pos_zero = 0.0f;
+  int rc;
+  CUtensorMap tm_z;
+  if (staged) {
+    if ((rc = make_z_map(&tm_z, z, N, D)) != LIPVQ_OK) return rc;
+  } else {
+    memset(&tm_z, 0, sizeof(tm_z));
+  }
+  {
+    CUtensorMap tm_hi, tm_lo;
+    if ((rc = make_map(&tm_hi, ehi, Kp, g1.Dp, g1.BN)) != LIPVQ_OK) return rc;
+    if ((rc = make_map(&tm_lo, elo, Kp, g1.Dp, g1.BN)) != LIPVQ_OK) return rc;
+    p.NC = g1.NC; p.BN = g1.BN; p.T = g1.T; p.stages = g1.stages; p.resident = g1.resident; p.nbufA = g1.nbufA; p.zstages = g1.zstages;
+    p.row_list = nullptr; p.n_rows_ptr = nullptr;
+    p.queue_out = work; p.queue_count = &hdr->flagged;
+    const float steps = (float)(g1.Dp / 16);
+    p.gamma_en = (float)(D + 4) * 5.9604645e-8f + (steps + 1.f) * u22;
+    p.gamma_dot = 9.7751617e-4f /* 2^-10 (1 + 2^-10) */ + (steps + 1.f) * u22;
+    if (g1.smem > smem_set1) {
+      LIPVQ_CUDA(cudaFuncSetAttribute(search_fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g1.smem));
+      smem_set1 = g1.smem;
+    }
+    const int grid = row_blocks < sms ? row_blocks : sms;
+    search_fused_kernel<1><<<grid, kThreads, g1.smem, stream>>>(tm_hi, tm_lo, tm_z, p);
+    LIPVQ_LAUNCHED("search_fused_kernel<1>");
+  }
+  *final_queue = work;
+  *final_count = &hdr->flagged;
+  if (g3.ok) {
+    CUtensorMap tm_hi, tm_lo;
+    if ((rc = make_map(&tm_hi, ehi, Kp, g3.Dp, g3.BN)) != LIPVQ_OK) return rc;
+    if ((rc = make_map(&tm_lo, elo, Kp, g3.Dp, g3.BN)) != LIPVQ_OK) return rc;
+    p.NC = g3.NC; p.BN = g3.BN; p.T = g3.T; p.stages = g3.stages; p.resident = g3.resident; p.nbufA = g3.nbufA; p.zstages = g3.zstages;
+    p.row_list = work; p.n_rows_ptr = &hdr->flagged;
+    p.queue_out = work2; p.queue_count = &hdr->flagged2;
+    const float steps = (float)(3 * g3.Dp / 16);
+    p.gamma_en = (float)(D + 4) * 5.9604645e-8f + (steps + 1.f) * u22;
+    p.gamma_dot = 4.f * u22 + (steps + 1.f) * u22;
+    if (g3.smem > smem_set3) {
+      LIPVQ_CUDA(cudaFuncSetAttribute(search_fused_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g3.smem));
+      smem_set3 = g3.smem;
+    }
+    // the queue length is only known on the device: size the grid for a modest queue, CTAs stride over the blocks
+    int grid = row_blocks < sms ? row_blocks : sms;
+    search_fused_kernel<3><<<grid, kThreads, g3.smem, stream>>>(tm_hi, tm_lo, tm_z, p);
+    LIPVQ_LAUNCHED("search_fused_kernel<3>");
+    *final_queue = work2;
+    *final_count = &hdr->flagged2;
+  }
+  return LIPVQ_OK;
+}
+
+int search_best_values(const float* z, int64_t N, int D, const float* cb, int metric, const int64_t* idx, float* best_out,
+                       cudaStream_t stream) {
+  best_value_kernel<<<(unsigned)ceil_div64(N * 32, 256), 256, 0, stream>>>(z, N, D, cb, metric, idx, best_out);
+  LIPVQ_LAUNCHED("best_value_kernel");
+  return LIPVQ_OK;
+}
+
+}  // namespace lipvq
