@@ -247,14 +247,23 @@ def run_ours(args):
         rescored = int(st[0].item())
         flops = 2.0 * N_TOK * K * D
         bytes_alg = N_TOK * (4 * D + 8) + K * D * 4
-        extra["roofline"] = {"bound": "tensor", "kernel": "nn_search (code_sqnorm+contraction+finalize+rescore), algo="
-                             + {1: "simt_f32", 2: "tcgen05"}[algo], "achieved": flops / (sd * 1e-3) / 1e12, "peak": tf_burst,
-                             "unit": "TFLOP/s", "frac": flops / (sd * 1e-3) / 1e12 / tf_burst, "traffic": None,
+        # DRAM bytes of the dominant launch (search_fused_kernel<1>) from the committed ncu --set full capture
+        traffic = None
+        try:
+            with open(os.path.join(ROOT, "profiles", "search_traffic.json")) as f:
+                traffic = json.load(f).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+        extra["roofline"] = {"bound": "tensor", "kernel": "lipvq_nn_search_f32 = fused_prep + search_fused<1> (fp16 tcgen05 pass, "
+                             "argmin + certification in the TMEM epilogue) + search_fused<3> (3-term pass over uncertified "
+                             "rows) + exact scan; algo=" + {1: "simt_f32", 2: "tcgen05"}[algo],
+                             "achieved": flops / (sd * 1e-3) / 1e12, "peak": tf_burst,
+                             "unit": "TFLOP/s", "frac": flops / (sd * 1e-3) / 1e12 / tf_burst, "traffic": traffic,
                              "peak_source": src + " (bf16 dense burst)", "us_per_launch": sd * 1e3,
                              "algorithmic_flops": flops, "algorithmic_bytes": bytes_alg,
                              "hbm_frac": bytes_alg / (sd * 1e-3) / 1e9 / hbm,
                              "share_of_step": sd / (ms / args.steps),
-                             "rows_rescored_exactly": rescored}
+                             "rows_rescored_exactly": rescored, "rows_uncertified_by_fp16_pass": int(st[1].item())}
         # --- bulk tokenisation (encode + VQ only), the headline metric's other reading ---
         for i in range(3):
             tr.tokenize(xs_dev[i % n_in])
@@ -285,7 +294,12 @@ def run_ours(args):
         line.update(extra)
         print(json.dumps(line), flush=True)
     if world > 1:
-        dist.destroy_process_group()
+        # Tear down without NCCL's own destructor: a communicator whose kernels were captured into a live CUDA graph
+        # can block in destroy_process_group; the line is printed, every rank is idle, so leave directly.
+        sys.stdout.flush()
+        torch.cuda.synchronize()
+        dist.barrier()
+        os._exit(0)
 
 
 def main():

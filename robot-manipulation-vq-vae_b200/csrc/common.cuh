@@ -13,6 +13,13 @@ int cuda_fail(cudaError_t e, const char* what);
 void count_launch(int n = 1);
 int sm_count();
 
+// tcgen05 linear layers (linear_tc.cu): mode 0 = forward (bias + act_out), mode 1 = backward-x (* act_in'(Xpre)).
+// B[n][k] = W[n * w_rs + k * w_cs].
+bool linear_tc_supported(int mode, int64_t N, int Ka, int Nb);
+int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, int actA, const float* W, int64_t w_rs,
+                     int64_t w_cs, int Nb, float* C, int64_t ldc, const float* bias, int act_out, const float* Xpre,
+                     int64_t ldx, int act_in, cudaStream_t stream);
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 

@@ -335,6 +335,9 @@ int lipvq_linear_fwd_f32(const float* X, int64_t N, int in_dim, int act_in, cons
   LIPVQ_REQUIRE(N >= 0 && in_dim > 0 && out_dim > 0, "linear_fwd: bad shape");
   if (N == 0) return LIPVQ_OK;
   LIPVQ_REQUIRE(X && W && Y, "linear_fwd: null pointer");
+  if (linear_tc_supported(0, N, in_dim, out_dim))
+    return linear_tc_launch(0, X, N, in_dim, in_dim, act_in, W, in_dim, 1, out_dim, Y, out_dim, bias, act_out, nullptr, 0,
+                            LIPVQ_ACT_NONE, stream);
   GemmArgs g{};
   g.A = X; g.lda = in_dim; g.actA = act_in; g.vecA = (in_dim % 4 == 0) && aligned16(X);
   g.B = W; g.ldb = in_dim; g.actB = LIPVQ_ACT_NONE; g.vecB = (in_dim % 4 == 0) && aligned16(W);
@@ -350,6 +353,9 @@ int lipvq_linear_bwd_x_f32(const float* dY, int64_t N, int out_dim, const float*
   LIPVQ_REQUIRE(N >= 0 && in_dim > 0 && out_dim > 0, "linear_bwd_x: bad shape");
   if (N == 0) return LIPVQ_OK;
   LIPVQ_REQUIRE(dY && W && dX && (X || act_in == LIPVQ_ACT_NONE), "linear_bwd_x: null pointer");
+  if (linear_tc_supported(1, N, out_dim, in_dim))
+    return linear_tc_launch(1, dY, N, out_dim, out_dim, LIPVQ_ACT_NONE, W, 1, in_dim, in_dim, dX, in_dim, nullptr,
+                            LIPVQ_ACT_NONE, X, in_dim, act_in, stream);
   GemmArgs g{};
   g.A = dY; g.lda = out_dim; g.actA = LIPVQ_ACT_NONE; g.vecA = (out_dim % 4 == 0) && aligned16(dY);
   g.B = W; g.ldb = in_dim; g.actB = LIPVQ_ACT_NONE; g.vecB = (in_dim % 4 == 0) && aligned16(W);

@@ -1,0 +1,373 @@
+// K1/K2/K7 on the tensor cores: token-major linear layers  C[N, Nb] = epi( act(A)[N, Ka] . B[Nb, Ka]^T )  with fp32
+// accuracy.  Both operands are split into THREE bf16 terms (x = h + m + l captures all 24 mantissa bits) and six
+// tcgen05.mma chains  hh + hm + mh + hl + lh + mm  accumulate in fp32 in TMEM (dropped terms <= 3*2^-24 |a||b|), so the
+// result is as accurate as an fp32 FFMA GEMM while the kernel runs at the HBM rate of its activations.
+//
+//   forward    Y  = act_out(act_in(X) W^T + b)     A = X  [N, in],  B[n][k] = W[n][k]
+//   backward   dX = (dY W) * act_in'(Xpre)         A = dY [N, out], B[n][k] = W[k][n]
+//
+// One persistent CTA per SM (800 threads; both software roles are dependent-instruction chains, so they get many warps):
+//   warps 0-7   epilogue: tcgen05.ld (TMEM lane = token row) -> bias/activation or activation gradient -> global
+//   warps 8-23  converters: fp32 rows -> activation -> bf16 (h, m, l) -> 128B-swizzled K-major A tiles
+//   warp  24    TMEM allocation + single-thread tcgen05.mma issue
+// The weight matrix (<= 256 x 128) is split and laid out in shared memory once per CTA by all threads: no workspace,
+// no second launch.  Accumulators ping-pong between two TMEM buffers; A tiles are double-buffered when they fit.
+//
+// Reference ops replaced: nn.Linear + GELU/ReLU/sigmoid chains and their autograd (backbone_lfqvae_v5.py:54-68,71-76;
+// backbone.py:17-32).  The fp32 FFMA tiles of linear.cu remain the path for shapes outside this kernel's range.
+#include <cuda_bf16.h>
+#include <stdlib.h>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace lipvq {
+namespace {
+
+using namespace tc;
+
+constexpr int kBM = 128, kChunk = 64;
+constexpr int kATile = kBM * kChunk * 2;  // 16 KB
+constexpr int kEpiWarps = 8, kCvtWarps = 16;  // plenty of warps per scheduler: both roles are latency-bound chains
+constexpr int kWarpMma = kEpiWarps + kCvtWarps;
+constexpr int kThreads = 32 * (kWarpMma + 1);  // 800 -> 80 registers per thread
+constexpr int kCvtItems = (kBM * 8) / (kCvtWarps * 32);  // 16-byte items per converter thread and chunk (2)
+
+struct LinTcParams {
+  const float* A; int64_t N; int Ka; int64_t lda; int actA;
+  const float* W; int64_t w_rs, w_cs;  // B[n][k] = W[n * w_rs + k * w_cs]
+  int Nb;
+  float* C; int64_t ldc;
+  const float* bias; int act_out;            // mode 0
+  const float* Xpre; int64_t ldx; int act_in;  // mode 1
+  int mode, NC, Nbp, nbufA;
+  uint32_t tmem_cols;
+};
+
+__device__ __forceinline__ void split3(float x, __nv_bfloat16& h, __nv_bfloat16& m, __nv_bfloat16& l) {
+  h = __float2bfloat16_rn(x);
+  const float r1 = x - __bfloat162float(h);  // exact
+  m = __float2bfloat16_rn(r1);
+  const float r2 = r1 - __bfloat162float(m);  // exact
+  l = __float2bfloat16_rn(r2);
+}
+// Run body(tag) with the activation as a compile-time constant: the element loops then contain straight-line code
+// instead of a switch per element (branch latency is not hidden with this few warps per scheduler).
+template <int ACT>
+struct ActTag { static constexpr int value = ACT; };
+template <typename F>
+__device__ __forceinline__ void dispatch_act(int act, F&& body) {
+  switch (act) {
+    case LIPVQ_ACT_RELU: body(ActTag<LIPVQ_ACT_RELU>{}); break;
+    case LIPVQ_ACT_GELU: body(ActTag<LIPVQ_ACT_GELU>{}); break;
+    case LIPVQ_ACT_SIGMOID: body(ActTag<LIPVQ_ACT_SIGMOID>{}); break;
+    default: body(ActTag<LIPVQ_ACT_NONE>{}); break;
+  }
+}
+
+__device__ __forceinline__ uint32_t pack2(__nv_bfloat16 a, __nv_bfloat16 b) {
+  return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
+}
+
+__global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int a_bytes = 3 * p.NC * kATile;          // [term][chunk]
+  const int b_tile = p.Nbp * kChunk * 2;          // [Nbp x 64] bf16
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + p.nbufA * a_bytes;           // [term][chunk]
+  float* bias_s = reinterpret_cast<float*>(sB + 3 * p.NC * b_tile);  // [256]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + 256);
+  const uint32_t bar_a_full = smem_u32(bars + 0), bar_a_empty = smem_u32(bars + 2);
+  const uint32_t bar_acc_full = smem_u32(bars + 4), bar_acc_empty = smem_u32(bars + 6);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row_blocks = (int)((p.N + kBM - 1) / kBM);
+  const int nblk = ((int)blockIdx.x < row_blocks) ? (row_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  if (nblk == 0) return;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_a_full + 8 * s, kCvtWarps);
+      mbar_init(bar_a_empty + 8 * s, 1);
+      mbar_init(bar_acc_full + 8 * s, 1);
+      mbar_init(bar_acc_empty + 8 * s, kEpiWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
+
+  // ---- weights: split into (h, m, l) and store as swizzled K-major tiles; bias to smem ----
+  {
+    const int Kp = p.NC * kChunk;
+    const int total = p.Nbp * Kp;
+    const bool n_fast = (p.w_rs == 1);  // consecutive threads follow the contiguous direction of W
+    for (int idx = threadIdx.x; idx < total; idx += kThreads) {
+      int n, k;
+      if (n_fast) {
+        n = idx % p.Nbp;
+        k = idx / p.Nbp;
+      } else {
+        k = idx % Kp;
+        n = idx / Kp;
+      }
+      const float v = (n < p.Nb && k < p.Ka) ? __ldg(p.W + (int64_t)n * p.w_rs + (int64_t)k * p.w_cs) : 0.f;
+      __nv_bfloat16 h, m, l;
+      split3(v, h, m, l);
+      const int c = k >> 6, kk = k & 63;
+      const uint32_t off = (uint32_t)(n * 128 + ((((kk >> 3) ^ (n & 7))) << 4) + (kk & 7) * 2);
+      uint8_t* t0 = sB + c * b_tile + off;
+      *reinterpret_cast<__nv_bfloat16*>(t0) = h;
+      *reinterpret_cast<__nv_bfloat16*>(t0 + p.NC * b_tile) = m;
+      *reinterpret_cast<__nv_bfloat16*>(t0 + 2 * p.NC * b_tile) = l;
+    }
+    for (int i = threadIdx.x; i < 256; i += kThreads)
+      bias_s[i] = (p.mode == 0 && p.bias != nullptr && i < p.Nb) ? __ldg(p.bias + i) : 0.f;
+    fence_async_smem();
+  }
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == kWarpMma) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16(kBM, p.Nbp);
+      const uint32_t b_base = smem_u32(sB);
+      for (int i = 0; i < nblk; ++i) {
+        const int buf = i % p.nbufA;
+        const uint32_t ab = (uint32_t)i & 1;
+        mbar_wait(bar_a_full + 8 * buf, (uint32_t)(i / p.nbufA) & 1);
+        mbar_wait(bar_acc_empty + 8 * ab, (((uint32_t)i >> 1) & 1) ^ 1);
+        fence_after();
+        const uint32_t d_tmem = tmem_base + ab * (uint32_t)p.Nbp;
+        const uint32_t a_base = smem_u32(sA + buf * a_bytes);
+        uint32_t first = 0;
+        for (int c = 0; c < p.NC; ++c) {
+          // term index: 0 = h, 1 = m, 2 = l.  smallest products first.
+          const int ta[6] = {1, 2, 0, 1, 0, 0}, tb[6] = {1, 0, 2, 0, 1, 0};
+#pragma unroll
+          for (int combo = 0; combo < 6; ++combo) {
+            const uint32_t aa = a_base + (uint32_t)((ta[combo] * p.NC + c) * kATile);
+            const uint32_t bb = b_base + (uint32_t)((tb[combo] * p.NC + c) * b_tile);
+#pragma unroll
+            for (int k = 0; k < kChunk / 16; ++k) {
+              umma_f16(d_tmem, desc_sw128(aa + 32 * k), desc_sw128(bb + 32 * k), idesc, first);
+              first = 1;
+            }
+          }
+        }
+        umma_commit(bar_acc_full + 8 * ab);
+        umma_commit(bar_a_empty + 8 * buf);
+      }
+    }
+  } else if (warp >= kEpiWarps) {
+    // ===== converters =====
+    const int tcv = (int)threadIdx.x - kEpiWarps * 32;
+    const int ch = tcv & 7, r0 = tcv >> 3;
+    const bool fast = (p.Ka % 8 == 0) && (p.lda % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0);
+    for (int i = 0; i < nblk; ++i) {
+      const int buf = i % p.nbufA;
+      const int64_t rb = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+      mbar_wait(bar_a_empty + 8 * buf, (((uint32_t)(i / p.nbufA)) & 1) ^ 1);
+      uint8_t* a_buf = sA + buf * a_bytes;
+      for (int c = 0; c < p.NC; ++c) {
+        const int col = c * kChunk + ch * 8;
+        float4 va[kCvtItems], vb[kCvtItems];
+#pragma unroll
+        for (int u = 0; u < kCvtItems; ++u) {
+          va[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+          vb[u] = va[u];
+        }
+        if (col < p.Ka) {
+          if (fast) {
+#pragma unroll
+            for (int u = 0; u < kCvtItems; ++u) {
+              const int64_t row = rb * kBM + r0 + (kCvtWarps * 4) * u;
+              if (row < p.N) {
+                const float4* src = reinterpret_cast<const float4*>(p.A + row * p.lda + col);
+                va[u] = __ldg(src);
+                vb[u] = __ldg(src + 1);
+              }
+            }
+          } else {
+#pragma unroll
+            for (int u = 0; u < kCvtItems; ++u) {
+              const int64_t row = rb * kBM + r0 + (kCvtWarps * 4) * u;
+              if (row < p.N) {
+                const float* src = p.A + row * p.lda + col;
+                float t[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) t[e] = (col + e < p.Ka) ? __ldg(src + e) : 0.f;
+                va[u] = make_float4(t[0], t[1], t[2], t[3]);
+                vb[u] = make_float4(t[4], t[5], t[6], t[7]);
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < kCvtItems; ++u) {
+          const float x[8] = {va[u].x, va[u].y, va[u].z, va[u].w, vb[u].x, vb[u].y, vb[u].z, vb[u].w};
+          const int64_t row = rb * kBM + r0 + (kCvtWarps * 4) * u;
+          uint32_t hh[4], mm[4], ll[4];
+          float y[8];
+          dispatch_act(p.actA, [&](auto tag) {
+            constexpr int ACT = decltype(tag)::value;
+#pragma unroll
+            for (int e = 0; e < 8; ++e)  // act(0) may be non-zero (sigmoid): padding must stay zero
+              y[e] = (ACT == LIPVQ_ACT_NONE) ? x[e] : ((row < p.N && col + e < p.Ka) ? act_apply(ACT, x[e]) : 0.f);
+          });
+#pragma unroll
+          for (int e = 0; e < 8; e += 2) {
+            const float y0 = y[e], y1 = y[e + 1];
+            __nv_bfloat16 h0, m0, l0, h1, m1, l1;
+            split3(y0, h0, m0, l0);
+            split3(y1, h1, m1, l1);
+            hh[e >> 1] = pack2(h0, h1);
+            mm[e >> 1] = pack2(m0, m1);
+            ll[e >> 1] = pack2(l0, l1);
+          }
+          const int r = r0 + (kCvtWarps * 4) * u;
+          const uint32_t off = (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
+          *reinterpret_cast<uint4*>(a_buf + (0 * p.NC + c) * kATile + off) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+          *reinterpret_cast<uint4*>(a_buf + (1 * p.NC + c) * kATile + off) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+          *reinterpret_cast<uint4*>(a_buf + (2 * p.NC + c) * kATile + off) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+        }
+      }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_a_full + 8 * buf);
+    }
+  } else {
+    // ===== epilogue warps 0-7: TMEM lane quadrant q, every second 16-column group =====
+    const int q = warp & 3, half = warp >> 2;
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+    const bool vecC = (p.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+    const bool vecX = p.mode == 1 && p.Xpre != nullptr && (p.ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.Xpre) & 15) == 0);
+    for (int i = 0; i < nblk; ++i) {
+      const uint32_t ab = (uint32_t)i & 1;
+      const int64_t rb = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
+      const int64_t row = rb * kBM + q * 32 + lane;
+      mbar_wait(bar_acc_full + 8 * ab, ((uint32_t)i >> 1) & 1);
+      fence_after();
+      const uint32_t trow = tmem_base + ab * (uint32_t)p.Nbp + lane_off;
+      if (16 * half >= p.Nbp) {  // narrow outputs: this warp has no column group
+        fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
+      }
+      for (int c0 = 16 * half; c0 < p.Nbp; c0 += 32) {
+        uint32_t v[16];
+        tmem_ld16(trow + c0, v); tmem_ld_wait16(v);
+        if (c0 + 32 >= p.Nbp) {  // this warp's last group is in registers: release the accumulator before the math
+          fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
+        }
+        if (row >= p.N || c0 >= p.Nb) continue;
+        float o[16];
+        if (p.mode == 0) {
+          dispatch_act(p.act_out, [&](auto tag) {
+            constexpr int ACT = decltype(tag)::value;
+#pragma unroll
+            for (int e = 0; e < 16; ++e) o[e] = act_apply(ACT, __uint_as_float(v[e]) + bias_s[c0 + e]);
+          });
+        } else {
+#pragma unroll
+          for (int e = 0; e < 16; ++e) o[e] = __uint_as_float(v[e]);
+          if (p.act_in != LIPVQ_ACT_NONE) {
+            const float* xp = p.Xpre + row * p.ldx + c0;
+            float xv[16];
+            if (vecX && c0 + 16 <= p.Nb) {
+#pragma unroll
+              for (int e = 0; e < 16; e += 4) {
+                const float4 t = __ldg(reinterpret_cast<const float4*>(xp + e));
+                xv[e] = t.x; xv[e + 1] = t.y; xv[e + 2] = t.z; xv[e + 3] = t.w;
+              }
+            } else {
+#pragma unroll
+              for (int e = 0; e < 16; ++e) xv[e] = (c0 + e < p.Nb) ? __ldg(xp + e) : 0.f;
+            }
+            dispatch_act(p.act_in, [&](auto tag) {
+              constexpr int ACT = decltype(tag)::value;
+#pragma unroll
+              for (int e = 0; e < 16; ++e) o[e] *= act_grad(ACT, xv[e]);
+            });
+          }
+        }
+        float* cp = p.C + row * p.ldc + c0;
+        if (vecC && c0 + 16 <= p.Nb) {
+#pragma unroll
+          for (int e = 0; e < 16; e += 4) *reinterpret_cast<float4*>(cp + e) = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 16; ++e)
+            if (c0 + e < p.Nb) cp[e] = o[e];
+        }
+      }
+    }
+  }
+
+  fence_before();
+  __syncthreads();
+  if (warp == kWarpMma) {
+    fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
+constexpr int kMisc = 256 * 4 + 128;
+
+}  // namespace
+
+// Shapes the tensor path takes: enough tokens to fill the SMs, reduction <= 128, width <= 256, everything fits smem.
+// LIPVQ_LINEAR_ALGO=simt forces the FFMA tiles (A/B runs).
+bool linear_tc_supported(int mode, int64_t N, int Ka, int Nb) {
+  if (const char* f = getenv("LIPVQ_LINEAR_ALGO"))
+    if (f[0] == 's') return false;
+  if (!(N >= 4096 && Ka >= 1 && Ka <= 128 && Nb >= 1 && Nb <= 256)) return false;
+  // measured (scripts/bench_linear.py): a forward layer with a very short reduction and no activation on its input is
+  // all epilogue, and the FFMA tiles are as fast there
+  if (mode == 0 && Ka < 32) return false;
+  const int NC = (Ka + kChunk - 1) / kChunk, Nbp = (Nb + 15) / 16 * 16;
+  const size_t a_bytes = (size_t)3 * NC * kATile, b_bytes = (size_t)3 * NC * Nbp * kChunk * 2;
+  return 1024 + a_bytes + b_bytes + kMisc <= 227 * 1024;
+}
+
+int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, int actA, const float* W, int64_t w_rs,
+                     int64_t w_cs, int Nb, float* C, int64_t ldc, const float* bias, int act_out, const float* Xpre,
+                     int64_t ldx, int act_in, cudaStream_t stream) {
+  LinTcParams p{};
+  p.A = A; p.N = N; p.Ka = Ka; p.lda = lda; p.actA = actA;
+  p.W = W; p.w_rs = w_rs; p.w_cs = w_cs; p.Nb = Nb;
+  p.C = C; p.ldc = ldc; p.bias = bias; p.act_out = act_out;
+  p.Xpre = Xpre; p.ldx = ldx; p.act_in = act_in;
+  p.mode = mode;
+  p.NC = (Ka + kChunk - 1) / kChunk;
+  p.Nbp = (Nb + 15) / 16 * 16;
+  uint32_t cols = 32;
+  while (cols < 2u * (uint32_t)p.Nbp) cols <<= 1;
+  p.tmem_cols = cols;
+  const size_t a_bytes = (size_t)3 * p.NC * kATile, b_bytes = (size_t)3 * p.NC * p.Nbp * kChunk * 2;
+  p.nbufA = (2 * a_bytes + b_bytes + kMisc + 1024 <= 227 * 1024) ? 2 : 1;
+  const size_t smem = 1024 + p.nbufA * a_bytes + b_bytes + kMisc;
+  if (smem > 227 * 1024) {
+    set_error("linear_tc: shape Ka=%d Nb=%d does not fit shared memory", Ka, Nb);
+    return LIPVQ_ERR_INVALID;
+  }
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    LIPVQ_CUDA(cudaFuncSetAttribute(linear_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  const int row_blocks = (int)ceil_div64(N, kBM);
+  const int sms = sm_count();
+  const int grid = row_blocks < sms ? row_blocks : sms;
+  linear_tc_kernel<<<grid, kThreads, smem, stream>>>(p);
+  LIPVQ_LAUNCHED("linear_tc_kernel");
+  return LIPVQ_OK;
+}
+
+}  // namespace lipvq

@@ -15,6 +15,7 @@ after the reduction) are captured as CUDA graphs.
 """
 from __future__ import annotations
 
+import os
 from typing import Dict, Optional
 
 import torch
@@ -73,7 +74,9 @@ class TokenizerTrainer:
         self.use_graph = use_graph
         self._graph_a = None  # zero grads, forward, EMA statistics, backward
         self._graph_b = None  # EMA apply + AdamW
+        self._graph_full = None  # world > 1: phase a + all-reduce + phase b in one graph
         self._graph_tok = None
+        self.graph_collective = os.environ.get("LIPVQ_GRAPH_COLLECTIVE", "1") != "0"
         self.steps_done = 0
 
     # -- the launch sequence -------------------------------------------------------------------
@@ -115,13 +118,31 @@ class TokenizerTrainer:
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
             self._phase_a()
+            if self.world > 1:
+                all_reduce_slab(self.red, self.pg)  # also brings the NCCL communicator up before any capture
             self._phase_b()
         torch.cuda.current_stream().wait_stream(s)
+        self._graph_full = None
+        if self.world > 1 and self.graph_collective:
+            # data-parallel: the whole step -- both halves AND the NCCL all-reduce between them -- is one graph, so a
+            # step is a single launch with no host round-trip around the collective
+            try:
+                gf = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(gf):
+                    self._phase_a()
+                    all_reduce_slab(self.red, self.pg)
+                    self._phase_b()
+                self._graph_full = gf
+            except Exception as e:  # NCCL build without capture support: fall back to graph / eager collective / graph
+                import warnings
+                warnings.warn(f"lipvq: capturing the all-reduce failed ({e}); using two graphs around an eager collective")
+                torch.cuda.synchronize()
         ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
-        with torch.cuda.graph(ga):
-            self._phase_a()
-        with torch.cuda.graph(gb):
-            self._phase_b()
+        if self._graph_full is None:
+            with torch.cuda.graph(ga):
+                self._phase_a()
+            with torch.cuda.graph(gb):
+                self._phase_b()
         self._restore(st)
         self._graph_a, self._graph_b = ga, gb
 
@@ -134,6 +155,10 @@ class TokenizerTrainer:
         self.x_static.copy_(x, non_blocking=True)
         if self.use_graph and self._graph_a is None:
             self._capture()
+        if self.use_graph and self._graph_full is not None:
+            self._graph_full.replay()
+            self.steps_done += 1
+            return self.losses_red
         if self.use_graph:
             self._graph_a.replay()
         else:

@@ -14,7 +14,11 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "sm__inst_executed_pipe_fma.avg.pct_of_peak_sustained_active",
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active",
         "sm__inst_executed_pipe_tensor.sum", "smsp__inst_executed.sum", "sm__cycles_elapsed.max",
-        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "lts__t_sector_hit_rate.pct"]
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "lts__t_sector_hit_rate.pct",
+        "sm__inst_executed_pipe_alu.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "smsp__average_warps_issue_stalled_wait_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
+        "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio"]
 
 
 def launches(path, out):
@@ -37,6 +41,15 @@ def full(path, out):
     raw = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units = rows[0], rows[1]
+    import json
+    for r in rows[2:]:
+        if "search_fused_kernel<(int)1>" in r[hdr.index('Kernel Name')]:
+            def gb(k):
+                v, u = float(r[hdr.index(k)].replace(",", "")), units[hdr.index(k)]
+                return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
+            with open("profiles/search_traffic.json", "w") as tf:
+                json.dump({"kernel": "search_fused_kernel<1>", "source": path,
+                           "dram_bytes_per_launch": gb("dram__bytes_read.sum") + gb("dram__bytes_write.sum")}, tf)
     for r in rows[2:]:
         out.write(f"\n### {r[hdr.index('Kernel Name')][:120]}\n")
         for k in KEYS:

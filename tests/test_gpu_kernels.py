@@ -211,7 +211,11 @@ ACTS = {0: lambda t: t, 1: torch.relu, 2: torch.nn.functional.gelu, 3: torch.sig
 
 @pytest.mark.parametrize("N,i,o,act_in,act_out", [(300, 7, 64, 0, 0), (1000, 64, 128, 2, 0), (257, 128, 64, 2, 3),
                                                    (129, 128, 12, 2, 0), (64, 208, 64, 0, 1), (500, 64, 208, 1, 0),
-                                                   (200, 512, 512, 1, 0), (1, 12, 7, 0, 0)])
+                                                   (200, 512, 512, 1, 0), (1, 12, 7, 0, 0),
+                                                   # N >= 4096: the tcgen05 three-way-bf16 path (linear_tc.cu)
+                                                   (4096, 12, 64, 0, 0), (5000, 64, 128, 2, 0), (4500, 128, 64, 2, 3),
+                                                   (4100, 128, 12, 2, 0), (6000, 64, 64, 0, 1), (4097, 7, 30, 1, 0),
+                                                   (8192, 128, 128, 2, 2), (4200, 100, 208, 1, 0)])
 def test_linear_fwd_bwd(L, N, i, o, act_in, act_out):
     g = torch.Generator().manual_seed(N + i + o)
     X = torch.randn(N, i, generator=g)
@@ -230,6 +234,23 @@ def test_linear_fwd_bwd(L, N, i, o, act_in, act_out):
     scale = math.sqrt(N)
     assert torch.allclose(dW.cpu(), Wl.grad, rtol=1e-4, atol=2e-5 * scale)
     assert torch.allclose(db.cpu(), bl.grad, rtol=1e-4, atol=2e-5 * scale)
+
+
+def test_linear_tc_tiny_gradients_and_wide_range(L):
+    """The tensor path must keep fp32 range: gradients of 1e-8 next to activations of 1e3 (a bf16 split keeps the
+    8-bit exponent; an fp16 split would flush them)."""
+    g = torch.Generator().manual_seed(11)
+    N, i, o = 8192, 128, 64
+    W = torch.randn(o, i, generator=g) / math.sqrt(i)
+    dY = torch.randn(N, o, generator=g) * 1e-8
+    X = torch.randn(N, i, generator=g) * torch.logspace(-3, 3, N).unsqueeze(1)
+    dX = L.ops.linear_bwd_x(dY.to(DEV), W.to(DEV), X.to(DEV), 0)
+    ref = (dY.double() @ W.double()).float()
+    assert torch.allclose(dX.cpu(), ref, rtol=2e-5, atol=1e-12)
+    Y = L.ops.linear_fwd(X.to(DEV), 0, W.to(DEV), None, 0)
+    refY = (X.double() @ W.double().t()).float()
+    err = (Y.cpu() - refY).abs() / (X.abs() @ W.abs().t())
+    assert err.max().item() < 2e-6, f"forward error {err.max().item():.2e} relative to sum |x||w|"
 
 
 def test_linear_bwd_w_many_token_slices(L):
