@@ -13,14 +13,20 @@ int cuda_fail(cudaError_t e, const char* what);
 void count_launch(int n = 1);
 int sm_count();
 
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
 // tcgen05 linear layers (linear_tc.cu): mode 0 = forward (bias + act_out), mode 1 = backward-x (* act_in'(Xpre)).
 // B[n][k] = W[n * w_rs + k * w_cs].
 bool linear_tc_supported(int mode, int64_t N, int Ka, int Nb);
 int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, int actA, const float* W, int64_t w_rs,
                      int64_t w_cs, int Nb, float* C, int64_t ldc, const float* bias, int act_out, const float* Xpre,
                      int64_t ldx, int act_in, cudaStream_t stream);
+// weight gradient dW += dY^T act(X), db += colsum(dY) with the reduction over tokens on the tensor cores
+bool linear_tc_bwd_w_supported(int64_t N, int out_dim, int in_dim, int actX, const float* dY, const float* X);
+int linear_tc_bwd_w_launch(const float* dY, int64_t N, int out_dim, const float* X, int in_dim, int actX, float* dW, float* db,
+                           cudaStream_t stream);
 
-inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
 inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 }  // namespace lipvq

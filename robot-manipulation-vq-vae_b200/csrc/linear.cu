@@ -371,6 +371,8 @@ int lipvq_linear_bwd_w_f32(const float* dY, int64_t N, int out_dim, const float*
   LIPVQ_REQUIRE(N >= 0 && in_dim > 0 && out_dim > 0, "linear_bwd_w: bad shape");
   if (N == 0) return LIPVQ_OK;
   LIPVQ_REQUIRE(dY && X && dW, "linear_bwd_w: null pointer");
+  if (linear_tc_bwd_w_supported(N, out_dim, in_dim, act_in, dY, X))
+    return linear_tc_bwd_w_launch(dY, N, out_dim, X, in_dim, act_in, dW, db, stream);
   GemmArgs g{};
   g.A = dY; g.lda = out_dim; g.actA = LIPVQ_ACT_NONE; g.vecA = (out_dim % 4 == 0) && aligned16(dY);
   g.B = X; g.ldb = in_dim; g.actB = act_in; g.vecB = (in_dim % 4 == 0) && aligned16(X);

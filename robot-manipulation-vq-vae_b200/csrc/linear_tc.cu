@@ -318,6 +318,159 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
   }
 }
 
+// ---- weight gradient:  dW[o][k] += sum_t dY[t][o] * act(X)[t][k],  db[o] += sum_t dY[t][o] ---------------------------
+// The reduction runs over tokens, so both operands are needed K-major with K = token: the converters transpose while they
+// split (thread = one token, 2-byte stores that land 32 consecutive tokens in one 64-byte run of the swizzled row).
+//   A tile [128 x 64 tokens]: row o = dY[:, o] (rows >= out_dim stay zero)      M = 128
+//   B tile [Np  x 64 tokens]: row k = act(X)[:, k], row in_dim = ones (-> db)   N = Np = pad16(in_dim + 1)
+// Every CTA accumulates its share of the 64-token blocks in ONE TMEM accumulator (no per-block epilogue) and adds it to
+// dW / db with fire-and-forget reductions at the end.  Double-buffered tiles; same warp roles as above.
+constexpr int kWTok = 64;  // tokens per block = one 128-byte swizzle row of bf16
+
+struct LinTcWParams {
+  const float* dY; const float* X; int64_t N; int out_dim, in_dim; int actX;
+  float* dW; float* db;
+  int Np;
+  uint32_t tmem_cols;
+};
+
+__global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinTcWParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  const int a_tile = kBM * 128, b_tile = p.Np * 128;       // one term: [rows x 64 tokens] bf16
+  const int buf_bytes = 3 * (a_tile + b_tile);             // [A h,m,l | B h,m,l]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * buf_bytes);
+  const uint32_t bar_full = smem_u32(bars + 0), bar_empty = smem_u32(bars + 2), bar_done = smem_u32(bars + 4);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 6);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int blocks = (int)((p.N + kWTok - 1) / kWTok);
+  const int nblk = ((int)blockIdx.x < blocks) ? (blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  if (nblk == 0) return;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_full + 8 * s, kCvtWarps);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    mbar_init(bar_done, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
+  for (int i = threadIdx.x; i < 2 * buf_bytes / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  fence_async_smem();
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == kWarpMma) {
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16(kBM, p.Np);
+      uint32_t acc = 0;
+      for (int i = 0; i < nblk; ++i) {
+        const int buf = i & 1;
+        mbar_wait(bar_full + 8 * buf, ((uint32_t)i >> 1) & 1);
+        fence_after();
+        const uint32_t a0 = smem_u32(smem + buf * buf_bytes), b0 = a0 + 3 * (uint32_t)a_tile;
+        const int ta[6] = {1, 2, 0, 1, 0, 0}, tb[6] = {1, 0, 2, 0, 1, 0};  // smallest products first
+#pragma unroll
+        for (int combo = 0; combo < 6; ++combo) {
+          const uint32_t aa = a0 + (uint32_t)(ta[combo] * a_tile), bb = b0 + (uint32_t)(tb[combo] * b_tile);
+#pragma unroll
+          for (int k = 0; k < kWTok / 16; ++k) {
+            umma_f16(tmem_base, desc_sw128(aa + 32 * k), desc_sw128(bb + 32 * k), idesc, acc);
+            acc = 1;
+          }
+        }
+        umma_commit(bar_empty + 8 * buf);
+      }
+      umma_commit(bar_done);
+    }
+  } else if (warp >= kEpiWarps) {
+    // ===== converters: thread = (token, part); part p takes the 4-column groups p, p + 8, p + 16, ... =====
+    const int tcv = (int)threadIdx.x - kEpiWarps * 32;
+    const int tok = tcv & (kWTok - 1), part = tcv >> 6;  // 8 parts
+    const uint32_t tok_off = (uint32_t)((tok & 7) * 2);
+    const int tchunk = tok >> 3;
+    auto put3 = [&](uint8_t* tile0, int tile_bytes, int r, float v) {
+      __nv_bfloat16 h, m, l;
+      split3(v, h, m, l);
+      uint8_t* d = tile0 + r * 128 + ((tchunk ^ (r & 7)) << 4) + tok_off;
+      *reinterpret_cast<__nv_bfloat16*>(d) = h;
+      *reinterpret_cast<__nv_bfloat16*>(d + tile_bytes) = m;
+      *reinterpret_cast<__nv_bfloat16*>(d + 2 * tile_bytes) = l;
+    };
+    for (int i = 0; i < nblk; ++i) {
+      const int buf = i & 1;
+      const int64_t t = ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * kWTok + tok;
+      const bool live = t < p.N;
+      float4 ya[4], xa[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int o = 4 * (part + 8 * j), k = 4 * (part + 8 * j);
+        ya[j] = (live && o < p.out_dim) ? __ldg(reinterpret_cast<const float4*>(p.dY + t * p.out_dim + o)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        xa[j] = (live && k < p.in_dim) ? __ldg(reinterpret_cast<const float4*>(p.X + t * p.in_dim + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      mbar_wait(bar_empty + 8 * buf, (((uint32_t)i >> 1) & 1) ^ 1);
+      uint8_t* a0 = smem + buf * buf_bytes;
+      uint8_t* b0 = a0 + 3 * a_tile;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int o = 4 * (part + 8 * j);
+        if (o < p.out_dim) {
+          put3(a0, a_tile, o, ya[j].x); put3(a0, a_tile, o + 1, ya[j].y);
+          put3(a0, a_tile, o + 2, ya[j].z); put3(a0, a_tile, o + 3, ya[j].w);
+        }
+      }
+      dispatch_act(p.actX, [&](auto tag) {
+        constexpr int ACT = decltype(tag)::value;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int k = 4 * (part + 8 * j);
+          if (k < p.in_dim) {  // dead tokens of the last block contribute zeros (act(0) may be non-zero)
+            put3(b0, b_tile, k, live ? act_apply(ACT, xa[j].x) : 0.f);
+            put3(b0, b_tile, k + 1, live ? act_apply(ACT, xa[j].y) : 0.f);
+            put3(b0, b_tile, k + 2, live ? act_apply(ACT, xa[j].z) : 0.f);
+            put3(b0, b_tile, k + 3, live ? act_apply(ACT, xa[j].w) : 0.f);
+          }
+        }
+      });
+      if (part == 0) put3(b0, b_tile, p.in_dim, live ? 1.f : 0.f);  // ones row: column in_dim of the product is db
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_full + 8 * buf);
+    }
+  } else {
+    // ===== epilogue warps 0-7: TMEM lane = output row o; every second 16-column group; one pass at the very end =====
+    const int q = warp & 3, half = warp >> 2;
+    const int o = q * 32 + lane;
+    mbar_wait(bar_done, 0);
+    fence_after();
+    const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
+    for (int c0 = 16 * half; c0 < p.Np; c0 += 32) {
+      uint32_t v[16];
+      tmem_ld16(trow + c0, v);
+      tmem_ld_wait16(v);
+      if (o < p.out_dim) {
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const int k = c0 + e;
+          if (k < p.in_dim) atomicAdd(p.dW + (size_t)o * p.in_dim + k, __uint_as_float(v[e]));
+          else if (k == p.in_dim && p.db != nullptr) atomicAdd(p.db + o, __uint_as_float(v[e]));
+        }
+      }
+    }
+  }
+
+  fence_before();
+  __syncthreads();
+  if (warp == kWarpMma) {
+    fence_after();
+    tmem_dealloc(tmem_base, p.tmem_cols);
+  }
+}
+
 constexpr int kMisc = 256 * 4 + 128;
 
 }  // namespace
@@ -367,6 +520,37 @@ int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, i
   const int grid = row_blocks < sms ? row_blocks : sms;
   linear_tc_kernel<<<grid, kThreads, smem, stream>>>(p);
   LIPVQ_LAUNCHED("linear_tc_kernel");
+  return LIPVQ_OK;
+}
+
+bool linear_tc_bwd_w_supported(int64_t N, int out_dim, int in_dim, int actX, const float* dY, const float* X) {
+  if (const char* f = getenv("LIPVQ_LINEAR_ALGO"))
+    if (f[0] == 's') return false;
+  // measured (scripts/bench_linear.py): the transposing converter pays off where it also absorbs an activation;
+  // plain dY^T X products stay on the FFMA tiles
+  if (actX == LIPVQ_ACT_NONE && !(getenv("LIPVQ_LINEAR_ALGO") && getenv("LIPVQ_LINEAR_ALGO")[0] == 't')) return false;
+  return N >= 4096 && out_dim >= 4 && out_dim <= 128 && in_dim >= 4 && in_dim <= 128 && out_dim % 4 == 0 && in_dim % 4 == 0 &&
+         aligned16(dY) && aligned16(X);
+}
+
+int linear_tc_bwd_w_launch(const float* dY, int64_t N, int out_dim, const float* X, int in_dim, int actX, float* dW, float* db,
+                           cudaStream_t stream) {
+  LinTcWParams p{};
+  p.dY = dY; p.X = X; p.N = N; p.out_dim = out_dim; p.in_dim = in_dim; p.actX = actX; p.dW = dW; p.db = db;
+  p.Np = (in_dim + 1 + 15) / 16 * 16;
+  uint32_t cols = 32;
+  while (cols < (uint32_t)p.Np) cols <<= 1;
+  p.tmem_cols = cols;
+  const size_t smem = 1024 + 2 * (size_t)3 * (kBM * 128 + p.Np * 128) + 128;
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    LIPVQ_CUDA(cudaFuncSetAttribute(linear_tc_bwd_w_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set = smem;
+  }
+  const int blocks = (int)ceil_div64(N, kWTok);
+  const int sms = sm_count();
+  linear_tc_bwd_w_kernel<<<blocks < sms ? blocks : sms, kThreads, smem, stream>>>(p);
+  LIPVQ_LAUNCHED("linear_tc_bwd_w_kernel");
   return LIPVQ_OK;
 }
 

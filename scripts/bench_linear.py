@@ -43,4 +43,6 @@ for (i, o, act_in, act_out) in [(12, 64, 0, 0), (64, 128, 2, 0), (128, 64, 2, 3)
         os.environ["LIPVQ_LINEAR_ALGO"] = algo
         res[f"fwd_{algo}_us"] = timeit(lambda: ops.linear_fwd(X, act_in, W, b, act_out, out=Y))
         res[f"bwdx_{algo}_us"] = timeit(lambda: ops.linear_bwd_x(dY, W, X, act_in, out=dX))
+        dW, db = torch.zeros(o, i, device="cuda"), torch.zeros(o, device="cuda")
+        res[f"bwdw_{algo}_us"] = timeit(lambda: ops.linear_bwd_w(dY, X, act_in, dW, db))
     print(json.dumps(res), flush=True)

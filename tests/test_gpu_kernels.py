@@ -236,6 +236,19 @@ def test_linear_fwd_bwd(L, N, i, o, act_in, act_out):
     assert torch.allclose(db.cpu(), bl.grad, rtol=1e-4, atol=2e-5 * scale)
 
 
+def test_linear_tc_bwd_w_forced(L, monkeypatch):
+    """dW/db on the tensor cores for a layer without input activation (the dispatcher keeps those on the FFMA tiles;
+    LIPVQ_LINEAR_ALGO=tc forces the tcgen05 kernel so it stays covered), ragged token count."""
+    monkeypatch.setenv("LIPVQ_LINEAR_ALGO", "tc")
+    g = torch.Generator().manual_seed(5)
+    N, i, o = 10007, 64, 64
+    X, dY = torch.randn(N, i, generator=g), torch.randn(N, o, generator=g)
+    dW, db = torch.zeros(o, i, device=DEV), torch.zeros(o, device=DEV)
+    L.ops.linear_bwd_w(dY.to(DEV), X.to(DEV), 0, dW, db)
+    assert torch.allclose(dW.cpu(), (dY.double().t() @ X.double()).float(), rtol=1e-4, atol=2e-3)
+    assert torch.allclose(db.cpu(), dY.double().sum(0).float(), rtol=1e-4, atol=2e-3)
+
+
 def test_linear_tc_tiny_gradients_and_wide_range(L):
     """The tensor path must keep fp32 range: gradients of 1e-8 next to activations of 1e3 (a bf16 split keeps the
     8-bit exponent; an fp16 split would flush them)."""
