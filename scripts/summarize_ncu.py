@@ -43,7 +43,7 @@ def full(path, out):
     hdr, units = rows[0], rows[1]
     import json
     for r in rows[2:]:
-        if "search_fused_kernel<(int)1>" in r[hdr.index('Kernel Name')]:
+        if "search_fused_kernel<1>" in r[hdr.index("Kernel Name")] or "search_fused_kernel<(int)1>" in r[hdr.index("Kernel Name")]:
             def gb(k):
                 v, u = float(r[hdr.index(k)].replace(",", "")), units[hdr.index(k)]
                 return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
