@@ -157,6 +157,95 @@ __global__ void __launch_bounds__(256)
   }
 }
 
+// ---- shared-memory privatised scatter (K4 backward / K5 statistics) ------------------------------------------------
+// When the whole [K, D] table fits in shared memory (K*D <= ~50 K floats: every tokenizer codebook of the reference),
+// each CTA (one per SM, a contiguous slice of rows) accumulates its rows into a private copy with shared-memory
+// reductions and adds only the touched entries to global memory once at the end.  A collapsed codebook -- every token
+// on a handful of codes, the normal state of a fresh EMA quantizer -- then costs ~#SM global reductions per entry
+// instead of N, which is what made the run-length kernels above L2-atomic-bound (profiles/r1g_launches.md).
+// Lane mapping: LPR = pow2 >= D/4 lanes own one row (one float4 each, or a strided loop for D > 128).
+constexpr int kScatThreads = 512;
+
+__device__ __forceinline__ void scatter_flush(const float* s_tab, int64_t n, float* __restrict__ g) {
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+    const float v = s_tab[i];
+    if (v != 0.f) atomicAdd(g + i, v);
+  }
+}
+
+template <bool BWD>
+__global__ void __launch_bounds__(kScatThreads, 1)
+    scatter_smem_kernel(const float* __restrict__ z, const float* __restrict__ zq, const int64_t* __restrict__ idx,
+                        const float* __restrict__ dzq_up, const float* __restrict__ gscale_dev, float w_commit,
+                        float w_codebook, int ste, const float* __restrict__ sig_out, int64_t N, int D, int K, int lpr,
+                        float* __restrict__ dz, float* __restrict__ tab_g, float* __restrict__ counts_g) {
+  extern __shared__ __align__(16) float s_tab[];  // [K*D] (+ [K] counts for the statistics)
+  float* s_cnt = s_tab + (size_t)K * D;
+  const int64_t tab_n = (int64_t)K * D + (BWD ? 0 : K);
+  for (int64_t i = threadIdx.x; i < tab_n; i += blockDim.x) s_tab[i] = 0.f;
+  __syncthreads();
+
+  float cz = 0.f, cq = 0.f;
+  if (BWD) {
+    const float g = gscale_dev ? __ldg(gscale_dev) : 1.f;
+    const float coef = (float)(2.0 / ((double)N * (double)D)) * g;
+    cz = w_commit * coef;
+    cq = w_codebook * coef;
+  }
+  const int64_t per_cta = (N + gridDim.x - 1) / gridDim.x;
+  const int64_t r_beg = (int64_t)blockIdx.x * per_cta;
+  const int64_t r_end = (r_beg + per_cta < N) ? r_beg + per_cta : N;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  const int rpw = 32 / lpr;                 // rows per warp pass
+  const int sub = lane / lpr, c4 = lane % lpr;
+  const int nvec = D >> 2;
+  for (int64_t r0 = r_beg + (int64_t)warp * rpw; r0 < r_end; r0 += (int64_t)nwarps * rpw) {
+    const int64_t r = r0 + sub;
+    if (r >= r_end) continue;
+    int64_t k = __ldg(idx + r);
+    k = k < 0 ? 0 : (k >= K ? K - 1 : k);
+    if (!BWD && c4 == 0) atomicAdd(s_cnt + k, 1.f);
+    for (int v = c4; v < nvec; v += lpr) {
+      const int64_t o = r * D + 4 * v;
+      const float4 zv = __ldg(reinterpret_cast<const float4*>(z + o));
+      float4 add = zv;
+      if (BWD) {
+        const float4 qv = __ldg(reinterpret_cast<const float4*>(zq + o));
+        float4 up = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (dzq_up) up = __ldg(reinterpret_cast<const float4*>(dzq_up + o));
+        float4 gz, gq;
+        gz.x = cz * (zv.x - qv.x); gz.y = cz * (zv.y - qv.y); gz.z = cz * (zv.z - qv.z); gz.w = cz * (zv.w - qv.w);
+        gq.x = cq * (qv.x - zv.x); gq.y = cq * (qv.y - zv.y); gq.z = cq * (qv.z - zv.z); gq.w = cq * (qv.w - zv.w);
+        if (ste) { gz.x += up.x; gz.y += up.y; gz.z += up.z; gz.w += up.w; }
+        else     { gq.x += up.x; gq.y += up.y; gq.z += up.z; gq.w += up.w; }
+        if (sig_out) {
+          const float4 y = __ldg(reinterpret_cast<const float4*>(sig_out + o));
+          gz.x *= y.x * (1.f - y.x); gz.y *= y.y * (1.f - y.y); gz.z *= y.z * (1.f - y.z); gz.w *= y.w * (1.f - y.w);
+        }
+        if (dz) *reinterpret_cast<float4*>(dz + o) = gz;
+        add = gq;
+      }
+      if (!BWD || tab_g) {
+        float* t = s_tab + k * D + 4 * v;
+        atomicAdd(t, add.x); atomicAdd(t + 1, add.y); atomicAdd(t + 2, add.z); atomicAdd(t + 3, add.w);
+      }
+    }
+  }
+  __syncthreads();
+  if (tab_g) scatter_flush(s_tab, (int64_t)K * D, tab_g);
+  if (!BWD) scatter_flush(s_cnt, K, counts_g);
+}
+
+// shared-memory table fits?  (leave room for the driver's reserved kilobyte)
+inline bool scatter_fits(int K, int D, bool with_counts) {
+  return ((size_t)K * D + (with_counts ? K : 0)) * sizeof(float) <= 200 * 1024;
+}
+inline int scatter_lpr(int D) {
+  int lpr = 1;
+  while (lpr < 32 && lpr * 4 < D) lpr <<= 1;
+  return lpr;
+}
+
 // ---- K5 statistics ----------------------------------------------------------------------------------------------
 // Same sub-warp-group walk as above: the running sum of the current code lives in registers and is flushed with one
 // vector red per element (and one red for the count) only when the code changes.
@@ -423,7 +512,17 @@ int lipvq_gather_ste_loss_bwd_f32(const float* z, const float* z_q, const int64_
   const bool vec = (D % 4 == 0) && aligned16(z) && aligned16(z_q) && (!dzq_up || aligned16(dzq_up)) &&
                    (!sigmoid_out || aligned16(sigmoid_out)) && (!dz_out || aligned16(dz_out)) &&
                    (!dcodebook || aligned16(dcodebook));
-  if (vec && D <= 512) {
+  if (vec && scatter_fits(K, D, false) && N >= 4096) {
+    const size_t smem = (size_t)K * D * sizeof(float);
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+      LIPVQ_CUDA(cudaFuncSetAttribute(scatter_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      smem_set = smem;
+    }
+    scatter_smem_kernel<true><<<sm_count(), kScatThreads, smem, stream>>>(z, z_q, idx, dzq_up, gscale_dev, w_commit,
+                                                                          w_codebook, ste, sigmoid_out, N, D, K,
+                                                                          scatter_lpr(D), dz_out, dcodebook, nullptr);
+  } else if (vec && D <= 512) {
     const RunsPlan rp = plan_runs(N, D);
 #define LIPVQ_GB(G_, V_)                                                                                          \
   gather_bwd_runs_kernel<G_, V_><<<rp.grid, 256, 0, stream>>>(z, z_q, idx, dzq_up, gscale_dev, w_commit, w_codebook, \
@@ -450,7 +549,17 @@ int lipvq_ema_stats_f32(const float* z, const int64_t* idx, int64_t N, int D, in
   if (N == 0) return LIPVQ_OK;
   LIPVQ_REQUIRE(z && idx && counts && sums, "ema_stats: null pointer");
   const bool vec = (D % 4 == 0) && D <= 512 && aligned16(z) && aligned16(sums);
-  if (vec) {
+  if (vec && scatter_fits(K, D, true) && N >= 4096) {
+    const size_t smem = ((size_t)K * D + K) * sizeof(float);
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+      LIPVQ_CUDA(cudaFuncSetAttribute(scatter_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      smem_set = smem;
+    }
+    scatter_smem_kernel<false><<<sm_count(), kScatThreads, smem, stream>>>(z, nullptr, idx, nullptr, nullptr, 0.f, 0.f, 0,
+                                                                           nullptr, N, D, K, scatter_lpr(D), nullptr, sums,
+                                                                           counts);
+  } else if (vec) {
     const RunsPlan rp = plan_runs(N, D);
 #define LIPVQ_ES(G_, V_) \
   ema_stats_runs_kernel<G_, V_><<<rp.grid, 256, 0, stream>>>(z, idx, N, D, K, rp.rows_per_group, counts, sums)

@@ -158,6 +158,33 @@ def test_gather_fwd_bwd(L):
     assert torch.equal(zq3.cpu(), cb3[i3])
 
 
+def test_gather_bwd_and_stats_shared_memory_path(L):
+    """N >= 4096 with a table that fits shared memory: the privatised scatter kernels (quantize.cu), on a collapsed
+    assignment (all tokens on 5 codes, the state of a fresh EMA quantizer) and on a spread one."""
+    for spread in (False, True):
+        N, K, D = 8192 + 37, 512, 64
+        g = torch.Generator().manual_seed(31 + spread)
+        z = torch.rand(N, D, generator=g)
+        cb = torch.randn(K, D, generator=g)
+        idx = torch.randint(0, K if spread else 5, (N,), generator=g)
+        up = torch.randn(N, D, generator=g)
+        zl, cl = z.clone().requires_grad_(True), cb.clone().requires_grad_(True)
+        q = cl[idx]
+        loss = 0.25 * torch.nn.functional.mse_loss(q.detach(), zl) + 0.25 * torch.nn.functional.mse_loss(q, zl.detach()) + (up * q).sum()
+        loss.backward()
+        zd, id_ = z.to(DEV), idx.to(DEV)
+        zq = cb[idx].to(DEV)
+        dz, dcb = torch.empty_like(zd), torch.zeros(K, D, device=DEV)
+        L.ops.gather_bwd(zd, zq, id_, up.to(DEV), None, 0.25, 0.25, False, None, K, dz, dcb)
+        assert torch.allclose(dz.cpu(), zl.grad, rtol=1e-5, atol=1e-9)
+        assert torch.allclose(dcb.cpu(), cl.grad, rtol=1e-4, atol=1e-2 if not spread else 1e-4)
+        counts, sums = torch.zeros(K, device=DEV), torch.zeros(K, D, device=DEV)
+        L.ops.ema_stats(zd, id_, counts, sums)
+        assert torch.equal(counts.cpu(), torch.bincount(idx, minlength=K).float())
+        ref = torch.zeros(K, D, dtype=torch.float64).index_add_(0, idx, z.double()).float()
+        assert torch.allclose(sums.cpu(), ref, rtol=1e-4, atol=1e-3)
+
+
 # ------------------------------------------------------------------------------------------------ K5 / K6
 @pytest.mark.parametrize("N,K,D", [(256, 64, 32), (4096, 512, 64), (333, 20, 208), (100, 9, 7)])
 def test_ema_stats_and_apply(L, N, K, D):
