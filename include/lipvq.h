@@ -51,7 +51,7 @@ enum {
 enum {
   LIPVQ_ALGO_AUTO = 0,
   LIPVQ_ALGO_SIMT_F32 = 1, /* shared-memory staged fp32 FFMA tiles, warp-shuffle argmin */
-  LIPVQ_ALGO_TCGEN05 = 2   /* TMA-fed tcgen05/TMEM split-bf16 contraction, argmin in the TMEM epilogue */
+  LIPVQ_ALGO_TCGEN05 = 2   /* fused tcgen05/TMEM search: fp16 pass + 3-term fp16 pass, argmin + certification in the epilogue */
 };
 
 /* activations understood by the fused linear kernels */
@@ -80,16 +80,19 @@ LIPVQ_API uint64_t lipvq_launch_count(void);
  * 247-255), the squared form of VQVAE.quantize (backbone.py:57-63) and the matmul+argmax of
  * HierarchicalVQVAE._compute_similarities/quantize_* (heirarchical_vqvae.py:421-449).
  *
- * Never materialises [N,K].  Scores ||e||^2 - 2 z.e are produced by the chosen contraction
- * (fp32 FFMA tiles, or split-bf16 tcgen05 MMAs accumulated in TMEM) with a per-row running
- * top-2; rows whose two best scores are closer than a rigorous error bound of the contraction
- * are re-scored by an exact fp32 direct-difference scan (sqrt applied for METRIC_L2, first-min
- * tie rule), so indices equal the reference's except where the reference's own fp32 rounding
- * decides (relative distance gap < 1e-6).
+ * Never materialises [N,K].  Scores ||e-mu||^2 - 2 (z-mu).(e-mu) are produced by the chosen
+ * contraction with a per-row running top-2; a row is decided only when its two best scores
+ * are further apart than a rigorous error bound of that contraction, otherwise it moves to the
+ * next precision level: fp16 tcgen05 MMAs (fp32 accumulation in TMEM) over every row, a
+ * three-term fp16 split over the rows left, and finally an exact fp32 direct-difference scan
+ * (sqrt applied for METRIC_L2, first-min tie rule).  The fp32 FFMA path has two levels (FFMA
+ * tiles, exact scan).  Indices therefore equal the reference's except where the reference's
+ * own fp32 rounding decides (relative distance gap < 1e-6).
  *
  *   z [N,D], codebook [K,D] fp32; idx_out [N] int64; best_out [N] fp32 or NULL (exact winning
  *   distance / squared distance / similarity, as the metric defines).
- *   stats_out: NULL or 4 x int32 on device: {rows rescored exactly, 0, 0, 0}.
+ *   stats_out: NULL or 4 x int32 on device: {rows decided by the exact scan, rows the first
+ *   (fastest) level could not certify, 0, 0}.
  * --------------------------------------------------------------------------------------------- */
 LIPVQ_API size_t lipvq_nn_search_workspace_bytes(int64_t N, int D, int K, int metric, int algo);
 LIPVQ_API int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook, int K, int metric, int algo,
@@ -160,6 +163,10 @@ LIPVQ_API int lipvq_codebook_usage_f32(const float* cluster_size, int K, float d
  *   fwd:   Y[n,o] = act_out( sum_i act_in(X[n,i]) * W[o,i] + bias[o] )           X:[N,in] W:[out,in]
  *   bwd_x: dX[n,i] = ( sum_o dY[n,o] * W[o,i] ) * act_in'(X[n,i])                 (gradient at X, the stored pre-activation)
  *   bwd_w: dW[o,i] += sum_n dY[n,o] * act_in(X[n,i]) ;  db[o] += sum_n dY[n,o]    (ACCUMULATED INTO; db may be NULL)
+ *
+ * Two implementations behind each entry point, chosen per shape (LIPVQ_LINEAR_ALGO=simt|tc overrides):
+ * tcgen05 MMAs on three-way bf16 splits of both operands (six chains, fp32 accumulation in TMEM; as
+ * accurate as fp32 FFMA) for N >= 4096 tokens and dims <= 128, fp32 FFMA tiles otherwise.
  * --------------------------------------------------------------------------------------------- */
 LIPVQ_API int lipvq_linear_fwd_f32(const float* X, int64_t N, int in_dim, int act_in, const float* W, const float* bias,
                          int out_dim, int act_out, float* Y, void* stream);
