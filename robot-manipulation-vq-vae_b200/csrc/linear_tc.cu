@@ -103,24 +103,29 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
     const int Kp = p.NC * kChunk;
     const int total = p.Nbp * Kp;
     const bool n_fast = (p.w_rs == 1);  // consecutive threads follow the contiguous direction of W
-    for (int idx = threadIdx.x; idx < total; idx += kThreads) {
-      int n, k;
-      if (n_fast) {
-        n = idx % p.Nbp;
-        k = idx / p.Nbp;
-      } else {
-        k = idx % Kp;
-        n = idx / Kp;
+    // batches of 8 elements per thread with the (L2-latency) loads issued before the first store
+    for (int base = 0; base < total; base += 8 * kThreads) {
+      float wv[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int idx = base + u * kThreads + (int)threadIdx.x;
+        const int n = n_fast ? idx % p.Nbp : idx / Kp, k = n_fast ? idx / p.Nbp : idx % Kp;
+        wv[u] = (idx < total && n < p.Nb && k < p.Ka) ? __ldg(p.W + (int64_t)n * p.w_rs + (int64_t)k * p.w_cs) : 0.f;
       }
-      const float v = (n < p.Nb && k < p.Ka) ? __ldg(p.W + (int64_t)n * p.w_rs + (int64_t)k * p.w_cs) : 0.f;
-      __nv_bfloat16 h, m, l;
-      split3(v, h, m, l);
-      const int c = k >> 6, kk = k & 63;
-      const uint32_t off = (uint32_t)(n * 128 + ((((kk >> 3) ^ (n & 7))) << 4) + (kk & 7) * 2);
-      uint8_t* t0 = sB + c * b_tile + off;
-      *reinterpret_cast<__nv_bfloat16*>(t0) = h;
-      *reinterpret_cast<__nv_bfloat16*>(t0 + p.NC * b_tile) = m;
-      *reinterpret_cast<__nv_bfloat16*>(t0 + 2 * p.NC * b_tile) = l;
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int idx = base + u * kThreads + (int)threadIdx.x;
+        if (idx >= total) continue;
+        const int n = n_fast ? idx % p.Nbp : idx / Kp, k = n_fast ? idx / p.Nbp : idx % Kp;
+        __nv_bfloat16 h, m, l;
+        split3(wv[u], h, m, l);
+        const int c = k >> 6, kk = k & 63;
+        const uint32_t off = (uint32_t)(n * 128 + ((((kk >> 3) ^ (n & 7))) << 4) + (kk & 7) * 2);
+        uint8_t* t0 = sB + c * b_tile + off;
+        *reinterpret_cast<__nv_bfloat16*>(t0) = h;
+        *reinterpret_cast<__nv_bfloat16*>(t0 + p.NC * b_tile) = m;
+        *reinterpret_cast<__nv_bfloat16*>(t0 + 2 * p.NC * b_tile) = l;
+      }
     }
     for (int i = threadIdx.x; i < 256; i += kThreads)
       bias_s[i] = (p.mode == 0 && p.bias != nullptr && i < p.Nb) ? __ldg(p.bias + i) : 0.f;

@@ -5,6 +5,8 @@
 // Reference anchors: backbone_lfqvae_v5.py:47,74,80-81 (gather, detach-copy, two MSE terms); backbone.py:66-74
 // (STE); hq_vae.py:103-130,262-279 and heirarchical_vqvae.py:498-541 (EMA counts/sums/update);
 // heirarchical_vqvae.py:687-706 (usage summary).
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace lipvq {
@@ -199,35 +201,58 @@ __global__ void __launch_bounds__(kScatThreads, 1)
   const int rpw = 32 / lpr;                 // rows per warp pass
   const int sub = lane / lpr, c4 = lane % lpr;
   const int nvec = D >> 2;
-  for (int64_t r0 = r_beg + (int64_t)warp * rpw; r0 < r_end; r0 += (int64_t)nwarps * rpw) {
-    const int64_t r = r0 + sub;
-    if (r >= r_end) continue;
-    int64_t k = __ldg(idx + r);
-    k = k < 0 ? 0 : (k >= K ? K - 1 : k);
-    if (!BWD && c4 == 0) atomicAdd(s_cnt + k, 1.f);
-    for (int v = c4; v < nvec; v += lpr) {
-      const int64_t o = r * D + 4 * v;
-      const float4 zv = __ldg(reinterpret_cast<const float4*>(z + o));
-      float4 add = zv;
-      if (BWD) {
-        const float4 qv = __ldg(reinterpret_cast<const float4*>(zq + o));
-        float4 up = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (dzq_up) up = __ldg(reinterpret_cast<const float4*>(dzq_up + o));
-        float4 gz, gq;
-        gz.x = cz * (zv.x - qv.x); gz.y = cz * (zv.y - qv.y); gz.z = cz * (zv.z - qv.z); gz.w = cz * (zv.w - qv.w);
-        gq.x = cq * (qv.x - zv.x); gq.y = cq * (qv.y - zv.y); gq.z = cq * (qv.z - zv.z); gq.w = cq * (qv.w - zv.w);
-        if (ste) { gz.x += up.x; gz.y += up.y; gz.z += up.z; gz.w += up.w; }
-        else     { gq.x += up.x; gq.y += up.y; gq.z += up.z; gq.w += up.w; }
-        if (sig_out) {
-          const float4 y = __ldg(reinterpret_cast<const float4*>(sig_out + o));
-          gz.x *= y.x * (1.f - y.x); gz.y *= y.y * (1.f - y.y); gz.z *= y.z * (1.f - y.z); gz.w *= y.w * (1.f - y.w);
+  // UN row passes per iteration with every load issued up front: the loop is otherwise one DRAM latency per pass
+  constexpr int UN = 4;
+  const int64_t pass = (int64_t)nwarps * rpw;
+  for (int64_t r0 = r_beg + (int64_t)warp * rpw; r0 < r_end; r0 += pass * UN) {
+    for (int v0 = 0; v0 < nvec; v0 += lpr) {  // one trip for D <= 128
+      const int v = v0 + c4;
+      int64_t kk[UN];
+      float4 zv[UN], qv[UN], up[UN], yv[UN];
+      bool ok[UN];
+#pragma unroll
+      for (int u = 0; u < UN; ++u) {
+        const int64_t r = r0 + u * pass + sub;
+        ok[u] = (r < r_end) && (v < nvec);
+        kk[u] = 0;
+        zv[u] = qv[u] = up[u] = yv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ok[u]) {
+          const int64_t o = r * D + 4 * v;
+          kk[u] = __ldg(idx + r);
+          zv[u] = __ldg(reinterpret_cast<const float4*>(z + o));
+          if (BWD) {
+            qv[u] = __ldg(reinterpret_cast<const float4*>(zq + o));
+            if (dzq_up) up[u] = __ldg(reinterpret_cast<const float4*>(dzq_up + o));
+            if (sig_out) yv[u] = __ldg(reinterpret_cast<const float4*>(sig_out + o));
+          }
         }
-        if (dz) *reinterpret_cast<float4*>(dz + o) = gz;
-        add = gq;
       }
-      if (!BWD || tab_g) {
-        float* t = s_tab + k * D + 4 * v;
-        atomicAdd(t, add.x); atomicAdd(t + 1, add.y); atomicAdd(t + 2, add.z); atomicAdd(t + 3, add.w);
+#pragma unroll
+      for (int u = 0; u < UN; ++u) {
+        if (!ok[u]) continue;
+        const int64_t r = r0 + u * pass + sub;
+        const int64_t o = r * D + 4 * v;
+        const int64_t k = kk[u] < 0 ? 0 : (kk[u] >= K ? K - 1 : kk[u]);
+        if (!BWD && v == 0) atomicAdd(s_cnt + k, 1.f);
+        float4 add = zv[u];
+        if (BWD) {
+          const float4 z4 = zv[u], q4 = qv[u];
+          float4 gz, gq;
+          gz.x = cz * (z4.x - q4.x); gz.y = cz * (z4.y - q4.y); gz.z = cz * (z4.z - q4.z); gz.w = cz * (z4.w - q4.w);
+          gq.x = cq * (q4.x - z4.x); gq.y = cq * (q4.y - z4.y); gq.z = cq * (q4.z - z4.z); gq.w = cq * (q4.w - z4.w);
+          if (ste) { gz.x += up[u].x; gz.y += up[u].y; gz.z += up[u].z; gz.w += up[u].w; }
+          else     { gq.x += up[u].x; gq.y += up[u].y; gq.z += up[u].z; gq.w += up[u].w; }
+          if (sig_out) {
+            const float4 y = yv[u];
+            gz.x *= y.x * (1.f - y.x); gz.y *= y.y * (1.f - y.y); gz.z *= y.z * (1.f - y.z); gz.w *= y.w * (1.f - y.w);
+          }
+          if (dz) *reinterpret_cast<float4*>(dz + o) = gz;
+          add = gq;
+        }
+        if (!BWD || tab_g) {
+          float* t = s_tab + k * D + 4 * v;
+          atomicAdd(t, add.x); atomicAdd(t + 1, add.y); atomicAdd(t + 2, add.z); atomicAdd(t + 3, add.w);
+        }
       }
     }
   }
