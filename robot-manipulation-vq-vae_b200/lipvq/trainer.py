@@ -77,6 +77,12 @@ class TokenizerTrainer:
         self._graph_full = None  # world > 1: phase a + all-reduce + phase b in one graph
         self._graph_tok = None
         self.graph_collective = os.environ.get("LIPVQ_GRAPH_COLLECTIVE", "1") != "0"
+        # input prefetch (step(x, prefetch=x_next)): the next batch's H2D copy runs on its own stream under this step
+        self._stage = None
+        self._copy_stream = None
+        self._stage_ready = None
+        self._stage_free = None
+        self._stage_src = None
         self.steps_done = 0
 
     # -- the launch sequence -------------------------------------------------------------------
@@ -146,13 +152,37 @@ class TokenizerTrainer:
         self._restore(st)
         self._graph_a, self._graph_b = ga, gb
 
-    def step(self, x: torch.Tensor) -> torch.Tensor:
+    def _load_input(self, x: torch.Tensor, prefetch: Optional[torch.Tensor]) -> None:
+        cur = torch.cuda.current_stream()
+        if self._stage_src is not None and x is self._stage_src:
+            cur.wait_event(self._stage_ready)          # the copy issued during the previous step
+            self.x_static.copy_(self._stage, non_blocking=True)
+        else:
+            self.x_static.copy_(x, non_blocking=True)
+        self._stage_src = None
+        if prefetch is not None:
+            if tuple(prefetch.shape) != tuple(self.x_static.shape):
+                raise RuntimeError(f"prefetch: expected shape {tuple(self.x_static.shape)}, got {tuple(prefetch.shape)}")
+            if self._stage is None:
+                self._stage = torch.empty_like(self.x_static)
+                self._copy_stream = torch.cuda.Stream(device=self.device)
+                self._stage_ready, self._stage_free = torch.cuda.Event(), torch.cuda.Event()
+            self._stage_free.record(cur)                # staging buffer is free once x_static has been filled from it
+            self._copy_stream.wait_event(self._stage_free)
+            with torch.cuda.stream(self._copy_stream):
+                self._stage.copy_(prefetch, non_blocking=True)
+                self._stage_ready.record(self._copy_stream)
+            self._stage_src = prefetch
+
+    def step(self, x: torch.Tensor, prefetch: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One optimisation step on x [N,F] (device tensor, or pinned host tensor -> async H2D).
+        ``prefetch``: the batch of the NEXT step (same shape); its host->device copy is started on a separate stream
+        so it runs under this step's kernels -- pass the same tensor object as ``x`` to the next call.
         Returns a VIEW of the 4 loss scalars (loss, recon, commitment, codebook; summed over ranks -- divide
         by ``world``) that the next step overwrites."""
         if tuple(x.shape) != tuple(self.x_static.shape):
             raise RuntimeError(f"expected input of shape {tuple(self.x_static.shape)}, got {tuple(x.shape)}")
-        self.x_static.copy_(x, non_blocking=True)
+        self._load_input(x, prefetch)
         if self.use_graph and self._graph_a is None:
             self._capture()
         if self.use_graph and self._graph_full is not None:

@@ -128,3 +128,25 @@ def test_t1_training_step_at_baseline_batch():
     assert losses[-1] < losses[0]
     toks = tr.tokenize(x.to(DEV))
     assert toks.shape == (N,) and int(toks.min()) >= 0 and int(toks.max()) < K
+
+
+def test_trainer_prefetch_matches_plain_steps():
+    """step(x, prefetch=x_next) (next batch's H2D copy under this step's kernels) gives the same losses as feeding the
+    same pinned batches one call at a time (to fp32 reduction-order noise: dW/db/codebook sums use atomics)."""
+    import lipvq as L
+    from lipvq.trainer import TokenizerTrainer
+    F_, D, K, N = 12, 64, 512, 8192
+    xs = [(torch.rand(N, F_, generator=torch.Generator().manual_seed(50 + i)) * 2 - 1).pin_memory() for i in range(4)]
+    out = []
+    for use_prefetch in (False, True):
+        torch.manual_seed(0)
+        m = L.LLFQVAE_V4(F_, D, K)
+        m.quantizer = L.LFQQuantizerEMA(K, D)
+        m.to(DEV).train()
+        tr = TokenizerTrainer(m, N, use_graph=True)
+        ls = []
+        for i in range(6):
+            nxt = xs[(i + 1) % 4] if use_prefetch else None
+            ls.append(tr.step(xs[i % 4], prefetch=nxt).cpu().clone())
+        out.append(torch.stack(ls))
+    assert torch.allclose(out[0], out[1], rtol=2e-5, atol=1e-7), (out[0] - out[1]).abs().max()
