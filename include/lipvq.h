@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 1
+#define LIPVQ_ABI_VERSION 2
 #define LIPVQ_API __attribute__((visibility("default")))
 
 enum {
@@ -59,7 +59,9 @@ enum {
   LIPVQ_ACT_NONE = 0,
   LIPVQ_ACT_RELU = 1,
   LIPVQ_ACT_GELU = 2,    /* exact erf GELU (nn.GELU() default) */
-  LIPVQ_ACT_SIGMOID = 3
+  LIPVQ_ACT_SIGMOID = 3,
+  LIPVQ_ACT_GIVEN = 4    /* lipvq_linear_bwd_x_f32 only: X already holds act'(pre-activation), as written by
+                            lipvq_linear_fwd_dual_f32 */
 };
 
 /* EMA codebook normalisation variants */
@@ -170,6 +172,12 @@ LIPVQ_API int lipvq_codebook_usage_f32(const float* cluster_size, int K, float d
  * --------------------------------------------------------------------------------------------- */
 LIPVQ_API int lipvq_linear_fwd_f32(const float* X, int64_t N, int in_dim, int act_in, const float* W, const float* bias,
                          int out_dim, int act_out, float* Y, void* stream);
+/* Training-time forward: Y = act_out(pre) AND dYdpre = act_out'(pre), pre = act_in(X) W^T + b, from one evaluation of
+ * the activation in the producing layer's epilogue.  Consumers then read Y with act_in = NONE and the backward pass
+ * multiplies by dYdpre (act_in = LIPVQ_ACT_GIVEN) instead of re-evaluating erf per consumer.  Same arithmetic as
+ * nn.Linear -> nn.GELU and its autograd (backbone_lfqvae_v5.py:54-68). */
+LIPVQ_API int lipvq_linear_fwd_dual_f32(const float* X, int64_t N, int in_dim, int act_in, const float* W, const float* bias,
+                              int out_dim, int act_out, float* Y, float* dYdpre, void* stream);
 LIPVQ_API int lipvq_linear_bwd_x_f32(const float* dY, int64_t N, int out_dim, const float* W, int in_dim, const float* X,
                            int act_in, float* dX, void* stream);
 LIPVQ_API int lipvq_linear_bwd_w_f32(const float* dY, int64_t N, int out_dim, const float* X, int in_dim, int act_in, float* dW,

@@ -17,10 +17,11 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 
 // tcgen05 linear layers (linear_tc.cu): mode 0 = forward (bias + act_out), mode 1 = backward-x (* act_in'(Xpre)).
 // B[n][k] = W[n * w_rs + k * w_cs].
-bool linear_tc_supported(int mode, int64_t N, int Ka, int Nb);
+// dual (forward only): C2 also receives act_out'(pre) -- one activation evaluation serves every later consumer.
+bool linear_tc_supported(int mode, int64_t N, int Ka, int Nb, bool dual = false);
 int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, int actA, const float* W, int64_t w_rs,
                      int64_t w_cs, int Nb, float* C, int64_t ldc, const float* bias, int act_out, const float* Xpre,
-                     int64_t ldx, int act_in, cudaStream_t stream);
+                     int64_t ldx, int act_in, cudaStream_t stream, float* C2 = nullptr);
 // weight gradient dW += dY^T act(X), db += colsum(dY) with the reduction over tokens on the tensor cores
 bool linear_tc_bwd_w_supported(int64_t N, int out_dim, int in_dim, int actX, const float* dY, const float* X);
 int linear_tc_bwd_w_launch(const float* dY, int64_t N, int out_dim, const float* X, int in_dim, int actX, float* dW, float* db,
@@ -78,6 +79,7 @@ __device__ __forceinline__ float act_grad(int act, float x) {
       const float y = 1.f / (1.f + expf(-x));
       return y * (1.f - y);
     }
+    case LIPVQ_ACT_GIVEN: return x;  // the caller stored act'(pre) itself
     default: return 1.f;
   }
 }

@@ -323,6 +323,16 @@ __global__ void __launch_bounds__(256)
 }
 
 }  // namespace
+// y = act(pre), pre_io = act'(pre)   (fallback of the dual forward on the FFMA path)
+__global__ void __launch_bounds__(256)
+    act_dual_kernel(float* __restrict__ pre_io, float* __restrict__ y, int act, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const float pre = pre_io[i];
+    y[i] = act_apply(act, pre);
+    pre_io[i] = act_grad(act, pre);
+  }
+}
+
 }  // namespace lipvq
 
 using namespace lipvq;
@@ -345,6 +355,27 @@ int lipvq_linear_fwd_f32(const float* X, int64_t N, int in_dim, int act_in, cons
   g.M = N; g.N = out_dim; g.K = in_dim; g.k_chunk = (in_dim + BK - 1) / BK * BK;
   g.bias = bias; g.act_out = act_out;
   return launch_gemm_bn<L_KC, L_KC, MODE_FWD>(g, stream);
+}
+
+int lipvq_linear_fwd_dual_f32(const float* X, int64_t N, int in_dim, int act_in, const float* W, const float* bias,
+                              int out_dim, int act_out, float* Y, float* dYdpre, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(N >= 0 && in_dim > 0 && out_dim > 0, "linear_fwd_dual: bad shape");
+  if (N == 0) return LIPVQ_OK;
+  LIPVQ_REQUIRE(X && W && Y && dYdpre, "linear_fwd_dual: null pointer");
+  LIPVQ_REQUIRE(act_out >= LIPVQ_ACT_NONE && act_out <= LIPVQ_ACT_SIGMOID, "linear_fwd_dual: bad activation %d", act_out);
+  if (linear_tc_supported(0, N, in_dim, out_dim, true))
+    return linear_tc_launch(0, X, N, in_dim, in_dim, act_in, W, in_dim, 1, out_dim, Y, out_dim, bias, act_out, nullptr, 0,
+                            LIPVQ_ACT_NONE, stream, dYdpre);
+  // FFMA tiles: pre-activation into dYdpre, then one elementwise pass
+  const int rc = lipvq_linear_fwd_f32(X, N, in_dim, act_in, W, bias, out_dim, LIPVQ_ACT_NONE, dYdpre, stream_);
+  if (rc != LIPVQ_OK) return rc;
+  const int64_t numel = N * (int64_t)out_dim;
+  int64_t blocks = ceil_div64(numel, 256);
+  if (blocks > 8 * sm_count()) blocks = 8 * sm_count();
+  act_dual_kernel<<<(unsigned)blocks, 256, 0, stream>>>(dYdpre, Y, act_out, numel);
+  LIPVQ_LAUNCHED("act_dual_kernel");
+  return LIPVQ_OK;
 }
 
 int lipvq_linear_bwd_x_f32(const float* dY, int64_t N, int out_dim, const float* W, int in_dim, const float* X,

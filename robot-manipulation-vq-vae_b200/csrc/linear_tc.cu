@@ -7,9 +7,11 @@
 //   backward   dX = (dY W) * act_in'(Xpre)         A = dY [N, out], B[n][k] = W[k][n]
 //
 // One persistent CTA per SM (800 threads; both software roles are dependent-instruction chains, so they get many warps):
-//   warps 0-7   epilogue: tcgen05.ld (TMEM lane = token row) -> bias/activation or activation gradient -> global
-//   warps 8-23  converters: fp32 rows -> activation -> bf16 (h, m, l) -> 128B-swizzled K-major A tiles
+//   warps 0-15  epilogue: tcgen05.ld (TMEM lane = token row) -> bias/activation (and its derivative) or activation
+//               gradient -> per-warp swizzled scratch tile -> global stores with whole sectors per row
+//   warps 16-23 converters: fp32 rows -> (activation) -> bf16 (h, m, l) -> 128B-swizzled K-major A tiles
 //   warp  24    TMEM allocation + single-thread tcgen05.mma issue
+// (the weight-gradient kernel below keeps 8 epilogue + 16 converter warps: all of its work is conversion)
 // The weight matrix (<= 256 x 128) is split and laid out in shared memory once per CTA by all threads: no workspace,
 // no second launch.  Accumulators ping-pong between two TMEM buffers; A tiles are double-buffered when they fit.
 //
@@ -31,13 +33,32 @@ constexpr int kATile = kBM * kChunk * 2;  // 16 KB
 constexpr int kEpiWarps = 8, kCvtWarps = 16;  // plenty of warps per scheduler: both roles are latency-bound chains
 constexpr int kWarpMma = kEpiWarps + kCvtWarps;
 constexpr int kThreads = 32 * (kWarpMma + 1);  // 800 -> 80 registers per thread
-constexpr int kCvtItems = (kBM * 8) / (kCvtWarps * 32);  // 16-byte items per converter thread and chunk (2)
+// forward / backward-x kernel: activations are evaluated in the epilogue (once per element, see the dual forward), so
+// that role gets sixteen warps (four per TMEM lane quadrant, splitting the columns) and the converters eight
+constexpr int kEpiF = 16, kCvtF = 8;
+static_assert(kEpiF + kCvtF == kWarpMma, "same MMA warp and block size in both kernels");
+constexpr int kCvtItems = (kBM * 8) / (kCvtF * 32);  // 16-byte items per converter thread and chunk (4)
+
+#ifdef LIPVQ_TRACE
+// developer build: lane 0 of every warp of CTA 0 logs (clock64 << 8 | event)
+constexpr int kTraceMax = 1024;
+__device__ unsigned long long g_ltrace[32][kTraceMax];
+__device__ int g_ltrace_n[32];
+#define TR(ev)                                                                                  \
+  do {                                                                                          \
+    if (blockIdx.x == 0 && lane == 0 && tr_n < kTraceMax)                                       \
+      g_ltrace[warp][tr_n++] = ((unsigned long long)clock64() << 8) | (unsigned long long)(ev); \
+  } while (0)
+#else
+#define TR(ev) do {} while (0)
+#endif
 
 struct LinTcParams {
   const float* A; int64_t N; int Ka; int64_t lda; int actA;
   const float* W; int64_t w_rs, w_cs;  // B[n][k] = W[n * w_rs + k * w_cs]
   int Nb;
   float* C; int64_t ldc;
+  float* C2;                                 // mode 0, optional: act_out'(pre), same layout as C
   const float* bias; int act_out;            // mode 0
   const float* Xpre; int64_t ldx; int act_in;  // mode 1
   int mode, NC, Nbp, nbufA;
@@ -61,6 +82,7 @@ __device__ __forceinline__ void dispatch_act(int act, F&& body) {
     case LIPVQ_ACT_RELU: body(ActTag<LIPVQ_ACT_RELU>{}); break;
     case LIPVQ_ACT_GELU: body(ActTag<LIPVQ_ACT_GELU>{}); break;
     case LIPVQ_ACT_SIGMOID: body(ActTag<LIPVQ_ACT_SIGMOID>{}); break;
+    case LIPVQ_ACT_GIVEN: body(ActTag<LIPVQ_ACT_GIVEN>{}); break;
     default: body(ActTag<LIPVQ_ACT_NONE>{}); break;
   }
 }
@@ -77,7 +99,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
   uint8_t* sA = smem;
   uint8_t* sB = sA + p.nbufA * a_bytes;           // [term][chunk]
   float* bias_s = reinterpret_cast<float*>(sB + 3 * p.NC * b_tile);  // [256]
-  uint64_t* bars = reinterpret_cast<uint64_t*>(bias_s + 256);
+  float* epi_scr = bias_s + 256;                                     // [1 or 2 banks][16 epilogue warps][32 x 16] fp32
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_scr + (p.C2 != nullptr ? 2 : 1) * kEpiF * 512);
   const uint32_t bar_a_full = smem_u32(bars + 0), bar_a_empty = smem_u32(bars + 2);
   const uint32_t bar_acc_full = smem_u32(bars + 4), bar_acc_empty = smem_u32(bars + 6);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
@@ -86,45 +109,70 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
   const int row_blocks = (int)((p.N + kBM - 1) / kBM);
   const int nblk = ((int)blockIdx.x < row_blocks) ? (row_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   if (nblk == 0) return;
+#ifdef LIPVQ_TRACE
+  int tr_n = 0;
+  TR(0);
+#endif
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < 2; ++s) {
-      mbar_init(bar_a_full + 8 * s, kCvtWarps);
+      mbar_init(bar_a_full + 8 * s, kCvtF);
       mbar_init(bar_a_empty + 8 * s, 1);
       mbar_init(bar_acc_full + 8 * s, 1);
-      mbar_init(bar_acc_empty + 8 * s, kEpiWarps);
+      mbar_init(bar_acc_empty + 8 * s, kEpiF);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
 
   // ---- weights: split into (h, m, l) and store as swizzled K-major tiles; bias to smem ----
+  // An item is one 16-byte chunk of a tile row: 8 consecutive k of one output n.  Threads follow the contiguous direction
+  // of W (k for the forward layout, n for the transposed one), so the loads coalesce; the swizzle spreads the 16-byte
+  // stores of consecutive n over the banks.
   {
-    const int Kp = p.NC * kChunk;
-    const int total = p.Nbp * Kp;
-    const bool n_fast = (p.w_rs == 1);  // consecutive threads follow the contiguous direction of W
-    // batches of 8 elements per thread with the (L2-latency) loads issued before the first store
-    for (int base = 0; base < total; base += 8 * kThreads) {
-      float wv[8];
+    const int KC = p.NC * (kChunk / 8);  // chunks per row: 8 or 16
+    const int items = p.Nbp * KC;
+    const bool k_fast = (p.w_cs == 1);
+    const bool vec = k_fast && (p.w_rs % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.W) & 15) == 0);
+    for (int base = 0; base < items; base += 2 * kThreads) {
+      float wv[2][8];
+      int nn[2], kc[2];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int idx = base + u * kThreads + (int)threadIdx.x;
-        const int n = n_fast ? idx % p.Nbp : idx / Kp, k = n_fast ? idx / p.Nbp : idx % Kp;
-        wv[u] = (idx < total && n < p.Nb && k < p.Ka) ? __ldg(p.W + (int64_t)n * p.w_rs + (int64_t)k * p.w_cs) : 0.f;
+      for (int u = 0; u < 2; ++u) {
+        const int it = base + u * kThreads + (int)threadIdx.x;
+        nn[u] = k_fast ? it / KC : it % p.Nbp;
+        kc[u] = k_fast ? it % KC : it / p.Nbp;
+        const int k0 = kc[u] * 8;
+        const bool live = it < items && nn[u] < p.Nb;
+        const float* src = p.W + (int64_t)nn[u] * p.w_rs + (int64_t)k0 * p.w_cs;
+        if (live && vec && k0 + 8 <= p.Ka) {
+          const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
+          wv[u][0] = a.x; wv[u][1] = a.y; wv[u][2] = a.z; wv[u][3] = a.w;
+          wv[u][4] = b.x; wv[u][5] = b.y; wv[u][6] = b.z; wv[u][7] = b.w;
+        } else {
+#pragma unroll
+          for (int e = 0; e < 8; ++e) wv[u][e] = (live && k0 + e < p.Ka) ? __ldg(src + (int64_t)e * p.w_cs) : 0.f;
+        }
       }
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-        const int idx = base + u * kThreads + (int)threadIdx.x;
-        if (idx >= total) continue;
-        const int n = n_fast ? idx % p.Nbp : idx / Kp, k = n_fast ? idx / p.Nbp : idx % Kp;
-        __nv_bfloat16 h, m, l;
-        split3(wv[u], h, m, l);
-        const int c = k >> 6, kk = k & 63;
-        const uint32_t off = (uint32_t)(n * 128 + ((((kk >> 3) ^ (n & 7))) << 4) + (kk & 7) * 2);
-        uint8_t* t0 = sB + c * b_tile + off;
-        *reinterpret_cast<__nv_bfloat16*>(t0) = h;
-        *reinterpret_cast<__nv_bfloat16*>(t0 + p.NC * b_tile) = m;
-        *reinterpret_cast<__nv_bfloat16*>(t0 + 2 * p.NC * b_tile) = l;
+      for (int u = 0; u < 2; ++u) {
+        const int it = base + u * kThreads + (int)threadIdx.x;
+        if (it >= items) continue;
+        uint32_t hh[4], mm[4], ll[4];
+#pragma unroll
+        for (int e = 0; e < 8; e += 2) {
+          __nv_bfloat16 h0, m0, l0, h1, m1, l1;
+          split3(wv[u][e], h0, m0, l0);
+          split3(wv[u][e + 1], h1, m1, l1);
+          hh[e >> 1] = pack2(h0, h1);
+          mm[e >> 1] = pack2(m0, m1);
+          ll[e >> 1] = pack2(l0, l1);
+        }
+        const int c = kc[u] >> 3, n = nn[u];
+        uint8_t* t0 = sB + c * b_tile + (uint32_t)(n * 128 + (((kc[u] & 7) ^ (n & 7)) << 4));
+        *reinterpret_cast<uint4*>(t0) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+        *reinterpret_cast<uint4*>(t0 + p.NC * b_tile) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+        *reinterpret_cast<uint4*>(t0 + 2 * p.NC * b_tile) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
       }
     }
     for (int i = threadIdx.x; i < 256; i += kThreads)
@@ -135,6 +183,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
   __syncthreads();
   fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  TR(1);
 
   if (warp == kWarpMma) {
     // ===== MMA issuer =====
@@ -145,8 +194,10 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
         const int buf = i % p.nbufA;
         const uint32_t ab = (uint32_t)i & 1;
         mbar_wait(bar_a_full + 8 * buf, (uint32_t)(i / p.nbufA) & 1);
+        TR(30);
         mbar_wait(bar_acc_empty + 8 * ab, (((uint32_t)i >> 1) & 1) ^ 1);
         fence_after();
+        TR(31);
         const uint32_t d_tmem = tmem_base + ab * (uint32_t)p.Nbp;
         const uint32_t a_base = smem_u32(sA + buf * a_bytes);
         uint32_t first = 0;
@@ -166,17 +217,17 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
         }
         umma_commit(bar_acc_full + 8 * ab);
         umma_commit(bar_a_empty + 8 * buf);
+        TR(32);
       }
     }
-  } else if (warp >= kEpiWarps) {
-    // ===== converters =====
-    const int tcv = (int)threadIdx.x - kEpiWarps * 32;
-    const int ch = tcv & 7, r0 = tcv >> 3;
+  } else if (warp >= kEpiF) {
+    // ===== converters: fp32 rows -> (activation) -> bf16 (h, m, l) -> swizzled A tiles =====
+    const int tcv = (int)threadIdx.x - kEpiF * 32;
+    const int ch = tcv & 7, r0 = tcv >> 3;  // 16-byte chunk of the 128-byte tile row; rows r0 + 32 u
     const bool fast = (p.Ka % 8 == 0) && (p.lda % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.A) & 15) == 0);
     for (int i = 0; i < nblk; ++i) {
       const int buf = i % p.nbufA;
       const int64_t rb = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
-      mbar_wait(bar_a_empty + 8 * buf, (((uint32_t)(i / p.nbufA)) & 1) ^ 1);
       uint8_t* a_buf = sA + buf * a_bytes;
       for (int c = 0; c < p.NC; ++c) {
         const int col = c * kChunk + ch * 8;
@@ -187,35 +238,32 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
           vb[u] = va[u];
         }
         if (col < p.Ka) {
-          if (fast) {
 #pragma unroll
-            for (int u = 0; u < kCvtItems; ++u) {
-              const int64_t row = rb * kBM + r0 + (kCvtWarps * 4) * u;
-              if (row < p.N) {
-                const float4* src = reinterpret_cast<const float4*>(p.A + row * p.lda + col);
-                va[u] = __ldg(src);
-                vb[u] = __ldg(src + 1);
-              }
-            }
-          } else {
+          for (int u = 0; u < kCvtItems; ++u) {
+            const int64_t row = rb * kBM + r0 + 32 * u;
+            if (row >= p.N) continue;
+            const float* src = p.A + row * p.lda + col;
+            if (fast) {
+              va[u] = __ldg(reinterpret_cast<const float4*>(src));
+              vb[u] = __ldg(reinterpret_cast<const float4*>(src) + 1);
+            } else {
+              float t[8];
 #pragma unroll
-            for (int u = 0; u < kCvtItems; ++u) {
-              const int64_t row = rb * kBM + r0 + (kCvtWarps * 4) * u;
-              if (row < p.N) {
-                const float* src = p.A + row * p.lda + col;
-                float t[8];
-#pragma unroll
-                for (int e = 0; e < 8; ++e) t[e] = (col + e < p.Ka) ? __ldg(src + e) : 0.f;
-                va[u] = make_float4(t[0], t[1], t[2], t[3]);
-                vb[u] = make_float4(t[4], t[5], t[6], t[7]);
-              }
+              for (int e = 0; e < 8; ++e) t[e] = (col + e < p.Ka) ? __ldg(src + e) : 0.f;
+              va[u] = make_float4(t[0], t[1], t[2], t[3]);
+              vb[u] = make_float4(t[4], t[5], t[6], t[7]);
             }
           }
+        }
+        if (c == 0) {  // the loads above are already in flight while this waits for the MMAs that read the buffer
+          TR(20);
+          mbar_wait(bar_a_empty + 8 * buf, (((uint32_t)(i / p.nbufA)) & 1) ^ 1);
+          TR(21);
         }
 #pragma unroll
         for (int u = 0; u < kCvtItems; ++u) {
           const float x[8] = {va[u].x, va[u].y, va[u].z, va[u].w, vb[u].x, vb[u].y, vb[u].z, vb[u].w};
-          const int64_t row = rb * kBM + r0 + (kCvtWarps * 4) * u;
+          const int64_t row = rb * kBM + r0 + 32 * u;
           uint32_t hh[4], mm[4], ll[4];
           float y[8];
           dispatch_act(p.actA, [&](auto tag) {
@@ -226,15 +274,14 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
           });
 #pragma unroll
           for (int e = 0; e < 8; e += 2) {
-            const float y0 = y[e], y1 = y[e + 1];
             __nv_bfloat16 h0, m0, l0, h1, m1, l1;
-            split3(y0, h0, m0, l0);
-            split3(y1, h1, m1, l1);
+            split3(y[e], h0, m0, l0);
+            split3(y[e + 1], h1, m1, l1);
             hh[e >> 1] = pack2(h0, h1);
             mm[e >> 1] = pack2(m0, m1);
             ll[e >> 1] = pack2(l0, l1);
           }
-          const int r = r0 + (kCvtWarps * 4) * u;
+          const int r = r0 + 32 * u;
           const uint32_t off = (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
           *reinterpret_cast<uint4*>(a_buf + (0 * p.NC + c) * kATile + off) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
           *reinterpret_cast<uint4*>(a_buf + (1 * p.NC + c) * kATile + off) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
@@ -244,36 +291,114 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
       fence_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_a_full + 8 * buf);
+      TR(23);
     }
   } else {
-    // ===== epilogue warps 0-7: TMEM lane quadrant q, every second 16-column group =====
-    const int q = warp & 3, half = warp >> 2;
+    // ===== epilogue warps 0-15: TMEM lane quadrant q = warp & 3, 16-column groups part, part + 4, ... =====
+    // TMEM hands each lane one token row, but a warp-wide global access with one row per lane touches 32 different
+    // lines.  Every 32x16 group therefore passes through this warp's swizzled scratch tile, so global loads (Xpre) and
+    // stores run with four lanes per 64-byte row segment (whole sectors).
+    const int q = warp & 3, part = warp >> 2;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-    const bool vecC = (p.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0);
+    const bool vecC = (p.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0) &&
+                      ((reinterpret_cast<uintptr_t>(p.C2) & 15) == 0);
     const bool vecX = p.mode == 1 && p.Xpre != nullptr && (p.ldx % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.Xpre) & 15) == 0);
+    const bool mulX = p.mode == 1 && p.act_in != LIPVQ_ACT_NONE;
+    const bool dual = p.mode == 0 && p.C2 != nullptr;
+    float* scr = epi_scr + warp * 512;           // [32 rows][4 chunks of 4 floats]; chunk j of row r sits at j ^ ((r >> 1) & 3)
+    float* scr2 = scr + kEpiF * 512;             // derivative tile of the dual forward
+    const int gr = lane >> 2, gj = lane & 3;     // coalesced side: row 8 * it + gr, chunk gj
+    const int rsw = (lane >> 1) & 3;             // row side: this lane's token row, chunk j at j ^ rsw
+    float* my_row = scr + lane * 16;
+    auto load_x = [&](int c0, int64_t row0, float4 (&xr)[4]) {
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int r = 8 * it + gr, col = c0 + 4 * gj;
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row0 + r < p.N && col < p.Nb) {
+          const float* xp = p.Xpre + (row0 + r) * p.ldx + col;
+          if (vecX && col + 4 <= p.Nb) {
+            t = __ldg(reinterpret_cast<const float4*>(xp));
+          } else {
+            t.x = __ldg(xp);
+            if (col + 1 < p.Nb) t.y = __ldg(xp + 1);
+            if (col + 2 < p.Nb) t.z = __ldg(xp + 2);
+            if (col + 3 < p.Nb) t.w = __ldg(xp + 3);
+          }
+        }
+        xr[it] = t;
+      }
+    };
+    auto store_tile = [&](const float* tile, float* dst, int c0, int64_t row0) {
+#pragma unroll
+      for (int it = 0; it < 4; ++it) {
+        const int r = 8 * it + gr, col = c0 + 4 * gj;
+        const float4 t = *reinterpret_cast<const float4*>(tile + r * 16 + ((gj ^ ((r >> 1) & 3)) << 2));
+        if (row0 + r < p.N && col < p.Nb) {
+          float* cp = dst + (row0 + r) * p.ldc + col;
+          if (vecC && col + 4 <= p.Nb) {
+            *reinterpret_cast<float4*>(cp) = t;
+          } else {
+            cp[0] = t.x;
+            if (col + 1 < p.Nb) cp[1] = t.y;
+            if (col + 2 < p.Nb) cp[2] = t.z;
+            if (col + 3 < p.Nb) cp[3] = t.w;
+          }
+        }
+      }
+    };
     for (int i = 0; i < nblk; ++i) {
       const uint32_t ab = (uint32_t)i & 1;
       const int64_t rb = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
-      const int64_t row = rb * kBM + q * 32 + lane;
+      const int64_t row0 = rb * kBM + q * 32;
+      float4 xr[4];
+      if (mulX && 16 * part < p.Nbp) load_x(16 * part, row0, xr);  // independent of the MMA: in flight during the wait
+      TR(10);
       mbar_wait(bar_acc_full + 8 * ab, ((uint32_t)i >> 1) & 1);
       fence_after();
+      TR(11);
       const uint32_t trow = tmem_base + ab * (uint32_t)p.Nbp + lane_off;
-      if (16 * half >= p.Nbp) {  // narrow outputs: this warp has no column group
+      if (16 * part >= p.Nbp) {  // narrow outputs: this warp has no column group
         fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
       }
-      for (int c0 = 16 * half; c0 < p.Nbp; c0 += 32) {
+      for (int c0 = 16 * part; c0 < p.Nbp; c0 += 64) {
+        const bool last = c0 + 64 >= p.Nbp;
+        if (mulX) {
+#pragma unroll
+          for (int it = 0; it < 4; ++it) {
+            const int r = 8 * it + gr;
+            *reinterpret_cast<float4*>(scr + r * 16 + ((gj ^ ((r >> 1) & 3)) << 2)) = xr[it];
+          }
+          __syncwarp();
+        }
         uint32_t v[16];
         tmem_ld16(trow + c0, v); tmem_ld_wait16(v);
-        if (c0 + 32 >= p.Nbp) {  // this warp's last group is in registers: release the accumulator before the math
+        if (last) {  // this warp's last load: release the accumulator before the math
           fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
+        } else if (mulX) {
+          load_x(c0 + 64, row0, xr);
         }
-        if (row >= p.N || c0 >= p.Nb) continue;
         float o[16];
-        if (p.mode == 0) {
+        if (dual) {  // value and derivative from one evaluation (erf is shared after inlining)
+          dispatch_act(p.act_out, [&](auto tag) {
+            constexpr int ACT = decltype(tag)::value;
+#pragma unroll
+            for (int e4 = 0; e4 < 4; ++e4) {
+              float d[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float pre = __uint_as_float(v[4 * e4 + e]) + bias_s[c0 + 4 * e4 + e];
+                o[4 * e4 + e] = act_apply(ACT, pre);
+                d[e] = act_grad(ACT, pre);
+              }
+              *reinterpret_cast<float4*>(scr2 + lane * 16 + ((e4 ^ rsw) << 2)) = make_float4(d[0], d[1], d[2], d[3]);
+            }
+          });
+        } else if (p.mode == 0) {
           dispatch_act(p.act_out, [&](auto tag) {
             constexpr int ACT = decltype(tag)::value;
 #pragma unroll
@@ -282,18 +407,12 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
         } else {
 #pragma unroll
           for (int e = 0; e < 16; ++e) o[e] = __uint_as_float(v[e]);
-          if (p.act_in != LIPVQ_ACT_NONE) {
-            const float* xp = p.Xpre + row * p.ldx + c0;
+          if (mulX) {
             float xv[16];
-            if (vecX && c0 + 16 <= p.Nb) {
 #pragma unroll
-              for (int e = 0; e < 16; e += 4) {
-                const float4 t = __ldg(reinterpret_cast<const float4*>(xp + e));
-                xv[e] = t.x; xv[e + 1] = t.y; xv[e + 2] = t.z; xv[e + 3] = t.w;
-              }
-            } else {
-#pragma unroll
-              for (int e = 0; e < 16; ++e) xv[e] = (c0 + e < p.Nb) ? __ldg(xp + e) : 0.f;
+            for (int e4 = 0; e4 < 4; ++e4) {
+              const float4 t = *reinterpret_cast<const float4*>(my_row + ((e4 ^ rsw) << 2));
+              xv[4 * e4] = t.x; xv[4 * e4 + 1] = t.y; xv[4 * e4 + 2] = t.z; xv[4 * e4 + 3] = t.w;
             }
             dispatch_act(p.act_in, [&](auto tag) {
               constexpr int ACT = decltype(tag)::value;
@@ -302,25 +421,29 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
             });
           }
         }
-        float* cp = p.C + row * p.ldc + c0;
-        if (vecC && c0 + 16 <= p.Nb) {
 #pragma unroll
-          for (int e = 0; e < 16; e += 4) *reinterpret_cast<float4*>(cp + e) = make_float4(o[e], o[e + 1], o[e + 2], o[e + 3]);
-        } else {
-#pragma unroll
-          for (int e = 0; e < 16; ++e)
-            if (c0 + e < p.Nb) cp[e] = o[e];
-        }
+        for (int e4 = 0; e4 < 4; ++e4)  // the slots this lane just read: no cross-lane hazard
+          *reinterpret_cast<float4*>(my_row + ((e4 ^ rsw) << 2)) = make_float4(o[4 * e4], o[4 * e4 + 1], o[4 * e4 + 2], o[4 * e4 + 3]);
+        __syncwarp();
+        store_tile(scr, p.C, c0, row0);
+        if (dual) store_tile(scr2, p.C2, c0, row0);
+        __syncwarp();
       }
+      TR(14);
     }
   }
 
+  TR(2);
   fence_before();
   __syncthreads();
   if (warp == kWarpMma) {
     fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
   }
+#ifdef LIPVQ_TRACE
+  TR(3);
+  if (blockIdx.x == 0 && lane == 0) g_ltrace_n[warp] = tr_n;
+#endif
 }
 
 // ---- weight gradient:  dW[o][k] += sum_t dY[t][o] * act(X)[t][k],  db[o] += sum_t dY[t][o] ---------------------------
@@ -352,6 +475,10 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
   const int blocks = (int)((p.N + kWTok - 1) / kWTok);
   const int nblk = ((int)blockIdx.x < blocks) ? (blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   if (nblk == 0) return;
+#ifdef LIPVQ_TRACE
+  int tr_n = 0;
+  TR(0);
+#endif
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < 2; ++s) {
@@ -368,6 +495,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
   __syncthreads();
   fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  TR(1);
 
   if (warp == kWarpMma) {
     if (lane == 0) {
@@ -377,6 +505,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
         const int buf = i & 1;
         mbar_wait(bar_full + 8 * buf, ((uint32_t)i >> 1) & 1);
         fence_after();
+        TR(30);
         const uint32_t a0 = smem_u32(smem + buf * buf_bytes), b0 = a0 + 3 * (uint32_t)a_tile;
         const int ta[6] = {1, 2, 0, 1, 0, 0}, tb[6] = {1, 0, 2, 0, 1, 0};  // smallest products first
 #pragma unroll
@@ -389,6 +518,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
           }
         }
         umma_commit(bar_empty + 8 * buf);
+        TR(32);
       }
       umma_commit(bar_done);
     }
@@ -417,7 +547,9 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
         ya[j] = (live && o < p.out_dim) ? __ldg(reinterpret_cast<const float4*>(p.dY + t * p.out_dim + o)) : make_float4(0.f, 0.f, 0.f, 0.f);
         xa[j] = (live && k < p.in_dim) ? __ldg(reinterpret_cast<const float4*>(p.X + t * p.in_dim + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
+      TR(20);
       mbar_wait(bar_empty + 8 * buf, (((uint32_t)i >> 1) & 1) ^ 1);
+      TR(21);
       uint8_t* a0 = smem + buf * buf_bytes;
       uint8_t* b0 = a0 + 3 * a_tile;
 #pragma unroll
@@ -445,13 +577,16 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
       fence_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_full + 8 * buf);
+      TR(23);
     }
   } else {
     // ===== epilogue warps 0-7: TMEM lane = output row o; every second 16-column group; one pass at the very end =====
     const int q = warp & 3, half = warp >> 2;
     const int o = q * 32 + lane;
+    TR(10);
     mbar_wait(bar_done, 0);
     fence_after();
+    TR(11);
     const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16);
     for (int c0 = 16 * half; c0 < p.Np; c0 += 32) {
       uint32_t v[16];
@@ -468,39 +603,49 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
     }
   }
 
+  TR(2);
   fence_before();
   __syncthreads();
   if (warp == kWarpMma) {
     fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
   }
+#ifdef LIPVQ_TRACE
+  TR(3);
+  if (blockIdx.x == 0 && lane == 0) g_ltrace_n[warp] = tr_n;
+#endif
 }
+#undef TR
 
-constexpr int kMisc = 256 * 4 + 128;
+constexpr int kMisc = 256 * 4 + kEpiF * 2048 + 128;  // bias, epilogue scratch (one bank), barriers
+constexpr int kDualScratch = kEpiF * 2048;            // second scratch bank of the dual forward
 
 }  // namespace
 
 // Shapes the tensor path takes: enough tokens to fill the SMs, reduction <= 128, width <= 256, everything fits smem.
 // LIPVQ_LINEAR_ALGO=simt forces the FFMA tiles (A/B runs).
-bool linear_tc_supported(int mode, int64_t N, int Ka, int Nb) {
+bool linear_tc_supported(int mode, int64_t N, int Ka, int Nb, bool dual) {
   if (const char* f = getenv("LIPVQ_LINEAR_ALGO"))
     if (f[0] == 's') return false;
   if (!(N >= 4096 && Ka >= 1 && Ka <= 128 && Nb >= 1 && Nb <= 256)) return false;
   // measured (scripts/bench_linear.py): a forward layer with a very short reduction and no activation on its input is
   // all epilogue, and the FFMA tiles are as fast there
-  if (mode == 0 && Ka < 32) return false;
+  // (the dual forward evaluates the activation in the epilogue, which the FFMA path cannot fuse: always worth it)
+  if (mode == 0 && Ka < 32 && !dual) return false;
   const int NC = (Ka + kChunk - 1) / kChunk, Nbp = (Nb + 15) / 16 * 16;
   const size_t a_bytes = (size_t)3 * NC * kATile, b_bytes = (size_t)3 * NC * Nbp * kChunk * 2;
-  return 1024 + a_bytes + b_bytes + kMisc <= 227 * 1024;
+  return 1024 + a_bytes + b_bytes + kMisc + (dual ? kDualScratch : 0) <= 227 * 1024;
 }
 
 int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, int actA, const float* W, int64_t w_rs,
                      int64_t w_cs, int Nb, float* C, int64_t ldc, const float* bias, int act_out, const float* Xpre,
-                     int64_t ldx, int act_in, cudaStream_t stream) {
+                     int64_t ldx, int act_in, cudaStream_t stream, float* C2) {
   LinTcParams p{};
   p.A = A; p.N = N; p.Ka = Ka; p.lda = lda; p.actA = actA;
   p.W = W; p.w_rs = w_rs; p.w_cs = w_cs; p.Nb = Nb;
   p.C = C; p.ldc = ldc; p.bias = bias; p.act_out = act_out;
+  p.C2 = (mode == 0) ? C2 : nullptr;
+  const size_t misc = kMisc + (p.C2 ? kDualScratch : 0);
   p.Xpre = Xpre; p.ldx = ldx; p.act_in = act_in;
   p.mode = mode;
   p.NC = (Ka + kChunk - 1) / kChunk;
@@ -509,8 +654,8 @@ int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, i
   while (cols < 2u * (uint32_t)p.Nbp) cols <<= 1;
   p.tmem_cols = cols;
   const size_t a_bytes = (size_t)3 * p.NC * kATile, b_bytes = (size_t)3 * p.NC * p.Nbp * kChunk * 2;
-  p.nbufA = (2 * a_bytes + b_bytes + kMisc + 1024 <= 227 * 1024) ? 2 : 1;
-  const size_t smem = 1024 + p.nbufA * a_bytes + b_bytes + kMisc;
+  p.nbufA = (2 * a_bytes + b_bytes + misc + 1024 <= 227 * 1024) ? 2 : 1;
+  const size_t smem = 1024 + p.nbufA * a_bytes + b_bytes + misc;
   if (smem > 227 * 1024) {
     set_error("linear_tc: shape Ka=%d Nb=%d does not fit shared memory", Ka, Nb);
     return LIPVQ_ERR_INVALID;
@@ -560,3 +705,11 @@ int linear_tc_bwd_w_launch(const float* dY, int64_t N, int out_dim, const float*
 }
 
 }  // namespace lipvq
+
+#ifdef LIPVQ_TRACE
+extern "C" LIPVQ_API int lipvq_debug_trace_linear(unsigned long long* out, int* counts) {
+  if (cudaMemcpyFromSymbol(out, lipvq::g_ltrace, sizeof(unsigned long long) * 32 * lipvq::kTraceMax) != cudaSuccess) return -1;
+  if (cudaMemcpyFromSymbol(counts, lipvq::g_ltrace_n, sizeof(int) * 32) != cudaSuccess) return -1;
+  return lipvq::kTraceMax;
+}
+#endif

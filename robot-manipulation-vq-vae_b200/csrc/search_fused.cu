@@ -35,6 +35,20 @@ constexpr int kZStage = kBM * kChunk * 4;     // one staged (row block, chunk): 
 constexpr int kStatSlots = 4;
 constexpr float kF16Safe = 3.0e4f;  // |x| below this survives the -2 scaling and fp16 conversion without overflow
 
+#ifdef LIPVQ_TRACE
+// developer build: lane 0 of every warp of CTA 0 logs (clock64 << 8 | event) for the fp16 pass
+constexpr int kTraceMax = 4096;
+__device__ unsigned long long g_trace[16][kTraceMax];
+__device__ int g_trace_n[16];
+#define TR(ev)                                                                                             \
+  do {                                                                                                     \
+    if (TERMS == 1 && blockIdx.x == 0 && lane == 0 && tr_n < kTraceMax)                                    \
+      g_trace[warp][tr_n++] = ((unsigned long long)clock64() << 8) | (unsigned long long)(ev);             \
+  } while (0)
+#else
+#define TR(ev) do {} while (0)
+#endif
+
 struct FusedParams {
   const float* z;
   const int* row_list;    // pass 2: rows to process (work queue of pass 1); nullptr = rows 0..N-1
@@ -315,6 +329,10 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t tmem_cols = 2u * (uint32_t)p.BN;  // 256 or 512
+#ifdef LIPVQ_TRACE
+  int tr_n = 0;
+  TR(0);
+#endif
 
   int64_t n_rows = p.N;
   if (p.n_rows_ptr) {
@@ -355,6 +373,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  TR(1);
 
   if (warp == kWarpTma) {
     // ===== TMA producer: code tiles =====
@@ -391,11 +410,13 @@ __global__ void __launch_bounds__(kThreads, 1)
         const int buf = i % p.nbufA;
         mbar_wait(bar_a_full + 8 * buf, (uint32_t)(i / p.nbufA) & 1);
         tc_fence_after();
+        TR(30);
         const uint32_t a_base = smem_u32(sA + buf * a_bytes);
         for (int j = 0; j < p.T; ++j, ++t) {
           const uint32_t ab = t & 1;
           mbar_wait(bar_acc_empty + 8 * ab, (t >> 1) & 1);  // epilogue drained it and stored this tile's ||e||^2
           tc_fence_after();
+          TR(31);
           const uint32_t d_tmem = tmem_base + ab * (uint32_t)p.BN;
           for (int c = 0; c < p.NC; ++c, ++sidx) {
             uint32_t st, par;
@@ -421,6 +442,7 @@ __global__ void __launch_bounds__(kThreads, 1)
             if (!p.resident) umma_commit(bar_b_empty + 8 * st);
           }
           umma_commit(bar_acc_full + 8 * ab);
+          TR(32);
         }
         umma_commit(bar_a_empty + 8 * buf);  // z block free once every MMA of this row block has retired
       }
@@ -457,7 +479,9 @@ __global__ void __launch_bounds__(kThreads, 1)
       float zn2[8], zo2[8];
 #pragma unroll
       for (int u = 0; u < 8; ++u) zn2[u] = zo2[u] = 0.f;
+      TR(20);
       mbar_wait(bar_a_empty + 8 * buf, ((uint32_t)(i / p.nbufA) & 1) ^ 1);
+      TR(21);
       uint8_t* a_buf = sA + buf * a_bytes;
       for (int c = 0; c < p.NC; ++c) {
         const int col = c * kChunk + ch * 8;
@@ -471,6 +495,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           const uint32_t unit = (uint32_t)(i * p.NC + c);
           const uint32_t st = unit % (uint32_t)p.zstages, par = (unit / (uint32_t)p.zstages) & 1;
           mbar_wait(bar_z_full + 8 * st, par);
+          TR(22);
           const float* zt = reinterpret_cast<const float*>(sZ + st * kZStage) + ch * 8;
 #pragma unroll
           for (int u = 0; u < 8; ++u)
@@ -552,6 +577,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy smem writes -> visible to the MMA
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_a_full + 8 * buf);
+      TR(23);
     }
   } else {
     // ===== epilogue warps 0-7: two groups of four; group g owns accumulator buffer g and drains every second tile =====
@@ -617,8 +643,10 @@ __global__ void __launch_bounds__(kThreads, 1)
       float4 en0 = make_float4(0.f, 0.f, 0.f, 0.f), en1 = en0;
       if (more) en_prefetch((t + 2) % p.T, en0, en1);
       float2 st = make_float2(0.f, 0.f);
+      TR(10);
       mbar_wait(bar_acc_full + 8 * g, (uint32_t)(t >> 1) & 1);
       tc_fence_after();
+      TR(11);
       auto fold = [&](const uint32_t (&v)[32], int kb) {
         float prev[4];
 #pragma unroll
@@ -640,10 +668,13 @@ __global__ void __launch_bounds__(kThreads, 1)
           // last load of this buffer has landed: hand it back to the MMA warp before folding the chunk.
           // (the converter may recycle the stat slot only after MMAs that need this release: read it first)
           if (j == p.T - 1) st = rowstat[(i % kStatSlots) * kBM + q * 32 + lane];
+          TR(12);
           if (more) en_store(en0, en1);
+          TR(13);
         }
         fold(v, kb0 + c0);
       }
+      TR(14);
       const bool last_of_block = (j == p.T - 1);
       const bool leaves_block = last_of_block || (j + 2 >= p.T);  // this group's next tile belongs to another row block
       if (!leaves_block) continue;
@@ -712,12 +743,17 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
   }
 
+  TR(2);
   tc_fence_before();
   __syncthreads();
   if (warp == kWarpMma) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
   }
+#ifdef LIPVQ_TRACE
+  TR(3);
+  if (TERMS == 1 && blockIdx.x == 0 && lane == 0) g_trace_n[warp] = tr_n;
+#endif
 }
 
 // exact winning value for the optional best_out: one warp per row
@@ -965,3 +1001,11 @@ int search_best_values(const float* z, int64_t N, int D, const float* cb, int me
 }
 
 }  // namespace lipvq
+
+#ifdef LIPVQ_TRACE
+extern "C" LIPVQ_API int lipvq_debug_trace(unsigned long long* out, int* counts) {
+  if (cudaMemcpyFromSymbol(out, lipvq::g_trace, sizeof(unsigned long long) * 16 * lipvq::kTraceMax) != cudaSuccess) return -1;
+  if (cudaMemcpyFromSymbol(counts, lipvq::g_trace_n, sizeof(int) * 16) != cudaSuccess) return -1;
+  return lipvq::kTraceMax;
+}
+#endif

@@ -3,7 +3,7 @@
 Importing this package loads liblipvq.so; it raises ImportError when the extension has not been built.
 """
 from . import _cabi
-from ._cabi import (ACT_GELU, ACT_NONE, ACT_RELU, ACT_SIGMOID, ALGO_AUTO, ALGO_SIMT_F32, ALGO_TCGEN05, EMA_LAPLACE,
+from ._cabi import (ACT_GELU, ACT_GIVEN, ACT_NONE, ACT_RELU, ACT_SIGMOID, ALGO_AUTO, ALGO_SIMT_F32, ALGO_TCGEN05, EMA_LAPLACE,
                     EMA_NORMALIZE, EMA_SIMPLE, METRIC_DOT, METRIC_L2, METRIC_L2SQ, launch_count)
 from . import ops
 from .modules import LFQQuantizer, LFQQuantizerEMA, LipschitzMLP, LLFQVAE_V4

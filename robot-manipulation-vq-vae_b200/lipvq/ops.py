@@ -151,6 +151,21 @@ def linear_fwd(x, act_in: int, W, bias, act_out: int, out=None):
     return y
 
 
+def linear_fwd_dual(x, act_in: int, W, bias, act_out: int, out, dout):
+    """out = act_out(pre), dout = act_out'(pre) with pre = act_in(x) W^T + b: the activation is evaluated once, in the
+    producing layer (training forward).  Consumers read ``out`` with act_in = NONE; linear_bwd_x takes ``dout`` with
+    act_in = ACT_GIVEN."""
+    in_dim = x.shape[-1]
+    N = x.numel() // in_dim
+    out_dim = W.shape[0]
+    if W.shape[1] != in_dim:
+        raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({N}x{in_dim} and {W.shape[1]}x{out_dim})")
+    A.check(lib.lipvq_linear_fwd_dual_f32(_chk(x, F32, "x"), N, in_dim, act_in, _chk(W, F32, "W"), _chk(bias, F32, "bias", True),
+                                          out_dim, act_out, _chk(out, F32, "y"), _chk(dout, F32, "dy_dpre"), _stream()),
+            "linear_fwd_dual")
+    return out, dout
+
+
 def linear_bwd_x(dY, W, Xpre, act_in: int, out=None):
     out_dim, in_dim = W.shape
     N = dY.numel() // out_dim

@@ -31,7 +31,9 @@ PARAM_SHAPES = lambda F, D, K, H=128: {  # state_dict order/names of LLFQVAE_V4 
 
 @dataclass
 class T1Buffers:
-    """Activations of one step.  Pre-activations are stored; consumers apply GELU while loading."""
+    """Activations of one step.  Hidden layers store GELU(pre) (a1, a2, c1, c2) and, for training, GELU'(pre) (the d*
+    buffers): the producing layer's epilogue evaluates erf once and every consumer (next layer, weight gradient, input
+    gradient) reads the result."""
     N: int
     F: int
     D: int
@@ -53,6 +55,12 @@ class T1Buffers:
             "ws": torch.empty(max(1, ops.search_workspace_bytes(N, D, K)), dtype=torch.uint8, device=dev),
         }
 
+    def alloc_derivatives(self):
+        N, H, dev = self.N, self.H, self.device
+        if "da1_act" not in self.t:
+            e = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
+            self.t.update({"da1_act": e(N, 64), "da2_act": e(N, H), "dc1_act": e(N, 64), "dc2_act": e(N, H)})
+
     def alloc_backward(self):
         N, F, D, H, dev = self.N, self.F, self.D, self.H, self.device
         e = lambda *s: torch.empty(*s, dtype=torch.float32, device=dev)
@@ -68,17 +76,22 @@ def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: 
     (the bulk-tokenisation path: encode + VQ)."""
     t = b.t
     ops.lipschitz_scale_fwd(p["to_latent.W"], p["to_latent.ci"], t["Wn"])
-    ops.linear_fwd(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_NONE, out=t["a1"])
-    ops.linear_fwd(t["a1"], A.ACT_GELU, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_NONE, out=t["a2"])
-    ops.linear_fwd(t["a2"], A.ACT_GELU, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"])
+    if encode_only:
+        ops.linear_fwd(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, out=t["a1"])
+        ops.linear_fwd(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, out=t["a2"])
+    else:
+        b.alloc_derivatives()
+        ops.linear_fwd_dual(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, t["a1"], t["da1_act"])
+        ops.linear_fwd_dual(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, t["a2"], t["da2_act"])
+    ops.linear_fwd(t["a2"], A.ACT_NONE, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"])
     ops.nn_search(t["z_e"], p["quantizer.codebook"], A.METRIC_L2, algo, out=t["idx"], workspace=t["ws"])
     if encode_only:
         return
     t["sq"].zero_()
     ops.gather_fwd(t["z_e"], t["idx"], p["quantizer.codebook"], t["sq"][1:], z_q=t["z_q"])
-    ops.linear_fwd(t["z_q"], A.ACT_NONE, p["decoder.0.weight"], p["decoder.0.bias"], A.ACT_NONE, out=t["c1"])
-    ops.linear_fwd(t["c1"], A.ACT_GELU, p["decoder.2.weight"], p["decoder.2.bias"], A.ACT_NONE, out=t["c2"])
-    ops.linear_fwd(t["c2"], A.ACT_GELU, p["to_output.weight"], p["to_output.bias"], A.ACT_NONE, out=t["x_recon"])
+    ops.linear_fwd_dual(t["z_q"], A.ACT_NONE, p["decoder.0.weight"], p["decoder.0.bias"], A.ACT_GELU, t["c1"], t["dc1_act"])
+    ops.linear_fwd_dual(t["c1"], A.ACT_NONE, p["decoder.2.weight"], p["decoder.2.bias"], A.ACT_GELU, t["c2"], t["dc2_act"])
+    ops.linear_fwd(t["c2"], A.ACT_NONE, p["to_output.weight"], p["to_output.bias"], A.ACT_NONE, out=t["x_recon"])
     ops.mse_fwd_bwd(t["x_recon"], x, t["sq"][0:1])
     ops.t1_loss_finalize(t["sq"], float(b.N) * b.F, float(b.N) * b.D, 0.25, 0.25, t["losses"])
 
@@ -93,10 +106,10 @@ def backward(p: Dict[str, torch.Tensor], g: Dict[str, torch.Tensor], x: torch.Te
     # d recon_loss / d x_recon (the forward pass already produced the loss value; sq is not reused)
     ops.mse_fwd_bwd(t["x_recon"], x, scratch, gscale=gscale, dY=t["dxr"])
     # decoder
-    ops.linear_bwd_w(t["dxr"], t["c2"], A.ACT_GELU, g["to_output.weight"], g["to_output.bias"])
-    ops.linear_bwd_x(t["dxr"], p["to_output.weight"], t["c2"], A.ACT_GELU, out=t["dc2"])
-    ops.linear_bwd_w(t["dc2"], t["c1"], A.ACT_GELU, g["decoder.2.weight"], g["decoder.2.bias"])
-    ops.linear_bwd_x(t["dc2"], p["decoder.2.weight"], t["c1"], A.ACT_GELU, out=t["dc1"])
+    ops.linear_bwd_w(t["dxr"], t["c2"], A.ACT_NONE, g["to_output.weight"], g["to_output.bias"])
+    ops.linear_bwd_x(t["dxr"], p["to_output.weight"], t["dc2_act"], A.ACT_GIVEN, out=t["dc2"])
+    ops.linear_bwd_w(t["dc2"], t["c1"], A.ACT_NONE, g["decoder.2.weight"], g["decoder.2.bias"])
+    ops.linear_bwd_x(t["dc2"], p["decoder.2.weight"], t["dc1_act"], A.ACT_GIVEN, out=t["dc1"])
     ops.linear_bwd_w(t["dc1"], t["z_q"], A.ACT_NONE, g["decoder.0.weight"], g["decoder.0.bias"])
     ops.linear_bwd_x(t["dc1"], p["decoder.0.weight"], None, A.ACT_NONE, out=t["dzq"])
     # quantizer: codebook rows get recon grad + 0.25*codebook-loss grad; encoder gets 0.25*commitment grad,
@@ -105,12 +118,12 @@ def backward(p: Dict[str, torch.Tensor], g: Dict[str, torch.Tensor], x: torch.Te
                    g["quantizer.codebook"])
     # Lipschitz layer: G = dL/dW_norm, then through min(1, softplus(ci)/||W_i||_1)
     t["G"].zero_()
-    ops.linear_bwd_w(t["dzpre"], t["a2"], A.ACT_GELU, t["G"], g["to_latent.b"])
+    ops.linear_bwd_w(t["dzpre"], t["a2"], A.ACT_NONE, t["G"], g["to_latent.b"])
     ops.lipschitz_scale_bwd(t["G"], p["to_latent.W"], p["to_latent.ci"], g["to_latent.W"], g["to_latent.ci"])
-    ops.linear_bwd_x(t["dzpre"], t["Wn"], t["a2"], A.ACT_GELU, out=t["da2"])
+    ops.linear_bwd_x(t["dzpre"], t["Wn"], t["da2_act"], A.ACT_GIVEN, out=t["da2"])
     # encoder
-    ops.linear_bwd_w(t["da2"], t["a1"], A.ACT_GELU, g["encoder.2.weight"], g["encoder.2.bias"])
-    ops.linear_bwd_x(t["da2"], p["encoder.2.weight"], t["a1"], A.ACT_GELU, out=t["da1"])
+    ops.linear_bwd_w(t["da2"], t["a1"], A.ACT_NONE, g["encoder.2.weight"], g["encoder.2.bias"])
+    ops.linear_bwd_x(t["da2"], p["encoder.2.weight"], t["da1_act"], A.ACT_GIVEN, out=t["da1"])
     ops.linear_bwd_w(t["da1"], x, A.ACT_NONE, g["encoder.0.weight"], g["encoder.0.bias"])
 
 

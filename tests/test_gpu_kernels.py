@@ -263,6 +263,38 @@ def test_linear_fwd_bwd(L, N, i, o, act_in, act_out):
     assert torch.allclose(db.cpu(), bl.grad, rtol=1e-4, atol=2e-5 * scale)
 
 
+@pytest.mark.parametrize("N,i,o,act", [(300, 12, 64, 2), (4096, 12, 64, 2), (5001, 64, 128, 2), (4500, 64, 64, 3),
+                                        (4100, 128, 12, 1), (4099, 64, 200, 2), (777, 64, 128, 0)])
+def test_linear_fwd_dual_and_given_derivative(L, N, i, o, act):
+    """Training forward: activation value and derivative from one evaluation in the producing layer (tcgen05 epilogue
+    for N >= 4096, FFMA tiles + elementwise pass below), consumed by linear_bwd_x with ACT_GIVEN."""
+    g = torch.Generator().manual_seed(N + o)
+    X = torch.randn(N, i, generator=g)
+    W = torch.randn(o, i, generator=g) / math.sqrt(i)
+    b = torch.randn(o, generator=g)
+    pre = torch.nn.functional.linear(X.double(), W.double(), b.double()).requires_grad_(True)  # fp64 reference
+    ref = ACTS[act](pre)
+    ref.sum().backward()
+    Y, dYd = torch.empty(N, o, device=DEV), torch.empty(N, o, device=DEV)
+    L.ops.linear_fwd_dual(X.to(DEV), 0, W.to(DEV), b.to(DEV), act, Y, dYd)
+    # fp32-accurate pre-activation (2e-6 of sum |x||w|, as in the wide-range test) through activations whose value and
+    # derivative are at most 1.13-Lipschitz; relu'/given derivatives may flip only where |pre| is inside that bound
+    bound = 2.5e-6 * (X.abs() @ W.abs().t() + b.abs()) + 1e-6
+    assert ((Y.cpu().double() - ref.detach()).abs() <= bound).all()
+    derr = (dYd.cpu().double() - pre.grad).abs()
+    if act == 1:
+        derr = derr * (pre.detach().abs() > bound)
+    assert (derr <= bound).all()
+    # next layer's input gradient through the stored derivative == through the activation itself
+    o2 = 48
+    W2 = torch.randn(o2, o, generator=g) / math.sqrt(o)
+    dY2 = torch.randn(N, o2, generator=g)
+    viaX = L.ops.linear_bwd_x(dY2.to(DEV), W2.to(DEV), pre.detach().float().to(DEV), act)
+    given = L.ops.linear_bwd_x(dY2.to(DEV), W2.to(DEV), dYd, L.ACT_GIVEN)
+    off = ((given - viaX).abs() > 2e-5 + 1e-4 * viaX.abs()).sum().item()
+    assert off <= (o2 if act == 1 else 0)  # relu: one pre-activation within rounding of 0 may flip one row of dX
+
+
 def test_linear_tc_bwd_w_forced(L, monkeypatch):
     """dW/db on the tensor cores for a layer without input activation (the dispatcher keeps those on the FFMA tiles;
     LIPVQ_LINEAR_ALGO=tc forces the tcgen05 kernel so it stays covered), ragged token count."""
