@@ -372,58 +372,56 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
             *reinterpret_cast<float4*>(scr + r * 16 + ((gj ^ ((r >> 1) & 3)) << 2)) = xr[it];
           }
           __syncwarp();
+          if (!last) load_x(c0 + 64, row0, xr);  // next group's, in flight during this group's math
         }
-        uint32_t v[16];
-        tmem_ld16(trow + c0, v); tmem_ld_wait16(v);
-        if (last) {  // this warp's last load: release the accumulator before the math
-          fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
-        } else if (mulX) {
-          load_x(c0 + 64, row0, xr);
-        }
-        float o[16];
-        if (dual) {  // value and derivative from one evaluation (erf is shared after inlining)
-          dispatch_act(p.act_out, [&](auto tag) {
-            constexpr int ACT = decltype(tag)::value;
-#pragma unroll
-            for (int e4 = 0; e4 < 4; ++e4) {
-              float d[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float pre = __uint_as_float(v[4 * e4 + e]) + bias_s[c0 + 4 * e4 + e];
-                o[4 * e4 + e] = act_apply(ACT, pre);
-                d[e] = act_grad(ACT, pre);
-              }
-              *reinterpret_cast<float4*>(scr2 + lane * 16 + ((e4 ^ rsw) << 2)) = make_float4(d[0], d[1], d[2], d[3]);
+        // four columns per iteration, rolled: the activation bodies (erf, exp) are long, and sixteen unrolled copies of
+        // each variant overflow the instruction cache of the scheduler
+#pragma unroll 1
+        for (int e4 = 0; e4 < 4; ++e4) {
+          uint32_t v[4];
+          tmem_ld4(trow + c0 + 4 * e4, v); tmem_ld_wait4(v);
+          if (e4 == 3) {
+            if (last) {  // this warp's last load: release the accumulator before the math
+              fence_before();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
             }
-          });
-        } else if (p.mode == 0) {
-          dispatch_act(p.act_out, [&](auto tag) {
-            constexpr int ACT = decltype(tag)::value;
-#pragma unroll
-            for (int e = 0; e < 16; ++e) o[e] = act_apply(ACT, __uint_as_float(v[e]) + bias_s[c0 + e]);
-          });
-        } else {
-#pragma unroll
-          for (int e = 0; e < 16; ++e) o[e] = __uint_as_float(v[e]);
-          if (mulX) {
-            float xv[16];
-#pragma unroll
-            for (int e4 = 0; e4 < 4; ++e4) {
-              const float4 t = *reinterpret_cast<const float4*>(my_row + ((e4 ^ rsw) << 2));
-              xv[4 * e4] = t.x; xv[4 * e4 + 1] = t.y; xv[4 * e4 + 2] = t.z; xv[4 * e4 + 3] = t.w;
-            }
-            dispatch_act(p.act_in, [&](auto tag) {
+          }
+          float* slot = my_row + ((e4 ^ rsw) << 2);
+          float o[4];
+          if (dual) {  // value and derivative from one evaluation (erf is shared after inlining)
+            float d[4];
+            dispatch_act(p.act_out, [&](auto tag) {
               constexpr int ACT = decltype(tag)::value;
 #pragma unroll
-              for (int e = 0; e < 16; ++e) o[e] *= act_grad(ACT, xv[e]);
+              for (int e = 0; e < 4; ++e) {
+                const float pre = __uint_as_float(v[e]) + bias_s[c0 + 4 * e4 + e];
+                o[e] = act_apply(ACT, pre);
+                d[e] = act_grad(ACT, pre);
+              }
             });
-          }
-        }
+            *reinterpret_cast<float4*>(slot + kEpiF * 512) = make_float4(d[0], d[1], d[2], d[3]);
+          } else if (p.mode == 0) {
+            dispatch_act(p.act_out, [&](auto tag) {
+              constexpr int ACT = decltype(tag)::value;
 #pragma unroll
-        for (int e4 = 0; e4 < 4; ++e4)  // the slots this lane just read: no cross-lane hazard
-          *reinterpret_cast<float4*>(my_row + ((e4 ^ rsw) << 2)) = make_float4(o[4 * e4], o[4 * e4 + 1], o[4 * e4 + 2], o[4 * e4 + 3]);
+              for (int e = 0; e < 4; ++e) o[e] = act_apply(ACT, __uint_as_float(v[e]) + bias_s[c0 + 4 * e4 + e]);
+            });
+          } else {
+#pragma unroll
+            for (int e = 0; e < 4; ++e) o[e] = __uint_as_float(v[e]);
+            if (mulX) {
+              const float4 t = *reinterpret_cast<const float4*>(slot);
+              const float xv[4] = {t.x, t.y, t.z, t.w};
+              dispatch_act(p.act_in, [&](auto tag) {
+                constexpr int ACT = decltype(tag)::value;
+#pragma unroll
+                for (int e = 0; e < 4; ++e) o[e] *= act_grad(ACT, xv[e]);
+              });
+            }
+          }
+          *reinterpret_cast<float4*>(slot) = make_float4(o[0], o[1], o[2], o[3]);  // the slot this lane just read
+        }
         __syncwarp();
         store_tile(scr, p.C, c0, row0);
         if (dual) store_tile(scr2, p.C2, c0, row0);

