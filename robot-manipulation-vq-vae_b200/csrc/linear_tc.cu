@@ -65,12 +65,19 @@ struct LinTcParams {
   uint32_t tmem_cols;
 };
 
-__device__ __forceinline__ void split3(float x, __nv_bfloat16& h, __nv_bfloat16& m, __nv_bfloat16& l) {
-  h = __float2bfloat16_rn(x);
-  const float r1 = x - __bfloat162float(h);  // exact
-  m = __float2bfloat16_rn(r1);
-  const float r2 = r1 - __bfloat162float(m);  // exact
-  l = __float2bfloat16_rn(r2);
+// Three-way bf16 split of two values at once, packed as (x0 | x1 << 16) per term.  The packed conversion
+// (cvt.rn.bf16x2.f32) issues on the ordinary pipes; the scalar F2F form runs on the quarter-rate conversion unit and
+// was what bounded the converters.  x - float(bf16(x)) is exact, so h + m + l reproduces all 24 mantissa bits.
+__device__ __forceinline__ uint32_t bf16x2_rn(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ void split3_pair(float x0, float x1, uint32_t& h, uint32_t& m, uint32_t& l) {
+  h = bf16x2_rn(x0, x1);
+  const float r0 = x0 - __uint_as_float(h << 16), r1 = x1 - __uint_as_float(h & 0xFFFF0000u);
+  m = bf16x2_rn(r0, r1);
+  l = bf16x2_rn(r0 - __uint_as_float(m << 16), r1 - __uint_as_float(m & 0xFFFF0000u));
 }
 // Run body(tag) with the activation as a compile-time constant: the element loops then contain straight-line code
 // instead of a switch per element (branch latency is not hidden with this few warps per scheduler).
@@ -87,9 +94,6 @@ __device__ __forceinline__ void dispatch_act(int act, F&& body) {
   }
 }
 
-__device__ __forceinline__ uint32_t pack2(__nv_bfloat16 a, __nv_bfloat16 b) {
-  return (uint32_t)__bfloat16_as_ushort(a) | ((uint32_t)__bfloat16_as_ushort(b) << 16);
-}
 
 __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -161,12 +165,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
         uint32_t hh[4], mm[4], ll[4];
 #pragma unroll
         for (int e = 0; e < 8; e += 2) {
-          __nv_bfloat16 h0, m0, l0, h1, m1, l1;
-          split3(wv[u][e], h0, m0, l0);
-          split3(wv[u][e + 1], h1, m1, l1);
-          hh[e >> 1] = pack2(h0, h1);
-          mm[e >> 1] = pack2(m0, m1);
-          ll[e >> 1] = pack2(l0, l1);
+          split3_pair(wv[u][e], wv[u][e + 1], hh[e >> 1], mm[e >> 1], ll[e >> 1]);
         }
         const int c = kc[u] >> 3, n = nn[u];
         uint8_t* t0 = sB + c * b_tile + (uint32_t)(n * 128 + (((kc[u] & 7) ^ (n & 7)) << 4));
@@ -274,12 +273,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
           });
 #pragma unroll
           for (int e = 0; e < 8; e += 2) {
-            __nv_bfloat16 h0, m0, l0, h1, m1, l1;
-            split3(y[e], h0, m0, l0);
-            split3(y[e + 1], h1, m1, l1);
-            hh[e >> 1] = pack2(h0, h1);
-            mm[e >> 1] = pack2(m0, m1);
-            ll[e >> 1] = pack2(l0, l1);
+            split3_pair(y[e], y[e + 1], hh[e >> 1], mm[e >> 1], ll[e >> 1]);
           }
           const int r = r0 + 32 * u;
           const uint32_t off = (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
@@ -627,12 +621,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
           uint32_t hh[4], mm[4], ll[4];
 #pragma unroll
           for (int e = 0; e < 8; e += 2) {
-            __nv_bfloat16 h0, m0, l0, h1, m1, l1;
-            split3(w[u][e], h0, m0, l0);
-            split3(w[u][e + 1], h1, m1, l1);
-            hh[e >> 1] = pack2(h0, h1);
-            mm[e >> 1] = pack2(m0, m1);
-            ll[e >> 1] = pack2(l0, l1);
+            split3_pair(w[u][e], w[u][e + 1], hh[e >> 1], mm[e >> 1], ll[e >> 1]);
           }
           uint8_t* d = (isA ? a0 : b0) + (c >> 3) * kWBlk + (tk >> 3) * 1024 + (tk & 7) * 128 + (((c & 7) ^ (tk & 7)) << 4);
           const int term = isA ? a_term : b_term;
