@@ -584,60 +584,61 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
         }
       }
     };
-    float w[2][8];
-    load_unit(0, w);
-    for (int i = 0; i < nblk; ++i) {
+    auto convert_unit = [&](int unit, float (&w)[2][8]) {
+      if (unit >= total_units) return;
+      const int i = unit / nbatch, b = unit - i * nbatch;
       const int buf = i & 1;
       const int64_t t0 = ((int64_t)blockIdx.x + (int64_t)i * gridDim.x) * kWTok;
       uint8_t* a0 = smem + buf * buf_bytes;
       uint8_t* b0 = a0 + 3 * a_term;
-      for (int b = 0; b < nbatch; ++b) {
-        float wn[2][8];
-        load_unit(i * nbatch + b + 1, wn);
-        if (b == 0) {
-          TR(20);
-          mbar_wait(bar_empty + 8 * buf, (((uint32_t)i >> 1) & 1) ^ 1);
-          TR(21);
-        }
-#pragma unroll
-        for (int u = 0; u < 2; ++u) {
-          const int it = b * 2 * kCT + u * kCT + tcv;
-          if (it >= items) continue;
-          const int tk = __float2int_rd(((float)it + 0.5f) * rcpCT), cc = it - tk * CT;
-          const bool isA = cc < p.CA;
-          const int c = isA ? cc : cc - p.CA;
-          const bool live = t0 + tk < p.N;
-          if (!isA) {
-            if (p.actX != LIPVQ_ACT_NONE)
-              dispatch_act(p.actX, [&](auto tag) {
-                constexpr int ACT = decltype(tag)::value;
-#pragma unroll
-                for (int e = 0; e < 8; ++e) w[u][e] = (live && c * 8 + e < p.in_dim) ? act_apply(ACT, w[u][e]) : 0.f;
-              });
-#pragma unroll
-            for (int e = 0; e < 8; ++e)
-              if (c * 8 + e == p.in_dim) w[u][e] = 1.f;  // ones column: db = dY^T 1 (dead tokens have dY = 0)
-          }
-          uint32_t hh[4], mm[4], ll[4];
-#pragma unroll
-          for (int e = 0; e < 8; e += 2) {
-            split3_pair(w[u][e], w[u][e + 1], hh[e >> 1], mm[e >> 1], ll[e >> 1]);
-          }
-          uint8_t* d = (isA ? a0 : b0) + (c >> 3) * kWBlk + (tk >> 3) * 1024 + (tk & 7) * 128 + (((c & 7) ^ (tk & 7)) << 4);
-          const int term = isA ? a_term : b_term;
-          *reinterpret_cast<uint4*>(d) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
-          *reinterpret_cast<uint4*>(d + term) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
-          *reinterpret_cast<uint4*>(d + 2 * term) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
-        }
-#pragma unroll
-        for (int u = 0; u < 2; ++u)
-#pragma unroll
-          for (int e = 0; e < 8; ++e) w[u][e] = wn[u][e];
+      if (b == 0) {
+        TR(20);
+        mbar_wait(bar_empty + 8 * buf, (((uint32_t)i >> 1) & 1) ^ 1);
+        TR(21);
       }
-      fence_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_full + 8 * buf);
-      TR(23);
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int it = b * 2 * kCT + u * kCT + tcv;
+        if (it >= items) continue;
+        const int tk = __float2int_rd(((float)it + 0.5f) * rcpCT), cc = it - tk * CT;
+        const bool isA = cc < p.CA;
+        const int c = isA ? cc : cc - p.CA;
+        const bool live = t0 + tk < p.N;
+        if (!isA) {
+          if (p.actX != LIPVQ_ACT_NONE)
+            dispatch_act(p.actX, [&](auto tag) {
+              constexpr int ACT = decltype(tag)::value;
+#pragma unroll
+              for (int e = 0; e < 8; ++e) w[u][e] = (live && c * 8 + e < p.in_dim) ? act_apply(ACT, w[u][e]) : 0.f;
+            });
+#pragma unroll
+          for (int e = 0; e < 8; ++e)
+            if (c * 8 + e == p.in_dim) w[u][e] = 1.f;  // ones column: db = dY^T 1 (dead tokens have dY = 0)
+        }
+        uint32_t hh[4], mm[4], ll[4];
+#pragma unroll
+        for (int e = 0; e < 8; e += 2) split3_pair(w[u][e], w[u][e + 1], hh[e >> 1], mm[e >> 1], ll[e >> 1]);
+        uint8_t* d = (isA ? a0 : b0) + (c >> 3) * kWBlk + (tk >> 3) * 1024 + (tk & 7) * 128 + (((c & 7) ^ (tk & 7)) << 4);
+        const int term = isA ? a_term : b_term;
+        *reinterpret_cast<uint4*>(d) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+        *reinterpret_cast<uint4*>(d + term) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+        *reinterpret_cast<uint4*>(d + 2 * term) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+      }
+      if (b == nbatch - 1) {
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_full + 8 * buf);
+        TR(23);
+      }
+    };
+    // two register sets in ping-pong (a copy at the end of the iteration would wait for the loads it is meant to hide)
+    float w0[2][8], w1[2][8];
+    load_unit(0, w0);
+    for (int unit = 0; unit < total_units; unit += 2) {
+      load_unit(unit + 1, w1);
+      convert_unit(unit, w0);
+      load_unit(unit + 2, w0);
+      convert_unit(unit + 1, w1);
     }
   } else {
     // ===== epilogue warps 0-7: TMEM lane = output row o; every second 16-column group; one pass at the very end =====
