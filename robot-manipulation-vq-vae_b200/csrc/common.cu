@@ -2,6 +2,7 @@
 #include <atomic>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 
 #include "common.cuh"
 
@@ -23,6 +24,15 @@ int cuda_fail(cudaError_t e, const char* what) {
 }
 
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+  static int cached = -1;
+  if (cached < 0) {
+    const char* e = getenv("LIPVQ_PDL");
+    cached = (e && e[0] == '0') ? 0 : 1;
+  }
+  return cached == 1;
+}
 
 int sm_count() {
   static int cached = 0;

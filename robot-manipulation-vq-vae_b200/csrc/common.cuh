@@ -56,6 +56,27 @@ inline int64_t ceil_div64(int64_t a, int64_t b) { return (a + b - 1) / b; }
 
 namespace lipvq {
 
+// Programmatic dependent launch: a kernel launched with launch_pdl may start (prologue, barrier / TMEM setup) while the
+// kernel before it in the stream is still draining; it calls grid_dep_wait() before touching anything that kernel
+// wrote.  grid_dep_launch() in the earlier kernel lets the dependent grid be scheduled as soon as SMs free up.
+__device__ __forceinline__ void grid_dep_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void grid_dep_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+bool pdl_enabled();  // LIPVQ_PDL=0 turns the attribute off (A/B runs)
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 __device__ __forceinline__ float act_apply(int act, float x) {
   switch (act) {
     case LIPVQ_ACT_RELU: return x > 0.f ? x : 0.f;

@@ -168,7 +168,20 @@ __global__ void __launch_bounds__(256)
 // Lane mapping: LPR = pow2 >= D/4 lanes own one row (one float4 each, or a strided loop for D > 128).
 constexpr int kScatThreads = 512;
 
+// Adds this CTA's table to the global one.  Every CTA holds the SAME K*D addresses, so the walk starts at a
+// CTA-dependent offset (the CTAs would otherwise hit each address at the same moment) and moves 16 bytes per reduction.
 __device__ __forceinline__ void scatter_flush(const float* s_tab, int64_t n, float* __restrict__ g) {
+  if ((n & 3) == 0 && (reinterpret_cast<uintptr_t>(g) & 15) == 0) {
+    const int64_t n4 = n >> 2;
+    const int64_t start = (n4 / gridDim.x) * blockIdx.x;
+    for (int64_t i = threadIdx.x; i < n4; i += blockDim.x) {
+      int64_t j = i + start;
+      if (j >= n4) j -= n4;
+      const float4 v = reinterpret_cast<const float4*>(s_tab)[j];
+      if (v.x != 0.f || v.y != 0.f || v.z != 0.f || v.w != 0.f) atomicAdd(reinterpret_cast<float4*>(g) + j, v);
+    }
+    return;
+  }
   for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
     const float v = s_tab[i];
     if (v != 0.f) atomicAdd(g + i, v);

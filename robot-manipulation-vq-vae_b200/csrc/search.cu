@@ -309,6 +309,7 @@ __global__ void __launch_bounds__(256)
   __shared__ float s_bv[8];
   __shared__ int s_bk[8];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  grid_dep_wait();  // launched as a programmatic dependent of the last search pass
   const int nflag = *count;
   if (stats_out && blockIdx.x == 0 && threadIdx.x == 0) {
     stats_out[0] = nflag;         // rows decided by the exact scan
@@ -540,8 +541,8 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
     const int* count = nullptr;
     const int rc = search_fused_launch(z, N, D, codebook, K, metric, plan, ws, idx_out, stream, &queue, &count);
     if (rc != LIPVQ_OK) return rc;
-    rescore_kernel<<<rs_blocks, 256, rs_smem, stream>>>(z, D, codebook, K, metric, count, &hdr->flagged, queue, idx_out,
-                                                        nullptr, stats_out, vec, lpc);
+    LIPVQ_CUDA(launch_pdl(rescore_kernel, dim3(rs_blocks), dim3(256), rs_smem, stream, z, D, codebook, K, metric, count,
+                          (const int*)&hdr->flagged, queue, idx_out, (float*)nullptr, stats_out, vec, lpc));
     LIPVQ_LAUNCHED("rescore_kernel");
     if (best_out) return search_best_values(z, N, D, codebook, metric, idx_out, best_out, stream);
     return LIPVQ_OK;

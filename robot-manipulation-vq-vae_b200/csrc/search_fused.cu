@@ -208,6 +208,7 @@ __global__ void __launch_bounds__(256)
                       __half* __restrict__ elo, SearchHdr* hdr) {
   __shared__ float mu_s[512];
   __shared__ float s_part[8];
+  grid_dep_launch();  // the fp16 pass may set up (barriers, TMEM) while this kernel runs; it waits before reading
   constexpr int RMAX = 32;
   const int R = (int)(N < RMAX ? N : RMAX);
   const int64_t stride = N / R;
@@ -334,8 +335,10 @@ __global__ void __launch_bounds__(kThreads, 1)
   TR(0);
 #endif
 
+  grid_dep_launch();
   int64_t n_rows = p.N;
   if (p.n_rows_ptr) {
+    grid_dep_wait();  // the row count is the previous pass's output
     const int64_t q = (int64_t)*p.n_rows_ptr;
     n_rows = q < p.N ? q : p.N;
   }
@@ -369,6 +372,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
   }
+  if (!p.n_rows_ptr) grid_dep_wait();  // everything above overlapped the preparation kernel's tail
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -964,7 +968,7 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
       smem_set1 = g1.smem;
     }
     const int grid = row_blocks < sms ? row_blocks : sms;
-    search_fused_kernel<1><<<grid, kThreads, g1.smem, stream>>>(tm_hi, tm_lo, tm_z, p);
+    LIPVQ_CUDA(launch_pdl(search_fused_kernel<1>, dim3(grid), dim3(kThreads), g1.smem, stream, tm_hi, tm_lo, tm_z, p));
     LIPVQ_LAUNCHED("search_fused_kernel<1>");
   }
   *final_queue = work;
@@ -985,7 +989,7 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
     }
     // the queue length is only known on the device: size the grid for a modest queue, CTAs stride over the blocks
     int grid = row_blocks < sms ? row_blocks : sms;
-    search_fused_kernel<3><<<grid, kThreads, g3.smem, stream>>>(tm_hi, tm_lo, tm_z, p);
+    LIPVQ_CUDA(launch_pdl(search_fused_kernel<3>, dim3(grid), dim3(kThreads), g3.smem, stream, tm_hi, tm_lo, tm_z, p));
     LIPVQ_LAUNCHED("search_fused_kernel<3>");
     *final_queue = work2;
     *final_count = &hdr->flagged2;
