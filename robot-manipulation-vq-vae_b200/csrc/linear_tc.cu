@@ -704,10 +704,7 @@ bool linear_tc_supported(int mode, int64_t N, int Ka, int Nb, bool dual) {
   if (const char* f = getenv("LIPVQ_LINEAR_ALGO"))
     if (f[0] == 's') return false;
   if (!(N >= 4096 && Ka >= 1 && Ka <= 128 && Nb >= 1 && Nb <= 256)) return false;
-  // measured (scripts/bench_linear.py): a forward layer with a very short reduction and no activation on its input is
-  // all epilogue, and the FFMA tiles are as fast there
-  // (the dual forward evaluates the activation in the epilogue, which the FFMA path cannot fuse: always worth it)
-  if (mode == 0 && Ka < 32 && !dual) return false;
+  (void)mode;
   const int NC = (Ka + kChunk - 1) / kChunk, Nbp = (Nb + 15) / 16 * 16;
   const size_t a_bytes = (size_t)3 * NC * kATile, b_bytes = (size_t)3 * NC * Nbp * kChunk * 2;
   return 1024 + a_bytes + b_bytes + kMisc + (dual ? kDualScratch : 0) <= 227 * 1024;
