@@ -254,6 +254,22 @@ LIPVQ_API int lipvq_adamw_step_f32(float* p, const float* g, float* m, float* v,
  * when step_dev != NULL above, the step number is read from it instead of `step`. */
 LIPVQ_API int lipvq_counter_add_i32(int32_t* ctr, int delta, void* stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Data-parallel reduction slab: one-shot sum all-reduce over NVLink peer memory (csrc/allreduce.cu).
+ * Every rank holds a symmetric buffer [slab (n floats) | flags] mapped into all peers
+ * (torch.distributed._symmetric_memory); peer_ptrs_dev is a device array of the W base addresses as seen from this
+ * process, in rank order.  out (local, 16-byte aligned) receives sum over ranks of slab[0..n); all ranks get the same
+ * bits.  cta_epoch: lipvq_allreduce_oneshot_ctas() zero-initialised uint32 on the device, private to this rank; the
+ * flags region (lipvq_allreduce_oneshot_flag_bytes(world) bytes at flag_offset_bytes) must be zero before the first
+ * call on any rank.  Every rank must issue the call the same number of times (it is a collective).
+ * Replaces the dist.all_reduce a data-parallel port of the reference would add around
+ * hq_vae.py:264-275 (EMA statistics) and optimizer.step() (gradients); NCCL stays available as the fallback.
+ * --------------------------------------------------------------------------------------------- */
+LIPVQ_API int lipvq_allreduce_oneshot_ctas(void);
+LIPVQ_API size_t lipvq_allreduce_oneshot_flag_bytes(int world);
+LIPVQ_API int lipvq_allreduce_oneshot_f32(const uint64_t* peer_ptrs_dev, int rank, int world, int64_t n,
+                                int64_t flag_offset_bytes, float* out, uint32_t* cta_epoch, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -58,6 +58,9 @@ SIGNATURES = {
     "lipvq_t1_loss_finalize": (_i, [_p, _d, _d, _f, _f, _p, _p]),
     "lipvq_adamw_step_f32": (_i, [_p, _p, _p, _p, _i64, _i, _p, _f, _f, _f, _f, _f, _f, _p]),
     "lipvq_counter_add_i32": (_i, [_p, _i, _p]),
+    "lipvq_allreduce_oneshot_ctas": (_i, []),
+    "lipvq_allreduce_oneshot_flag_bytes": (C.c_size_t, [_i]),
+    "lipvq_allreduce_oneshot_f32": (_i, [_p, _i, _i, _i64, _i64, _p, _p, _p]),
 }
 
 

@@ -74,3 +74,39 @@ def all_reduce_slab(slab: torch.Tensor, group: Optional[dist.ProcessGroup] = Non
     if world > 1:
         dist.all_reduce(slab, op=dist.ReduceOp.SUM, group=group)
     return world
+
+
+class PeerSlab:
+    """Reduction slab in symmetric (peer-mapped) memory + the one-shot NVLink all-reduce kernel (csrc/allreduce.cu).
+
+    ``slab``  -- this rank's [length] fp32 input (phase A accumulates into it; every peer can read it)
+    ``out``   -- [length] fp32, local: sum over ranks after ``all_reduce()`` (same bits on every rank)
+    The allocation / handle exchange is torch.distributed._symmetric_memory; the data path is one kernel of ours,
+    capturable in a CUDA graph.  Raises if symmetric memory cannot be set up (caller falls back to NCCL)."""
+
+    def __init__(self, length: int, device: torch.device, group: Optional[dist.ProcessGroup] = None):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        from ._cabi import lib
+        group = group if group is not None else dist.group.WORLD
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.n = (int(length) + 3) // 4 * 4
+        ctas = int(lib.lipvq_allreduce_oneshot_ctas())
+        flag_floats = int(lib.lipvq_allreduce_oneshot_flag_bytes(self.world)) // 4
+        self.buf = symm_mem.empty(self.n + flag_floats, dtype=torch.float32, device=device)
+        self.buf.zero_()
+        self.hdl = symm_mem.rendezvous(self.buf, group.group_name)
+        torch.cuda.synchronize(device)
+        dist.barrier(group)  # every rank's flags are zero before anyone raises one
+        self.slab = self.buf[:length]
+        self._out = torch.zeros(self.n, dtype=torch.float32, device=device)
+        self.out = self._out[:length]
+        self.epoch = torch.zeros(ctas, dtype=torch.int32, device=device)
+        self.peer_ptrs_dev = int(self.hdl.buffer_ptrs_dev)
+
+    def all_reduce(self) -> None:
+        from . import _cabi
+        _cabi.check(_cabi.lib.lipvq_allreduce_oneshot_f32(self.peer_ptrs_dev, self.rank, self.world, self.n, self.n * 4,
+                                                          self._out.data_ptr(), self.epoch.data_ptr(),
+                                                          torch.cuda.current_stream().cuda_stream), "allreduce_oneshot")
+

@@ -24,7 +24,7 @@ import torch.distributed as dist
 from . import _cabi as A
 from . import ops, t1
 from .modules import LFQQuantizerEMA, LLFQVAE_V4, _T1_KEYS
-from .parallel import SlabLayout, all_reduce_slab
+from .parallel import PeerSlab, SlabLayout, all_reduce_slab
 
 
 class TokenizerTrainer:
@@ -50,8 +50,19 @@ class TokenizerTrainer:
         self.layout = SlabLayout(list(_T1_KEYS), [tuple(named[k].shape) for k in _T1_KEYS], K, D, self.ema)
         L = self.layout
         self.flat_p = torch.empty(L.P, dtype=torch.float32, device=dev)
-        self.red = torch.zeros(L.length, dtype=torch.float32, device=dev)
-        self.flat_g = self.red[:L.P]
+        # reduction slab: phase A accumulates into ``red``; phase B reads the cross-rank sum from ``red_out``.  With the
+        # NVLink peer all-reduce (default for world > 1) red lives in symmetric memory and red_out is a local buffer;
+        # with NCCL (fallback, or LIPVQ_DP_COLLECTIVE=nccl) the all-reduce is in place and both are the same tensor.
+        self.peer = None
+        if self.world > 1 and os.environ.get("LIPVQ_DP_COLLECTIVE", "peer") == "peer":
+            try:
+                self.peer = PeerSlab(L.length, dev, process_group)
+            except Exception as e:
+                import warnings
+                warnings.warn(f"lipvq: symmetric memory unavailable ({e}); data-parallel reduction uses NCCL")
+        self.red = self.peer.slab if self.peer is not None else torch.zeros(L.length, dtype=torch.float32, device=dev)
+        self.red_out = self.peer.out if self.peer is not None else self.red
+        self.flat_g = self.red_out[:L.P]
         self.flat_m = torch.zeros(L.P, dtype=torch.float32, device=dev)
         self.flat_v = torch.zeros(L.P, dtype=torch.float32, device=dev)
         self.p: Dict[str, torch.Tensor] = {}
@@ -65,7 +76,9 @@ class TokenizerTrainer:
                 self.g[k] = L.grad_view(self.red, k)
         if self.ema:
             self.counts, self.sums = L.counts(self.red), L.sums(self.red)
-        self.losses_red = L.losses(self.red)
+            self.counts_out, self.sums_out = L.counts(self.red_out), L.sums(self.red_out)
+        self.losses_in = L.losses(self.red)
+        self.losses_red = L.losses(self.red_out)
         self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)
         self.scratch = torch.zeros(1, dtype=torch.float64, device=dev)
         self.bufs = t1.T1Buffers(self.N, F_, D, K, H, dev)
@@ -92,12 +105,18 @@ class TokenizerTrainer:
         if self.ema:
             t1.ema_stats(self.bufs, self.counts, self.sums)
         t1.backward(self.p, self.g, self.x_static, self.bufs)
-        self.losses_red.copy_(self.bufs.t["losses"])
+        self.losses_in.copy_(self.bufs.t["losses"])
+
+    def _reduce(self):
+        if self.peer is not None:
+            self.peer.all_reduce()
+        else:
+            all_reduce_slab(self.red, self.pg)
 
     def _phase_b(self):
         if self.ema:
             q = self.model.quantizer
-            ops.ema_apply(self.counts, self.sums, q.ema_cluster_size, q.ema_codebook, self.p["quantizer.codebook"],
+            ops.ema_apply(self.counts_out, self.sums_out, q.ema_cluster_size, q.ema_codebook, self.p["quantizer.codebook"],
                           q.decay, q.epsilon, A.EMA_SIMPLE, self.scratch)
         ops.counter_add(self.step_dev, 1)
         ops.adamw_step(self.flat_p, self.flat_g, self.flat_m, self.flat_v, 0, self.step_dev, self.lr, self.betas,
@@ -125,7 +144,7 @@ class TokenizerTrainer:
         with torch.cuda.stream(s):
             self._phase_a()
             if self.world > 1:
-                all_reduce_slab(self.red, self.pg)  # also brings the NCCL communicator up before any capture
+                self._reduce()  # also brings the NCCL communicator up before any capture
             self._phase_b()
         torch.cuda.current_stream().wait_stream(s)
         self._graph_full = None
@@ -136,7 +155,7 @@ class TokenizerTrainer:
                 gf = torch.cuda.CUDAGraph()
                 with torch.cuda.graph(gf):
                     self._phase_a()
-                    all_reduce_slab(self.red, self.pg)
+                    self._reduce()
                     self._phase_b()
                 self._graph_full = gf
             except Exception as e:  # NCCL build without capture support: fall back to graph / eager collective / graph
@@ -194,7 +213,7 @@ class TokenizerTrainer:
         else:
             self._phase_a()
         if self.world > 1:
-            all_reduce_slab(self.red, self.pg)
+            self._reduce()
         if self.use_graph:
             self._graph_b.replay()
         else:
