@@ -266,6 +266,8 @@ __device__ __forceinline__ float softplus_f(float x) {
 __global__ void __launch_bounds__(256)
     lipschitz_fwd_kernel(const float* __restrict__ W, const float* __restrict__ ci, int out_dim, int in_dim,
                          float* __restrict__ scale, float* __restrict__ Wn) {
+  grid_dep_wait();  // programmatic dependent launch: nothing above touches memory
+  grid_dep_launch();
   const int o = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (o >= out_dim) return;
   const float* w = W + (size_t)o * in_dim;
@@ -280,6 +282,8 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     lipschitz_bwd_kernel(const float* __restrict__ G, const float* __restrict__ W, const float* __restrict__ ci,
                          int out_dim, int in_dim, float* __restrict__ dW, float* __restrict__ dci) {
+  grid_dep_wait();  // programmatic dependent launch: nothing above touches memory
+  grid_dep_launch();
   const int o = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (o >= out_dim) return;
   const float* w = W + (size_t)o * in_dim;
@@ -444,8 +448,7 @@ int lipvq_lipschitz_scale_fwd_f32(const float* W, const float* ci, int out_dim, 
                                   float* W_norm, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   LIPVQ_REQUIRE(W && ci && W_norm && out_dim > 0 && in_dim > 0, "lipschitz_scale_fwd: bad argument");
-  lipschitz_fwd_kernel<<<(unsigned)ceil_div64((int64_t)out_dim * 32, 256), 256, 0, stream>>>(W, ci, out_dim, in_dim,
-                                                                                             scale, W_norm);
+  LIPVQ_CUDA(launch_pdl(lipschitz_fwd_kernel, dim3((unsigned)ceil_div64((int64_t)out_dim * 32, 256)), dim3(256), 0, stream, W, ci, out_dim, in_dim, scale, W_norm));
   LIPVQ_LAUNCHED("lipschitz_fwd_kernel");
   return LIPVQ_OK;
 }
@@ -454,8 +457,7 @@ int lipvq_lipschitz_scale_bwd_f32(const float* G, const float* W, const float* c
                                   float* dci, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   LIPVQ_REQUIRE(G && W && ci && dW && dci && out_dim > 0 && in_dim > 0, "lipschitz_scale_bwd: bad argument");
-  lipschitz_bwd_kernel<<<(unsigned)ceil_div64((int64_t)out_dim * 32, 256), 256, 0, stream>>>(G, W, ci, out_dim, in_dim,
-                                                                                             dW, dci);
+  LIPVQ_CUDA(launch_pdl(lipschitz_bwd_kernel, dim3((unsigned)ceil_div64((int64_t)out_dim * 32, 256)), dim3(256), 0, stream, G, W, ci, out_dim, in_dim, dW, dci));
   LIPVQ_LAUNCHED("lipschitz_bwd_kernel");
   return LIPVQ_OK;
 }

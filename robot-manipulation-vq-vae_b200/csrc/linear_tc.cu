@@ -128,6 +128,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
+  grid_dep_wait();  // launched as a programmatic dependent: barrier / TMEM setup above overlapped the previous kernel's tail
+  grid_dep_launch();
 
   // ---- weights: split into (h, m, l) and store as swizzled K-major tiles; bias to smem ----
   // An item is one 16-byte chunk of a tile row: 8 consecutive k of one output n.  Threads follow the contiguous direction
@@ -497,6 +499,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
   if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
   // chunks the converters never write (columns past out_dim / in_dim + 1) must read as zero
   for (int i = threadIdx.x; i < (2 * buf_bytes + kWBlk) / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  grid_dep_wait();  // programmatic dependent launch: everything above is local to the CTA
+  grid_dep_launch();
   fence_async_smem();
   fence_before();
   __syncthreads();
@@ -741,7 +745,7 @@ int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, i
   const int row_blocks = (int)ceil_div64(N, kBM);
   const int sms = sm_count();
   const int grid = row_blocks < sms ? row_blocks : sms;
-  linear_tc_kernel<<<grid, kThreads, smem, stream>>>(p);
+  LIPVQ_CUDA(launch_pdl(linear_tc_kernel, dim3(grid), dim3(kThreads), smem, stream, p));
   LIPVQ_LAUNCHED("linear_tc_kernel");
   return LIPVQ_OK;
 }
@@ -778,7 +782,7 @@ int linear_tc_bwd_w_launch(const float* dY, int64_t N, int out_dim, const float*
   }
   const int blocks = (int)ceil_div64(N, kWTok);
   const int sms = sm_count();
-  linear_tc_bwd_w_kernel<<<blocks < sms ? blocks : sms, kThreads, smem, stream>>>(p);
+  LIPVQ_CUDA(launch_pdl(linear_tc_bwd_w_kernel, dim3(blocks < sms ? blocks : sms), dim3(kThreads), smem, stream, p));
   LIPVQ_LAUNCHED("linear_tc_bwd_w_kernel");
   return LIPVQ_OK;
 }

@@ -10,6 +10,8 @@ __global__ void __launch_bounds__(256)
     adamw_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
                  int64_t n, int step_host, const int32_t* __restrict__ step_dev, float lr, float beta1, float beta2,
                  float eps, float weight_decay, float grad_scale) {
+  grid_dep_wait();  // programmatic dependent launch: nothing above touches memory
+  grid_dep_launch();
   __shared__ float s_c[3];
   if (threadIdx.x == 0) {
     const int step = step_dev ? *step_dev : step_host;
@@ -35,7 +37,11 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-__global__ void counter_add_kernel(int32_t* ctr, int delta) { *ctr += delta; }
+__global__ void counter_add_kernel(int32_t* ctr, int delta) {
+  grid_dep_wait();
+  grid_dep_launch();
+  *ctr += delta;
+}
 
 }  // namespace
 }  // namespace lipvq
@@ -55,8 +61,7 @@ int lipvq_adamw_step_f32(float* p, const float* g, float* m, float* v, int64_t n
   int64_t blocks = ceil_div64(n, 256);
   const int64_t cap = (int64_t)sm_count() * 8;
   if (blocks > cap) blocks = cap;
-  adamw_kernel<<<(unsigned)blocks, 256, 0, stream>>>(p, g, m, v, n, step, step_dev, lr, beta1, beta2, eps, weight_decay,
-                                                     grad_scale);
+  LIPVQ_CUDA(launch_pdl(adamw_kernel, dim3((unsigned)blocks), dim3(256), 0, stream, p, g, m, v, n, step, step_dev, lr, beta1, beta2, eps, weight_decay, grad_scale));
   LIPVQ_LAUNCHED("adamw_kernel");
   return LIPVQ_OK;
 }
@@ -64,7 +69,7 @@ int lipvq_adamw_step_f32(float* p, const float* g, float* m, float* v, int64_t n
 int lipvq_counter_add_i32(int32_t* ctr, int delta, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   LIPVQ_REQUIRE(ctr, "counter_add: null pointer");
-  counter_add_kernel<<<1, 1, 0, stream>>>(ctr, delta);
+  LIPVQ_CUDA(launch_pdl(counter_add_kernel, dim3(1), dim3(1), 0, stream, ctr, delta));
   LIPVQ_LAUNCHED("counter_add_kernel");
   return LIPVQ_OK;
 }

@@ -20,6 +20,8 @@ __global__ void __launch_bounds__(256)
     gather_fwd_kernel(const float* __restrict__ z, const int64_t* __restrict__ idx, const float* __restrict__ cb,
                       int64_t N, int D, int K, float* __restrict__ zq, float* __restrict__ zst,
                       double* __restrict__ sqerr) {
+  grid_dep_wait();  // programmatic dependent launch: nothing above touches memory
+  grid_dep_launch();
   constexpr int W = VEC ? 4 : 1;
   const int64_t total = N * (int64_t)(D / W);  // work items: one vector (or scalar) element each
   const int per_row = D / W;
@@ -194,6 +196,8 @@ __global__ void __launch_bounds__(kScatThreads, 1)
                         const float* __restrict__ dzq_up, const float* __restrict__ gscale_dev, float w_commit,
                         float w_codebook, int ste, const float* __restrict__ sig_out, int64_t N, int D, int K, int lpr,
                         float* __restrict__ dz, float* __restrict__ tab_g, float* __restrict__ counts_g) {
+  grid_dep_wait();  // programmatic dependent launch: nothing above touches memory
+  grid_dep_launch();
   extern __shared__ __align__(16) float s_tab[];  // [K*D] (+ [K] counts for the statistics)
   float* s_cnt = s_tab + (size_t)K * D;
   const int64_t tab_n = (int64_t)K * D + (BWD ? 0 : K);
@@ -375,6 +379,8 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     ema_size_kernel(const float* __restrict__ counts, int K, float decay, float omd, float* __restrict__ ema_size,
                     double* __restrict__ total) {
+  grid_dep_wait();  // programmatic dependent launch: nothing above touches memory
+  grid_dep_launch();
   double local = 0.0;
   for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < K; k += gridDim.x * blockDim.x) {
     const float s = fmaf(omd, counts[k], ema_size[k] * decay);  // mul_(decay).add_(x, alpha=1-decay)
@@ -389,6 +395,8 @@ __global__ void __launch_bounds__(256)
     ema_codebook_kernel(const float* __restrict__ sums, int K, int D, float decay, float omd, float eps, int variant,
                         const float* __restrict__ ema_size, const double* __restrict__ total,
                         float* __restrict__ ema_sum, float* __restrict__ codebook) {
+  grid_dep_wait();  // programmatic dependent launch: nothing above touches memory
+  grid_dep_launch();
   const int k = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (k >= K) return;
   const float size = ema_size[k];
@@ -476,6 +484,8 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     mse_kernel(const float* __restrict__ y, const float* __restrict__ t, int64_t n, const float* __restrict__ gscale_dev,
                int act_out, double* __restrict__ sqerr, float* __restrict__ dy) {
+  grid_dep_wait();  // programmatic dependent launch: nothing above touches memory
+  grid_dep_launch();
   const float g = gscale_dev ? __ldg(gscale_dev) : 1.f;
   const float coef = (float)(2.0 / (double)n) * g;
   double local = 0.0;
@@ -498,6 +508,8 @@ __global__ void __launch_bounds__(256)
 
 __global__ void t1_loss_finalize_kernel(const double* __restrict__ sq2, double n_recon, double n_lat, float w_commit,
                                         float w_cb, float* __restrict__ out4) {
+  grid_dep_wait();  // programmatic dependent launch: nothing above touches memory
+  grid_dep_launch();
   const float recon = (float)(sq2[0] / n_recon);
   const float q = (float)(sq2[1] / n_lat);
   // loss = recon_loss + 0.25 * commitment_loss + 0.25 * codebook_loss, left to right (backbone_lfqvae_v5.py:83)
@@ -532,9 +544,9 @@ int lipvq_gather_ste_loss_fwd_f32(const float* z, const int64_t* idx, const floa
   const int64_t items = N * (int64_t)(vec ? D / 4 : D);
   const int grid = stream_grid(items, 256, 8);
   if (vec)
-    gather_fwd_kernel<true><<<grid, 256, 0, stream>>>(z, idx, codebook, N, D, K, z_q_out, z_st_out, sqerr_sum);
+    LIPVQ_CUDA(launch_pdl(gather_fwd_kernel<true>, dim3(grid), dim3(256), 0, stream, z, idx, codebook, N, D, K, z_q_out, z_st_out, sqerr_sum));
   else
-    gather_fwd_kernel<false><<<grid, 256, 0, stream>>>(z, idx, codebook, N, D, K, z_q_out, z_st_out, sqerr_sum);
+    LIPVQ_CUDA(launch_pdl(gather_fwd_kernel<false>, dim3(grid), dim3(256), 0, stream, z, idx, codebook, N, D, K, z_q_out, z_st_out, sqerr_sum));
   LIPVQ_LAUNCHED("gather_fwd_kernel");
   return LIPVQ_OK;
 }
@@ -557,9 +569,7 @@ int lipvq_gather_ste_loss_bwd_f32(const float* z, const float* z_q, const int64_
       LIPVQ_CUDA(cudaFuncSetAttribute(scatter_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       smem_set = smem;
     }
-    scatter_smem_kernel<true><<<sm_count(), kScatThreads, smem, stream>>>(z, z_q, idx, dzq_up, gscale_dev, w_commit,
-                                                                          w_codebook, ste, sigmoid_out, N, D, K,
-                                                                          scatter_lpr(D), dz_out, dcodebook, nullptr);
+    LIPVQ_CUDA(launch_pdl(scatter_smem_kernel<true>, dim3(sm_count()), dim3(kScatThreads), smem, stream, z, z_q, idx, dzq_up, gscale_dev, w_commit, w_codebook, ste, sigmoid_out, N, D, K, scatter_lpr(D), dz_out, dcodebook, nullptr));
   } else if (vec && D <= 512) {
     const RunsPlan rp = plan_runs(N, D);
 #define LIPVQ_GB(G_, V_)                                                                                          \
@@ -594,9 +604,7 @@ int lipvq_ema_stats_f32(const float* z, const int64_t* idx, int64_t N, int D, in
       LIPVQ_CUDA(cudaFuncSetAttribute(scatter_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
       smem_set = smem;
     }
-    scatter_smem_kernel<false><<<sm_count(), kScatThreads, smem, stream>>>(z, nullptr, idx, nullptr, nullptr, 0.f, 0.f, 0,
-                                                                           nullptr, N, D, K, scatter_lpr(D), nullptr, sums,
-                                                                           counts);
+    LIPVQ_CUDA(launch_pdl(scatter_smem_kernel<false>, dim3(sm_count()), dim3(kScatThreads), smem, stream, z, nullptr, idx, nullptr, nullptr, 0.f, 0.f, 0, nullptr, N, D, K, scatter_lpr(D), nullptr, sums, counts));
   } else if (vec) {
     const RunsPlan rp = plan_runs(N, D);
 #define LIPVQ_ES(G_, V_) \
@@ -624,10 +632,10 @@ int lipvq_ema_apply_f32(const float* counts, const float* sums, int K, int D, fl
   LIPVQ_REQUIRE(((uintptr_t)scratch & 7u) == 0, "ema_apply: scratch must be 8-byte aligned");
   double* total = (double*)scratch;
   LIPVQ_CUDA(cudaMemsetAsync(total, 0, sizeof(double), stream));
+  // (normal launch: its predecessor in the stream is the memset above, not a kernel)
   ema_size_kernel<<<stream_grid(K, 256, 4), 256, 0, stream>>>(counts, K, decay, one_minus_decay, ema_size, total);
   LIPVQ_LAUNCHED("ema_size_kernel");
-  ema_codebook_kernel<<<(unsigned)ceil_div64((int64_t)K * 32, 256), 256, 0, stream>>>(
-      sums, K, D, decay, one_minus_decay, eps, variant, ema_size, total, ema_sum, codebook);
+  LIPVQ_CUDA(launch_pdl(ema_codebook_kernel, dim3((unsigned)ceil_div64((int64_t)K * 32, 256)), dim3(256), 0, stream, sums, K, D, decay, one_minus_decay, eps, variant, ema_size, total, ema_sum, codebook));
   LIPVQ_LAUNCHED("ema_codebook_kernel");
   return LIPVQ_OK;
 }
@@ -657,7 +665,7 @@ int lipvq_mse_fwd_bwd_f32(const float* Y, const float* T, int64_t numel, const f
   if (numel == 0) return LIPVQ_OK;
   LIPVQ_REQUIRE(Y && T && sqerr_sum, "mse: null pointer");
   LIPVQ_REQUIRE(act_out == LIPVQ_ACT_NONE || act_out == LIPVQ_ACT_RELU, "mse: act_out must be NONE or RELU");
-  mse_kernel<<<stream_grid(numel, 256, 8), 256, 0, stream>>>(Y, T, numel, gscale_dev, act_out, sqerr_sum, dY);
+  LIPVQ_CUDA(launch_pdl(mse_kernel, dim3(stream_grid(numel, 256, 8)), dim3(256), 0, stream, Y, T, numel, gscale_dev, act_out, sqerr_sum, dY));
   LIPVQ_LAUNCHED("mse_kernel");
   return LIPVQ_OK;
 }
@@ -666,7 +674,7 @@ int lipvq_t1_loss_finalize(const double* sq2, double n_recon, double n_lat, floa
                            float* losses_out4, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   LIPVQ_REQUIRE(sq2 && losses_out4 && n_recon > 0 && n_lat > 0, "t1_loss_finalize: bad argument");
-  t1_loss_finalize_kernel<<<1, 1, 0, stream>>>(sq2, n_recon, n_lat, w_commit, w_cb, losses_out4);
+  LIPVQ_CUDA(launch_pdl(t1_loss_finalize_kernel, dim3(1), dim3(1), 0, stream, sq2, n_recon, n_lat, w_commit, w_cb, losses_out4));
   LIPVQ_LAUNCHED("t1_loss_finalize_kernel");
   return LIPVQ_OK;
 }

@@ -208,6 +208,7 @@ __global__ void __launch_bounds__(256)
                       __half* __restrict__ elo, SearchHdr* hdr) {
   __shared__ float mu_s[512];
   __shared__ float s_part[8];
+  grid_dep_wait();    // (itself a programmatic dependent of whatever produced z)
   grid_dep_launch();  // the fp16 pass may set up (barriers, TMEM) while this kernel runs; it waits before reading
   constexpr int RMAX = 32;
   const int R = (int)(N < RMAX ? N : RMAX);
@@ -931,6 +932,7 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
   {
     int blocks = (Kp + 7) / 8;
     if (blocks > sms) blocks = sms;
+    // (normal launch: its predecessor in the stream is the header memset, not a kernel)
     fused_prep_kernel<<<blocks, 256, 0, stream>>>(z, N, D, cb, K, Kp, g1.Dp, metric, mu, enorm, ehi, elo, hdr);
     LIPVQ_LAUNCHED("fused_prep_kernel");
   }
