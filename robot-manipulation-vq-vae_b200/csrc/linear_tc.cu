@@ -107,7 +107,8 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
   uint64_t* bars = reinterpret_cast<uint64_t*>(epi_scr + (p.C2 != nullptr ? 2 : 1) * kEpiF * 512);
   const uint32_t bar_a_full = smem_u32(bars + 0), bar_a_empty = smem_u32(bars + 2);
   const uint32_t bar_acc_full = smem_u32(bars + 4), bar_acc_empty = smem_u32(bars + 6);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  const uint32_t bar_w = smem_u32(bars + 8);  // weights and bias are in shared memory
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row_blocks = (int)((p.N + kBM - 1) / kBM);
@@ -125,63 +126,15 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
       mbar_init(bar_acc_full + 8 * s, 1);
       mbar_init(bar_acc_empty + 8 * s, kEpiF);
     }
+    mbar_init(bar_w, kEpiF);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
   grid_dep_wait();  // launched as a programmatic dependent: barrier / TMEM setup above overlapped the previous kernel's tail
   grid_dep_launch();
 
-  // ---- weights: split into (h, m, l) and store as swizzled K-major tiles; bias to smem ----
-  // An item is one 16-byte chunk of a tile row: 8 consecutive k of one output n.  Threads follow the contiguous direction
-  // of W (k for the forward layout, n for the transposed one), so the loads coalesce; the swizzle spreads the 16-byte
-  // stores of consecutive n over the banks.
-  {
-    const int KC = p.NC * (kChunk / 8);  // chunks per row: 8 or 16
-    const int items = p.Nbp * KC;
-    const bool k_fast = (p.w_cs == 1);
-    const bool vec = k_fast && (p.w_rs % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.W) & 15) == 0);
-    for (int base = 0; base < items; base += 2 * kThreads) {
-      float wv[2][8];
-      int nn[2], kc[2];
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int it = base + u * kThreads + (int)threadIdx.x;
-        nn[u] = k_fast ? it / KC : it % p.Nbp;
-        kc[u] = k_fast ? it % KC : it / p.Nbp;
-        const int k0 = kc[u] * 8;
-        const bool live = it < items && nn[u] < p.Nb;
-        const float* src = p.W + (int64_t)nn[u] * p.w_rs + (int64_t)k0 * p.w_cs;
-        if (live && vec && k0 + 8 <= p.Ka) {
-          const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
-          wv[u][0] = a.x; wv[u][1] = a.y; wv[u][2] = a.z; wv[u][3] = a.w;
-          wv[u][4] = b.x; wv[u][5] = b.y; wv[u][6] = b.z; wv[u][7] = b.w;
-        } else {
-#pragma unroll
-          for (int e = 0; e < 8; ++e) wv[u][e] = (live && k0 + e < p.Ka) ? __ldg(src + (int64_t)e * p.w_cs) : 0.f;
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int it = base + u * kThreads + (int)threadIdx.x;
-        if (it >= items) continue;
-        uint32_t hh[4], mm[4], ll[4];
-#pragma unroll
-        for (int e = 0; e < 8; e += 2) {
-          split3_pair(wv[u][e], wv[u][e + 1], hh[e >> 1], mm[e >> 1], ll[e >> 1]);
-        }
-        const int c = kc[u] >> 3, n = nn[u];
-        uint8_t* t0 = sB + c * b_tile + (uint32_t)(n * 128 + (((kc[u] & 7) ^ (n & 7)) << 4));
-        *reinterpret_cast<uint4*>(t0) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
-        *reinterpret_cast<uint4*>(t0 + p.NC * b_tile) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
-        *reinterpret_cast<uint4*>(t0 + 2 * p.NC * b_tile) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
-      }
-    }
-    for (int i = threadIdx.x; i < 256; i += kThreads)
-      bias_s[i] = (p.mode == 0 && p.bias != nullptr && i < p.Nb) ? __ldg(p.bias + i) : 0.f;
-    fence_async_smem();
-  }
   fence_before();
-  __syncthreads();
+  __syncthreads();  // barriers initialised, TMEM base published
   fence_after();
   const uint32_t tmem_base = *tmem_slot;
   TR(1);
@@ -191,6 +144,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
     if (lane == 0) {
       const uint32_t idesc = idesc_bf16(kBM, p.Nbp);
       const uint32_t b_base = smem_u32(sB);
+      mbar_wait(bar_w, 0);
       for (int i = 0; i < nblk; ++i) {
         const int buf = i % p.nbufA;
         const uint32_t ab = (uint32_t)i & 1;
@@ -294,6 +248,60 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
     // TMEM hands each lane one token row, but a warp-wide global access with one row per lane touches 32 different
     // lines.  Every 32x16 group therefore passes through this warp's swizzled scratch tile, so global loads (Xpre) and
     // stores run with four lanes per 64-byte row segment (whole sectors).
+    // ---- weights: split into (h, m, l) and store as swizzled K-major tiles; bias to smem ----
+    // (done by the sixteen epilogue warps, which have nothing to drain yet, while the converters already fill the
+    //  first A tile; the MMA warp waits for bar_w before its first instruction)
+    // An item is one 16-byte chunk of a tile row: 8 consecutive k of one output n.  Threads follow the contiguous direction
+    // of W (k for the forward layout, n for the transposed one), so the loads coalesce; the swizzle spreads the 16-byte
+    // stores of consecutive n over the banks.
+    {
+      const int KC = p.NC * (kChunk / 8);  // chunks per row: 8 or 16
+      const int items = p.Nbp * KC;
+      const bool k_fast = (p.w_cs == 1);
+      const bool vec = k_fast && (p.w_rs % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.W) & 15) == 0);
+      for (int base = 0; base < items; base += 2 * kEpiF * 32) {
+        float wv[2][8];
+        int nn[2], kc[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int it = base + u * kEpiF * 32 + (int)threadIdx.x;
+          nn[u] = k_fast ? it / KC : it % p.Nbp;
+          kc[u] = k_fast ? it % KC : it / p.Nbp;
+          const int k0 = kc[u] * 8;
+          const bool live = it < items && nn[u] < p.Nb;
+          const float* src = p.W + (int64_t)nn[u] * p.w_rs + (int64_t)k0 * p.w_cs;
+          if (live && vec && k0 + 8 <= p.Ka) {
+            const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
+            wv[u][0] = a.x; wv[u][1] = a.y; wv[u][2] = a.z; wv[u][3] = a.w;
+            wv[u][4] = b.x; wv[u][5] = b.y; wv[u][6] = b.z; wv[u][7] = b.w;
+          } else {
+#pragma unroll
+            for (int e = 0; e < 8; ++e) wv[u][e] = (live && k0 + e < p.Ka) ? __ldg(src + (int64_t)e * p.w_cs) : 0.f;
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int it = base + u * kEpiF * 32 + (int)threadIdx.x;
+          if (it >= items) continue;
+          uint32_t hh[4], mm[4], ll[4];
+#pragma unroll
+          for (int e = 0; e < 8; e += 2) {
+            split3_pair(wv[u][e], wv[u][e + 1], hh[e >> 1], mm[e >> 1], ll[e >> 1]);
+          }
+          const int c = kc[u] >> 3, n = nn[u];
+          uint8_t* t0 = sB + c * b_tile + (uint32_t)(n * 128 + (((kc[u] & 7) ^ (n & 7)) << 4));
+          *reinterpret_cast<uint4*>(t0) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+          *reinterpret_cast<uint4*>(t0 + p.NC * b_tile) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+          *reinterpret_cast<uint4*>(t0 + 2 * p.NC * b_tile) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+        }
+      }
+      for (int i = threadIdx.x; i < 256; i += kEpiF * 32)
+        bias_s[i] = (p.mode == 0 && p.bias != nullptr && i < p.Nb) ? __ldg(p.bias + i) : 0.f;
+      fence_async_smem();
+    }
+    asm volatile("bar.sync 1, 512;" ::: "memory");  // bias visible to every epilogue warp
+    if (lane == 0) mbar_arrive(bar_w);
+
     const int q = warp & 3, part = warp >> 2;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     const bool vecC = (p.ldc % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.C) & 15) == 0) &&
