@@ -92,7 +92,10 @@ def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: 
     ops.linear_fwd_dual(t["z_q"], A.ACT_NONE, p["decoder.0.weight"], p["decoder.0.bias"], A.ACT_GELU, t["c1"], t["dc1_act"])
     ops.linear_fwd_dual(t["c1"], A.ACT_NONE, p["decoder.2.weight"], p["decoder.2.bias"], A.ACT_GELU, t["c2"], t["dc2_act"])
     ops.linear_fwd(t["c2"], A.ACT_NONE, p["to_output.weight"], p["to_output.bias"], A.ACT_NONE, out=t["x_recon"])
-    ops.mse_fwd_bwd(t["x_recon"], x, t["sq"][0:1])
+    # when the backward buffers already exist (a training step) the same pass also writes d recon_loss / d x_recon,
+    # which backward() then finds in place as long as the loss gradient is 1 (the trainer's case)
+    b.dxr_from_forward = "dxr" in t
+    ops.mse_fwd_bwd(t["x_recon"], x, t["sq"][0:1], dY=t["dxr"] if b.dxr_from_forward else None)
     ops.t1_loss_finalize(t["sq"], float(b.N) * b.F, float(b.N) * b.D, 0.25, 0.25, t["losses"])
 
 
@@ -104,7 +107,8 @@ def backward(p: Dict[str, torch.Tensor], g: Dict[str, torch.Tensor], x: torch.Te
     t = b.t
     scratch = t["scratch"]
     # d recon_loss / d x_recon (the forward pass already produced the loss value; sq is not reused)
-    ops.mse_fwd_bwd(t["x_recon"], x, scratch, gscale=gscale, dY=t["dxr"])
+    if gscale is not None or not getattr(b, "dxr_from_forward", False):
+        ops.mse_fwd_bwd(t["x_recon"], x, scratch, gscale=gscale, dY=t["dxr"])
     # decoder
     ops.linear_bwd_w(t["dxr"], t["c2"], A.ACT_NONE, g["to_output.weight"], g["to_output.bias"])
     ops.linear_bwd_x(t["dxr"], p["to_output.weight"], t["dc2_act"], A.ACT_GIVEN, out=t["dc2"])
