@@ -87,7 +87,8 @@ def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: 
     ops.nn_search(t["z_e"], p["quantizer.codebook"], A.METRIC_L2, algo, out=t["idx"], workspace=t["ws"])
     if encode_only:
         return
-    t["sq"].zero_()
+    if not getattr(b, "zeroed_by_caller", False):  # the trainer clears sq and G with one fill at the start of the step
+        t["sq"].zero_()
     ops.gather_fwd(t["z_e"], t["idx"], p["quantizer.codebook"], t["sq"][1:], z_q=t["z_q"])
     ops.linear_fwd_dual(t["z_q"], A.ACT_NONE, p["decoder.0.weight"], p["decoder.0.bias"], A.ACT_GELU, t["c1"], t["dc1_act"])
     ops.linear_fwd_dual(t["c1"], A.ACT_NONE, p["decoder.2.weight"], p["decoder.2.bias"], A.ACT_GELU, t["c2"], t["dc2_act"])
@@ -121,7 +122,8 @@ def backward(p: Dict[str, torch.Tensor], g: Dict[str, torch.Tensor], x: torch.Te
     ops.gather_bwd(t["z_e"], t["z_q"], t["idx"], t["dzq"], gscale, 0.25, 0.25, False, t["z_e"], b.K, t["dzpre"],
                    g["quantizer.codebook"])
     # Lipschitz layer: G = dL/dW_norm, then through min(1, softplus(ci)/||W_i||_1)
-    t["G"].zero_()
+    if not getattr(b, "zeroed_by_caller", False):
+        t["G"].zero_()
     ops.linear_bwd_w(t["dzpre"], t["a2"], A.ACT_NONE, t["G"], g["to_latent.b"])
     ops.lipschitz_scale_bwd(t["G"], p["to_latent.W"], p["to_latent.ci"], g["to_latent.W"], g["to_latent.ci"])
     ops.linear_bwd_x(t["dzpre"], t["Wn"], t["da2_act"], A.ACT_GIVEN, out=t["da2"])

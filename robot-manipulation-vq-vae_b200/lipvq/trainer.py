@@ -83,6 +83,14 @@ class TokenizerTrainer:
         self.scratch = torch.zeros(1, dtype=torch.float64, device=dev)
         self.bufs = t1.T1Buffers(self.N, F_, D, K, H, dev)
         self.bufs.alloc_backward()
+        # buffers that must be zero when a step starts (sum-of-squares accumulators, the Lipschitz layer's dense
+        # gradient) share one arena so one fill clears them; the loss scalars are written straight into the slab
+        arena = torch.zeros(D * H + 4, dtype=torch.float32, device=dev)
+        self._arena = arena
+        self.bufs.t["G"] = arena[:D * H].view(D, H)
+        self.bufs.t["sq"] = arena[D * H:D * H + 4].view(torch.float64)
+        self.bufs.zeroed_by_caller = True
+        self.bufs.t["losses"] = self.losses_in
         self.x_static = torch.empty(self.N, F_, dtype=torch.float32, device=dev)
         self.use_graph = use_graph
         self._graph_a = None  # zero grads, forward, EMA statistics, backward
@@ -101,11 +109,11 @@ class TokenizerTrainer:
     # -- the launch sequence -------------------------------------------------------------------
     def _phase_a(self):
         self.red.zero_()
+        self._arena.zero_()
         t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo)
         if self.ema:
             t1.ema_stats(self.bufs, self.counts, self.sums)
         t1.backward(self.p, self.g, self.x_static, self.bufs)
-        self.losses_in.copy_(self.bufs.t["losses"])
 
     def _reduce(self):
         if self.peer is not None:
