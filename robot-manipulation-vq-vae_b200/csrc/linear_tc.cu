@@ -467,7 +467,8 @@ struct LinTcWParams {
   float* dW; float* db;
   int Np;        // MMA N: pad16(in_dim + 1)
   int nbA, nbB;  // 64-column blocks of A (1 or 2) and B (1..3)
-  int CA, CB;    // 16-byte chunks per token: ceil(out_dim / 8), ceil((in_dim + 1) / 8)
+  int CA, CB;    // 16-byte chunks per token the converters write: ceil(out_dim / 8) of dY, CB of X
+  int ones_sep;  // in_dim % 8 == 0: the ones column has a chunk of its own, written once at kernel start (CB = in_dim / 8)
   uint32_t tmem_cols;
 };
 
@@ -507,6 +508,14 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
   if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
   // chunks the converters never write (columns past out_dim / in_dim + 1) must read as zero
   for (int i = threadIdx.x; i < (2 * buf_bytes + kWBlk) / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  if (p.ones_sep) {  // constant chunk (1, 0, ..., 0) of every token, h term, both buffers: never touched again
+    __syncthreads();
+    if (threadIdx.x < 2 * kWTok) {
+      const int tk = threadIdx.x & (kWTok - 1), buf = threadIdx.x >> 6, c1 = p.in_dim >> 3;
+      uint8_t* d = smem + buf * buf_bytes + 3 * a_term + (c1 >> 3) * kWBlk + (tk >> 3) * 1024 + (tk & 7) * 128 + (((c1 & 7) ^ (tk & 7)) << 4);
+      *reinterpret_cast<uint4*>(d) = make_uint4(0x00003F80u, 0, 0, 0);  // bf16 1.0 in the low half
+    }
+  }
   grid_dep_wait();  // programmatic dependent launch: everything above is local to the CTA
   grid_dep_launch();
   fence_async_smem();
@@ -623,9 +632,11 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
 #pragma unroll
               for (int e = 0; e < 8; ++e) w[u][e] = (live && c * 8 + e < p.in_dim) ? act_apply(ACT, w[u][e]) : 0.f;
             });
+          if (!p.ones_sep) {  // in_dim % 8 != 0: the ones column (db = dY^T 1; dead tokens have dY = 0) shares a data chunk
 #pragma unroll
-          for (int e = 0; e < 8; ++e)
-            if (c * 8 + e == p.in_dim) w[u][e] = 1.f;  // ones column: db = dY^T 1 (dead tokens have dY = 0)
+            for (int e = 0; e < 8; ++e)
+              if (c * 8 + e == p.in_dim) w[u][e] = 1.f;
+          }
         }
         uint32_t hh[4], mm[4], ll[4];
 #pragma unroll
@@ -778,7 +789,8 @@ int linear_tc_bwd_w_launch(const float* dY, int64_t N, int out_dim, const float*
   p.nbA = (out_dim + 63) / 64;
   p.nbB = (in_dim + 1 + 63) / 64;
   p.CA = (out_dim + 7) / 8;
-  p.CB = (in_dim + 1 + 7) / 8;
+  p.ones_sep = (in_dim % 8 == 0) ? 1 : 0;
+  p.CB = p.ones_sep ? in_dim / 8 : (in_dim + 1 + 7) / 8;
   uint32_t cols = 32;
   while (cols < (uint32_t)p.Np) cols <<= 1;
   p.tmem_cols = cols;
