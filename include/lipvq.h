@@ -166,7 +166,7 @@ LIPVQ_API int lipvq_codebook_usage_f32(const float* cluster_size, int K, float d
  *   bwd_x: dX[n,i] = ( sum_o dY[n,o] * W[o,i] ) * act_in'(X[n,i])                 (gradient at X, the stored pre-activation)
  *   bwd_w: dW[o,i] += sum_n dY[n,o] * act_in(X[n,i]) ;  db[o] += sum_n dY[n,o]    (ACCUMULATED INTO; db may be NULL)
  *
- * Two implementations behind each entry point, chosen per shape (LIPVQ_LINEAR_ALGO=simt|tc overrides):
+ * Two implementations behind each entry point, chosen per shape (LIPVQ_LINEAR_ALGO=simt forces the second):
  * tcgen05 MMAs on three-way bf16 splits of both operands (six chains, fp32 accumulation in TMEM; as
  * accurate as fp32 FFMA) for N >= 4096 tokens and dims <= 128, fp32 FFMA tiles otherwise.
  * --------------------------------------------------------------------------------------------- */

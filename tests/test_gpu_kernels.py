@@ -295,10 +295,9 @@ def test_linear_fwd_dual_and_given_derivative(L, N, i, o, act):
     assert off <= (o2 if act == 1 else 0)  # relu: one pre-activation within rounding of 0 may flip one row of dX
 
 
-def test_linear_tc_bwd_w_forced(L, monkeypatch):
-    """dW/db on the tensor cores for a layer without input activation (the dispatcher keeps those on the FFMA tiles;
-    LIPVQ_LINEAR_ALGO=tc forces the tcgen05 kernel so it stays covered), ragged token count."""
-    monkeypatch.setenv("LIPVQ_LINEAR_ALGO", "tc")
+def test_linear_tc_bwd_w_plain_and_simt_agree(L, monkeypatch):
+    """dW/db of a layer without input activation, ragged token count: the tcgen05 kernel (MN-major operands, default for
+    N >= 4096) against fp64, and the FFMA tiles (LIPVQ_LINEAR_ALGO=simt) on the same data so both stay covered."""
     g = torch.Generator().manual_seed(5)
     N, i, o = 10007, 64, 64
     X, dY = torch.randn(N, i, generator=g), torch.randn(N, o, generator=g)
@@ -306,6 +305,10 @@ def test_linear_tc_bwd_w_forced(L, monkeypatch):
     L.ops.linear_bwd_w(dY.to(DEV), X.to(DEV), 0, dW, db)
     assert torch.allclose(dW.cpu(), (dY.double().t() @ X.double()).float(), rtol=1e-4, atol=2e-3)
     assert torch.allclose(db.cpu(), dY.double().sum(0).float(), rtol=1e-4, atol=2e-3)
+    monkeypatch.setenv("LIPVQ_LINEAR_ALGO", "simt")
+    dW2, db2 = torch.zeros(o, i, device=DEV), torch.zeros(o, device=DEV)
+    L.ops.linear_bwd_w(dY.to(DEV), X.to(DEV), 0, dW2, db2)
+    assert torch.allclose(dW2, dW, rtol=1e-4, atol=2e-3) and torch.allclose(db2, db, rtol=1e-4, atol=2e-3)
 
 
 def test_linear_tc_tiny_gradients_and_wide_range(L):
