@@ -131,7 +131,6 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
   }
   if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
   grid_dep_wait();  // launched as a programmatic dependent: barrier / TMEM setup above overlapped the previous kernel's tail
-  grid_dep_launch();
 
   fence_before();
   __syncthreads();  // barriers initialised, TMEM base published
@@ -436,6 +435,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
   }
 
   TR(2);
+  grid_dep_launch();  // this CTA's work is done: the next kernel may be scheduled (a waiting dependent polls, so not earlier)
   fence_before();
   __syncthreads();
   if (warp == kWarpMma) {
@@ -517,7 +517,6 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
     }
   }
   grid_dep_wait();  // programmatic dependent launch: everything above is local to the CTA
-  grid_dep_launch();
   fence_async_smem();
   fence_before();
   __syncthreads();
@@ -703,6 +702,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
   }
 
   TR(2);
+  grid_dep_launch();  // this CTA's work is done: the next kernel may be scheduled (a waiting dependent polls, so not earlier)
   fence_before();
   __syncthreads();
   if (warp == kWarpMma) {

@@ -197,7 +197,6 @@ __global__ void __launch_bounds__(kScatThreads, 1)
                         float w_codebook, int ste, const float* __restrict__ sig_out, int64_t N, int D, int K, int lpr,
                         float* __restrict__ dz, float* __restrict__ tab_g, float* __restrict__ counts_g) {
   grid_dep_wait();  // programmatic dependent launch: nothing above touches memory
-  grid_dep_launch();
   extern __shared__ __align__(16) float s_tab[];  // [K*D] (+ [K] counts for the statistics)
   float* s_cnt = s_tab + (size_t)K * D;
   const int64_t tab_n = (int64_t)K * D + (BWD ? 0 : K);
@@ -274,6 +273,7 @@ __global__ void __launch_bounds__(kScatThreads, 1)
     }
   }
   __syncthreads();
+  grid_dep_launch();  // only the flush is left: the next kernel may be scheduled (it waits for our completion at its top)
   if (tab_g) scatter_flush(s_tab, (int64_t)K * D, tab_g);
   if (!BWD) scatter_flush(s_cnt, K, counts_g);
 }

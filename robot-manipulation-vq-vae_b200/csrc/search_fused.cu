@@ -336,7 +336,6 @@ __global__ void __launch_bounds__(kThreads, 1)
   TR(0);
 #endif
 
-  grid_dep_launch();
   int64_t n_rows = p.N;
   if (p.n_rows_ptr) {
     grid_dep_wait();  // the row count is the previous pass's output
@@ -749,6 +748,9 @@ __global__ void __launch_bounds__(kThreads, 1)
   }
 
   TR(2);
+  // dependents (next pass / exact scan) may be scheduled now: a waiting dependent polls, so it must not sit next to
+  // CTAs that still work (the C3 sweep lost 10-20 % with the trigger at the top of the kernel)
+  grid_dep_launch();
   tc_fence_before();
   __syncthreads();
   if (warp == kWarpMma) {
