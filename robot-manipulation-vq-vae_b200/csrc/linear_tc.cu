@@ -435,9 +435,9 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
   }
 
   TR(2);
-  grid_dep_launch();  // this CTA's work is done: the next kernel may be scheduled (a waiting dependent polls, so not earlier)
   fence_before();
   __syncthreads();
+  grid_dep_launch();  // every role of this CTA is done: the next kernel may be scheduled (a waiting dependent polls, so not earlier)
   if (warp == kWarpMma) {
     fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
@@ -702,9 +702,9 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
   }
 
   TR(2);
-  grid_dep_launch();  // this CTA's work is done: the next kernel may be scheduled (a waiting dependent polls, so not earlier)
   fence_before();
   __syncthreads();
+  grid_dep_launch();  // every role of this CTA is done: the next kernel may be scheduled (a waiting dependent polls, so not earlier)
   if (warp == kWarpMma) {
     fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);

@@ -748,11 +748,12 @@ __global__ void __launch_bounds__(kThreads, 1)
   }
 
   TR(2);
-  // dependents (next pass / exact scan) may be scheduled now: a waiting dependent polls, so it must not sit next to
-  // CTAs that still work (the C3 sweep lost 10-20 % with the trigger at the top of the kernel)
-  grid_dep_launch();
   tc_fence_before();
   __syncthreads();
+  // every role of this CTA is done (the first thread to get here would otherwise trigger for the whole CTA -- the idle
+  // lanes of the single-thread roles arrive at once): dependents (next pass / exact scan) may be scheduled now.  A
+  // waiting dependent polls, so it must not sit next to CTAs that still work (the C3 sweep lost 10-20 % that way).
+  grid_dep_launch();
   if (warp == kWarpMma) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(tmem_cols) : "memory");
