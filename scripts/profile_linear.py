@@ -1,0 +1,30 @@
+"""Three launches each of the dual forward (64 -> 128, GELU value + derivative), the input gradient through the stored
+derivative and the weight gradient at the bench's token count: the target of `ncu -k regex:linear_tc` captures.
+usage: python scripts/profile_linear.py"""
+import math
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "robot-manipulation-vq-vae_b200"))
+import lipvq  # noqa: E402
+from lipvq import ops  # noqa: E402
+
+N, i, o = 65536, 64, 128
+g = torch.Generator().manual_seed(0)
+X = torch.randn(N, i, generator=g).cuda()
+W = (torch.randn(o, i, generator=g) / math.sqrt(i)).cuda()
+b = torch.randn(o, generator=g).cuda()
+Y, dYd = torch.empty(N, o, device="cuda"), torch.empty(N, o, device="cuda")
+dY = torch.randn(N, o, generator=g).cuda()
+dX = torch.empty(N, i, device="cuda")
+dW, db = torch.zeros(o, i, device="cuda"), torch.zeros(o, device="cuda")
+for _ in range(3):
+    ops.linear_fwd_dual(X, lipvq.ACT_NONE, W, b, lipvq.ACT_GELU, Y, dYd)      # launches 0-2
+for _ in range(3):
+    ops.linear_bwd_x(dY, W, X, lipvq.ACT_GIVEN, out=dX)                        # launches 3-5
+for _ in range(3):
+    ops.linear_bwd_w(dY, X, lipvq.ACT_NONE, dW, db)                            # linear_tc_bwd_w launches 0-2
+torch.cuda.synchronize()
