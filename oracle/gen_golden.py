@@ -147,6 +147,62 @@ def gen_t2(hv, tag, A, E, Kz, Kq, stages, layers, B, T):
           usage_z_used=usage["z_used"], usage_q_used=usage["q_used"])
 
 
+def _blobs(n_super, n_sub, per, dim, seed):
+    """Well-separated hierarchical blobs: n_super super-clusters of n_sub sub-blobs each.  k-means with k = n_super or
+    k = n_super * n_sub then has one unambiguous optimum, so the fixture does not depend on sklearn's thread count."""
+    g = torch.Generator().manual_seed(seed)
+    sup = torch.randn(n_super, dim, generator=g) * 4.0
+    pts = []
+    for s in range(n_super):
+        for _ in range(n_sub):
+            c = sup[s] + torch.randn(dim, generator=g) * 0.5
+            pts.append(c + torch.randn(per, dim, generator=g) * 0.02)
+    x = torch.cat(pts)
+    return x[torch.randperm(x.shape[0], generator=g)]
+
+
+def gen_t3_hier(hq, tag):
+    """HierarchicalLFQHVQVAE.forward (hq_vae.py:289-415) run by the reference itself: 11-key dict, all parameter
+    gradients, EMA / usage buffers of both quantizers after the step (k-means skipped, dead-code replacement off)."""
+    torch.manual_seed(4)
+    m = hq.HierarchicalLFQHVQVAE(7, 32, 16, num_z_codes=64, num_q_codes=32)
+    for qz in (m.z_quantizer, m.q_quantizer):
+        qz.initialized, qz.dead_threshold = True, 0
+    with torch.no_grad():
+        m.z_quantizer.codebook.copy_(torch.rand(64, 32))
+        m.q_quantizer.codebook.copy_(torch.rand(32, 16))
+    sd0 = {k: v.clone() for k, v in m.state_dict().items()}
+    x = torch.rand(200, 7, generator=torch.Generator().manual_seed(123)) * 2 - 1
+    out = m(x)
+    m.zero_grad()
+    out["loss"].backward()
+    grads = {"grad." + k: p.grad.clone() for k, p in m.named_parameters() if p.grad is not None}
+    post = {"post." + k: v.clone() for k, v in m.state_dict().items()}
+    _save(tag, x=x, **{"out." + k: v for k, v in out.items()}, **{"sd." + k: v for k, v in sd0.items()}, **grads, **post)
+
+
+def gen_kmeans(hq, hv, tag):
+    """The two k-means initialisers run by the reference: HierarchicalVQVAE.initialize_codebooks_with_current_batch
+    (heirarchical_vqvae.py:321-419, sklearn random_state=42) and LFQQuantizerEMA_KMeans.kmeans_init (hq_vae.py:65-78,
+    numpy global RNG) on blob data whose optimum is unambiguous."""
+    emb = _blobs(8, 2, 16, 16, 7).view(16, 16, 16)  # [B=16, T=16, E=16]: 8 super-clusters x 2 sub-blobs x 16 points
+    torch.manual_seed(0)
+    m = hv.HierarchicalVQVAE(7, embed_dim=16, num_subclusters=16, num_clusters=8, num_stages=1, num_layers_per_stage=1,
+                             dropout=0.0, kmeans_init=True)
+    np.random.seed(0)
+    m.initialize_codebooks_with_current_batch(emb)
+    t2 = {"t2." + k: m.state_dict()[k].clone() for k in
+          ("codebook_z", "codebook_q", "cluster_size_z", "cluster_size_q", "embed_avg_z", "embed_avg_q",
+           "codebooks_initialized")}
+    z = torch.sigmoid(_blobs(8, 1, 32, 8, 9))  # [256, 8] latents in (0,1), 8 blobs
+    torch.manual_seed(1)
+    q = hq.LFQQuantizerEMA_KMeans(8, 8, dead_threshold=0)
+    torch.manual_seed(5)
+    np.random.seed(5)
+    q.kmeans_init(z)
+    _save(tag, emb=emb, z=z, **t2, hq_codebook=q.codebook.data.clone(), hq_ema_codebook=q.ema_codebook.data.clone())
+
+
 def main():
     v5 = _load("ref_v5", "robomimic/models/vq_vae/backbone_lfqvae_v5.py")
     hq = _load("ref_hq", "robomimic/models/vq_vae/hq_vae.py")
@@ -159,6 +215,8 @@ def main():
     gen_quantizers(hq, "quantizers", 256, 64, 32)
     gen_t4(bb, "t4_classic", 7, 32, 128, 64)
     gen_t2(hv, "t2_hvq", 7, 64, 64, 32, 2, 3, 4, 16)
+    gen_t3_hier(hq, "t3_hier")
+    gen_kmeans(hq, hv, "kmeans_init")
 
 
 if __name__ == "__main__":

@@ -19,7 +19,9 @@ Reference anchors (paths relative to the reference checkout):
   * nearest-code search (L2) ...... backbone_lfqvae_v5.py:37-48
   * T1 tokenizer fwd + losses ..... backbone_lfqvae_v5.py:51-84
   * EMA quantizer ................. robomimic/models/vq_vae/hq_vae.py:224-281
-  * Laplace/k-means EMA quantizer . hq_vae.py:84-130 (k-means init excluded: host-side RNG)
+  * Laplace/k-means EMA quantizer . hq_vae.py:84-130; k-means init hq_vae.py:65-78 (sklearn, host side)
+  * hierarchical Lipschitz VQ-VAE . hq_vae.py:289-415
+  * HVQ k-means codebook init ..... robomimic/algo/heirarchical_vqvae.py:321-419 (sklearn + assignment statistics)
   * classic VQ-VAE (STE) .......... robomimic/models/vq_vae/backbone.py:38-76
   * MS-TCN encoder/decoder ........ robomimic/algo/heirarchical_vqvae.py:8-214
   * cosine quantize / EMA / loss .. heirarchical_vqvae.py:421-541, 590-685
@@ -251,6 +253,76 @@ def t1_train_step(p: Params, x: torch.Tensor, opt_state: Dict, *, ema: Dict | No
     res = {k: v.detach() for k, v in out.items()}
     res["grads"] = grads
     return res
+
+
+# --------------------------------------------------------------------------------------
+# T3: HierarchicalLFQHVQVAE (hq_vae.py:289-415): T1 encoder -> Lipschitz -> Laplace-EMA quantizer Z ->
+# Lipschitz q_encoder on z_q.detach() -> Laplace-EMA quantizer Q -> T1 decoder
+# --------------------------------------------------------------------------------------
+def t3_forward(p: Params, x: torch.Tensor) -> Dict[str, torch.Tensor]:
+    """Functional restatement of HierarchicalLFQHVQVAE.forward with both quantizers already initialised and dead-code
+    replacement off.  Returns the reference's 11 keys plus ``post``: the buffers / codebooks each quantizer holds after
+    the call (EMA runs unconditionally, hq_vae.py:103-130)."""
+    h = F.gelu(F.linear(F.gelu(F.linear(x, p["encoder.0.weight"], p["encoder.0.bias"])), p["encoder.2.weight"],
+                        p["encoder.2.bias"]))
+    z_e = lipschitz_sigmoid(h, p["to_z_latent.W"], p["to_z_latent.b"], p["to_z_latent.ci"])
+    post: Params = {}
+
+    def quant(pref: str, e: torch.Tensor):
+        cb = p[pref + ".codebook"]
+        idx = nearest_code_l2(e.detach(), cb.detach())
+        q = cb[idx]
+        with torch.no_grad():
+            size, esum, new_cb = ema_update_laplace(e.detach(), idx, p[pref + ".ema_cluster_size"], p[pref + ".ema_codebook"])
+            counts = F.one_hot(idx, cb.shape[0]).float().sum(0)
+            uc, uma, ent = usage_stats(counts, p[pref + ".usage_counts"], p[pref + ".usage_ma"], p[pref + ".entropy_ma"])
+        post.update({pref + ".ema_cluster_size": size, pref + ".ema_codebook": esum, pref + ".codebook": new_cb,
+                     pref + ".usage_counts": uc, pref + ".usage_ma": uma, pref + ".entropy_ma": ent})
+        return q, idx
+
+    z_q, z_idx = quant("z_quantizer", z_e)
+    commit_z, codebook_z = F.mse_loss(z_e, z_q.detach()), F.mse_loss(z_q, z_e.detach())
+    q_e = lipschitz_sigmoid(z_q.detach(), p["q_encoder.W"], p["q_encoder.b"], p["q_encoder.ci"])
+    q_q, q_idx = quant("q_quantizer", q_e)
+    commit_q, codebook_q = F.mse_loss(q_e, q_q.detach()), F.mse_loss(q_q, q_e.detach())
+    d = F.gelu(F.linear(F.gelu(F.linear(q_q, p["decoder.0.weight"], p["decoder.0.bias"])), p["decoder.2.weight"],
+                        p["decoder.2.bias"]))
+    x_recon = F.linear(d, p["to_output.weight"], p["to_output.bias"])
+    recon = F.mse_loss(x_recon, x)
+    loss = recon + 0.25 * (commit_z + codebook_z) + 0.25 * (commit_q + codebook_q)
+    return {"loss": loss, "recon_loss": recon, "z_commit": commit_z, "z_codebook": codebook_z, "q_commit": commit_q,
+            "q_codebook": codebook_q, "x_recon": x_recon, "z_q": z_q, "q_q": q_q, "z_indices": z_idx, "q_indices": q_idx,
+            "post": post}
+
+
+def hvq_assignment_stats(sample: torch.Tensor, codebook: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """heirarchical_vqvae.py:377-394 (cosine branch): counts = bincount(argmax(normalize(x) @ codebook^T)),
+    sums[k] = sum of the un-normalised rows assigned to k."""
+    assign = torch.argmax(torch.matmul(F.normalize(sample, dim=-1), codebook.t()), dim=1)
+    K = codebook.shape[0]
+    counts = torch.bincount(assign, minlength=K).float()
+    sums = torch.zeros_like(codebook)
+    for k in range(K):
+        m = (assign == k).nonzero(as_tuple=False).squeeze(-1)
+        if m.numel() > 0:
+            sums[k] = sample[m].sum(dim=0)
+    return counts, sums
+
+
+def hvq_kmeans_init(embeddings: torch.Tensor, num_subclusters: int, num_clusters: int) -> Params:
+    """heirarchical_vqvae.py:321-419 with kmeans_init=True, use_cosine=True (<= sample_limit rows, so no subsampling):
+    sklearn KMeans(n_init=10, random_state=42, max_iter=300) for Z and Q, centres L2-normalised, EMA statistics from
+    the assignment of the same rows."""
+    from sklearn.cluster import KMeans
+    flat = embeddings.reshape(-1, embeddings.shape[-1])
+    sample = flat.cpu().numpy()
+    out: Params = {}
+    for tag, k in (("z", num_subclusters), ("q", num_clusters)):
+        km = KMeans(n_clusters=k, n_init=10, random_state=42, max_iter=300).fit(sample)
+        cb = F.normalize(torch.from_numpy(km.cluster_centers_).float(), dim=-1)
+        counts, sums = hvq_assignment_stats(flat, cb)
+        out.update({"codebook_" + tag: cb, "cluster_size_" + tag: counts, "embed_avg_" + tag: sums})
+    return out
 
 
 # --------------------------------------------------------------------------------------

@@ -11,6 +11,9 @@
 // Flags carry a per-CTA call counter (monotonic, kept on the device so a captured graph replays correctly).
 // The symmetric allocation and the peer pointers come from torch.distributed._symmetric_memory (host plumbing);
 // the data path is this kernel only.  NCCL remains the fallback (lipvq/parallel.py).
+#include <stdio.h>
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace lipvq {
@@ -34,7 +37,7 @@ __device__ __forceinline__ float4 ld_peer_f4(const float4* p) {  // system-scope
 
 // flags of one rank: [2 phases][world][gridDim.x] uint32 at byte offset flag_off of its symmetric buffer
 __device__ __forceinline__ void exchange(const uint64_t* peer_ptrs, int64_t flag_off, int phase, int rank, int world,
-                                         uint32_t epoch) {
+                                         uint32_t epoch, long long timeout_clocks) {
   const int G = gridDim.x, b = blockIdx.x;
   if ((int)threadIdx.x < world) {
     uint32_t* theirs = reinterpret_cast<uint32_t*>(peer_ptrs[threadIdx.x] + flag_off) + ((size_t)phase * world + rank) * G + b;
@@ -44,9 +47,16 @@ __device__ __forceinline__ void exchange(const uint64_t* peer_ptrs, int64_t flag
     long long t0 = 0;
     uint32_t spins = 0;
     while ((int32_t)(ld_acquire_sys(mine) - epoch) < 0) {
-      if ((++spins & 255u) == 0) {  // a rank that never arrives traps the others instead of hanging the box
+      if ((++spins & 255u) == 0) {
+        // A rank that NEVER arrives must not hang the box for good -- but a rank that is merely late (rank-0-only
+        // checkpointing or validation, a data-loader stall, first-step warm-up) has to be waited for, as NCCL would.
+        // The bound is LIPVQ_PEER_TIMEOUT_S (default 1800 s, NCCL's default watchdog); on expiry say who is missing.
         if (t0 == 0) t0 = clock64();
-        else if (clock64() - t0 > 60000000000LL) __trap();
+        else if (clock64() - t0 > timeout_clocks) {
+          printf("lipvq: peer all-reduce: rank %d gave up waiting for rank %d (phase %d, call %u) after LIPVQ_PEER_TIMEOUT_S; "
+                 "that rank stopped issuing steps\n", rank, (int)threadIdx.x, phase, epoch);
+          __trap();
+        }
       }
     }
   }
@@ -55,12 +65,12 @@ __device__ __forceinline__ void exchange(const uint64_t* peer_ptrs, int64_t flag
 
 __global__ void __launch_bounds__(kArThreads)
     allreduce_oneshot_kernel(const uint64_t* __restrict__ peer_ptrs, int rank, int world, int64_t n4, int64_t flag_off,
-                             float4* __restrict__ out, uint32_t* __restrict__ cta_epoch) {
+                             float4* __restrict__ out, uint32_t* __restrict__ cta_epoch, long long timeout_clocks) {
   __shared__ uint32_t s_epoch;
   if (threadIdx.x == 0) s_epoch = ++cta_epoch[blockIdx.x];
   __syncthreads();
   const uint32_t epoch = s_epoch;
-  exchange(peer_ptrs, flag_off, 0, rank, world, epoch);
+  exchange(peer_ptrs, flag_off, 0, rank, world, epoch, timeout_clocks);
   for (int64_t i = (int64_t)blockIdx.x * kArThreads + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kArThreads) {
     float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int r = 0; r < world; ++r) {  // rank order on every rank: identical bits everywhere
@@ -70,7 +80,7 @@ __global__ void __launch_bounds__(kArThreads)
     out[i] = acc;
   }
   __syncthreads();
-  exchange(peer_ptrs, flag_off, 1, rank, world, epoch);
+  exchange(peer_ptrs, flag_off, 1, rank, world, epoch, timeout_clocks);
 }
 
 }  // namespace
@@ -81,6 +91,20 @@ using namespace lipvq;
 extern "C" {
 
 int lipvq_allreduce_oneshot_ctas(void) { return 32; }
+
+// how long a rank waits for a peer's flag before it gives up (SM clocks; ~2 GHz)
+static long long peer_timeout_clocks() {
+  static long long cached = 0;
+  if (cached == 0) {
+    double s = 1800.0;
+    if (const char* e = getenv("LIPVQ_PEER_TIMEOUT_S")) {
+      const double v = atof(e);
+      if (v > 0.0) s = v;
+    }
+    cached = (long long)(s * 2.0e9);
+  }
+  return cached;
+}
 
 size_t lipvq_allreduce_oneshot_flag_bytes(int world) {
   return (size_t)2 * (size_t)(world > 0 ? world : 1) * (size_t)lipvq_allreduce_oneshot_ctas() * sizeof(uint32_t);
@@ -95,7 +119,7 @@ int lipvq_allreduce_oneshot_f32(const uint64_t* peer_ptrs_dev, int rank, int wor
   if (n == 0) return LIPVQ_OK;
   LIPVQ_REQUIRE(peer_ptrs_dev && out && cta_epoch && aligned16(out), "allreduce_oneshot: null or misaligned pointer");
   allreduce_oneshot_kernel<<<lipvq_allreduce_oneshot_ctas(), kArThreads, 0, stream>>>(
-      peer_ptrs_dev, rank, world, n / 4, flag_offset_bytes, reinterpret_cast<float4*>(out), cta_epoch);
+      peer_ptrs_dev, rank, world, n / 4, flag_offset_bytes, reinterpret_cast<float4*>(out), cta_epoch, peer_timeout_clocks());
   LIPVQ_LAUNCHED("allreduce_oneshot_kernel");
   return LIPVQ_OK;
 }

@@ -34,13 +34,19 @@ bool pdl_enabled() {
   return cached == 1;
 }
 
+int current_device() {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0) return 0;
+  return dev < kMaxDevices ? dev : kMaxDevices - 1;
+}
+
 int sm_count() {
-  static int cached = 0;
-  if (cached > 0) return cached;
-  int dev = 0, n = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess) return 148;
+  static int cached[kMaxDevices] = {};  // per device: a process may drive several GPUs
+  const int dev = current_device();
+  if (cached[dev] > 0) return cached[dev];
+  int n = 0;
   if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) return 148;
-  cached = n;
+  cached[dev] = n;
   return n;
 }
 

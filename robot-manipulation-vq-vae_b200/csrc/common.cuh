@@ -11,7 +11,9 @@ namespace lipvq {
 void set_error(const char* fmt, ...);
 int cuda_fail(cudaError_t e, const char* what);
 void count_launch(int n = 1);
-int sm_count();
+int sm_count();                 // of the CURRENT device
+constexpr int kMaxDevices = 64;  // per-device caches (SM count, shared-memory opt-in of each kernel) are indexed by this
+int current_device();
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
 

@@ -756,10 +756,11 @@ int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, i
     set_error("linear_tc: shape Ka=%d Nb=%d does not fit shared memory", Ka, Nb);
     return LIPVQ_ERR_INVALID;
   }
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
+  static size_t smem_set[kMaxDevices] = {};  // the attribute is per device
+  const int dev_ = current_device();
+  if (smem > smem_set[dev_]) {
     LIPVQ_CUDA(cudaFuncSetAttribute(linear_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
+    smem_set[dev_] = smem;
   }
   const int row_blocks = (int)ceil_div64(N, kBM);
   const int sms = sm_count();
@@ -795,10 +796,11 @@ int linear_tc_bwd_w_launch(const float* dY, int64_t N, int out_dim, const float*
   while (cols < (uint32_t)p.Np) cols <<= 1;
   p.tmem_cols = cols;
   const size_t smem = bwd_w_smem(out_dim, in_dim);
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
+  static size_t smem_set[kMaxDevices] = {};  // the attribute is per device
+  const int dev_ = current_device();
+  if (smem > smem_set[dev_]) {
     LIPVQ_CUDA(cudaFuncSetAttribute(linear_tc_bwd_w_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set = smem;
+    smem_set[dev_] = smem;
   }
   const int blocks = (int)ceil_div64(N, kWTok);
   const int sms = sm_count();

@@ -564,10 +564,11 @@ int lipvq_gather_ste_loss_bwd_f32(const float* z, const float* z_q, const int64_
                    (!dcodebook || aligned16(dcodebook));
   if (vec && scatter_fits(K, D, false) && N >= 4096) {
     const size_t smem = (size_t)K * D * sizeof(float);
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
+    static size_t smem_set[kMaxDevices] = {};  // the attribute is per device
+  const int dev_ = current_device();
+    if (smem > smem_set[dev_]) {
       LIPVQ_CUDA(cudaFuncSetAttribute(scatter_smem_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      smem_set = smem;
+      smem_set[dev_] = smem;
     }
     LIPVQ_CUDA(launch_pdl(scatter_smem_kernel<true>, dim3(sm_count()), dim3(kScatThreads), smem, stream, z, z_q, idx, dzq_up, gscale_dev, w_commit, w_codebook, ste, sigmoid_out, N, D, K, scatter_lpr(D), dz_out, dcodebook, nullptr));
   } else if (vec && D <= 512) {
@@ -599,10 +600,11 @@ int lipvq_ema_stats_f32(const float* z, const int64_t* idx, int64_t N, int D, in
   const bool vec = (D % 4 == 0) && D <= 512 && aligned16(z) && aligned16(sums);
   if (vec && scatter_fits(K, D, true) && N >= 4096) {
     const size_t smem = ((size_t)K * D + K) * sizeof(float);
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
+    static size_t smem_set[kMaxDevices] = {};  // the attribute is per device
+  const int dev_ = current_device();
+    if (smem > smem_set[dev_]) {
       LIPVQ_CUDA(cudaFuncSetAttribute(scatter_smem_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-      smem_set = smem;
+      smem_set[dev_] = smem;
     }
     LIPVQ_CUDA(launch_pdl(scatter_smem_kernel<false>, dim3(sm_count()), dim3(kScatThreads), smem, stream, z, nullptr, idx, nullptr, nullptr, 0.f, 0.f, 0, nullptr, N, D, K, scatter_lpr(D), nullptr, sums, counts));
   } else if (vec) {

@@ -940,7 +940,8 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
     LIPVQ_LAUNCHED("fused_prep_kernel");
   }
 
-  static size_t smem_set1 = 0, smem_set3 = 0;
+  static size_t smem_set1[kMaxDevices] = {}, smem_set3[kMaxDevices] = {};  // the attribute is per device
+  const int dev_ = current_device();
   const int row_blocks = (int)ceil_div64(N, kBM);
   const float u22 = 2.3841858e-7f;  // 2^-22: bound used per accumulation step of the tensor core (truncating adder)
   const float gamma_ref = 4.f * (float)(D + 4) * 5.9604645e-8f;
@@ -968,9 +969,9 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
     const float steps = (float)(g1.Dp / 16);
     p.gamma_en = (float)(D + 4) * 5.9604645e-8f + (steps + 1.f) * u22;
     p.gamma_dot = 9.7751617e-4f /* 2^-10 (1 + 2^-10) */ + (steps + 1.f) * u22;
-    if (g1.smem > smem_set1) {
+    if (g1.smem > smem_set1[dev_]) {
       LIPVQ_CUDA(cudaFuncSetAttribute(search_fused_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g1.smem));
-      smem_set1 = g1.smem;
+      smem_set1[dev_] = g1.smem;
     }
     const int grid = row_blocks < sms ? row_blocks : sms;
     LIPVQ_CUDA(launch_pdl(search_fused_kernel<1>, dim3(grid), dim3(kThreads), g1.smem, stream, tm_hi, tm_lo, tm_z, p));
@@ -988,9 +989,9 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
     const float steps = (float)(3 * g3.Dp / 16);
     p.gamma_en = (float)(D + 4) * 5.9604645e-8f + (steps + 1.f) * u22;
     p.gamma_dot = 4.f * u22 + (steps + 1.f) * u22;
-    if (g3.smem > smem_set3) {
+    if (g3.smem > smem_set3[dev_]) {
       LIPVQ_CUDA(cudaFuncSetAttribute(search_fused_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g3.smem));
-      smem_set3 = g3.smem;
+      smem_set3[dev_] = g3.smem;
     }
     // the queue length is only known on the device: size the grid for a modest queue, CTAs stride over the blocks
     int grid = row_blocks < sms ? row_blocks : sms;

@@ -4,6 +4,7 @@ arithmetic op here is a hand-written sm_100a kernel; nothing falls back to torch
 """
 from __future__ import annotations
 
+import threading
 from typing import Optional, Tuple
 
 import torch
@@ -13,22 +14,52 @@ from . import _cabi as A
 lib = A.lib
 
 
+class _CallState(threading.local):
+    dev = None  # device of the operands validated by _chk since the last C call on this thread
+
+
+_cs = _CallState()
+
+
 def _stream() -> int:
-    return torch.cuda.current_stream().cuda_stream
+    """The current stream of the OPERANDS' device (torch's current device may be another one: the reference's
+    nn.Modules work on any device after .to(), so do these)."""
+    dev = _cs.dev
+    return torch.cuda.current_stream(dev).cuda_stream if dev is not None else torch.cuda.current_stream().cuda_stream
 
 
 def _chk(t: Optional[torch.Tensor], dtype, name: str, allow_none: bool = False) -> int:
     if t is None:
         if allow_none:
             return 0
+        _cs.dev = None
         raise ValueError(f"{name} is required")
+    err = None
     if not t.is_cuda:
-        raise RuntimeError(f"{name} must be a CUDA tensor: lipvq has no CPU path")
-    if t.dtype != dtype:
-        raise TypeError(f"{name} must be {dtype}, got {t.dtype}")
-    if not t.is_contiguous():
-        raise ValueError(f"{name} must be contiguous")
+        err = RuntimeError(f"{name} must be a CUDA tensor: lipvq has no CPU path")
+    elif t.dtype != dtype:
+        err = TypeError(f"{name} must be {dtype}, got {t.dtype}")
+    elif not t.is_contiguous():
+        err = ValueError(f"{name} must be contiguous")
+    elif _cs.dev is not None and t.device != _cs.dev:
+        err = RuntimeError(f"{name} is on {t.device} but the other operands are on {_cs.dev}: all operands of a lipvq "
+                           "call must live on one device")
+    if err is not None:
+        _cs.dev = None
+        raise err
+    _cs.dev = t.device
     return t.data_ptr()
+
+
+def _call(fn, what: str, *args) -> None:
+    """Run one C-ABI entry point with the operands' device current (kernel launches, per-device attribute caches and
+    the stream handle all refer to it) and raise on a non-zero status."""
+    dev, _cs.dev = _cs.dev, None
+    if dev is None or dev.index == torch.cuda.current_device():
+        A.check(fn(*args), what)
+    else:
+        with torch.cuda.device(dev):
+            A.check(fn(*args), what)
 
 
 F32, I64, I32, F64 = torch.float32, torch.int64, torch.int32, torch.float64
@@ -61,10 +92,11 @@ def nn_search(z: torch.Tensor, codebook: torch.Tensor, metric: int = A.METRIC_L2
     need = lib.lipvq_nn_search_workspace_bytes(N, D, K, metric, algo)
     ws = workspace if workspace is not None else _workspace(need, z.device)
     if ws.numel() * ws.element_size() < need:
+        _cs.dev = None
         raise ValueError(f"workspace too small: {ws.numel() * ws.element_size()} < {need}")
-    A.check(lib.lipvq_nn_search_f32(zp, N, D, cp, K, metric, algo, _chk(idx, I64, "idx"),
+    _call(lib.lipvq_nn_search_f32, "nn_search", zp, N, D, cp, K, metric, algo, _chk(idx, I64, "idx"),
                                     _chk(best, F32, "best", True), _chk(stats, I32, "stats", True),
-                                    ws.data_ptr(), ws.numel() * ws.element_size(), _stream()), "nn_search")
+                                    ws.data_ptr(), ws.numel() * ws.element_size(), _stream())
     res = (idx,)
     if want_best:
         res += (best,)
@@ -85,7 +117,7 @@ def l2_normalize_rows(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> to
     D = x.shape[-1]
     rows = x.numel() // D
     y = out if out is not None else torch.empty_like(x)
-    A.check(lib.lipvq_l2_normalize_rows_f32(_chk(x, F32, "x"), rows, D, _chk(y, F32, "y"), _stream()), "l2_normalize_rows")
+    _call(lib.lipvq_l2_normalize_rows_f32, "l2_normalize_rows", _chk(x, F32, "x"), rows, D, _chk(y, F32, "y"), _stream())
     return y
 
 
@@ -96,46 +128,45 @@ def gather_fwd(z, idx, codebook, sqerr: torch.Tensor, z_q=None, z_st=None, want_
         z_q = torch.empty_like(z)
     if want_ste and z_st is None:
         z_st = torch.empty_like(z)
-    A.check(lib.lipvq_gather_ste_loss_fwd_f32(_chk(z, F32, "z"), _chk(idx, I64, "idx"), _chk(codebook, F32, "codebook"),
+    _call(lib.lipvq_gather_ste_loss_fwd_f32, "gather_fwd", _chk(z, F32, "z"), _chk(idx, I64, "idx"), _chk(codebook, F32, "codebook"),
                                               N, D, K, _chk(z_q, F32, "z_q"), _chk(z_st, F32, "z_st", True),
-                                              _chk(sqerr, F64, "sqerr"), _stream()), "gather_fwd")
+                                              _chk(sqerr, F64, "sqerr"), _stream())
     return z_q, z_st
 
 
 def gather_bwd(z, z_q, idx, dzq_up, gscale, w_commit: float, w_codebook: float, ste: bool, sigmoid_out, K: int,
                dz_out, dcodebook):
     N, D = z.shape
-    A.check(lib.lipvq_gather_ste_loss_bwd_f32(_chk(z, F32, "z"), _chk(z_q, F32, "z_q"), _chk(idx, I64, "idx"),
+    _call(lib.lipvq_gather_ste_loss_bwd_f32, "gather_bwd", _chk(z, F32, "z"), _chk(z_q, F32, "z_q"), _chk(idx, I64, "idx"),
                                               _chk(dzq_up, F32, "dzq_up", True), _chk(gscale, F32, "gscale", True),
                                               w_commit, w_codebook, int(ste), _chk(sigmoid_out, F32, "sigmoid_out", True),
                                               N, D, K, _chk(dz_out, F32, "dz_out", True),
-                                              _chk(dcodebook, F32, "dcodebook", True), _stream()), "gather_bwd")
+                                              _chk(dcodebook, F32, "dcodebook", True), _stream())
 
 
 def ema_stats(z, idx, counts, sums):
     N, D = z.shape
     K = counts.numel()
-    A.check(lib.lipvq_ema_stats_f32(_chk(z, F32, "z"), _chk(idx, I64, "idx"), N, D, K, _chk(counts, F32, "counts"),
-                                    _chk(sums, F32, "sums"), _stream()), "ema_stats")
+    _call(lib.lipvq_ema_stats_f32, "ema_stats", _chk(z, F32, "z"), _chk(idx, I64, "idx"), N, D, K, _chk(counts, F32, "counts"),
+                                    _chk(sums, F32, "sums"), _stream())
 
 
 def ema_apply(counts, sums, ema_size, ema_sum, codebook, decay: float, eps: float, variant: int, scratch):
     K, D = ema_sum.shape
-    A.check(lib.lipvq_ema_apply_f32(_chk(counts, F32, "counts"), _chk(sums, F32, "sums"), K, D, decay, 1.0 - decay, eps,
+    _call(lib.lipvq_ema_apply_f32, "ema_apply", _chk(counts, F32, "counts"), _chk(sums, F32, "sums"), K, D, decay, 1.0 - decay, eps,
                                     variant, _chk(ema_size, F32, "ema_size"), _chk(ema_sum, F32, "ema_sum"),
-                                    _chk(codebook, F32, "codebook"), _chk(scratch, F64, "scratch"), _stream()), "ema_apply")
+                                    _chk(codebook, F32, "codebook"), _chk(scratch, F64, "scratch"), _stream())
 
 
 def usage_stats(counts, usage_counts, usage_ma, entropy_ma):
-    A.check(lib.lipvq_usage_stats_f32(_chk(counts, F32, "counts"), counts.numel(), _chk(usage_counts, F32, "usage_counts"),
-                                      _chk(usage_ma, F32, "usage_ma"), _chk(entropy_ma, F32, "entropy_ma"), _stream()),
-            "usage_stats")
+    _call(lib.lipvq_usage_stats_f32, "usage_stats", _chk(counts, F32, "counts"), counts.numel(), _chk(usage_counts, F32, "usage_counts"),
+                                      _chk(usage_ma, F32, "usage_ma"), _chk(entropy_ma, F32, "entropy_ma"), _stream())
 
 
 def codebook_usage(cluster_size, dead_thr: float) -> torch.Tensor:
     out = torch.empty(2, dtype=I32, device=cluster_size.device)
-    A.check(lib.lipvq_codebook_usage_f32(_chk(cluster_size, F32, "cluster_size"), cluster_size.numel(), dead_thr,
-                                         _chk(out, I32, "out"), _stream()), "codebook_usage")
+    _call(lib.lipvq_codebook_usage_f32, "codebook_usage", _chk(cluster_size, F32, "cluster_size"), cluster_size.numel(), dead_thr,
+                                         _chk(out, I32, "out"), _stream())
     return out
 
 
@@ -146,8 +177,8 @@ def linear_fwd(x, act_in: int, W, bias, act_out: int, out=None):
     if W.shape[1] != in_dim:
         raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({N}x{in_dim} and {W.shape[1]}x{out_dim})")
     y = out if out is not None else torch.empty(*x.shape[:-1], out_dim, dtype=F32, device=x.device)
-    A.check(lib.lipvq_linear_fwd_f32(_chk(x, F32, "x"), N, in_dim, act_in, _chk(W, F32, "W"), _chk(bias, F32, "bias", True),
-                                     out_dim, act_out, _chk(y, F32, "y"), _stream()), "linear_fwd")
+    _call(lib.lipvq_linear_fwd_f32, "linear_fwd", _chk(x, F32, "x"), N, in_dim, act_in, _chk(W, F32, "W"), _chk(bias, F32, "bias", True),
+                                     out_dim, act_out, _chk(y, F32, "y"), _stream())
     return y
 
 
@@ -160,9 +191,8 @@ def linear_fwd_dual(x, act_in: int, W, bias, act_out: int, out, dout):
     out_dim = W.shape[0]
     if W.shape[1] != in_dim:
         raise RuntimeError(f"mat1 and mat2 shapes cannot be multiplied ({N}x{in_dim} and {W.shape[1]}x{out_dim})")
-    A.check(lib.lipvq_linear_fwd_dual_f32(_chk(x, F32, "x"), N, in_dim, act_in, _chk(W, F32, "W"), _chk(bias, F32, "bias", True),
-                                          out_dim, act_out, _chk(out, F32, "y"), _chk(dout, F32, "dy_dpre"), _stream()),
-            "linear_fwd_dual")
+    _call(lib.lipvq_linear_fwd_dual_f32, "linear_fwd_dual", _chk(x, F32, "x"), N, in_dim, act_in, _chk(W, F32, "W"), _chk(bias, F32, "bias", True),
+                                          out_dim, act_out, _chk(out, F32, "y"), _chk(dout, F32, "dy_dpre"), _stream())
     return out, dout
 
 
@@ -170,9 +200,9 @@ def linear_bwd_x(dY, W, Xpre, act_in: int, out=None):
     out_dim, in_dim = W.shape
     N = dY.numel() // out_dim
     dX = out if out is not None else torch.empty(*dY.shape[:-1], in_dim, dtype=F32, device=dY.device)
-    A.check(lib.lipvq_linear_bwd_x_f32(_chk(dY, F32, "dY"), N, out_dim, _chk(W, F32, "W"), in_dim,
+    _call(lib.lipvq_linear_bwd_x_f32, "linear_bwd_x", _chk(dY, F32, "dY"), N, out_dim, _chk(W, F32, "W"), in_dim,
                                        _chk(Xpre, F32, "Xpre", act_in == A.ACT_NONE), act_in, _chk(dX, F32, "dX"),
-                                       _stream()), "linear_bwd_x")
+                                       _stream())
     return dX
 
 
@@ -180,14 +210,14 @@ def linear_bwd_w(dY, X, act_in: int, dW, db):
     """dW += dY^T act_in(X); db += colsum(dY).  dW/db are accumulated into."""
     out_dim, in_dim = dW.shape
     N = dY.numel() // out_dim
-    A.check(lib.lipvq_linear_bwd_w_f32(_chk(dY, F32, "dY"), N, out_dim, _chk(X, F32, "X"), in_dim, act_in,
-                                       _chk(dW, F32, "dW"), _chk(db, F32, "db", True), _stream()), "linear_bwd_w")
+    _call(lib.lipvq_linear_bwd_w_f32, "linear_bwd_w", _chk(dY, F32, "dY"), N, out_dim, _chk(X, F32, "X"), in_dim, act_in,
+                                       _chk(dW, F32, "dW"), _chk(db, F32, "db", True), _stream())
 
 
 def act_bwd_from_output(dY, Y, act: int, out=None):
     dX = out if out is not None else torch.empty_like(dY)
-    A.check(lib.lipvq_act_bwd_from_output_f32(_chk(dY, F32, "dY"), _chk(Y, F32, "Y"), act, dY.numel(), _chk(dX, F32, "dX"),
-                                              _stream()), "act_bwd_from_output")
+    _call(lib.lipvq_act_bwd_from_output_f32, "act_bwd_from_output", _chk(dY, F32, "dY"), _chk(Y, F32, "Y"), act, dY.numel(), _chk(dX, F32, "dX"),
+                                              _stream())
     return dX
 
 
@@ -195,40 +225,39 @@ def lipschitz_scale_fwd(W, ci, W_norm=None, scale=None):
     out_dim, in_dim = W.shape
     if W_norm is None:
         W_norm = torch.empty_like(W)
-    A.check(lib.lipvq_lipschitz_scale_fwd_f32(_chk(W, F32, "W"), _chk(ci, F32, "ci"), out_dim, in_dim,
-                                              _chk(scale, F32, "scale", True), _chk(W_norm, F32, "W_norm"), _stream()),
-            "lipschitz_scale_fwd")
+    _call(lib.lipvq_lipschitz_scale_fwd_f32, "lipschitz_scale_fwd", _chk(W, F32, "W"), _chk(ci, F32, "ci"), out_dim, in_dim,
+                                              _chk(scale, F32, "scale", True), _chk(W_norm, F32, "W_norm"), _stream())
     return W_norm
 
 
 def lipschitz_scale_bwd(G, W, ci, dW, dci):
     out_dim, in_dim = W.shape
-    A.check(lib.lipvq_lipschitz_scale_bwd_f32(_chk(G, F32, "G"), _chk(W, F32, "W"), _chk(ci, F32, "ci"), out_dim, in_dim,
-                                              _chk(dW, F32, "dW"), _chk(dci, F32, "dci"), _stream()), "lipschitz_scale_bwd")
+    _call(lib.lipvq_lipschitz_scale_bwd_f32, "lipschitz_scale_bwd", _chk(G, F32, "G"), _chk(W, F32, "W"), _chk(ci, F32, "ci"), out_dim, in_dim,
+                                              _chk(dW, F32, "dW"), _chk(dci, F32, "dci"), _stream())
 
 
 def mse_fwd_bwd(y, target, sqerr, gscale=None, act_out: int = A.ACT_NONE, dY=None):
     if y.shape != target.shape:
         raise RuntimeError(f"mse: shape mismatch {tuple(y.shape)} vs {tuple(target.shape)}")
-    A.check(lib.lipvq_mse_fwd_bwd_f32(_chk(y, F32, "y"), _chk(target, F32, "target"), y.numel(),
+    _call(lib.lipvq_mse_fwd_bwd_f32, "mse_fwd_bwd", _chk(y, F32, "y"), _chk(target, F32, "target"), y.numel(),
                                       _chk(gscale, F32, "gscale", True), act_out, _chk(sqerr, F64, "sqerr"),
-                                      _chk(dY, F32, "dY", True), _stream()), "mse_fwd_bwd")
+                                      _chk(dY, F32, "dY", True), _stream())
 
 
 def t1_loss_finalize(sq2, n_recon: float, n_lat: float, w_commit: float, w_cb: float, out4):
-    A.check(lib.lipvq_t1_loss_finalize(_chk(sq2, F64, "sq2"), float(n_recon), float(n_lat), w_commit, w_cb,
-                                       _chk(out4, F32, "out4"), _stream()), "t1_loss_finalize")
+    _call(lib.lipvq_t1_loss_finalize, "t1_loss_finalize", _chk(sq2, F64, "sq2"), float(n_recon), float(n_lat), w_commit, w_cb,
+                                       _chk(out4, F32, "out4"), _stream())
 
 
 def adamw_step(p, g, m, v, step: int, step_dev=None, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=1e-4,
                grad_scale: float = 1.0):
-    A.check(lib.lipvq_adamw_step_f32(_chk(p, F32, "p"), _chk(g, F32, "g"), _chk(m, F32, "m"), _chk(v, F32, "v"), p.numel(),
+    _call(lib.lipvq_adamw_step_f32, "adamw_step", _chk(p, F32, "p"), _chk(g, F32, "g"), _chk(m, F32, "m"), _chk(v, F32, "v"), p.numel(),
                                      int(step), _chk(step_dev, I32, "step_dev", True), lr, betas[0], betas[1], eps,
-                                     weight_decay, grad_scale, _stream()), "adamw_step")
+                                     weight_decay, grad_scale, _stream())
 
 
 def counter_add(ctr, delta: int = 1):
-    A.check(lib.lipvq_counter_add_i32(_chk(ctr, I32, "ctr"), delta, _stream()), "counter_add")
+    _call(lib.lipvq_counter_add_i32, "counter_add", _chk(ctr, I32, "ctr"), delta, _stream())
 
 
 # ---- K8: MS-TCN layers, LayerNorm, normalize backward -------------------------------------------------
@@ -242,14 +271,14 @@ def conv_pack_weights(W, want_fwd=True, want_bwd=True):
         raise RuntimeError(f"dilated conv kernels support kernel_size 3, got {k}")
     Wf = torch.empty(Eo, 3, Ei, dtype=F32, device=W.device) if want_fwd else None
     Wb = torch.empty(3, Eo, Ei, dtype=F32, device=W.device) if want_bwd else None
-    A.check(lib.lipvq_conv_pack_weights_f32(_chk(W, F32, "W"), Eo, Ei, _chk(Wf, F32, "Wf", True), _chk(Wb, F32, "Wb", True),
-                                            _stream()), "conv_pack_weights")
+    _call(lib.lipvq_conv_pack_weights_f32, "conv_pack_weights", _chk(W, F32, "W"), Eo, Ei, _chk(Wf, F32, "Wf", True), _chk(Wb, F32, "Wb", True),
+                                            _stream())
     return Wf, Wb
 
 
 def conv_unpack_grad(dWf, dW):
     Eo, Ei, _ = dW.shape
-    A.check(lib.lipvq_conv_unpack_grad_f32(_chk(dWf, F32, "dWf"), Eo, Ei, _chk(dW, F32, "dW"), _stream()), "conv_unpack_grad")
+    _call(lib.lipvq_conv_unpack_grad_f32, "conv_unpack_grad", _chk(dWf, F32, "dWf"), Eo, Ei, _chk(dW, F32, "dW"), _stream())
 
 
 def dilated_conv_fwd(x, T: int, Wf, bias, dilation: int, drop_p: float = 0.0, seed: int = 0):
@@ -258,9 +287,9 @@ def dilated_conv_fwd(x, T: int, Wf, bias, dilation: int, drop_p: float = 0.0, se
     Eo = Wf.shape[0]
     out = torch.empty(N, Eo, dtype=F32, device=x.device)
     mask = torch.empty(N, Eo, dtype=U8, device=x.device)
-    A.check(lib.lipvq_dilated_conv_fwd_f32(_chk(x, F32, "x"), N, T, Ei, _chk(Wf, F32, "Wf"), _chk(bias, F32, "bias"), Eo,
+    _call(lib.lipvq_dilated_conv_fwd_f32, "dilated_conv_fwd", _chk(x, F32, "x"), N, T, Ei, _chk(Wf, F32, "Wf"), _chk(bias, F32, "bias"), Eo,
                                            dilation, drop_p, seed & 0xFFFFFFFF, _chk(out, F32, "out"), _chk(mask, U8, "mask"),
-                                           _stream()), "dilated_conv_fwd")
+                                           _stream())
     return out, mask
 
 
@@ -268,17 +297,16 @@ def dilated_conv_bwd_x(dout, mask, T: int, Wb, dilation: int, drop_p: float = 0.
     N, Eo = dout.shape
     Ei = Wb.shape[2]
     dx = torch.empty(N, Ei, dtype=F32, device=dout.device)
-    A.check(lib.lipvq_dilated_conv_bwd_x_f32(_chk(dout, F32, "dout"), _chk(mask, U8, "mask"), N, T, Eo, _chk(Wb, F32, "Wb"),
-                                             Ei, dilation, drop_p, _chk(dx, F32, "dx"), _stream()), "dilated_conv_bwd_x")
+    _call(lib.lipvq_dilated_conv_bwd_x_f32, "dilated_conv_bwd_x", _chk(dout, F32, "dout"), _chk(mask, U8, "mask"), N, T, Eo, _chk(Wb, F32, "Wb"),
+                                             Ei, dilation, drop_p, _chk(dx, F32, "dx"), _stream())
     return dx
 
 
 def dilated_conv_bwd_w(dout, mask, x, T: int, dilation: int, dWf, db, drop_p: float = 0.0):
     N, Eo = dout.shape
     Ei = x.shape[1]
-    A.check(lib.lipvq_dilated_conv_bwd_w_f32(_chk(dout, F32, "dout"), _chk(mask, U8, "mask"), _chk(x, F32, "x"), N, T, Eo, Ei,
-                                             dilation, drop_p, _chk(dWf, F32, "dWf"), _chk(db, F32, "db", True), _stream()),
-            "dilated_conv_bwd_w")
+    _call(lib.lipvq_dilated_conv_bwd_w_f32, "dilated_conv_bwd_w", _chk(dout, F32, "dout"), _chk(mask, U8, "mask"), _chk(x, F32, "x"), N, T, Eo, Ei,
+                                             dilation, drop_p, _chk(dWf, F32, "dWf"), _chk(db, F32, "db", True), _stream())
 
 
 def layernorm_fwd(x, w, b, eps: float):
@@ -287,9 +315,8 @@ def layernorm_fwd(x, w, b, eps: float):
     y = torch.empty_like(x)
     mean = torch.empty(rows, dtype=F32, device=x.device)
     rstd = torch.empty(rows, dtype=F32, device=x.device)
-    A.check(lib.lipvq_layernorm_fwd_f32(_chk(x, F32, "x"), rows, E, _chk(w, F32, "w"), _chk(b, F32, "b"), eps,
-                                        _chk(y, F32, "y"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd"), _stream()),
-            "layernorm_fwd")
+    _call(lib.lipvq_layernorm_fwd_f32, "layernorm_fwd", _chk(x, F32, "x"), rows, E, _chk(w, F32, "w"), _chk(b, F32, "b"), eps,
+                                        _chk(y, F32, "y"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd"), _stream())
     return y, mean, rstd
 
 
@@ -297,21 +324,21 @@ def layernorm_bwd(dy, x, mean, rstd, w, dw, db):
     E = x.shape[-1]
     rows = x.numel() // E
     dx = torch.empty_like(x)
-    A.check(lib.lipvq_layernorm_bwd_f32(_chk(dy, F32, "dy"), _chk(x, F32, "x"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd"),
+    _call(lib.lipvq_layernorm_bwd_f32, "layernorm_bwd", _chk(dy, F32, "dy"), _chk(x, F32, "x"), _chk(mean, F32, "mean"), _chk(rstd, F32, "rstd"),
                                         _chk(w, F32, "w"), rows, E, _chk(dx, F32, "dx"), _chk(dw, F32, "dw", True),
-                                        _chk(db, F32, "db", True), _stream()), "layernorm_bwd")
+                                        _chk(db, F32, "db", True), _stream())
     return dx
 
 
 def l2_normalize_rows_bwd(x, dy):
     D = x.shape[-1]
     dx = torch.empty_like(x)
-    A.check(lib.lipvq_l2_normalize_rows_bwd_f32(_chk(x, F32, "x"), _chk(dy, F32, "dy"), x.numel() // D, D, _chk(dx, F32, "dx"),
-                                                _stream()), "l2_normalize_rows_bwd")
+    _call(lib.lipvq_l2_normalize_rows_bwd_f32, "l2_normalize_rows_bwd", _chk(x, F32, "x"), _chk(dy, F32, "dy"), x.numel() // D, D, _chk(dx, F32, "dx"),
+                                                _stream())
     return dx
 
 
 def affine(x, a: float, b: float, out=None):
     y = out if out is not None else torch.empty_like(x)
-    A.check(lib.lipvq_affine_f32(_chk(x, F32, "x"), a, b, x.numel(), _chk(y, F32, "y"), _stream()), "affine")
+    _call(lib.lipvq_affine_f32, "affine", _chk(x, F32, "x"), a, b, x.numel(), _chk(y, F32, "y"), _stream())
     return y

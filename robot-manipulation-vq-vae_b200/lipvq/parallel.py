@@ -106,7 +106,9 @@ class PeerSlab:
 
     def all_reduce(self) -> None:
         from . import _cabi
-        _cabi.check(_cabi.lib.lipvq_allreduce_oneshot_f32(self.peer_ptrs_dev, self.rank, self.world, self.n, self.n * 4,
-                                                          self._out.data_ptr(), self.epoch.data_ptr(),
-                                                          torch.cuda.current_stream().cuda_stream), "allreduce_oneshot")
+        dev = self._out.device
+        with torch.cuda.device(dev):
+            _cabi.check(_cabi.lib.lipvq_allreduce_oneshot_f32(self.peer_ptrs_dev, self.rank, self.world, self.n, self.n * 4,
+                                                              self._out.data_ptr(), self.epoch.data_ptr(),
+                                                              torch.cuda.current_stream(dev).cuda_stream), "allreduce_oneshot")
 

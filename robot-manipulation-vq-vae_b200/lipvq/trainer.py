@@ -54,12 +54,30 @@ class TokenizerTrainer:
         # NVLink peer all-reduce (default for world > 1) red lives in symmetric memory and red_out is a local buffer;
         # with NCCL (fallback, or LIPVQ_DP_COLLECTIVE=nccl) the all-reduce is in place and both are the same tensor.
         self.peer = None
-        if self.world > 1 and os.environ.get("LIPVQ_DP_COLLECTIVE", "peer") == "peer":
-            try:
-                self.peer = PeerSlab(L.length, dev, process_group)
-            except Exception as e:
-                import warnings
-                warnings.warn(f"lipvq: symmetric memory unavailable ({e}); data-parallel reduction uses NCCL")
+        self.collective = "none"
+        if self.world > 1:
+            # LIPVQ_DP_COLLECTIVE: "peer" (default: our one-shot NVLink kernel; NCCL only if symmetric memory cannot be
+            # set up on EVERY rank, and then loudly), "peer!" (no fallback: raise), "nccl"
+            mode = os.environ.get("LIPVQ_DP_COLLECTIVE", "peer")
+            err = None
+            if mode in ("peer", "peer!"):
+                try:
+                    self.peer = PeerSlab(L.length, dev, process_group)
+                except Exception as e:  # noqa: BLE001 -- any failure of the symmetric-memory plumbing
+                    err = e
+                # the ranks must agree: a subset spinning in the peer kernel while the rest sit in NCCL is a hang
+                ok = torch.tensor([0 if self.peer is None else 1], dtype=torch.int32, device=dev)
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=process_group)
+                if int(ok.item()) == 0:
+                    self.peer = None
+                    msg = f"lipvq: NVLink peer all-reduce unavailable on at least one rank ({err}); "
+                    if mode == "peer!":
+                        raise RuntimeError(msg + "LIPVQ_DP_COLLECTIVE=peer! forbids the NCCL fallback")
+                    import warnings
+                    warnings.warn(msg + "ALL ranks use NCCL for the data-parallel reduction")
+            elif mode != "nccl":
+                raise ValueError(f"LIPVQ_DP_COLLECTIVE={mode!r}: expected peer, peer! or nccl")
+            self.collective = "peer" if self.peer is not None else "nccl"
         self.red = self.peer.slab if self.peer is not None else torch.zeros(L.length, dtype=torch.float32, device=dev)
         self.red_out = self.peer.out if self.peer is not None else self.red
         self.flat_g = self.red_out[:L.P]
@@ -148,13 +166,13 @@ class TokenizerTrainer:
         # the eager pass advanced the optimiser state, so put it back afterwards
         st = self._snapshot()
         s = torch.cuda.Stream(device=self.device)
-        s.wait_stream(torch.cuda.current_stream())
+        s.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(s):
             self._phase_a()
             if self.world > 1:
                 self._reduce()  # also brings the NCCL communicator up before any capture
             self._phase_b()
-        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.current_stream(self.device).wait_stream(s)
         self._graph_full = None
         if self.world > 1 and self.graph_collective:
             # data-parallel: the whole step -- both halves AND the NCCL all-reduce between them -- is one graph, so a
@@ -180,7 +198,7 @@ class TokenizerTrainer:
         self._graph_a, self._graph_b = ga, gb
 
     def _load_input(self, x: torch.Tensor, prefetch: Optional[torch.Tensor]) -> None:
-        cur = torch.cuda.current_stream()
+        cur = torch.cuda.current_stream(self.device)
         if self._stage_src is not None and x is self._stage_src:
             cur.wait_event(self._stage_ready)          # the copy issued during the previous step
             self.x_static.copy_(self._stage, non_blocking=True)
@@ -209,6 +227,10 @@ class TokenizerTrainer:
         by ``world``) that the next step overwrites."""
         if tuple(x.shape) != tuple(self.x_static.shape):
             raise RuntimeError(f"expected input of shape {tuple(self.x_static.shape)}, got {tuple(x.shape)}")
+        with torch.cuda.device(self.device):  # the trainer's streams, graphs and kernels live on the model's device
+            return self._step(x, prefetch)
+
+    def _step(self, x: torch.Tensor, prefetch: Optional[torch.Tensor]) -> torch.Tensor:
         self._load_input(x, prefetch)
         if self.use_graph and self._graph_a is None:
             self._capture()
@@ -238,16 +260,20 @@ class TokenizerTrainer:
         """encode + VQ only on x [N,F] (bulk tokenisation) -> int64 [N] (a buffer the next call overwrites)."""
         if tuple(x.shape) != tuple(self.x_static.shape):
             raise RuntimeError(f"expected input of shape {tuple(self.x_static.shape)}, got {tuple(x.shape)}")
+        with torch.cuda.device(self.device):
+            return self._tokenize(x)
+
+    def _tokenize(self, x: torch.Tensor) -> torch.Tensor:
         self.x_static.copy_(x, non_blocking=True)
         if not self.use_graph:
             t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True)
             return self.bufs.t["idx"]
         if self._graph_tok is None:
             s = torch.cuda.Stream(device=self.device)
-            s.wait_stream(torch.cuda.current_stream())
+            s.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(s):
                 t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True)
-            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.current_stream(self.device).wait_stream(s)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
                 t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True)

@@ -89,6 +89,30 @@ def test_tc_full_size_c3_shapes():
         assert (best.cpu()[:, None] <= d_rand * (1 + 1e-6)).all()
 
 
+@pytest.mark.parametrize("D,mode", [(64, "uniform"), (64, "t1"), (256, "uniform")])
+def test_tc_k65536_parity(D, mode):
+    """BASELINE C3's largest codebook, K = 65536 (N = 65536): the shape with the densest near-ties and the longest
+    exact-scan tail.  1024-row oracle subsample (row-chunked, bit-identical to the unchunked form), determinism, and
+    optimality against random codes, on both latent distributions of the sweep."""
+    import lipvq as L
+    N, K = 65536, 65536
+    g = torch.Generator().manual_seed(11 + D)
+    cb = (torch.rand(K, D, generator=g) * 2 - 1) * math.sqrt(6.0 / D)
+    z = torch.rand(N, D, generator=g) if mode == "uniform" else torch.sigmoid(0.05 * torch.randn(N, D, generator=g))
+    zd, cd = z.to(DEV), cb.to(DEV)
+    idx, best, stats = L.ops.nn_search(zd, cd, L.METRIC_L2, L.ALGO_TCGEN05, want_best=True, want_stats=True)
+    idx2 = L.ops.nn_search(zd, cd, L.METRIC_L2, L.ALGO_TCGEN05)
+    assert torch.equal(idx, idx2)
+    rows = torch.randperm(N, generator=torch.Generator().manual_seed(0))[:1024]
+    ref = O.nearest_code_l2(z[rows], cb, row_chunk=16)
+    assert_indices(z[rows], cb, idx.cpu()[rows], ref)
+    assert torch.allclose(best.cpu()[rows], torch.norm(z[rows] - cb[ref], dim=-1), rtol=1e-5, atol=1e-7)
+    rk = torch.randint(0, K, (N, 4), generator=torch.Generator().manual_seed(1))
+    d_rand = (z[:, None, :] - cb[rk]).norm(dim=-1)
+    assert (best.cpu()[:, None] <= d_rand * (1 + 1e-6)).all()
+    assert int(stats[0]) <= int(stats[1]) <= N
+
+
 @pytest.mark.parametrize("algo", ["simt", "tc"])
 def test_clustered_latents_stay_on_fast_path(algo):
     """Sigmoid latents of a fresh LipschitzMLP sit in a tight cluster around 0.5 and an EMA codebook tracks them with a

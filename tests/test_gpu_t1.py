@@ -113,9 +113,22 @@ def test_t1_training_step_at_baseline_batch():
     idx = tr.indices.clone()
     # oracle: same step on CPU
     ema = {"ema_cluster_size": p0.pop("quantizer.ema_cluster_size"), "ema_codebook": p0.pop("quantizer.ema_codebook")}
+    cb0 = p0["quantizer.codebook"].clone()  # the codebook the search saw (the step overwrites it)
+    z_gpu = tr.bufs.t["z_e"].clone().cpu()
     ref = O.t1_train_step(p0, x, {}, ema=ema)
-    bad = (idx.cpu() != ref["indices"]).sum().item()
-    assert bad <= 0.001 * N, f"{bad} token mismatches vs oracle"
+    # (i) the search itself: on the GPU's OWN latents every index is the oracle's, or a near-tie (fp64 gap < 1e-6)
+    assert_indices(z_gpu, cb0, idx, O.nearest_code_l2(z_gpu, cb0, row_chunk=2048), max_near_tie_frac=1e-4)
+    # (ii) end to end: the encoder's fp32 noise (~1e-6 on z_e) may flip a token only where the oracle's own two best
+    # codes are closer than that noise -- every mismatch is classified, none is just counted
+    assert torch.allclose(z_gpu, ref["z_e"], rtol=1e-4, atol=2e-6)
+    bad = (idx.cpu() != ref["indices"]).nonzero().flatten()
+    if bad.numel():
+        zz = ref["z_e"][bad].double()
+        dg = (zz - cb0[idx.cpu()[bad]].double()).norm(dim=-1)
+        dr = (zz - cb0[ref["indices"][bad]].double()).norm(dim=-1)
+        gap = ((dg - dr).abs() / dr).max().item()
+        assert gap < 2e-5, f"{bad.numel()} token mismatches vs oracle, worst relative distance gap {gap:.3e}"
+    assert bad.numel() <= 0.001 * N, f"{bad.numel()} token mismatches vs oracle"
     assert abs(l0[0].item() - ref["loss"].item()) <= 1e-4 * abs(ref["loss"].item())
     sd = m.state_dict()
     assert abs(sd["quantizer.ema_cluster_size"].sum().item() - 0.01 * N) <= 1e-3 * 0.01 * N

@@ -147,3 +147,40 @@ def test_row_chunked_search_is_bit_identical():
     full = O.nearest_code_l2(z, cb, row_chunk=300)
     for c in (1, 7, 64):
         assert torch.equal(O.nearest_code_l2(z, cb, row_chunk=c), full)
+
+
+def test_t3_hierarchical_lipschitz():
+    """oracle t3_forward vs the reference's HierarchicalLFQHVQVAE run (tests/golden/t3_hier.npz)."""
+    g = load_golden("t3_hier")
+    sd = sub(g, "sd")
+    frozen = ("ema_", "usage_", "entropy_")
+    p = {k: v.clone().requires_grad_(v.dtype.is_floating_point and not any(f in k for f in frozen)) for k, v in sd.items()}
+    out = O.t3_forward(p, g["x"])
+    ref = sub(g, "out")
+    assert torch.equal(out["z_indices"], ref["z_indices"]) and torch.equal(out["q_indices"], ref["q_indices"])
+    assert torch.equal(out["z_q"].detach(), ref["z_q"]) and torch.equal(out["q_q"].detach(), ref["q_q"])
+    for k in ("loss", "recon_loss", "z_commit", "z_codebook", "q_commit", "q_codebook", "x_recon"):
+        _close(out[k], ref[k])
+    out["loss"].backward()
+    for k, gr in sub(g, "grad").items():
+        _close(p[k].grad, gr, rtol=1e-5, atol=1e-8)
+    post = sub(g, "post")
+    for k, v in out["post"].items():
+        _close(v, post[k], rtol=1e-5, atol=1e-6)
+
+
+def test_kmeans_initialisers():
+    """oracle hvq_kmeans_init vs HierarchicalVQVAE.initialize_codebooks_with_current_batch run by the reference
+    (sklearn random_state=42: deterministic), and the blob centres LFQQuantizerEMA_KMeans.kmeans_init must find."""
+    g = load_golden("kmeans_init")
+    t2 = sub(g, "t2")
+    out = O.hvq_kmeans_init(g["emb"], 16, 8)
+    for k, v in out.items():
+        _close(v, t2[k], rtol=1e-5, atol=1e-5)
+    assert bool(t2["codebooks_initialized"])
+    assert t2["cluster_size_z"].sum().item() == g["emb"].shape[0] * g["emb"].shape[1]
+    # hq: 8 blobs of 32 rows -> the 8 centres are the blob means, in some order
+    cb = g["hq_codebook"]
+    assert torch.equal(cb, g["hq_ema_codebook"])
+    d = torch.cdist(g["z"], cb)
+    assert torch.equal(torch.bincount(d.argmin(1), minlength=8), torch.full((8,), 32))
