@@ -303,14 +303,18 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     rescore_kernel(const float* __restrict__ z, int D, const float* __restrict__ cb, int K, int metric,
                    const int* __restrict__ count, const int* __restrict__ first_count, const int* __restrict__ work,
-                   int64_t* __restrict__ idx_out, float* __restrict__ best_out, int32_t* __restrict__ stats_out, int vec,
+                   const int* __restrict__ work_first, int skip_rows, int64_t* __restrict__ idx_out, float* __restrict__ best_out, int32_t* __restrict__ stats_out, int vec,
                    int lpc) {
   extern __shared__ __align__(16) float zs[];
   __shared__ float s_bv[8];
   __shared__ int s_bk[8];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   grid_dep_wait();  // launched as a programmatic dependent of the last search pass
-  const int nflag = *count;
+  int nflag = *count;
+  if (work_first != nullptr && *first_count <= skip_rows) {  // the 3-term pass stepped aside: its input queue is ours
+    nflag = *first_count;
+    work = work_first;
+  }
   if (stats_out && blockIdx.x == 0 && threadIdx.x == 0) {
     stats_out[0] = nflag;         // rows decided by the exact scan
     stats_out[1] = *first_count;  // rows the first (fastest) level could not certify
@@ -542,7 +546,8 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
     const int rc = search_fused_launch(z, N, D, codebook, K, metric, plan, ws, idx_out, stream, &queue, &count);
     if (rc != LIPVQ_OK) return rc;
     LIPVQ_CUDA(launch_pdl(rescore_kernel, dim3(rs_blocks), dim3(256), rs_smem, stream, z, D, codebook, K, metric, count,
-                          (const int*)&hdr->flagged, queue, idx_out, (float*)nullptr, stats_out, vec, lpc));
+                          (const int*)&hdr->flagged, queue, (const int*)(queue == work ? nullptr : work),
+                          search_skip_rows(N, D, K), idx_out, (float*)nullptr, stats_out, vec, lpc));
     LIPVQ_LAUNCHED("rescore_kernel");
     if (best_out) return search_best_values(z, N, D, codebook, metric, idx_out, best_out, stream);
     return LIPVQ_OK;
@@ -568,7 +573,7 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
                                                                          idx_out, best_out);
   LIPVQ_LAUNCHED("finalize_kernel");
   rescore_kernel<<<rs_blocks, 256, rs_smem, stream>>>(z, D, codebook, K, metric, &hdr->flagged, &hdr->flagged, work,
-                                                      idx_out, best_out, stats_out, vec, lpc);
+                                                      (const int*)nullptr, 0, idx_out, best_out, stats_out, vec, lpc);
   LIPVQ_LAUNCHED("rescore_kernel");
   return LIPVQ_OK;
 }

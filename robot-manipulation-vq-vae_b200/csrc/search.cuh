@@ -37,6 +37,14 @@ void search_fused_plan(int D, int K, int* Kp, int* Dp);
 int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, const SearchPlan& plan,
                         char* ws, int64_t* idx_out, cudaStream_t stream, const int** final_queue,
                         const int** final_count);
+// Single-launch first pass for codebooks that fit shared memory (search_p1.cu): codebook preparation + fp16 tcgen05 pass
+// with the packed-key fold.  Uncertified rows are appended to queue (*queue_count must be zero on entry); mu / enorm /
+// ehi / elo ([Kp_pub][Dp] fp16) / hdr are published for the later passes.
+bool search_p1_supported(int64_t N, int D, int K);
+int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, int Kp_pub, float* mu,
+                     float* enorm, void* ehi, void* elo, SearchHdr* hdr, int* queue, int* queue_count, int64_t* idx_out,
+                     cudaStream_t stream);
+int search_skip_rows(int64_t N, int D, int K);
 int search_best_values(const float* z, int64_t N, int D, const float* cb, int metric, const int64_t* idx, float* best_out,
                        cudaStream_t stream);
 

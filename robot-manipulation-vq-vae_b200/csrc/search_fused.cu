@@ -53,6 +53,7 @@ struct FusedParams {
   const float* z;
   const int* row_list;    // pass 2: rows to process (work queue of pass 1); nullptr = rows 0..N-1
   const int* n_rows_ptr;  // pass 2: device-side row count
+  int skip_rows;          // pass 2: a queue this short is left to the exact scan (which then reads the same queue)
   int64_t N;
   int D, K, NC, BN, T;    // NC = Dp/64 chunks, BN = MMA N, T = Kp/BN code tiles
   int stages, resident, nbufA;
@@ -341,6 +342,12 @@ __global__ void __launch_bounds__(kThreads, 1)
     grid_dep_wait();  // the row count is the previous pass's output
     const int64_t q = (int64_t)*p.n_rows_ptr;
     n_rows = q < p.N ? q : p.N;
+    // A short queue is cheaper to scan exactly than to run through a second 148-CTA tensor-core pass (the fixed cost
+    // of this launch -- a second codebook load, a gather, pipeline fill -- was a 28 us cliff for 0.2 % of the rows).
+    if (n_rows <= (int64_t)p.skip_rows) {
+      grid_dep_launch();
+      return;
+    }
   }
   const int row_blocks = (int)((n_rows + kBM - 1) / kBM);
   const int nblk = ((int)blockIdx.x < row_blocks) ? (row_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
@@ -895,6 +902,17 @@ FusedGeom fused_geom(int D, int Kp, int terms, bool staged) {
   return g;
 }
 
+}  // namespace
+// Queue length up to which the 3-term pass is skipped and the exact scan takes the rows of the fp16 pass directly:
+// the exact scan costs ~K*D multiply-adds per row on one CTA, the 3-term pass ~25 us before its first row.
+int search_skip_rows(int64_t N, int D, int K) {
+  if (const char* e = getenv("LIPVQ_SEARCH_SKIP_ROWS")) return atoi(e);
+  const int64_t by_work = ((int64_t)1 << 27) / ((int64_t)K * D);
+  int64_t r = by_work < N / 8 ? by_work : N / 8;
+  if (r > 8192) r = 8192;
+  return (int)(r < 0 ? 0 : r);
+}
+namespace {
 inline int fused_kp(int K) { return K <= 128 ? 128 : (K + 255) / 256 * 256; }
 
 }  // namespace
@@ -932,7 +950,9 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
   int* work2 = (int*)(ws + plan.off_work2);
   const int sms = sm_count();
 
-  {
+  // Codebooks that fit shared memory: one launch prepares the codebook AND runs the fp16 pass (search_p1.cu)
+  const bool use_p1 = search_p1_supported(N, D, K) && g1.Dp <= 256;
+  if (!use_p1) {
     int blocks = (Kp + 7) / 8;
     if (blocks > sms) blocks = sms;
     // (normal launch: its predecessor in the stream is the header memset, not a kernel)
@@ -959,7 +979,11 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
   } else {
     memset(&tm_z, 0, sizeof(tm_z));
   }
-  {
+  if (use_p1) {
+    if ((rc = search_p1_launch(z, N, D, cb, K, metric, Kp, mu, enorm, ehi, elo, hdr, work, &hdr->flagged, idx_out, stream)) !=
+        LIPVQ_OK)
+      return rc;
+  } else {
     CUtensorMap tm_hi, tm_lo;
     if ((rc = make_map(&tm_hi, ehi, Kp, g1.Dp, g1.BN)) != LIPVQ_OK) return rc;
     if ((rc = make_map(&tm_lo, elo, Kp, g1.Dp, g1.BN)) != LIPVQ_OK) return rc;
@@ -985,6 +1009,7 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
     if ((rc = make_map(&tm_lo, elo, Kp, g3.Dp, g3.BN)) != LIPVQ_OK) return rc;
     p.NC = g3.NC; p.BN = g3.BN; p.T = g3.T; p.stages = g3.stages; p.resident = g3.resident; p.nbufA = g3.nbufA; p.zstages = g3.zstages;
     p.row_list = work; p.n_rows_ptr = &hdr->flagged;
+    p.skip_rows = search_skip_rows(N, D, K);
     p.queue_out = work2; p.queue_count = &hdr->flagged2;
     const float steps = (float)(3 * g3.Dp / 16);
     p.gamma_en = (float)(D + 4) * 5.9604645e-8f + (steps + 1.f) * u22;

@@ -37,8 +37,11 @@ def test_tc_search_l2_vs_oracle(N, K, D):
     # stats[1]: rows the single fp16 chain could not certify; stats[0]: rows left for the exact scan after the 3-term
     # pass.  D > 256 has no 3-term pass (shared memory), so everything the fp16 pass queues is scanned exactly.
     assert int(stats[0]) <= int(stats[1]) <= 0.6 * N
+    # a queue shorter than ~N/8 (and 2^27/(K*D) rows) skips the 3-term pass: the exact scan is cheaper than a second
+    # tensor-core launch there; longer queues must be thinned by the 3-term pass to a few percent
     lim = 0.02 if D <= 256 else 0.6
-    assert int(stats[0]) <= max(8, lim * N), f"{int(stats[0])} of {N} rows went through the exact scan"
+    allowed = max(8, lim * N) if int(stats[1]) > N // 8 else max(8, N // 8)
+    assert int(stats[0]) <= allowed, f"{int(stats[0])} of {N} rows went through the exact scan"
 
 
 def test_tc_matches_simt_path_and_other_metrics():
