@@ -471,6 +471,7 @@ SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo) {
     p.off_work2 = o; o = align_up(o + sizeof(int) * (size_t)(N > 0 ? N : 1), 256);
     p.off_ehi = o;  o = align_up(o + eb, 1024);
     p.off_elo = o;  o = align_up(o + eb, 1024);
+    p.off_img = o;  o = align_up(o + (search_p1_fits(N, D, K) ? search_p1_image_bytes(D, K) : 0), 1024);
   }
   p.total = o;
   return p;

@@ -11,7 +11,8 @@ struct SearchHdr {
   float mu_norm;        // ||mu||, mu = the centre subtracted from z and the codes before the contraction
   unsigned excl_inv_bits;  // fused path: max over codes excluded from the fp16 contraction of 1/||e_k-mu|| (0 = none)
   int flagged2;         // fused path: rows the 3-term pass could not certify either -> exact rescore
-  int pad[11];
+  int arrived;          // single-launch first pass: CTAs that have published their slice of the prepared codebook
+  int pad[10];
 };
 
 struct SearchPlan {
@@ -25,6 +26,7 @@ struct SearchPlan {
   size_t off_hdr, off_enorm, off_pbest, off_psecond, off_pidx, off_work;
   size_t off_work2;                  // tcgen05 path: second-level queue
   size_t off_ehi, off_elo;           // tcgen05 path: fp16 hi/lo of -2(e-mu), [Kp][Dp]
+  size_t off_img;                    // single-launch first pass: image of its shared-memory code tiles + norm slab
   size_t total;
 };
 
@@ -41,8 +43,10 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
 // with the packed-key fold.  Uncertified rows are appended to queue (*queue_count must be zero on entry); mu / enorm /
 // ehi / elo ([Kp_pub][Dp] fp16) / hdr are published for the later passes.
 bool search_p1_supported(int64_t N, int D, int K);
+bool search_p1_fits(int64_t N, int D, int K);  // geometry only (workspace planning)
+size_t search_p1_image_bytes(int D, int K);
 int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, int Kp_pub, float* mu,
-                     float* enorm, void* ehi, void* elo, SearchHdr* hdr, int* queue, int* queue_count, int64_t* idx_out,
+                     float* enorm, void* ehi, void* elo, void* img, SearchHdr* hdr, int* queue, int* queue_count, int64_t* idx_out,
                      cudaStream_t stream);
 int search_skip_rows(int64_t N, int D, int K);
 int search_best_values(const float* z, int64_t N, int D, const float* cb, int metric, const int64_t* idx, float* best_out,

@@ -980,7 +980,7 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
     memset(&tm_z, 0, sizeof(tm_z));
   }
   if (use_p1) {
-    if ((rc = search_p1_launch(z, N, D, cb, K, metric, Kp, mu, enorm, ehi, elo, hdr, work, &hdr->flagged, idx_out, stream)) !=
+    if ((rc = search_p1_launch(z, N, D, cb, K, metric, Kp, mu, enorm, ehi, elo, ws + plan.off_img, hdr, work, &hdr->flagged, idx_out, stream)) !=
         LIPVQ_OK)
       return rc;
   } else {

@@ -47,6 +47,20 @@ constexpr float kF16Safe = 3.0e4f;
 constexpr float kEnormMax = 6.0e4f;        // ||e-mu||^2 must fit an fp16 (it travels through the norm slab)
 constexpr float kSentinel = 65504.f;       // padding / excluded codes: 3 x 65504 in the slab, zeros in the tile
 
+#ifdef LIPVQ_TRACE
+// developer build: lane 0 of every warp of CTA 0 logs (clock64 << 8 | event)
+constexpr int kTraceMax = 4096;
+__device__ unsigned long long g_trace_p1[16][kTraceMax];
+__device__ int g_trace_p1_n[16];
+#define TR(ev)                                                                                             \
+  do {                                                                                                     \
+    if (blockIdx.x == 0 && lane == 0 && tr_n < kTraceMax)                                                  \
+      g_trace_p1[warp][tr_n++] = ((unsigned long long)clock64() << 8) | (unsigned long long)(ev);          \
+  } while (0)
+#else
+#define TR(ev) do {} while (0)
+#endif
+
 struct P1Params {
   const float* z;
   const float* cb;
@@ -55,13 +69,13 @@ struct P1Params {
   int nbufA, zstages;
   int metric;
   int Kp_pub;     // rows of the published arrays (the later passes' padded code count)
-  uint32_t kmask; // 0xFFFFFFE0 (see pack_key)
   int slab_swap;  // debug: swap LBO/SBO of the no-swizzle descriptors
   // outputs for the later passes (search_fused_kernel<3>, rescore): published by slices of the grid
   float* mu_g;
   float* enorm_g;
   __half* ehi_g;
   __half* elo_g;
+  uint8_t* img;  // global image of the shared-memory code tiles + norm slab ([T][NC][256 x 128 B] | [Kp x 32 B])
   SearchHdr* hdr;
   int* queue_out;
   int* queue_count;
@@ -77,6 +91,11 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* tm,
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(dst),
       "l"(reinterpret_cast<uint64_t>(tm)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
+}
+__device__ __forceinline__ void bulk_load_1d(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+               "l"(reinterpret_cast<uint64_t>(src)), "r"(bytes), "r"(bar)
+               : "memory");
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
   asm volatile(
@@ -94,6 +113,17 @@ __device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[32]) {
                  "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]),
                  "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]), "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]),
                  "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]), "+r"(v[31])
+               :
+               : "memory");
+}
+// one wait for two outstanding loads; "touches" both register sets so no use can be scheduled above it
+__device__ __forceinline__ void tmem_ld_wait2(uint32_t (&a)[32], uint32_t (&b)[32]) {
+  tmem_ld_wait(a);
+  asm volatile(""
+               : "+r"(b[0]), "+r"(b[1]), "+r"(b[2]), "+r"(b[3]), "+r"(b[4]), "+r"(b[5]), "+r"(b[6]), "+r"(b[7]), "+r"(b[8]),
+                 "+r"(b[9]), "+r"(b[10]), "+r"(b[11]), "+r"(b[12]), "+r"(b[13]), "+r"(b[14]), "+r"(b[15]), "+r"(b[16]),
+                 "+r"(b[17]), "+r"(b[18]), "+r"(b[19]), "+r"(b[20]), "+r"(b[21]), "+r"(b[22]), "+r"(b[23]), "+r"(b[24]),
+                 "+r"(b[25]), "+r"(b[26]), "+r"(b[27]), "+r"(b[28]), "+r"(b[29]), "+r"(b[30]), "+r"(b[31])
                :
                : "memory");
 }
@@ -121,13 +151,6 @@ __device__ __forceinline__ float ffma_sat(float a, float b, float c) {
   asm("fma.rn.sat.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
   return d;
 }
-// (s & mask) | col : the packed key of one score
-__device__ __forceinline__ float pack_key(uint32_t s, uint32_t mask, uint32_t col) {
-  uint32_t d;
-  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(s), "r"(mask), "r"(col));
-  return __uint_as_float(d);
-}
-
 struct RowBest {  // partial result of one epilogue group for one row, handed to the group that certifies the row
   float best, second, ma, mb;  // ma/mb: count (FOLD 0) or the two 16-bit near-best masks (FOLD 1) of the winning chunk
   int base;
@@ -138,7 +161,6 @@ struct RowBest {  // partial result of one epilogue group for one row, handed to
 //   0-7   epilogue: warp w owns TMEM lanes 32*(w&3).. (= rows); group w>>2 drains every second code tile
 //   8-11  converters: fp32 z rows -> centred fp16 -> swizzled A tiles (+ per-row ||z-mu||^2, ||z||^2)
 //   12    TMEM allocation + single-thread tcgen05.mma issue
-template <int FOLD>
 __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_constant__ CUtensorMap tm_z, const P1Params p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -150,7 +172,7 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
   uint8_t* sZ = sB + p.T * p.NC * b_tile;               // [zstages][128][64] fp32
   uint8_t* sE = sZ + p.zstages * kZStage;               // norm slab [Kp x 16] fp16, no swizzle
   uint8_t* sA1 = sE + p.Kp * 32;                        // ones slab [128 x 16] fp16
-  float2* rowstat = reinterpret_cast<float2*>(sA1 + kBM * 32);             // [kStatSlots][128]
+  float* rowstat = reinterpret_cast<float*>(sA1 + kBM * 32);               // [kStatSlots][128]: ||z-mu||^2 per row
   RowBest* xchg = reinterpret_cast<RowBest*>(rowstat + kStatSlots * kBM);  // [2][128]
   float* mu_s = reinterpret_cast<float*>(xchg + 2 * kBM);                  // [256]
   float* red_s = mu_s + 256;                                               // [32] block reductions
@@ -160,8 +182,13 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
   const uint32_t bar_z_full = smem_u32(bars + 8), bar_z_empty = smem_u32(bars + 12);
   const uint32_t bar_x_full = smem_u32(bars + 16), bar_x_empty = smem_u32(bars + 18);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
+  const uint32_t bar_img = smem_u32(bars + 21), bar_mu = smem_u32(bars + 22);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#ifdef LIPVQ_TRACE
+  int tr_n = 0;
+#endif
+  TR(0);
   const int row_blocks = (int)((p.N + kBM - 1) / kBM);
   const int nblk = ((int)blockIdx.x < row_blocks) ? (row_blocks - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   const int total_tiles = nblk * p.T;
@@ -176,6 +203,8 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
       mbar_init(bar_x_full + 8 * s, kEpiWarps / 2);
       mbar_init(bar_x_empty + 8 * s, kEpiWarps / 2);
     }
+    mbar_init(bar_img, 1);
+    mbar_init(bar_mu, 1);
     for (int s = 0; s < 4; ++s) {
       mbar_init(bar_z_full + 8 * s, 1);
       mbar_init(bar_z_empty + 8 * s, kCvtWarps);
@@ -184,185 +213,13 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
   }
   if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), 512);
   grid_dep_wait();  // z (and, in a training step, the codebook) are the previous kernels' outputs
-  __syncthreads();  // barriers initialised before the first bulk copy names one
-
-  // staged z rows: the first tiles start flowing now and land while the codebook is being prepared
-  const int total_units = nblk * p.NC;
-  auto z_issue = [&](int unit) {
-    const int i2 = unit / p.NC, c2 = unit - i2 * p.NC;
-    const uint32_t st = (uint32_t)unit % (uint32_t)p.zstages;
-    const int64_t l0 = ((int64_t)blockIdx.x + (int64_t)i2 * gridDim.x) * kBM;
-    mbar_expect_tx(bar_z_full + 8 * st, (uint32_t)kZStage);
-    tma_load_2d(smem_u32(sZ + st * kZStage), &tm_z, bar_z_full + 8 * st, c2 * kChunk, (int)l0);
-  };
-  if (p.zstages > 0 && threadIdx.x == kEpiWarps * 32)
-    for (int u = 0; u < p.zstages && u < total_units; ++u) z_issue(u);
-
-  // ---- prologue: mu, then the whole codebook -> fp16 tiles + norm slab (all threads) ----------------------------------
-  {
-    constexpr int RMAX = 32;
-    const int R = (int)(p.N < RMAX ? p.N : RMAX);
-    const int64_t stride = p.N / R;
-    for (int d = threadIdx.x; d < 256; d += kThreads) {
-      float m = 0.f;
-      if (d < p.D && p.metric != LIPVQ_METRIC_DOT) {
-        float v[RMAX];
-#pragma unroll
-        for (int i = 0; i < RMAX; ++i) v[i] = (i < R) ? __ldg(p.z + (int64_t)i * stride * p.D + d) : 0.f;
-        float s = 0.f;
-#pragma unroll
-        for (int i = 0; i < RMAX; ++i) s += v[i];  // same order as fused_prep_kernel / center_kernel
-        m = s / (float)R;
-      }
-      mu_s[d] = m;
-    }
-    // ones slab: columns 0..2 = 1.0 for every row
-    for (int r = threadIdx.x; r < kBM; r += kThreads) {
-      *reinterpret_cast<uint4*>(sA1 + slab_off(r, 0)) = make_uint4(0x3C003C00u, 0x00003C00u, 0u, 0u);  // 1, 1, 1, 0 ...
-      *reinterpret_cast<uint4*>(sA1 + slab_off(r, 8)) = make_uint4(0u, 0u, 0u, 0u);
-    }
-    __syncthreads();
-    if (warp == 0) {  // ||mu||
-      float t = 0.f;
-      for (int d = lane; d < 256; d += 32) t = fmaf(mu_s[d], mu_s[d], t);
-      t = warp_sum(t);
-      if (lane == 0) red_s[31] = t;
-    }
-  }
-  float emax2_loc = 0.f, excl_inv_loc = 0.f;  // per-thread partial maxima
-  {
-    // item = (code k, 16-byte output chunk ch8 of its row): 8 latent dims = two float4 loads.  Items of one row are
-    // consecutive lanes (Dp/8 = 8, 16 or 32 lanes), so ||e-mu||^2 is a fixed-order shuffle reduction.
-    const int ipr = Dp / 8;  // items per row: 8 (D<=64), 16, 24 (-> handled as 32 with idle lanes), 32
-    const int ipr_p2 = ipr <= 8 ? 8 : (ipr <= 16 ? 16 : 32);
-    const int rows_per_pass = kThreads / ipr_p2;  // whole rows per pass over the CTA (416/8 = 52, /16 = 26, /32 = 13)
-    const int sub = (int)threadIdx.x % ipr_p2, rslot = (int)threadIdx.x / ipr_p2;
-    const bool vec = (p.D % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.cb) & 15) == 0);
-    const bool publish_all = (gridDim.x == 1);
-    constexpr int UNR = 4;  // rows per thread in flight: the prologue is one or two round trips to L2, not ten
-    for (int k00 = 0; k00 < p.Kp; k00 += rows_per_pass * UNR) {
-      float x[UNR][8];
-      const int d0 = sub * 8;
-#pragma unroll
-      for (int u = 0; u < UNR; ++u) {
-        const int k = k00 + u * rows_per_pass + rslot;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) x[u][e] = 0.f;
-        if (k < p.K && sub < ipr && d0 < p.D) {
-          const float* src = p.cb + (size_t)k * p.D + d0;
-          if (vec && d0 + 8 <= p.D) {
-            const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
-            x[u][0] = a.x; x[u][1] = a.y; x[u][2] = a.z; x[u][3] = a.w; x[u][4] = b.x; x[u][5] = b.y; x[u][6] = b.z; x[u][7] = b.w;
-          } else {
-#pragma unroll
-            for (int e = 0; e < 8; ++e) x[u][e] = (d0 + e < p.D) ? __ldg(src + e) : 0.f;
-          }
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < UNR; ++u) {
-        const int k = k00 + u * rows_per_pass + rslot;
-        const bool live = k < p.K && sub < ipr && d0 < p.D;
-        float s = 0.f, amax = 0.f;
-        bool finite = true;
-        float cdiff[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float v = (live && d0 + e < p.D) ? x[u][e] - mu_s[d0 + e] : 0.f;
-          cdiff[e] = v;
-          s = fmaf(v, v, s);
-          amax = fmaxf(amax, fabsf(v));
-          finite = finite && (fabsf(v) <= 3.0e38f);
-        }
-        for (int o = 1; o < ipr_p2; o <<= 1) {
-          s += __shfl_xor_sync(0xffffffffu, s, o);
-          amax = fmaxf(amax, __shfl_xor_sync(0xffffffffu, amax, o));
-          finite = finite && (__shfl_xor_sync(0xffffffffu, (int)finite, o) != 0);
-        }
-        if (k >= p.Kp) continue;  // (after the shuffles: every lane of the warp takes part in them)
-        const bool valid = k < p.K;
-        const bool excluded = valid && (!finite || amax >= kF16Safe || (p.metric != LIPVQ_METRIC_DOT && !(s <= kEnormMax)));
-        const bool zero_row = !valid || excluded;
-        const bool publish = k < p.Kp_pub && (publish_all || (k % (int)gridDim.x) == (int)blockIdx.x);
-        if (sub < ipr) {
-          uint32_t hh[4], ll[4];
-#pragma unroll
-          for (int e = 0; e < 8; e += 2) {
-            const float va = zero_row ? 0.f : -2.f * cdiff[e], vb = zero_row ? 0.f : -2.f * cdiff[e + 1];
-            const __half2 hp = __floats2half2_rn(va, vb);
-            const float2 back = __half22float2(hp);
-            const __half2 lp = __floats2half2_rn(va - back.x, vb - back.y);
-            hh[e >> 1] = *reinterpret_cast<const uint32_t*>(&hp);
-            ll[e >> 1] = *reinterpret_cast<const uint32_t*>(&lp);
-          }
-          const int j = k / kBN, r = k % kBN, c = sub >> 3, ch = sub & 7;
-          *reinterpret_cast<uint4*>(sB + (size_t)(j * p.NC + c) * b_tile + r * 128 + ((ch ^ (r & 7)) << 4)) =
-              make_uint4(hh[0], hh[1], hh[2], hh[3]);
-          // later passes read the prepared codebook from global memory: each CTA publishes a slice of the rows
-          if (publish) {
-            *reinterpret_cast<uint4*>(p.ehi_g + (size_t)k * Dp + sub * 8) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
-            *reinterpret_cast<uint4*>(p.elo_g + (size_t)k * Dp + sub * 8) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
-          }
-        }
-        if (sub == 0) {
-          const float en = (p.metric == LIPVQ_METRIC_DOT) ? 0.f : s;
-          float h0, h1, h2;
-          if (zero_row) {
-            h0 = h1 = h2 = kSentinel;
-          } else {
-            h0 = __half2float(__float2half_rn(en));
-            h1 = __half2float(__float2half_rn(en - h0));
-            h2 = __half2float(__float2half_rn(en - h0 - h1));
-            emax2_loc = fmaxf(emax2_loc, s);
-          }
-          if (excluded) {
-            const float inv = (finite && s < 3.0e38f) ? rsqrtf(s) * 1.0001f : 3.0e38f;  // 1/||e-mu|| rounded up
-            excl_inv_loc = fmaxf(excl_inv_loc, inv);
-          }
-          uint32_t w0, w1;
-          {
-            const __half2 a = __floats2half2_rn(h0, h1), b = __floats2half2_rn(h2, 0.f);
-            w0 = *reinterpret_cast<const uint32_t*>(&a);
-            w1 = *reinterpret_cast<const uint32_t*>(&b);
-          }
-          *reinterpret_cast<uint4*>(sE + slab_off(k, 0)) = make_uint4(w0, w1, 0u, 0u);  // columns 0..7
-          *reinterpret_cast<uint4*>(sE + slab_off(k, 8)) = make_uint4(0u, 0u, 0u, 0u);  // columns 8..15
-          if (publish) p.enorm_g[k] = zero_row ? INFINITY : en;
-        }
-      }
-    }
-  }
-  // block-wide maxima (every CTA holds the same values: same data, same order)
-  {
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      emax2_loc = fmaxf(emax2_loc, __shfl_xor_sync(0xffffffffu, emax2_loc, o));
-      excl_inv_loc = fmaxf(excl_inv_loc, __shfl_xor_sync(0xffffffffu, excl_inv_loc, o));
-    }
-    if (lane == 0) {
-      red_s[warp] = emax2_loc;
-      red_s[16 + warp] = excl_inv_loc;
-    }
-  }
-  fence_async_smem();  // generic-proxy writes of the code tiles / slabs -> visible to the tensor core
   fence_before();
-  __syncthreads();
+  __syncthreads();  // barriers initialised, TMEM allocated
+  TR(6);
+
   fence_after();
-  float emax2 = 0.f, excl_inv = 0.f;
-  for (int w = 0; w <= kWarpMma; ++w) {
-    emax2 = fmaxf(emax2, red_s[w]);
-    excl_inv = fmaxf(excl_inv, red_s[16 + w]);
-  }
-  const float mu_norm = sqrtf(red_s[31]);
-  if (blockIdx.x == 0) {  // what the later passes read
-    for (int d = threadIdx.x; d < Dp; d += kThreads) p.mu_g[d] = mu_s[d];
-    if (threadIdx.x == 0) {
-      p.hdr->emax2_bits = __float_as_uint(emax2);
-      p.hdr->excl_inv_bits = __float_as_uint(excl_inv);
-      p.hdr->mu_norm = mu_norm;
-    }
-  }
   const uint32_t tmem_base = *tmem_slot;
+  TR(1);
 
   if (warp == kWarpMma) {
     // ===== MMA issuer (one thread) =====
@@ -371,15 +228,19 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
       const uint32_t lbo = p.slab_swap ? 256u : 128u, sbo = p.slab_swap ? 128u : 256u;
       const uint64_t a1desc = desc_noswz(smem_u32(sA1), lbo, sbo);
       uint32_t t = 0;
+      mbar_wait(bar_img, 0);  // code tiles + norm slab (bulk copies) and the ones slab are in place
+      fence_after();
       for (int i = 0; i < nblk; ++i) {
         const int buf = i % p.nbufA;
         mbar_wait(bar_a_full + 8 * buf, (uint32_t)(i / p.nbufA) & 1);
         fence_after();
+        TR(30);
         const uint32_t a_base = smem_u32(sA + buf * a_bytes);
         for (int j = 0; j < p.T; ++j, ++t) {
           const uint32_t ab = t & 1;
           mbar_wait(bar_acc_empty + 8 * ab, ((t >> 1) & 1) ^ 1);  // the epilogue has drained the tile before last
           fence_after();
+          TR(31);
           const uint32_t d_tmem = tmem_base + ab * (uint32_t)kBN;
           // score = ||e-mu||^2 (norm slab, overwrites the accumulator) - 2 (z-mu).(e-mu)
           umma_f16(d_tmem, a1desc, desc_noswz(smem_u32(sE + (size_t)j * kBN * 32), lbo, sbo), idesc, 0u);
@@ -390,6 +251,7 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
             for (int k = 0; k < kChunk / 16; ++k) umma_f16(d_tmem, desc_sw128(aa + 32 * k), desc_sw128(bb + 32 * k), idesc, 1u);
           }
           umma_commit(bar_acc_full + 8 * ab);
+          TR(32);
         }
         umma_commit(bar_a_empty + 8 * buf);
       }
@@ -399,6 +261,21 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
     const int tc_ = (int)threadIdx.x - kEpiWarps * 32;  // 0..127
     const int ch = tc_ & 7, r0 = tc_ >> 3;
     const bool fast = (p.D % 8 == 0) && ((reinterpret_cast<uintptr_t>(p.z) & 15) == 0);
+    // staged z rows: the first tiles start flowing now and land while the codebook is being prepared
+    const int total_units = nblk * p.NC;
+    auto z_issue = [&](int unit) {
+      const int i2 = unit / p.NC, c2 = unit - i2 * p.NC;
+      const uint32_t st = (uint32_t)unit % (uint32_t)p.zstages;
+      const int64_t l0 = ((int64_t)blockIdx.x + (int64_t)i2 * gridDim.x) * kBM;
+      mbar_expect_tx(bar_z_full + 8 * st, (uint32_t)kZStage);
+      tma_load_2d(smem_u32(sZ + st * kZStage), &tm_z, bar_z_full + 8 * st, c2 * kChunk, (int)l0);
+    };
+    if (p.zstages > 0 && tc_ == 0) {
+  #pragma unroll 1
+      for (int u = 0; u < p.zstages && u < total_units; ++u) z_issue(u);
+    }
+
+    mbar_wait(bar_mu, 0);  // mu is ready (the codebook may still be in preparation: the converters do not need it)
     for (int i = 0; i < nblk; ++i) {
       const int buf = i % p.nbufA;
       const int64_t rb = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
@@ -408,10 +285,12 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
         const int64_t lrow = rb * kBM + r0 + 16 * u;
         grow[u] = lrow < p.N ? lrow : -1;
       }
-      float zn2[8], zo2[8];
+      float zn2[8];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) zn2[u] = zo2[u] = 0.f;
+      for (int u = 0; u < 8; ++u) zn2[u] = 0.f;
+      TR(20);
       mbar_wait(bar_a_empty + 8 * buf, ((uint32_t)(i / p.nbufA) & 1) ^ 1);
+      TR(21);
       uint8_t* a_buf = sA + buf * a_bytes;
       for (int c = 0; c < p.NC; ++c) {
         const int col = c * kChunk + ch * 8;
@@ -425,6 +304,7 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
           const uint32_t unit = (uint32_t)(i * p.NC + c);
           const uint32_t st = unit % (uint32_t)p.zstages, par = (unit / (uint32_t)p.zstages) & 1;
           mbar_wait(bar_z_full + 8 * st, par);
+          TR(22);
           const float* zt = reinterpret_cast<const float*>(sZ + st * kZStage) + ch * 8;
 #pragma unroll
           for (int u = 0; u < 8; ++u)
@@ -468,159 +348,386 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
         for (int u = 0; u < 8; ++u) {
           const float x[8] = {va[u].x, va[u].y, va[u].z, va[u].w, vb[u].x, vb[u].y, vb[u].z, vb[u].w};
           uint32_t hh[4];
-          float amax = 0.f;
 #pragma unroll
           for (int e = 0; e < 8; e += 2) {
             const float za = x[e] - mu8[e], zb = x[e + 1] - mu8[e + 1];
-            zo2[u] = fmaf(x[e], x[e], zo2[u]);
-            zo2[u] = fmaf(x[e + 1], x[e + 1], zo2[u]);
             zn2[u] = fmaf(za, za, zn2[u]);
             zn2[u] = fmaf(zb, zb, zn2[u]);
-            amax = fmaxf(amax, fmaxf(fabsf(za), fabsf(zb)));
             const __half2 hp = __floats2half2_rn(za, zb);
             hh[e >> 1] = *reinterpret_cast<const uint32_t*>(&hp);
           }
-          if (!(amax < 6.0e4f)) zn2[u] = INFINITY;  // does not fit fp16 (or NaN): the row takes the exact path
           const int r = r0 + 16 * u;
           const uint32_t off = (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
           *reinterpret_cast<uint4*>(a_buf + c * a_tile + off) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
         }
       }
-      float2* stat = rowstat + (i % kStatSlots) * kBM;
+      TR(24);
+      // ||z-mu||^2 per row.  It also guards the fp16 range: every centred entry is at most sqrt(zn2) in magnitude, so a
+      // row with zn2 < 3.6e9 fits; anything else (huge, inf, NaN) is marked uncertifiable and takes the exact path.
+      float* stat = rowstat + (i % kStatSlots) * kBM;
+      {
+        // 8 partial sums (rows r0 + 16u) in each of the 8 lanes of a row group -> one total per lane, 7 shuffles
+        // (transposing butterfly: every step halves the values a lane still carries)
+        const bool b0 = ch & 1, b1 = ch & 2, b2 = ch & 4;
+        float k4[4];
 #pragma unroll
-      for (int u = 0; u < 8; ++u) {
-#pragma unroll
-        for (int o = 1; o < 8; o <<= 1) {
-          zn2[u] += __shfl_xor_sync(0xffffffffu, zn2[u], o);
-          zo2[u] += __shfl_xor_sync(0xffffffffu, zo2[u], o);
+        for (int jj = 0; jj < 4; ++jj) {
+          const float send = b0 ? zn2[jj] : zn2[4 + jj];
+          const float recv = __shfl_xor_sync(0xffffffffu, send, 1);
+          k4[jj] = (b0 ? zn2[4 + jj] : zn2[jj]) + recv;
         }
-        if (ch == 0) stat[r0 + 16 * u] = make_float2(zn2[u], zo2[u]);
+        float k2[2];
+#pragma unroll
+        for (int jj = 0; jj < 2; ++jj) {
+          const float send = b1 ? k4[jj] : k4[2 + jj];
+          const float recv = __shfl_xor_sync(0xffffffffu, send, 2);
+          k2[jj] = (b1 ? k4[2 + jj] : k4[jj]) + recv;
+        }
+        const float send = b2 ? k2[0] : k2[1];
+        const float tot = (b2 ? k2[1] : k2[0]) + __shfl_xor_sync(0xffffffffu, send, 4);
+        const int u = (b0 ? 4 : 0) + (b1 ? 2 : 0) + (b2 ? 1 : 0);
+        stat[r0 + 16 * u] = (tot < 3.6e9f) ? tot : INFINITY;
       }
+      TR(25);
       fence_async_smem();
+      TR(26);
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_a_full + 8 * buf);
+      TR(23);
     }
   } else {
-    // ===== epilogue warps 0-7 =====
+    // ===== epilogue warps 0-7: first the cooperative codebook preparation, then the fold =====
+    // ---- prologue: the codebook is prepared ONCE per launch, cooperatively ------------------------------------------------
+    // Converting the whole codebook in every CTA cost 15 000 cycles (148 x redundant work, measured).  Instead CTA b
+    // converts rows [b*R, (b+1)*R) (3-4 rows at K = 512) into a global IMAGE of the shared-memory layout (swizzled fp16
+    // tiles + norm slab), the CTAs meet at an arrive counter, and everyone bulk-copies the finished image (80 KB from L2).
+    // All CTAs are co-resident (grid <= number of SMs, one CTA per SM), so the spin cannot deadlock; it is bounded anyway.
+    // mu (mean of <= 32 sampled z rows) is needed before the conversion and by the z converters: every CTA derives it
+    // itself, with the sample loads and the slice's code rows requested together (one round trip).
+    // item = (code k, 16-byte output chunk of its row): 8 latent dims = two float4 loads; the items of one row sit in
+    // consecutive lanes (Dp/8 = 8, 16 or 32 of them), so ||e-mu||^2 is a fixed-order shuffle reduction.
+    const int ipr = Dp / 8;  // items per row: 8 (D <= 64), 16, 24 (-> handled as 32 with idle lanes), 32
+    const int ipr_p2 = ipr <= 8 ? 8 : (ipr <= 16 ? 16 : 32);
+    const int rpp = (kEpiWarps * 32) / ipr_p2;  // whole rows per pass over the 256 epilogue threads
+    const int sub = (int)threadIdx.x % ipr_p2, rslot = (int)threadIdx.x / ipr_p2;
+    const int d0 = sub * 8;
+    const bool col_live = sub < ipr && d0 < p.D;
+    const bool vec = (p.D % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.cb) & 15) == 0) && (d0 + 8 <= p.D);
+    const int slice_n = (p.Kp + (int)gridDim.x - 1) / (int)gridDim.x;
+    const int slice_lo = (int)blockIdx.x * slice_n, slice_hi = min(slice_lo + slice_n, p.Kp);
+    const size_t img_tiles_bytes = (size_t)p.T * p.NC * b_tile;
+    auto load_item = [&](int k, float (&x)[8]) {
+  #pragma unroll
+      for (int e = 0; e < 8; ++e) x[e] = 0.f;
+      if (k < slice_hi && k < p.K && col_live) {
+        const float* src = p.cb + (size_t)k * p.D + d0;
+        if (vec) {
+          const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
+          x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w; x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
+        } else {
+  #pragma unroll
+          for (int e = 0; e < 8; ++e)
+            if (d0 + e < p.D) x[e] = __ldg(src + e);
+        }
+      }
+    };
+    float xfirst[8];
+    {
+      // mu[d] = mean over R <= 32 evenly spaced rows.  The R x D samples are spread over the threads (a few loads each,
+      // all in flight together), parked in shared memory (the A buffers are idle until the converters start) and summed
+      // per dimension in row order -- the same value in every CTA, which the slice owners and the z converters rely on.
+      // (Straight-line code is fetched at ~8 cycles per instruction the first time: this is a loop, not 32 unrolled loads.)
+      constexpr int RMAX = 32;
+      const int R = (int)(p.N < RMAX ? p.N : RMAX);
+      const int64_t stride = p.N / R;
+      float* samp = reinterpret_cast<float*>(sA);  // [R][256]
+      const bool want_mu = p.metric != LIPVQ_METRIC_DOT;
+      if (want_mu) {
+        const int dl = (int)threadIdx.x & 63, il = (int)threadIdx.x >> 6;  // 64 dims x 4 row lanes
+        for (int db = 0; db < p.D; db += 64) {
+          const int d = db + dl;
+          if (d < p.D) {
+            float v[8];
+  #pragma unroll
+            for (int n = 0; n < 8; ++n) {
+              const int i = il + 4 * n;
+              v[n] = (i < R) ? __ldg(p.z + (int64_t)i * stride * p.D + d) : 0.f;
+            }
+  #pragma unroll
+            for (int n = 0; n < 8; ++n) {
+              const int i = il + 4 * n;
+              samp[i * 256 + d] = v[n];
+            }
+          }
+        }
+      }
+      TR(40);
+      load_item(slice_lo + rslot, xfirst);  // in flight together with the mu samples
+      TR(41);
+      // ones slab: columns 0..2 = 1.0 for every row
+      for (int r = threadIdx.x; r < kBM; r += kEpiWarps * 32) {
+        *reinterpret_cast<uint4*>(sA1 + slab_off(r, 0)) = make_uint4(0x3C003C00u, 0x00003C00u, 0u, 0u);  // 1, 1, 1, 0 ...
+        *reinterpret_cast<uint4*>(sA1 + slab_off(r, 8)) = make_uint4(0u, 0u, 0u, 0u);
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      {
+        const int d = (int)threadIdx.x;
+        float sum = 0.f;
+        if (want_mu && d < p.D) {
+  #pragma unroll 8
+          for (int i = 0; i < RMAX; ++i) sum += samp[i * 256 + d];  // rows >= R hold zeros; fixed order
+        }
+        mu_s[d] = sum / (float)R;
+      }
+      TR(42);
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 0) mbar_arrive(bar_mu);  // the z converters may start: they need mu only
+      TR(43);
+      if (warp == 0) {  // ||mu||
+        float t = 0.f;
+        for (int dd = lane; dd < 256; dd += 32) t = fmaf(mu_s[dd], mu_s[dd], t);
+        t = warp_sum(t);
+        if (lane == 0) red_s[31] = t;
+      }
+    }
+    TR(4);
+    {
+      float mu8[8];
+  #pragma unroll
+      for (int e = 0; e < 8; ++e) mu8[e] = (col_live && d0 + e < p.D) ? mu_s[d0 + e] : 0.f;
+      const int ch = sub & 7;
+      const bool dot = (p.metric == LIPVQ_METRIC_DOT);
+      const __half2 m2 = __floats2half2_rn(-2.f, -2.f);
+      float emax2_loc = 0.f, excl_inv_loc = 0.f;
+      for (int k0 = slice_lo; k0 < slice_hi; k0 += rpp) {
+        const int k = k0 + rslot;
+        float x[8];
+        if (k0 == slice_lo) {
+  #pragma unroll
+          for (int e = 0; e < 8; ++e) x[e] = xfirst[e];
+        } else {
+          load_item(k, x);
+        }
+        float c[8];
+        float s = 0.f, am = 0.f;
+  #pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          c[e] = x[e] - mu8[e];
+          s = fmaf(c[e], c[e], s);
+        }
+  #pragma unroll
+        for (int e = 0; e < 8; e += 2) am = fmaxf(am, fmaxf(fabsf(c[e]), fabsf(c[e + 1])));
+        for (int o = 1; o < ipr_p2; o <<= 1) {
+          s += __shfl_xor_sync(0xffffffffu, s, o);
+          am = fmaxf(am, __shfl_xor_sync(0xffffffffu, am, o));
+        }
+        if (k >= slice_hi || sub >= ipr) continue;  // (after the shuffles: every lane of the warp takes part in them)
+        // a code whose centred entries or norm do not fit fp16 (or that holds inf / NaN) is left out of the contraction
+        const bool excluded = k < p.K && (!(am < kF16Safe) || (dot ? !(s < 3.0e38f) : !(s <= kEnormMax)));
+        const bool zero_row = k >= p.K || excluded;
+        uint32_t hh[4], ll[4];
+  #pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float va = zero_row ? 0.f : -2.f * c[2 * e], vb = zero_row ? 0.f : -2.f * c[2 * e + 1];
+          const __half2 hp = __floats2half2_rn(va, vb);
+          const float2 back = __half22float2(hp);
+          const __half2 lp = __floats2half2_rn(va - back.x, vb - back.y);
+          hh[e] = *reinterpret_cast<const uint32_t*>(&hp);
+          ll[e] = *reinterpret_cast<const uint32_t*>(&lp);
+        }
+        (void)m2;
+        const uint4 hv = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+        const int j = k >> 8, r = k & 255;  // kBN = 256
+        // image of the shared-memory tile layout: [j][c] tiles of [256 x 64] fp16, 128-byte swizzle
+        *reinterpret_cast<uint4*>(p.img + ((size_t)j * p.NC + (sub >> 3)) * b_tile + r * 128 + ((ch ^ (r & 7)) << 4)) = hv;
+        if (k < p.Kp_pub) {  // linear copies for the 3-term pass (TMA applies the swizzle itself)
+          *reinterpret_cast<uint4*>(p.ehi_g + (size_t)k * Dp + d0) = hv;
+          *reinterpret_cast<uint4*>(p.elo_g + (size_t)k * Dp + d0) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+        }
+        if (sub == 0) {
+          const float en = dot ? 0.f : s;
+          float h0, h1, h2;
+          if (zero_row) {
+            h0 = h1 = h2 = kSentinel;
+          } else {
+            h0 = __half2float(__float2half_rn(en));
+            h1 = __half2float(__float2half_rn(en - h0));
+            h2 = __half2float(__float2half_rn(en - h0 - h1));
+            emax2_loc = fmaxf(emax2_loc, s);
+          }
+          if (excluded) {
+            const float inv = (s < 3.0e38f) ? rsqrtf(s) * 1.0001f : 3.0e38f;  // 1/||e-mu|| rounded up (NaN/inf: unusable)
+            excl_inv_loc = fmaxf(excl_inv_loc, inv);
+          }
+          const __half2 a = __floats2half2_rn(h0, h1), b = __floats2half2_rn(h2, 0.f);
+          uint8_t* slab = p.img + img_tiles_bytes;
+          *reinterpret_cast<uint4*>(slab + slab_off(k, 0)) =
+              make_uint4(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b), 0u, 0u);
+          *reinterpret_cast<uint4*>(slab + slab_off(k, 8)) = make_uint4(0u, 0u, 0u, 0u);
+          if (k < p.Kp_pub) p.enorm_g[k] = zero_row ? INFINITY : en;
+        }
+      }
+      // maxima over all codes: non-negative floats order like their bit patterns (header zeroed by the host-side memset)
+      if (emax2_loc > 0.f) atomicMax(&p.hdr->emax2_bits, __float_as_uint(emax2_loc));
+      if (excl_inv_loc > 0.f) atomicMax(&p.hdr->excl_inv_bits, __float_as_uint(excl_inv_loc));
+    }
+    TR(5);
+    fence_async_smem();  // (the ones slab, for the tensor core)
+    asm volatile("bar.sync 1, 256;" ::: "memory");  // this CTA's slice is written
+    TR(44);
+    if (threadIdx.x == 0) {
+      // arrive (release: the slice and the two maxima), then wait until every CTA has arrived (acquire)
+      __threadfence();
+      atomicAdd(&p.hdr->arrived, 1);
+      const int want = (int)gridDim.x;
+      long long t0 = 0;
+      uint32_t spins = 0;
+      for (;;) {
+        int seen;
+        asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(seen) : "l"(&p.hdr->arrived) : "memory");
+        if (seen >= want) break;
+        if ((++spins & 63u) == 0) {  // a launch that is not fully resident must fault, not hang
+          if (t0 == 0) t0 = clock64();
+          else if (clock64() - t0 > 4000000000LL) __trap();
+        }
+        __nanosleep(64);
+      }
+      TR(45);
+      // the image was written through the generic proxy (by other SMs); the bulk copies read it through the async proxy
+      asm volatile("fence.proxy.async;" ::: "memory");
+      const uint32_t slab_bytes = (uint32_t)p.Kp * 32u;
+      mbar_expect_tx(bar_img, (uint32_t)img_tiles_bytes + slab_bytes);
+  #pragma unroll 1
+      for (size_t off = 0; off < img_tiles_bytes; off += 32768)
+        bulk_load_1d(smem_u32(sB + off), p.img + off, 32768u, bar_img);
+  #pragma unroll 1
+      for (uint32_t off = 0; off < slab_bytes; off += 8192)
+        bulk_load_1d(smem_u32(sE + off), p.img + img_tiles_bytes + off, 8192u, bar_img);
+    }
+    TR(46);
+    mbar_wait(bar_img, 0);  // every thread: code tiles + norm slab have landed (async-proxy writes, visible to the MMA)
+    TR(47);
+    float emax2, excl_inv;
+    {
+      unsigned a, b;
+      asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(a) : "l"(&p.hdr->emax2_bits) : "memory");
+      asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(b) : "l"(&p.hdr->excl_inv_bits) : "memory");
+      emax2 = __uint_as_float(a);
+      excl_inv = __uint_as_float(b);
+    }
+    const float mu_norm = sqrtf(red_s[31]);
+    if (blockIdx.x == 0) {  // what the later passes read
+      for (int d = threadIdx.x; d < Dp; d += kEpiWarps * 32) p.mu_g[d] = mu_s[d];
+      if (threadIdx.x == 0) p.hdr->mu_norm = mu_norm;
+    }
+
+    // TMEM lane = row; group g = warp >> 2 drains every second code tile.  Per 32-column chunk and row:
+    //   best of the chunk      plain fp32 minimum, half an ALU instruction per score (FMNMX3)
+    //   near-best bit mask     u = sat((best + margin - s) * 2^80) is exactly 1 for s < best + margin and exactly 0 for
+    //                          s >= best + margin (a fractional value needs |thr - s| < 2^-80 and is caught by the
+    //                          integrality test at the end); mask += u * 2^column -- two FMA-pipe instructions per score,
+    //                          on the pipe the minimum leaves idle
+    //   chunk-level top-2      a handful of instructions per 32 scores: best, best of the OTHER chunks, and the mask of
+    //                          the winning chunk
+    // A row is certified when the winning chunk's mask has exactly one bit (that bit is the index) and every other
+    // chunk's best is further away than the margin.  Two chunks are folded per iteration: the dependent chains of one
+    // chunk (min tree, mask accumulation) are latency- not throughput-bound, the second chunk fills the gaps.
     const int q = warp & 3, g = warp >> 2;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     const uint32_t tbuf = tmem_base + (uint32_t)g * (uint32_t)kBN + lane_off;
     const float emax_g = sqrtf(emax2);
-    const uint32_t kmask = p.kmask;  // 0xFFFFFFE0, passed as data so that it lives in a register and the COLUMN is the LOP3 immediate
+    const bool dotm = (p.metric == LIPVQ_METRIC_DOT);
+    // margin(zn) = max(m_alg + m_c, gamma_ref * ref_mag) with every term bounded for ANY candidate code
+    // (||e-mu|| <= emax, distance <= zn + emax, ||z|| <= zn + ||mu||): a polynomial in zn = ||z-mu|| whose coefficients
+    // are per-launch constants
+    const float c_sub = 2.9802322e-8f * sqrtf((float)Dp + 16.f);
+    const float u32f = 5.9604645e-8f;
+    auto margin_of = [&](float zn, float emax, float dist) {
+      const float m_alg = 2.f * (p.gamma_en * emax * emax + p.gamma_dot * 2.f * zn * emax + c_sub * (zn + 2.f * emax + 3.f));
+      const float delta = u32f * (zn + emax + 4.f * mu_norm);
+      const float m_c = dotm ? 0.f : 2.f * (2.f * dist * delta + delta * delta);
+      const float ref_mag = dotm ? 2.f * zn * emax : dist * dist;
+      return fmaxf(m_alg + m_c, p.gamma_ref * ref_mag);
+    };
 
-    // running state of one row (lane): best score (FOLD 0: packed key), best of the OTHER chunks, first code of the
-    // winning chunk, and what is known about near-best scores inside the winning chunk
-    float best = INFINITY, second = INFINITY, ma = 0.f, mb = 0.f;
-    int base = 0;
-    float big = 0.f, t0 = 0.f, margin_row = 0.f;
+    float best = INFINITY, second = INFINITY, ma = 0.f, mb = 0.f;  // best, best of the other chunks, masks of the winning chunk
+    int base = 0;                                                  // first code of the winning chunk
+    float margin_row = 0.f, zn = 0.f;
     int cur_blk = -1;
-    float2 st = make_float2(0.f, 0.f);
-    constexpr float kH = 1.2089258e24f;  // 2^80 (FOLD 1): (thr - s) * 2^80 saturates to exactly 0 or 1 unless |thr - s| < 2^-80
+    constexpr float kH = 1.2089258e24f;  // 2^80
+    const float nH = -kH;
+
+    // fold one 32-column chunk held in v: chunk minimum + near-best masks (low / high 16 columns)
+    auto fold32 = [&](const uint32_t (&v)[32], float& cm, float& xa, float& xb) {
+      float k0_ = fminf(__uint_as_float(v[0]), __uint_as_float(v[1])), k1_ = fminf(__uint_as_float(v[2]), __uint_as_float(v[3]));
+      float k2_ = fminf(__uint_as_float(v[4]), __uint_as_float(v[5])), k3_ = fminf(__uint_as_float(v[6]), __uint_as_float(v[7]));
+#pragma unroll
+      for (int e = 8; e < 32; e += 8) {
+        k0_ = fmin3(k0_, __uint_as_float(v[e]), __uint_as_float(v[e + 1]));
+        k1_ = fmin3(k1_, __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3]));
+        k2_ = fmin3(k2_, __uint_as_float(v[e + 4]), __uint_as_float(v[e + 5]));
+        k3_ = fmin3(k3_, __uint_as_float(v[e + 6]), __uint_as_float(v[e + 7]));
+      }
+      cm = fmin3(k0_, k1_, fminf(k2_, k3_));
+      const float tH = (cm + margin_row) * kH;
+      float l0 = 0.f, l1 = 0.f, l2 = 0.f, l3 = 0.f, h0 = 0.f, h1 = 0.f, h2 = 0.f, h3 = 0.f;
+#pragma unroll
+      for (int e = 0; e < 16; e += 4) {
+        l0 = fmaf(ffma_sat(__uint_as_float(v[e]), nH, tH), (float)(1u << e), l0);
+        l1 = fmaf(ffma_sat(__uint_as_float(v[e + 1]), nH, tH), (float)(1u << (e + 1)), l1);
+        l2 = fmaf(ffma_sat(__uint_as_float(v[e + 2]), nH, tH), (float)(1u << (e + 2)), l2);
+        l3 = fmaf(ffma_sat(__uint_as_float(v[e + 3]), nH, tH), (float)(1u << (e + 3)), l3);
+        h0 = fmaf(ffma_sat(__uint_as_float(v[16 + e]), nH, tH), (float)(1u << e), h0);
+        h1 = fmaf(ffma_sat(__uint_as_float(v[17 + e]), nH, tH), (float)(1u << (e + 1)), h1);
+        h2 = fmaf(ffma_sat(__uint_as_float(v[18 + e]), nH, tH), (float)(1u << (e + 2)), h2);
+        h3 = fmaf(ffma_sat(__uint_as_float(v[19 + e]), nH, tH), (float)(1u << (e + 3)), h3);
+      }
+      xa = (l0 + l1) + (l2 + l3);
+      xb = (h0 + h1) + (h2 + h3);
+    };
+    auto merge_chunk = [&](float cm, float xa, float xb, int first_code) {
+      const bool rec = cm < best;
+      second = fminf(second, fmaxf(best, cm));
+      base = rec ? first_code : base;
+      ma = rec ? xa : ma;
+      mb = rec ? xb : mb;
+      best = fminf(best, cm);
+    };
     for (int t = g; t < total_tiles; t += 2) {
       const int i = t / p.T, j = t - i * p.T;
+      TR(10);
       mbar_wait(bar_acc_full + 8 * g, (uint32_t)(t >> 1) & 1);
       fence_after();
+      TR(11);
       if (i != cur_blk) {
-        // New row block.  The within-chunk margin is fixed per row BEFORE the scan, from bounds that hold for any
-        // candidate (||e-mu|| <= emax, distance <= ||z-mu|| + emax); the final test uses the refined bound, which is
-        // never larger.  (rowstat was written before bar_a_full completed and the MMA issuer observed that barrier
-        // before issuing the MMAs whose commit we just waited for: the read is ordered.)
+        // New row block: the in-chunk margin is fixed per row BEFORE the scan (bounds valid for any candidate); the
+        // final test may refine it, never enlarge it.  (rowstat was written before bar_a_full completed and the MMA
+        // issuer observed that barrier before issuing the MMAs whose commit we just waited for: the read is ordered.)
         cur_blk = i;
-        st = rowstat[(i % kStatSlots) * kBM + q * 32 + lane];
-        const float zn2 = st.x, zo2 = st.y;
-        const float zn = sqrtf(zn2);
-        const float dmax = zn + emax_g;
-        const float sub = 2.9802322e-8f * sqrtf((float)Dp + 16.f) * (zn + 2.f * emax_g + 3.f);
-        const float m_alg = 2.f * (p.gamma_en * emax_g * emax_g + p.gamma_dot * 2.f * zn * emax_g + sub);
-        const float delta = 5.9604645e-8f * (sqrtf(zo2) + emax_g + 3.f * mu_norm);
-        const float m_c = (p.metric == LIPVQ_METRIC_DOT) ? 0.f : 2.f * (2.f * dmax * delta + delta * delta);
-        const float ref_mag = (p.metric == LIPVQ_METRIC_DOT) ? 2.f * zn * emax_g : dmax * dmax;
-        const float smax = emax_g * emax_g + 2.f * zn * emax_g;  // |score| <= smax for every real code
-        const float slack = (FOLD == 0) ? 4.7683716e-6f * smax : 0.f;  // key truncation (2^-18) + rounding of the count FMAs
-        margin_row = (fmaxf(m_alg + m_c, p.gamma_ref * ref_mag) + 2.f * slack) * 1.0000002f + 1e-30f;
-        // FOLD 0: u(s) = sat((key_best - s) * big + t0): exactly 1 for the chunk's best (its key is within `slack` of its
-        // score), > 0 for every score below key_best + margin_row + slack, 0 beyond
-        big = 1.f / margin_row;
-        t0 = 1.f + slack * big + 1e-6f;
-        if (!(margin_row < 3.0e38f) || !(big > 0.f)) {  // non-finite row statistics: nothing can be certified
-          big = 0.f;
-          t0 = 2.f;  // every score counts: the count is never 1
-          margin_row = INFINITY;
-        }
+        const float zn2 = rowstat[(i % kStatSlots) * kBM + q * 32 + lane];
+        zn = sqrtf(zn2);
+        margin_row = margin_of(zn, emax_g, zn + emax_g) * 1.0000002f + 1e-30f;
+        if (!(margin_row < 3.0e38f)) margin_row = INFINITY;  // non-finite row statistics: nothing can be certified
       }
-      for (int c0 = 0; c0 < kBN; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld32(tbuf + c0, v);
-        tmem_ld_wait(v);
-        if (c0 + 32 >= kBN) {  // last load of this accumulator has landed: hand it back to the MMA warp
+#pragma unroll 1
+      for (int c0 = 0; c0 < kBN; c0 += 64) {
+        uint32_t va[32], vb[32];
+        tmem_ld32(tbuf + c0, va);
+        tmem_ld32(tbuf + c0 + 32, vb);
+        tmem_ld_wait2(va, vb);
+        if (c0 + 64 >= kBN) {  // last load of this accumulator has landed: hand it back to the MMA warp
           fence_before();
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_acc_empty + 8 * g);
+          TR(12);
         }
-        float cm, xa, xb = 0.f;
-        if (FOLD == 0) {
-          // --- best of the chunk: packed keys, four chains of FMNMX3 ---
-          float k0_ = fminf(pack_key(v[0], kmask, 0), pack_key(v[1], kmask, 1));
-          float k1_ = fminf(pack_key(v[2], kmask, 2), pack_key(v[3], kmask, 3));
-          float k2_ = fminf(pack_key(v[4], kmask, 4), pack_key(v[5], kmask, 5));
-          float k3_ = fminf(pack_key(v[6], kmask, 6), pack_key(v[7], kmask, 7));
-#pragma unroll
-          for (int e = 8; e < 32; e += 8) {
-            k0_ = fmin3(k0_, pack_key(v[e], kmask, e), pack_key(v[e + 1], kmask, e + 1));
-            k1_ = fmin3(k1_, pack_key(v[e + 2], kmask, e + 2), pack_key(v[e + 3], kmask, e + 3));
-            k2_ = fmin3(k2_, pack_key(v[e + 4], kmask, e + 4), pack_key(v[e + 5], kmask, e + 5));
-            k3_ = fmin3(k3_, pack_key(v[e + 6], kmask, e + 6), pack_key(v[e + 7], kmask, e + 7));
-          }
-          cm = fmin3(k0_, k1_, fminf(k2_, k3_));
-          // --- how many scores of the chunk lie within the margin of its best (FMA pipe) ---
-          const float t1 = fmaf(cm, big, t0);
-          const float nbig = -big;
-          float n0 = ffma_sat(__uint_as_float(v[0]), nbig, t1), n1 = ffma_sat(__uint_as_float(v[1]), nbig, t1);
-          float n2 = ffma_sat(__uint_as_float(v[2]), nbig, t1), n3 = ffma_sat(__uint_as_float(v[3]), nbig, t1);
-#pragma unroll
-          for (int e = 4; e < 32; e += 4) {
-            n0 += ffma_sat(__uint_as_float(v[e]), nbig, t1);
-            n1 += ffma_sat(__uint_as_float(v[e + 1]), nbig, t1);
-            n2 += ffma_sat(__uint_as_float(v[e + 2]), nbig, t1);
-            n3 += ffma_sat(__uint_as_float(v[e + 3]), nbig, t1);
-          }
-          xa = (n0 + n1) + (n2 + n3);
-        } else {
-          // --- best of the chunk: plain fp32 minimum (half an ALU instruction per score) ---
-          float k0_ = fminf(__uint_as_float(v[0]), __uint_as_float(v[1])), k1_ = fminf(__uint_as_float(v[2]), __uint_as_float(v[3]));
-          float k2_ = fminf(__uint_as_float(v[4]), __uint_as_float(v[5])), k3_ = fminf(__uint_as_float(v[6]), __uint_as_float(v[7]));
-#pragma unroll
-          for (int e = 8; e < 32; e += 8) {
-            k0_ = fmin3(k0_, __uint_as_float(v[e]), __uint_as_float(v[e + 1]));
-            k1_ = fmin3(k1_, __uint_as_float(v[e + 2]), __uint_as_float(v[e + 3]));
-            k2_ = fmin3(k2_, __uint_as_float(v[e + 4]), __uint_as_float(v[e + 5]));
-            k3_ = fmin3(k3_, __uint_as_float(v[e + 6]), __uint_as_float(v[e + 7]));
-          }
-          cm = fmin3(k0_, k1_, fminf(k2_, k3_));
-          // --- WHICH scores lie below best + margin, as an exact bit mask built on the FMA pipe:
-          //     u = sat((thr - s) * 2^80) is exactly 1 for s < thr and exactly 0 for s >= thr (a fractional value needs
-          //     |thr - s| < 2^-80 and is caught by the integrality test below); mask += u * 2^column.
-          const float tH = (cm + margin_row) * kH;
-          const float nH = -kH;
-          float l0 = 0.f, l1 = 0.f, h0 = 0.f, h1 = 0.f;
-#pragma unroll
-          for (int e = 0; e < 16; e += 2) {
-            l0 = fmaf(ffma_sat(__uint_as_float(v[e]), nH, tH), (float)(1u << e), l0);
-            l1 = fmaf(ffma_sat(__uint_as_float(v[e + 1]), nH, tH), (float)(1u << (e + 1)), l1);
-            h0 = fmaf(ffma_sat(__uint_as_float(v[16 + e]), nH, tH), (float)(1u << e), h0);
-            h1 = fmaf(ffma_sat(__uint_as_float(v[17 + e]), nH, tH), (float)(1u << (e + 1)), h1);
-          }
-          xa = l0 + l1;
-          xb = h0 + h1;
-        }
-        // --- chunk-level top-2 ---
-        const bool rec = cm < best;
-        second = fminf(second, fmaxf(best, cm));
-        base = rec ? (j * kBN + c0) : base;
-        ma = rec ? xa : ma;
-        mb = rec ? xb : mb;
-        best = fminf(best, cm);
+        float cma, xaa, xba, cmb, xab, xbb;
+        fold32(va, cma, xaa, xba);
+        fold32(vb, cmb, xab, xbb);
+        merge_chunk(cma, xaa, xba, j * kBN + c0);
+        merge_chunk(cmb, xab, xbb, j * kBN + c0 + 32);
       }
+      TR(14);
       const bool last_of_block = (j == p.T - 1);
       const bool leaves_block = last_of_block || (j + 2 >= p.T);
       if (!leaves_block) continue;
@@ -651,34 +758,23 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
       const int64_t rb = (int64_t)blockIdx.x + (int64_t)i * gridDim.x;
       const int64_t row = rb * kBM + q * 32 + lane;
       if (row < p.N) {
-        int bidx;
-        bool single;
-        if (FOLD == 0) {
-          bidx = base + (int)(__float_as_uint(best) & 31u);
-          single = (ma == 1.0f);
-        } else {
-          const int ilo = __float2int_rn(ma), ihi = __float2int_rn(mb);
-          const bool exact = ((float)ilo == ma) && ((float)ihi == mb) && ilo >= 0 && ihi >= 0 && ilo < 65536 && ihi < 65536;
-          const uint32_t mask = (uint32_t)ilo | ((uint32_t)ihi << 16);
-          single = exact && (__popc(mask) == 1);
-          bidx = base + __ffs((int)mask) - 1;
+        const int ilo = __float2int_rn(ma), ihi = __float2int_rn(mb);
+        const bool exact = ((float)ilo == ma) && ((float)ihi == mb) && ((unsigned)ilo < 65536u) && ((unsigned)ihi < 65536u);
+        const uint32_t mask = (uint32_t)ilo | ((uint32_t)ihi << 16);
+        const int bidx = base + __ffs((int)mask) - 1;
+        // exactly one score of the winning chunk within the margin of the best, and it is a real code
+        bool ok = exact && (__popc(mask) == 1) && (bidx < p.K) && (margin_row < 3.0e38f);
+        const float gap = second - best;
+        if (ok && !(gap > margin_row)) {
+          // refine: only codes that can still beat the candidate matter, ||e-mu|| <= ||z-mu|| + d_best (triangle inequality)
+          const float dhat = sqrtf(fmaxf(best + zn * zn, 0.f));
+          const float emax = dotm ? emax_g : fminf(emax_g, zn + 1.02f * dhat + 1e-30f);
+          ok = gap > fminf(margin_of(zn, emax, dhat), margin_row);
         }
-        const float zn2 = st.x, zo2 = st.y;
-        const float zn = sqrtf(zn2);
-        const float dhat = sqrtf(fmaxf(best + zn2, 0.f));
-        float emax = emax_g;
-        if (p.metric != LIPVQ_METRIC_DOT) emax = fminf(emax, zn + 1.02f * dhat + 1e-30f);
-        const float sub = 2.9802322e-8f * sqrtf((float)Dp + 16.f) * (zn + 2.f * emax + 3.f);
-        const float margin_alg = 2.f * (p.gamma_en * emax * emax + p.gamma_dot * 2.f * zn * emax + sub);
-        const float ref_mag = (p.metric == LIPVQ_METRIC_DOT) ? 2.f * zn * emax : fmaxf(best + zn2, 0.f);
-        const float delta = 5.9604645e-8f * (sqrtf(zo2) + emax + 3.f * mu_norm);
-        const float margin_c = (p.metric == LIPVQ_METRIC_DOT) ? 0.f : 2.f * (2.f * dhat * delta + delta * delta);
-        const float smax = emax_g * emax_g + 2.f * zn * emax_g;
-        const float slack = (FOLD == 0) ? 4.7683716e-6f * smax : 0.f;
-        // never larger than the bound the in-chunk test used
-        const float margin = fminf(fmaxf(margin_alg + margin_c, p.gamma_ref * ref_mag) + 2.f * slack, margin_row);
-        bool ok = (second - best > margin) && single && (bidx >= 0) && (bidx < p.K) && (margin_row < 3.0e38f);
-        if (excl_inv > 0.f) ok = ok && (p.metric != LIPVQ_METRIC_DOT) && ((zn + 1.02f * dhat) * excl_inv < 0.999f);
+        if (excl_inv > 0.f) {  // codes left out of the contraction: each is further than ||z-mu|| + d_best, or the row is queued
+          const float dhat = sqrtf(fmaxf(best + zn * zn, 0.f));
+          ok = ok && !dotm && ((zn + 1.02f * dhat) * excl_inv < 0.999f);
+        }
         if (ok) {
           p.idx_out[row] = (int64_t)bidx;
         } else {
@@ -690,6 +786,7 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
     }
   }
 
+  TR(2);
   fence_before();
   __syncthreads();
   grid_dep_launch();
@@ -697,6 +794,10 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
     fence_after();
     tmem_dealloc(tmem_base, 512);
   }
+#ifdef LIPVQ_TRACE
+  TR(3);
+  if (blockIdx.x == 0 && lane == 0) g_trace_p1_n[warp] = tr_n;
+#endif
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -739,7 +840,7 @@ struct P1Geom {
   bool ok;
 };
 
-constexpr int kMisc = kStatSlots * kBM * 8 + 2 * kBM * 32 + 256 * 4 + 32 * 4 + 24 * 8 + 64;
+constexpr int kMisc = kStatSlots * kBM * 4 + 2 * kBM * 32 + 256 * 4 + 32 * 4 + 24 * 8 + 64;
 
 P1Geom p1_geom(int D, int K, bool staged) {
   P1Geom g{};
@@ -768,17 +869,25 @@ P1Geom p1_geom(int D, int K, bool staged) {
 
 }  // namespace
 
-bool search_p1_supported(int64_t N, int D, int K) {
+bool search_p1_fits(int64_t N, int D, int K) {
   if (N < 1 || K < 1 || D < 1) return false;
-  if (const char* e = getenv("LIPVQ_SEARCH_P1"))
-    if (e[0] == '0') return false;
   return p1_geom(D, K, false).ok;
+}
+bool search_p1_supported(int64_t N, int D, int K) {
+  if (const char* e = getenv("LIPVQ_SEARCH_P1"))  // A/B switch: 0 = the round-1 prep + streamed first pass
+    if (e[0] == '0') return false;
+  return search_p1_fits(N, D, K);
+}
+
+size_t search_p1_image_bytes(int D, int K) {
+  const size_t Dp = (size_t)(D + kChunk - 1) / kChunk * kChunk, Kp = (size_t)(K + kBN - 1) / kBN * kBN;
+  return Kp * Dp * 2 + Kp * 32;
 }
 
 // One launch: codebook preparation + fp16 pass over all rows.  Uncertified rows are appended to `queue` (count at
 // *queue_count, which must be zero on entry); mu / enorm / ehi / elo / hdr are published for the later passes.
 int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, int Kp_pub, float* mu,
-                     float* enorm, void* ehi_, void* elo_, SearchHdr* hdr, int* queue, int* queue_count, int64_t* idx_out,
+                     float* enorm, void* ehi_, void* elo_, void* img, SearchHdr* hdr, int* queue, int* queue_count, int64_t* idx_out,
                      cudaStream_t stream) {
   __half* ehi = reinterpret_cast<__half*>(ehi_);
   __half* elo = reinterpret_cast<__half*>(elo_);
@@ -793,10 +902,10 @@ int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, i
   p.z = z; p.cb = cb; p.N = N; p.D = D; p.K = K; p.Kp = g.Kp; p.NC = g.NC; p.T = g.T;
   p.nbufA = g.nbufA; p.zstages = g.zstages; p.metric = metric;
   p.Kp_pub = Kp_pub;
-  p.kmask = 0xFFFFFFE0u;
   p.slab_swap = 0;
   if (const char* e = getenv("LIPVQ_SLAB_DESC_SWAP")) p.slab_swap = (e[0] == '1');
   p.mu_g = mu; p.enorm_g = enorm; p.ehi_g = ehi; p.elo_g = elo; p.hdr = hdr;
+  p.img = reinterpret_cast<uint8_t*>(img);
   p.queue_out = queue; p.queue_count = queue_count; p.idx_out = idx_out;
   const float u22 = 2.3841858e-7f;
   const float steps = (float)(g.Dp / 16 + 1);  // + the norm-slab MMA
@@ -810,26 +919,26 @@ int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, i
   } else {
     memset(&tm_z, 0, sizeof(tm_z));
   }
-  int fold = 1;  // 1: exact near-best bit mask on the FMA pipe (default); 0: packed keys + saturating count (A/B)
-  if (const char* e = getenv("LIPVQ_P1_FOLD")) fold = (e[0] == '0') ? 0 : 1;
-  static size_t smem_set[2][kMaxDevices] = {};
+  static size_t smem_set[kMaxDevices] = {};
   const int dev_ = current_device();
-  if (g.smem > smem_set[fold][dev_]) {
-    if (fold == 0)
-      LIPVQ_CUDA(cudaFuncSetAttribute(search_p1_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
-    else
-      LIPVQ_CUDA(cudaFuncSetAttribute(search_p1_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
-    smem_set[fold][dev_] = g.smem;
+  if (g.smem > smem_set[dev_]) {
+    LIPVQ_CUDA(cudaFuncSetAttribute(search_p1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)g.smem));
+    smem_set[dev_] = g.smem;
   }
   const int row_blocks = (int)ceil_div64(N, kBM);
   const int sms = sm_count();
   const int grid = row_blocks < sms ? row_blocks : sms;
-  if (fold == 0)
-    LIPVQ_CUDA(launch_pdl(search_p1_kernel<0>, dim3(grid), dim3(kThreads), g.smem, stream, tm_z, p));
-  else
-    LIPVQ_CUDA(launch_pdl(search_p1_kernel<1>, dim3(grid), dim3(kThreads), g.smem, stream, tm_z, p));
+  LIPVQ_CUDA(launch_pdl(search_p1_kernel, dim3(grid), dim3(kThreads), g.smem, stream, tm_z, p));
   LIPVQ_LAUNCHED("search_p1_kernel");
   return LIPVQ_OK;
 }
 
 }  // namespace lipvq
+
+#ifdef LIPVQ_TRACE
+extern "C" LIPVQ_API int lipvq_debug_trace_p1(unsigned long long* out, int* counts) {
+  if (cudaMemcpyFromSymbol(out, lipvq::g_trace_p1, sizeof(unsigned long long) * 16 * lipvq::kTraceMax) != cudaSuccess) return -1;
+  if (cudaMemcpyFromSymbol(counts, lipvq::g_trace_p1_n, sizeof(int) * 16) != cudaSuccess) return -1;
+  return lipvq::kTraceMax;
+}
+#endif

@@ -1,0 +1,30 @@
+"""A few nearest-code searches at one shape (for ncu / timing of the individual launches).
+usage: python scripts/search_once.py [N K D mode iters]"""
+import math
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "robot-manipulation-vq-vae_b200"))
+import lipvq  # noqa: E402
+from lipvq import ops  # noqa: E402
+
+N, K, D = (int(a) for a in sys.argv[1:4]) if len(sys.argv) > 3 else (65536, 512, 64)
+mode = sys.argv[4] if len(sys.argv) > 4 else "t1"
+iters = int(sys.argv[5]) if len(sys.argv) > 5 else 6
+g = torch.Generator().manual_seed(0)
+cb = ((torch.rand(K, D, generator=g) * 2 - 1) * math.sqrt(6.0 / D)).cuda()
+z = (torch.rand(N, D, generator=g) if mode == "uniform" else torch.sigmoid(0.05 * torch.randn(N, D, generator=g))).cuda()
+ws = torch.empty(ops.search_workspace_bytes(N, D, K, lipvq.METRIC_L2, lipvq.ALGO_TCGEN05), dtype=torch.uint8, device="cuda")
+idx = torch.empty(N, dtype=torch.int64, device="cuda")
+flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+for i in range(iters):
+    flush.zero_()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    ops.nn_search(z, cb, lipvq.METRIC_L2, lipvq.ALGO_TCGEN05, out=idx, workspace=ws)
+    b.record()
+    torch.cuda.synchronize()
+    print(f"iter {i}: {a.elapsed_time(b) * 1e3:.1f} us")

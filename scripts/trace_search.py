@@ -17,9 +17,10 @@ import lipvq  # noqa: E402
 from lipvq import _cabi, ops  # noqa: E402
 from bench_search import case  # noqa: E402
 
-NAMES = {0: "start", 1: "setup_done", 2: "role_done", 3: "exit",
+NAMES = {0: "start", 1: "setup_done", 2: "role_done", 3: "exit", 4: "mu_done", 5: "codebook_done", 6: "dep_wait_done", 40: "mu_loads_issued", 41: "slice_loads_issued",
+         42: "mu_reduced", 43: "mu_synced", 44: "slice_synced", 45: "all_arrived", 46: "bulk_issued", 47: "image_landed",
          10: "epi:wait_acc", 11: "epi:acc_full", 12: "epi:last_ld", 13: "epi:en_stored", 14: "epi:folded",
-         20: "cvt:wait_a_empty", 21: "cvt:a_empty", 22: "cvt:z_full", 23: "cvt:a_filled",
+         24: "cvt:converted", 25: "cvt:stats", 26: "cvt:fenced", 20: "cvt:wait_a_empty", 21: "cvt:a_empty", 22: "cvt:z_full", 23: "cvt:a_filled",
          30: "mma:a_full", 31: "mma:acc_empty", 32: "mma:issued"}
 
 
@@ -55,8 +56,14 @@ def main():
     idx = torch.empty(N, dtype=torch.int64, device="cuda")
     for _ in range(3):
         ops.nn_search(z, cb, lipvq.METRIC_L2, algo, out=idx, workspace=ws)
+    if "--cold" in sys.argv:  # L2 (data AND the kernel's code) evicted, as between the kernels of a training step
+        torch.empty(256 << 20, dtype=torch.uint8, device="cuda").zero_()
+        ops.nn_search(z, cb, lipvq.METRIC_L2, algo, out=idx, workspace=ws)
     torch.cuda.synchronize()
-    report("lipvq_debug_trace", 16, 4096, {0: "epi g0", 4: "epi g1", 8: "cvt", 12: "mma", 13: "tma"})
+    if os.environ.get("LIPVQ_SEARCH_P1", "1") != "0" and hasattr(_cabi.lib, "lipvq_debug_trace_p1"):
+        report("lipvq_debug_trace_p1", 16, 4096, {0: "epi g0", 4: "epi g1", 8: "cvt", 12: "mma"})
+    else:
+        report("lipvq_debug_trace", 16, 4096, {0: "epi g0", 4: "epi g1", 8: "cvt", 12: "mma", 13: "tma"})
 
 
 if __name__ == "__main__":
