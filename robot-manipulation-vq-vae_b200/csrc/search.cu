@@ -546,6 +546,8 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
     const int* count = nullptr;
     const int rc = search_fused_launch(z, N, D, codebook, K, metric, plan, ws, idx_out, stream, &queue, &count);
     if (rc != LIPVQ_OK) return rc;
+    static const bool dbg_no_tails = getenv("LIPVQ_DEBUG_NO_TAILS") != nullptr;  // timing experiments only
+    if (dbg_no_tails) return LIPVQ_OK;
     LIPVQ_CUDA(launch_pdl(rescore_kernel, dim3(rs_blocks), dim3(256), rs_smem, stream, z, D, codebook, K, metric, count,
                           (const int*)&hdr->flagged, queue, (const int*)(queue == work ? nullptr : work),
                           search_skip_rows(N, D, K), idx_out, (float*)nullptr, stats_out, vec, lpc));

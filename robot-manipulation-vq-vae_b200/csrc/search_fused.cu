@@ -1003,7 +1003,8 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
   }
   *final_queue = work;
   *final_count = &hdr->flagged;
-  if (g3.ok) {
+  static const bool dbg_no_tails = getenv("LIPVQ_DEBUG_NO_TAILS") != nullptr;  // timing experiments only: results incomplete
+  if (g3.ok && !dbg_no_tails) {
     CUtensorMap tm_hi, tm_lo;
     if ((rc = make_map(&tm_hi, ehi, Kp, g3.Dp, g3.BN)) != LIPVQ_OK) return rc;
     if ((rc = make_map(&tm_lo, elo, Kp, g3.Dp, g3.BN)) != LIPVQ_OK) return rc;

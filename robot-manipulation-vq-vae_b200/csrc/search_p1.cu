@@ -69,6 +69,7 @@ struct P1Params {
   int nbufA, zstages;
   int metric;
   int Kp_pub;     // rows of the published arrays (the later passes' padded code count)
+  int early_trigger;  // griddepcontrol.launch_dependents right after set-up instead of at the end
   int slab_swap;  // debug: swap LBO/SBO of the no-swizzle descriptors
   // outputs for the later passes (search_fused_kernel<3>, rescore): published by slices of the grid
   float* mu_g;
@@ -220,6 +221,10 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
   fence_after();
   const uint32_t tmem_base = *tmem_slot;
   TR(1);
+  // The later passes (almost always empty) may be scheduled as soon as SMs free up: their launch latency then hides
+  // behind this kernel's tail.  They cannot co-reside with it (shared memory), and they wait for this grid's completion
+  // (griddepcontrol.wait) before reading anything it wrote.
+  if (p.early_trigger) grid_dep_launch();
 
   if (warp == kWarpMma) {
     // ===== MMA issuer (one thread) =====
@@ -789,7 +794,7 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
   TR(2);
   fence_before();
   __syncthreads();
-  grid_dep_launch();
+  if (!p.early_trigger) grid_dep_launch();
   if (warp == kWarpMma) {
     fence_after();
     tmem_dealloc(tmem_base, 512);
@@ -903,6 +908,8 @@ int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, i
   p.nbufA = g.nbufA; p.zstages = g.zstages; p.metric = metric;
   p.Kp_pub = Kp_pub;
   p.slab_swap = 0;
+  p.early_trigger = 1;
+  if (const char* e = getenv("LIPVQ_P1_EARLY_TRIGGER")) p.early_trigger = (e[0] != '0');
   if (const char* e = getenv("LIPVQ_SLAB_DESC_SWAP")) p.slab_swap = (e[0] == '1');
   p.mu_g = mu; p.enorm_g = enorm; p.ehi_g = ehi; p.elo_g = elo; p.hdr = hdr;
   p.img = reinterpret_cast<uint8_t*>(img);

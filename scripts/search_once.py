@@ -13,15 +13,23 @@ from lipvq import ops  # noqa: E402
 
 N, K, D = (int(a) for a in sys.argv[1:4]) if len(sys.argv) > 3 else (65536, 512, 64)
 mode = sys.argv[4] if len(sys.argv) > 4 else "t1"
-iters = int(sys.argv[5]) if len(sys.argv) > 5 else 6
+iters = int(sys.argv[5]) if len(sys.argv) > 5 and sys.argv[5].isdigit() else 6
 g = torch.Generator().manual_seed(0)
 cb = ((torch.rand(K, D, generator=g) * 2 - 1) * math.sqrt(6.0 / D)).cuda()
 z = (torch.rand(N, D, generator=g) if mode == "uniform" else torch.sigmoid(0.05 * torch.randn(N, D, generator=g))).cuda()
 ws = torch.empty(ops.search_workspace_bytes(N, D, K, lipvq.METRIC_L2, lipvq.ALGO_TCGEN05), dtype=torch.uint8, device="cuda")
 idx = torch.empty(N, dtype=torch.int64, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+rot = "--rotate" in sys.argv
+if rot:  # inputs larger than L2: 16 different z buffers (268 MB) used in turn, no flush
+    zs = [z.clone() + 0 * i for i in range(16)]
 for i in range(iters):
-    flush.zero_()
+    if rot:
+        z = zs[i % 16]
+    elif "--readflush" in sys.argv:
+        flush.sum()  # evicts L2 by READING 256 MB: no dirty lines left behind
+    else:
+        flush.zero_()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     ops.nn_search(z, cb, lipvq.METRIC_L2, lipvq.ALGO_TCGEN05, out=idx, workspace=ws)
