@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 2
+#define LIPVQ_ABI_VERSION 3
 #define LIPVQ_API __attribute__((visibility("default")))
 
 enum {
@@ -158,9 +158,10 @@ LIPVQ_API int lipvq_codebook_usage_f32(const float* cluster_size, int K, float d
  * Replaces nn.Linear+nn.GELU chains (backbone_lfqvae_v5.py:54-68, 71, 75-76), nn.Linear+ReLU
  * (backbone.py:17-32), normalization()+LipschitzMLP.forward (backbone_lfqvae_v5.py:6-24).
  *
- * Activations are applied at the CONSUMER: a layer stores its pre-activation a = x W^T + b, the
- * next layer applies act_in while loading it.  One HBM write + one read per intermediate and
- * the backward pass has the pre-activations it needs without a second copy.
+ * A layer may apply an activation to its INPUT while loading it (act_in) and/or to its output in the epilogue
+ * (act_out).  The training step uses the producing side: lipvq_linear_fwd_dual_f32 stores act(pre) AND act'(pre) from
+ * one evaluation, every consumer then reads the stored values (act_in = NONE / LIPVQ_ACT_GIVEN).  The consumer side
+ * (act_in = GELU/RELU on a stored pre-activation) remains for stand-alone module calls.
  *
  *   fwd:   Y[n,o] = act_out( sum_i act_in(X[n,i]) * W[o,i] + bias[o] )           X:[N,in] W:[out,in]
  *   bwd_x: dX[n,i] = ( sum_o dY[n,o] * W[o,i] ) * act_in'(X[n,i])                 (gradient at X, the stored pre-activation)
@@ -269,6 +270,35 @@ LIPVQ_API int lipvq_allreduce_oneshot_ctas(void);
 LIPVQ_API size_t lipvq_allreduce_oneshot_flag_bytes(int world);
 LIPVQ_API int lipvq_allreduce_oneshot_f32(const uint64_t* peer_ptrs_dev, int rank, int world, int64_t n,
                                 int64_t flag_offset_bytes, float* out, uint32_t* cta_epoch, void* stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Callers and data formats either side of the tokenizer.
+ *
+ * Action-chunk input side.  Replaces, for demonstrations resident in HBM, the per-sample Python of
+ * SequenceDataset.get_item / get_sequence_from_demo (robomimic/utils/dataset.py:499-632): window of
+ * n_frame_stack-1 frames back and seq_length frames forward around index_in_demo, rows outside the demo
+ * repeated from its first / last frame ("pad_same"), optional (x - offset) / scale normalisation
+ * (obs_utils.normalize_dict, obs_utils.py:464-501).
+ *   data [L_total, A]: all demos back to back; demo_row0[d] = first row of demo d, demo_len[d] its length,
+ *   demo_seq0[d] = first sequence index of demo d in the dataset's index map (dataset.py:229-260);
+ *   sample_demo[b], sample_index[b]: the sampled sequences; out [B, T, A], T = n_frame_stack-1+seq_length;
+ *   pad_mask [B, T] uint8 (1 = real frame) or NULL; offset/scale [A] or both NULL.
+ * --------------------------------------------------------------------------------------------- */
+LIPVQ_API int lipvq_window_gather_f32(const float* data, const int64_t* demo_row0, const int32_t* demo_len,
+                                      const int64_t* demo_seq0, const int32_t* sample_demo, const int64_t* sample_index,
+                                      int64_t B, int A, int n_frame_stack, int seq_length, int pad_frame_stack,
+                                      const float* offset, const float* scale, float* out, uint8_t* pad_mask, void* stream);
+
+/* AdaptiveBinActionEmbedding (robomimic/models/bin_action/backbone.py:5-89): the A/B baseline tokenizer behind the same
+ * boundary (obs_nets.py:1214-1217, 1346).  fwd: optionally running_min/max <- min/max with the batch (:36-39), bin
+ * boundaries torch.linspace(min, max, num_bins+1) (:41-52), idx = clamp(bucketize(x) - 1, 0, num_bins-1) (:54-67),
+ * out[n, a*E:(a+1)*E] = tables[a][idx] (:80-86); idx_out [N, A] int64 or NULL.  bwd: dtables[a][idx[n,a]] += dout[n, a, :].
+ * tables [A][num_bins][E]. */
+LIPVQ_API int lipvq_bin_embed_fwd_f32(const float* actions, int64_t N, int A, int num_bins, int E, int update_stats,
+                                      float* running_min, float* running_max, const float* tables, float* out,
+                                      int64_t* idx_out, void* stream);
+LIPVQ_API int lipvq_bin_embed_bwd_f32(const float* dout, const int64_t* idx, int64_t N, int A, int num_bins, int E,
+                                      float* dtables, void* stream);
 
 #ifdef __cplusplus
 }

@@ -203,6 +203,136 @@ def gen_kmeans(hq, hv, tag):
     _save(tag, emb=emb, z=z, **t2, hq_codebook=q.codebook.data.clone(), hq_ema_codebook=q.ema_codebook.data.clone())
 
 
+def _stub_missing_packages():
+    """The reference's policy files import packages that are absent here (mamba_ssm, clip, h5py, matplotlib, ...) at
+    module level although the low-dim / vq_vae path never calls them: give them empty stand-ins so obs_nets.py and
+    policy_nets.py can be imported from /root/reference unmodified."""
+    import types
+
+    class _Any(types.ModuleType):
+        def __getattr__(self, k):
+            if k.startswith("__"):
+                raise AttributeError(k)
+            return object
+
+    for name in ("termcolor", "mamba_ssm", "clip", "h5py", "tensorboardX", "matplotlib", "matplotlib.pyplot", "matplotlib.cm",
+                 "imageio", "cv2"):
+        if name not in sys.modules:
+            try:
+                __import__(name)
+            except Exception:
+                sys.modules[name] = _Any(name)
+    sys.modules["termcolor"].colored = lambda s, *a, **k: s
+    if REF not in sys.path:
+        sys.path.insert(0, REF)
+
+
+ICRT_OBS = (("robot0_eef_pos", (3,)), ("robot0_eef_quat", (4,)), ("robot0_gripper_qpos", (2,)), ("lang_emb", (15,)))
+ICRT_KW = dict(ac_dim=12, transformer_embed_dim=64, transformer_num_layers=2, transformer_num_heads=4,
+               transformer_context_length=10, transformer_vq_vae_enabled=True, transformer_nn_parameter_for_timesteps=True,
+               num_modes=5, min_std=0.0001)
+
+
+def gen_icrt(tag):
+    """The tokenizer's caller run by the reference itself: ICLTransformerGMMActorNetwork (policy_nets.py:2375-2610) over
+    ICL_MIMO_Transformer / ICLObservationGroupEncoder / GPT_Backbone with the vq_vae action branch, low-dim observations,
+    eval mode (dropout off).  Saves weights, inputs, the tokenizer's output, GMM parameters, log-likelihood and the
+    gradients of the policy loss, plus AdaptiveBinActionEmbedding (bin_action/backbone.py) on the same actions."""
+    _stub_missing_packages()
+    from collections import OrderedDict
+    import robomimic.utils.obs_utils as ObsUtils
+    import robomimic.models.policy_nets as PN
+    from robomimic.models.bin_action.backbone import AdaptiveBinActionEmbedding
+    obs_shapes = OrderedDict(ICRT_OBS)
+    ObsUtils.initialize_obs_utils_with_obs_specs({"obs": {"low_dim": list(obs_shapes.keys())}})
+    enc_kwargs = {"low_dim": {"core_class": None, "core_kwargs": {}, "obs_randomizer_class": None, "obs_randomizer_kwargs": {}}}
+    torch.manual_seed(0)
+    net = PN.ICLTransformerGMMActorNetwork(obs_shapes=obs_shapes, encoder_kwargs=enc_kwargs, **ICRT_KW)
+    with torch.no_grad():
+        net.params["embed_timestep"].normal_(0, 0.02)  # zeros at init: give the parity test something to see
+    net.eval()
+    B, T = 3, 10
+    g = torch.Generator().manual_seed(1)
+    obs = {k: torch.randn(B, T, *s, generator=g) for k, s in obs_shapes.items()}
+    ctx = {k: torch.randn(B, T, *s, generator=g) for k, s in obs_shapes.items()}
+    ctx_actions = torch.rand(B, T, 12, generator=g) * 2 - 1
+    train_actions = torch.rand(B, T, 12, generator=g) * 2 - 1
+    sd = {k: v.clone() for k, v in net.state_dict().items()}
+    z_latent, _ = net.vq_vae_model(ctx_actions.reshape(B * T, 12))
+    dists = net.forward_train(obs_dict=obs, context_obs=ctx, actions=ctx_actions, low_noise_eval=False)
+    logp = dists.log_prob(train_actions)
+    action_loss = -logp.mean()
+    vq_loss = net._vq_vae_loss
+    net.zero_grad()
+    action_loss.backward()
+    keep = ("embed_encoder", "decoder.nets.mean", "transformer.0.nets.attention.nets.qkv", "embed_timestep", "output_ln",
+            "transformer.1.nets.mlp.2")
+    grads = {"grad." + k: p.grad.clone() for k, p in net.named_parameters() if p.grad is not None and any(t in k for t in keep)}
+    sd = {k: v for k, v in sd.items() if not k.startswith("vq_vae_model.")}  # alias of nets.encoder.action_network.*
+    base = dists.component_distribution.base_dist
+    torch.manual_seed(3)
+    bin_net = AdaptiveBinActionEmbedding(action_dim=12, output_dim=24, embedding_dim=8)
+    bin_sd = {k: v.clone() for k, v in bin_net.state_dict().items()}
+    a2 = ctx_actions.reshape(B * T, 12)
+    bin_out1 = bin_net(a2)
+    bin_out2 = bin_net(a2 * 0.5)  # second call: running min/max already set, narrower batch
+    bin_idx = bin_net.discretize(a2)
+    _save(tag, z_latent=z_latent, means=base.loc, scales=base.scale, logits=dists.mixture_distribution.logits, log_prob=logp,
+          action_loss=action_loss, vq_loss=vq_loss, ctx_actions=ctx_actions, train_actions=train_actions,
+          **{"obs." + k: v for k, v in obs.items()}, **{"ctx." + k: v for k, v in ctx.items()},
+          **{"sd." + k: v for k, v in sd.items()}, **grads, **{"bin_sd." + k: v for k, v in bin_sd.items()},
+          bin_out1=bin_out1, bin_out2=bin_out2, bin_idx=bin_idx,
+          **{"bin_post." + k: v.clone() for k, v in bin_net.state_dict().items()})
+
+
+def gen_dataset(tag):
+    """Action-chunk input side: the reference's own SequenceDataset.get_item (robomimic/utils/dataset.py:499-586) run on
+    in-memory demos.  The object is built without __init__ (which needs an HDF5 file and a language encoder); the index
+    map follows dataset.py:229-260; window, padding, pad mask and normalisation are the reference's code."""
+    _stub_missing_packages()
+    from collections import OrderedDict
+    import robomimic.utils.dataset as DS
+    rng = np.random.RandomState(0)
+    lens = [7, 23, 1, 12, 40]
+    demos = {f"demo_{i}": (rng.rand(L, 12).astype(np.float32) * 2 - 1) for i, L in enumerate(lens)}
+    stats = {"actions": {"offset": (rng.rand(1, 12).astype(np.float32) - 0.5), "scale": (rng.rand(1, 12).astype(np.float32) + 0.5)}}
+    out = {"lens": np.asarray(lens), **{"demo." + k: v for k, v in demos.items()},
+           "stats_offset": stats["actions"]["offset"], "stats_scale": stats["actions"]["scale"]}
+    cfgs = [(10, 1, True, True, False), (4, 3, True, True, True), (5, 2, True, False, False), (3, 2, False, True, True)]
+    for ci, (T, fs, pad_seq, pad_fs, norm) in enumerate(cfgs):
+        ds = DS.SequenceDataset.__new__(DS.SequenceDataset)
+        ds._hdf5_file = None
+        ds.seq_length, ds.n_frame_stack, ds.pad_seq_length, ds.pad_frame_stack = T, fs, pad_seq, pad_fs
+        ds.dataset_keys, ds.obs_keys, ds.action_keys = ("actions",), (), ("actions",)
+        ds.goal_mode, ds.load_next_obs, ds.get_pad_mask = None, False, True
+        ds.hdf5_cache_mode, ds.shuffled_obs_key_groups = None, []
+        ident = {"actions": {"offset": np.zeros((1, 12), np.float32), "scale": np.ones((1, 12), np.float32)}}
+        ds.action_normalization_stats = stats if norm else ident  # normalization=null in the shipped config -> identity stats
+        ds.get_action_normalization_stats = lambda ds=ds: ds.action_normalization_stats
+        ds._demo_id_to_demo_lang_emb = {}
+        ds.get_dataset_for_ep = lambda ep, key: demos[ep][:] if key == "actions" else None
+        ds._index_to_demo_id, ds._demo_id_to_start_indices, ds._demo_id_to_demo_length = {}, {}, {}
+        total = 0
+        for ep, L in zip(demos, lens):
+            n = L - (0 if pad_fs else fs - 1) - (0 if pad_seq else T - 1)
+            if pad_seq:
+                n = max(n, 1)
+            if n < 1 or (not pad_fs and L - (fs - 1) < 1):
+                continue  # the reference asserts here; such a demo cannot be in the dataset
+            ds._demo_id_to_start_indices[ep], ds._demo_id_to_demo_length[ep] = total, L
+            for _ in range(n):
+                ds._index_to_demo_id[total] = ep
+                total += 1
+        acts, masks = [], []
+        for index in range(total):
+            item = ds.get_item(index)
+            acts.append(np.asarray(item["actions"], dtype=np.float32))
+            masks.append(np.asarray(item["obs"]["pad_mask"])[:, 0])
+        out.update({f"c{ci}.cfg": np.asarray([T, fs, int(pad_seq), int(pad_fs), int(norm)]), f"c{ci}.actions": np.stack(acts),
+                    f"c{ci}.pad_mask": np.stack(masks), f"c{ci}.demos": np.asarray([int(e.split("_")[1]) for e in ds._demo_id_to_demo_length])})
+    _save(tag, **out)
+
+
 def main():
     v5 = _load("ref_v5", "robomimic/models/vq_vae/backbone_lfqvae_v5.py")
     hq = _load("ref_hq", "robomimic/models/vq_vae/hq_vae.py")
@@ -217,6 +347,8 @@ def main():
     gen_t2(hv, "t2_hvq", 7, 64, 64, 32, 2, 3, 4, 16)
     gen_t3_hier(hq, "t3_hier")
     gen_kmeans(hq, hv, "kmeans_init")
+    gen_icrt("icrt_policy")
+    gen_dataset("dataset_windows")
 
 
 if __name__ == "__main__":

@@ -490,3 +490,80 @@ def codebook_usage(cluster_size_z: torch.Tensor, cluster_size_q: torch.Tensor, t
             "q_utilization": float((cluster_size_q > 0).float().mean()),
             "q_used": q_used, "q_total": kq, "q_usage_pct": 100.0 * q_used / max(1, kq),
             "z_dead": int((cluster_size_z < thr_z).sum()), "q_dead": int((cluster_size_q < thr_q).sum())}
+
+
+# --------------------------------------------------------------------------------------
+# Callers / data formats either side of the path
+# --------------------------------------------------------------------------------------
+def sequence_index_map(lens, seq_length: int, frame_stack: int, pad_seq_length: bool, pad_frame_stack: bool):
+    """robomimic/utils/dataset.py:229-260: (demo_of_index, first_index_of_demo) for demos of the given lengths."""
+    index_to_demo, demo_seq0, total = [], [], 0
+    for d, L in enumerate(lens):
+        n = L - (0 if pad_frame_stack else frame_stack - 1) - (0 if pad_seq_length else seq_length - 1)
+        if pad_seq_length:
+            n = max(n, 1)
+        assert n >= 1
+        demo_seq0.append(total)
+        index_to_demo += [d] * n
+        total += n
+    return index_to_demo, demo_seq0
+
+
+def sequence_windows(demos, indices, seq_length: int, frame_stack: int, pad_seq_length: bool, pad_frame_stack: bool,
+                     offset=None, scale=None):
+    """dataset.py:499-632 for the action key: window [index_in_demo - (fs-1), index_in_demo + T) of the demo, rows outside
+    repeated from the first / last frame (TensorUtils.pad_sequence pad_same=True), pad mask, (x - offset) / scale."""
+    import numpy as np
+    lens = [len(d) for d in demos]
+    index_to_demo, demo_seq0 = sequence_index_map(lens, seq_length, frame_stack, pad_seq_length, pad_frame_stack)
+    acts, masks = [], []
+    for index in indices:
+        d = index_to_demo[index]
+        L = lens[d]
+        i = index - demo_seq0[d] + (0 if pad_frame_stack else frame_stack - 1)
+        lo, hi = max(0, i - (frame_stack - 1)), min(L, i + seq_length)
+        pad_b, pad_e = max(0, (frame_stack - 1) - i), max(0, i + seq_length - L)
+        seq = demos[d][lo:hi]
+        seq = np.concatenate([np.repeat(seq[:1], pad_b, 0), seq, np.repeat(seq[-1:], pad_e, 0)], 0)
+        if offset is not None:
+            seq = (seq - offset) / scale
+        acts.append(seq.astype(np.float32))
+        masks.append(np.array([0] * pad_b + [1] * (hi - lo) + [0] * pad_e, dtype=bool))
+    return np.stack(acts), np.stack(masks)
+
+
+def linspace_f32(lo: float, hi: float, steps: int):
+    """torch.linspace in fp32 (ATen RangeFactories, CPU): step = (hi-lo)/(steps-1) rounded to fp32; fma(step, i, start)
+    below the middle, fma(-step, steps-1-i, end) above (ONE rounding per element: the product is exact in double)."""
+    import numpy as np
+    lo, hi = np.float32(lo), np.float32(hi)
+    step = np.float32((hi - lo) / np.float32(steps - 1))
+    out = np.empty(steps, np.float32)
+    for i in range(steps):
+        out[i] = np.float32(float(lo) + float(step) * i) if i < steps // 2 else np.float32(float(hi) - float(step) * (steps - 1 - i))
+    return out
+
+
+def bin_discretize(actions: torch.Tensor, running_min: torch.Tensor, running_max: torch.Tensor, num_bins: int) -> torch.Tensor:
+    """robomimic/models/bin_action/backbone.py:41-67: clamp(bucketize(x, linspace(min, max, nb+1)) - 1, 0, nb-1)."""
+    cols = []
+    for a in range(actions.shape[1]):
+        b = torch.from_numpy(linspace_f32(float(running_min[a]), float(running_max[a]), num_bins + 1))
+        below = (b[None, :] < actions[:, a:a + 1]).sum(dim=1)  # bucketize(right=False)
+        cols.append(torch.clamp(below - 1, 0, num_bins - 1))
+    return torch.stack(cols, dim=1)
+
+
+def bin_embedding_forward(p: Params, actions: torch.Tensor, running_min: torch.Tensor, running_max: torch.Tensor,
+                          update: bool = True):
+    """AdaptiveBinActionEmbedding.forward (backbone.py:69-89) -> (out, indices, new running_min, new running_max)."""
+    if update:
+        running_min = torch.minimum(running_min, actions.min(dim=0)[0])
+        running_max = torch.maximum(running_max, actions.max(dim=0)[0])
+    A = actions.shape[1]
+    nb = p["embedding_layers.0.weight"].shape[0]
+    idx = bin_discretize(actions, running_min, running_max, nb)
+    emb = torch.cat([p[f"embedding_layers.{a}.weight"][idx[:, a]] for a in range(A)], dim=-1)
+    h = F.gelu(F.linear(emb, p["output_layer.0.weight"], p["output_layer.0.bias"]))
+    out = F.gelu(F.linear(h, p["output_layer.2.weight"], p["output_layer.2.bias"]))
+    return out, idx, running_min, running_max

@@ -10,7 +10,10 @@ from .modules import LFQQuantizer, LFQQuantizerEMA, LipschitzMLP, LLFQVAE_V4
 from .classic import VQVAE
 from .hvq import (ActionDecoder, ActionEncoder, DilatedTemporalConvLayer, HierarchicalVQVAE, MSTCNStage)
 from .hq import HierarchicalLFQHVQVAE, LFQQuantizerEMA_KMeans
+from .bin_action import AdaptiveBinActionEmbedding
+from .dataset import ActionSequenceDataset
+from . import icrt, icl_algo
 
 __all__ = ["ops", "LLFQVAE_V4", "LipschitzMLP", "LFQQuantizer", "LFQQuantizerEMA", "LFQQuantizerEMA_KMeans",
            "HierarchicalLFQHVQVAE", "VQVAE", "HierarchicalVQVAE", "ActionEncoder", "ActionDecoder", "MSTCNStage",
-           "DilatedTemporalConvLayer", "launch_count"]
+           "DilatedTemporalConvLayer", "AdaptiveBinActionEmbedding", "ActionSequenceDataset", "icrt", "icl_algo", "launch_count"]

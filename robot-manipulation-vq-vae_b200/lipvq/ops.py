@@ -342,3 +342,37 @@ def affine(x, a: float, b: float, out=None):
     y = out if out is not None else torch.empty_like(x)
     _call(lib.lipvq_affine_f32, "affine", _chk(x, F32, "x"), a, b, x.numel(), _chk(y, F32, "y"), _stream())
     return y
+
+
+def window_gather(data, demo_row0, demo_len, demo_seq0, sample_demo, sample_index, n_frame_stack: int, seq_length: int,
+                  pad_frame_stack: bool, offset=None, scale=None, want_mask: bool = False):
+    """[B, T, A] windows (+ [B, T] bool pad mask) of the HBM-resident demonstrations ``data`` [L_total, A]."""
+    B, A = sample_index.numel(), data.shape[1]
+    T = n_frame_stack - 1 + seq_length
+    out = torch.empty(B, T, A, dtype=F32, device=data.device)
+    mask = torch.empty(B, T, dtype=U8, device=data.device) if want_mask else None
+    _call(lib.lipvq_window_gather_f32, "window_gather", _chk(data, F32, "data"), _chk(demo_row0, I64, "demo_row0"),
+          _chk(demo_len, I32, "demo_len"), _chk(demo_seq0, I64, "demo_seq0"), _chk(sample_demo, I32, "sample_demo"),
+          _chk(sample_index, I64, "sample_index"), B, A, n_frame_stack, seq_length, int(pad_frame_stack),
+          _chk(offset, F32, "offset", True), _chk(scale, F32, "scale", True), _chk(out, F32, "out"), _chk(mask, U8, "mask", True),
+          _stream())
+    return (out, mask.bool()) if want_mask else out
+
+
+def bin_embed_fwd(actions, running_min, running_max, tables, update_stats: bool, want_idx: bool = True):
+    N, A = actions.shape
+    _, nb, E = tables.shape
+    out = torch.empty(N, A * E, dtype=F32, device=actions.device)
+    idx = torch.empty(N, A, dtype=I64, device=actions.device) if want_idx else None
+    _call(lib.lipvq_bin_embed_fwd_f32, "bin_embed_fwd", _chk(actions, F32, "actions"), N, A, nb, E, int(update_stats),
+          _chk(running_min, F32, "running_min"), _chk(running_max, F32, "running_max"), _chk(tables, F32, "tables"),
+          _chk(out, F32, "out"), _chk(idx, I64, "idx", True), _stream())
+    return out, idx
+
+
+def bin_embed_bwd(dout, idx, num_bins: int, E: int):
+    N, A = idx.shape
+    dt = torch.zeros(A, num_bins, E, dtype=F32, device=dout.device)
+    _call(lib.lipvq_bin_embed_bwd_f32, "bin_embed_bwd", _chk(dout, F32, "dout"), _chk(idx, I64, "idx"), N, A, num_bins, E,
+          _chk(dt, F32, "dtables"), _stream())
+    return dt

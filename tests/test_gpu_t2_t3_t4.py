@@ -264,7 +264,9 @@ def test_t3_hierarchical_lipschitz_vs_reference_fixture(L):
     post, sd = sub(g, "post"), m.state_dict()
     for pref in ("z_quantizer", "q_quantizer"):
         for k in ("ema_cluster_size", "ema_codebook", "usage_counts", "usage_ma", "entropy_ma"):
-            _close(sd[f"{pref}.{k}"], post[f"{pref}.{k}"], rtol=1e-5, atol=1e-6, what=f"{pref}.{k}")
+            # north_star gate: EMA buffers within 1e-4 relative after one step (q-level inputs passed through the GPU's
+            # own Lipschitz layer, so they carry its ~1e-6 fp32 noise)
+            _close(sd[f"{pref}.{k}"], post[f"{pref}.{k}"], rtol=1e-4, atol=1e-5, what=f"{pref}.{k}")
         _close(sd[f"{pref}.codebook"], post[f"{pref}.codebook"], rtol=1e-3, atol=1e-3, what=f"{pref}.codebook")
 
 
