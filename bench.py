@@ -109,8 +109,11 @@ def _cpu_step_fn(threads: int):
     return step
 
 
-def cpu_baseline(max_seconds: float = 25.0):
-    threads = os.cpu_count() or 1
+def cpu_baseline(max_seconds: float = 25.0, threads: int = 0, sample_chunks: int = 0):
+    global CPU_SAMPLE_CHUNKS
+    threads = threads or (os.cpu_count() or 1)
+    if sample_chunks:
+        CPU_SAMPLE_CHUNKS = sample_chunks
     step = _cpu_step_fn(threads)
     step()
     t0 = time.perf_counter()
@@ -119,9 +122,24 @@ def cpu_baseline(max_seconds: float = 25.0):
         step()
         n += 1
     dt = (time.perf_counter() - t0) / n
-    return {"value": CPU_SAMPLE_CHUNKS / dt, "unit": "chunks/s", "cores": threads, "kind": "port",
-            "sample": f"{n} training steps of {CPU_SAMPLE_CHUNKS} chunks ({CPU_SAMPLE_CHUNKS * T} tokens), same F/K/D, "
-                      f"oracle/lipvq_oracle.py (torch CPU restatement of the reference modules), {dt * 1e3:.0f} ms/step"}
+    out = {"value": CPU_SAMPLE_CHUNKS / dt, "unit": "chunks/s", "cores": threads, "kind": "port",
+           "sample": f"{n} training steps of {CPU_SAMPLE_CHUNKS} chunks ({CPU_SAMPLE_CHUNKS * T} tokens), same F/K/D, "
+                     f"oracle/lipvq_oracle.py (torch CPU restatement of the reference modules), {dt * 1e3:.0f} ms/step"}
+    torch.set_num_threads(os.cpu_count() or 1)
+    return out
+
+
+def cpu_cdist_argmin_us(N, K, D, rows=512, threads=0):
+    """The comparator BASELINE config 3 names: torch.cdist + argmin (heirarchical_vqvae.py:384,402,432) on the host cores,
+    on `rows` rows (row-chunked), scaled to N rows."""
+    torch.set_num_threads(threads or (os.cpu_count() or 1))
+    g = torch.Generator().manual_seed(0)
+    z, cb = torch.rand(rows, D, generator=g), (torch.rand(K, D, generator=g) * 2 - 1) * (6.0 / D) ** 0.5
+    torch.cdist(z[:64], cb).argmin(dim=1)
+    t0 = time.perf_counter()
+    for s0 in range(0, rows, 128):
+        torch.cdist(z[s0:s0 + 128], cb).argmin(dim=1)
+    return (time.perf_counter() - t0) * 1e6 * (N / rows)
 
 
 def run_reference(args):
@@ -151,6 +169,60 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------------
 # GPU arm
 # ----------------------------------------------------------------------------------------------
+def _sync_all(world):
+    import torch.distributed as dist
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def _time_events(fn, iters, flush=None):
+    """mean / min duration in us of fn() on the current stream, L2 flushed (written) between iterations"""
+    durs = []
+    for i in range(iters + 3):
+        if flush is not None:
+            flush.zero_()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        if i >= 3:
+            durs.append(a.elapsed_time(b) * 1e3)
+    return statistics.mean(durs), min(durs)
+
+
+def search_sweep(dev, hbm, tf_burst, flush, cpu_rows=256):
+    """BASELINE config 3: K in {512, 4096, 65536} x D in {64, 256}, N = 65536, raw latents z ~ U(0,1), with the
+    two baselines the config names: torch.cdist + argmin on the host cores and eager on the same B200."""
+    import lipvq
+    from lipvq import ops
+    out = []
+    N = N_TOK
+    for K, D in ((512, 64), (4096, 64), (65536, 64), (512, 256), (4096, 256), (65536, 256)):
+        g = torch.Generator().manual_seed(5 + K + D)
+        z = torch.rand(N, D, generator=g).to(dev)
+        cb = ((torch.rand(K, D, generator=g) * 2 - 1) * (6.0 / D) ** 0.5).to(dev)
+        algo = lipvq.ALGO_TCGEN05
+        ws = torch.empty(ops.search_workspace_bytes(N, D, K, lipvq.METRIC_L2, algo), dtype=torch.uint8, device=dev)
+        idx = torch.empty(N, dtype=torch.int64, device=dev)
+        iters = 3 if K * D >= 65536 * 64 else 8
+        us, mn = _time_events(lambda: ops.nn_search(z, cb, lipvq.METRIC_L2, algo, out=idx, workspace=ws), iters, flush)
+        _, st = ops.nn_search(z, cb, lipvq.METRIC_L2, algo, want_stats=True, workspace=ws)
+        eager_us, _ = _time_events(lambda: torch.cdist(z, cb).argmin(dim=1), 2 if K >= 65536 else 4, flush)
+        ref_idx = torch.cdist(z[:2048], cb, compute_mode="donot_use_mm_for_euclid_dist").argmin(dim=1)
+        flops = 2.0 * N * K * D
+        out.append({"N": N, "K": K, "D": D, "latents": "uniform", "us": round(us, 1), "min_us": round(mn, 1),
+                    "tflops": round(flops / us / 1e6, 1), "frac_tensor": round(flops / us / 1e6 / tf_burst, 4),
+                    "frac_hbm": round((N * (4 * D + 8) + K * D * 4) / us / 1e3 / hbm, 4),
+                    "rows_uncertified_by_fp16_pass": int(st[1]), "rows_exact_scan": int(st[0]),
+                    "index_mismatch_vs_eager_direct_2048": int((idx[:2048] != ref_idx).sum()),
+                    "baseline_gpu_eager_us": round(eager_us, 1),
+                    "baseline_cpu_us": round(cpu_cdist_argmin_us(N, K, D, rows=cpu_rows if K < 65536 else 64), 0)})
+        del z, cb, ws, idx
+    return out
+
+
 def run_ours(args):
     import torch.distributed as dist
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -160,6 +232,7 @@ def run_ours(args):
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback (use --impl reference for the CPU leg)")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    extra = {}
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     import lipvq
@@ -175,11 +248,6 @@ def run_ours(args):
     xs_host = [_synthetic_actions(N_TOK, 1000 + 17 * rank + i).pin_memory() for i in range(n_in)]
     xs_dev = [x.to(dev) for x in xs_host]
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
     # launches per step, counted on one eager (un-captured) step: graph replays do not pass through the C ABI
     snap = tr._snapshot()
     tr.use_graph = False
@@ -190,26 +258,46 @@ def run_ours(args):
     tr._restore(snap)
     tr.use_graph = True
 
+    # data-parallel self-check (the driver's test box has one GPU): the peer all-reduce against NCCL on the same slab,
+    # and bit-identical replicas after a few steps
+    collective_check = None
+    if world > 1:
+        for i in range(2):
+            tr.step(xs_dev[i % n_in])
+        torch.cuda.synchronize()
+        ok_sum = True
+        if tr.peer is not None:  # our kernel's sum vs NCCL's on the same slab (with NCCL itself there is nothing to compare)
+            ref = tr.red.detach().clone()
+            dist.all_reduce(ref, op=dist.ReduceOp.SUM)
+            ok_sum = bool(torch.allclose(tr.red_out.detach(), ref, rtol=1e-5, atol=1e-6))
+        flat = tr.flat_p.detach()
+        gathered = [torch.empty_like(flat) for _ in range(world)]
+        dist.all_gather(gathered, flat)
+        ok_rep = all(torch.equal(gathered[0], t) for t in gathered)
+        flag = torch.tensor([int(ok_sum and ok_rep)], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        collective_check = "ok" if int(flag) == 1 else f"FAILED (sum {ok_sum}, replicas {ok_rep})"
+
     for i in range(max(args.warmup, 3)):
         tr.step(xs_dev[i % n_in])
-    barrier()
+    _sync_all(world)
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
+    _sync_all(world)
     e0.record()
     for i in range(args.steps):
         tr.step(xs_dev[i % n_in])
     e1.record()
-    barrier()
+    _sync_all(world)
     ms = e0.elapsed_time(e1)
     loss_final = float(tr.losses_red[0].item()) / world
 
     # e2e: public API, pinned-host inputs, loss read back every step
     for i in range(3):
         tr.step(xs_host[i % n_in], prefetch=xs_host[(i + 1) % n_in]); tr.losses_red.cpu()
-    barrier()
+    _sync_all(world)
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     for i in range(args.steps):
@@ -218,90 +306,284 @@ def run_ours(args):
         tr.step(xs_host[i % n_in], prefetch=xs_host[(i + 1) % n_in])
         _ = tr.losses_red.cpu()
     e3.record()
-    barrier()
+    _sync_all(world)
     ms_e2e = e2.elapsed_time(e3)
+
+    # bulk tokenisation (encode + VQ), the metric's literal reading, on EVERY rank (the dataset shards over ranks, no
+    # collective): resident inputs, and end to end = pinned-host actions in, int64 indices back to pinned host memory
+    idx_host = torch.empty(N_TOK, dtype=torch.int64).pin_memory()
+    for i in range(3):
+        tr.tokenize(xs_dev[i % n_in])
+    _sync_all(world)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for i in range(args.steps):
+        tr.tokenize(xs_dev[i % n_in])
+    t1.record()
+    _sync_all(world)
+    ms_tok = t0.elapsed_time(t1)
+    for i in range(2):
+        idx_host.copy_(tr.tokenize(xs_host[i % n_in]), non_blocking=True)
+    _sync_all(world)
+    t2, t3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t2.record()
+    for i in range(args.steps):
+        idx_host.copy_(tr.tokenize(xs_host[i % n_in]), non_blocking=True)
+    t3.record()
+    _sync_all(world)
+    ms_tok_e2e = t2.elapsed_time(t3)
     clocks = sampler.stop() if rank == 0 else None
 
-    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    t = torch.tensor([ms, ms_e2e, ms_tok, ms_tok_e2e], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = float(t[0]), float(t[1])
+    ms, ms_e2e, ms_tok, ms_tok_e2e = (float(v) for v in t)
 
-    extra = {}
     if rank == 0:
         hbm, tf_burst, tf_sus, src = _peaks()
-        # --- dominant kernel: the fused distance+argmin search, timed alone on the step's own z_e / codebook ---
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+        # --- dominant kernel of the headline target: the fused distance+argmin search, timed alone on the step's own
+        #     z_e / codebook, L2 flushed (written) before every call ---
         z_e, cb = tr.bufs.t["z_e"], tr.p["quantizer.codebook"]
         algo = ops.pick_algo(N_TOK, D, K)
-        flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-        durs = []
-        for i in range(25):
-            flush.zero_()
-            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            a.record()
-            ops.nn_search(z_e, cb, lipvq.METRIC_L2, algo, out=tr.bufs.t["idx"], workspace=tr.bufs.t["ws"])
-            b.record()
-            torch.cuda.synchronize()
-            if i >= 5:
-                durs.append(a.elapsed_time(b))
-        sd = statistics.mean(durs)
+        sd, sd_min = _time_events(lambda: ops.nn_search(z_e, cb, lipvq.METRIC_L2, algo, out=tr.bufs.t["idx"],
+                                                        workspace=tr.bufs.t["ws"]), 20, flush)
         _, st = ops.nn_search(z_e, cb, lipvq.METRIC_L2, algo, want_stats=True, workspace=tr.bufs.t["ws"])
-        rescored = int(st[0].item())
         flops = 2.0 * N_TOK * K * D
         bytes_alg = N_TOK * (4 * D + 8) + K * D * 4
-        # DRAM bytes of the dominant launch (search_fused_kernel<1>) from the committed ncu --set full capture
         traffic = None
         try:
             with open(os.path.join(ROOT, "profiles", "search_traffic.json")) as f:
                 traffic = json.load(f).get("dram_bytes_per_launch")
         except Exception:
             pass
-        extra["roofline"] = {"bound": "tensor", "kernel": "lipvq_nn_search_f32 = fused_prep + search_fused<1> (fp16 tcgen05 pass, "
-                             "argmin + certification in the TMEM epilogue) + search_fused<3> (3-term pass over uncertified "
-                             "rows) + exact scan; algo=" + {1: "simt_f32", 2: "tcgen05"}[algo],
-                             "achieved": flops / (sd * 1e-3) / 1e12, "peak": tf_burst,
-                             "unit": "TFLOP/s", "frac": flops / (sd * 1e-3) / 1e12 / tf_burst, "traffic": traffic,
-                             "peak_source": src + " (bf16 dense burst)", "us_per_launch": sd * 1e3,
+        step_us = ms / args.steps * 1e3
+        extra["roofline"] = {"bound": "tensor", "kernel": "lipvq_nn_search_f32 = search_p1_kernel (one launch: cooperative codebook "
+                             "preparation + fp16 tcgen05 pass, best-only fold + exact near-best mask, certification) + "
+                             "search_fused<3> / exact scan (both empty unless rows stay uncertified); algo="
+                             + {1: "simt_f32", 2: "tcgen05"}[algo],
+                             "achieved": flops / sd / 1e6, "peak": tf_burst, "unit": "TFLOP/s",
+                             "frac": flops / sd / 1e6 / tf_burst, "traffic": traffic,
+                             "peak_source": src + " (bf16 dense burst)", "us_per_launch": sd, "us_per_launch_min": sd_min,
                              "algorithmic_flops": flops, "algorithmic_bytes": bytes_alg,
-                             "hbm_frac": bytes_alg / (sd * 1e-3) / 1e9 / hbm,
-                             "share_of_step": sd / (ms / args.steps),
-                             "rows_rescored_exactly": rescored, "rows_uncertified_by_fp16_pass": int(st[1].item())}
-        # --- bulk tokenisation (encode + VQ only), the headline metric's other reading ---
-        for i in range(3):
-            tr.tokenize(xs_dev[i % n_in])
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
-        a.record()
-        for i in range(args.steps):
-            tr.tokenize(xs_dev[i % n_in])
-        b.record()
-        torch.cuda.synchronize()
-        extra["tokenize_only"] = {"value": CHUNKS * args.steps / (a.elapsed_time(b) * 1e-3), "unit": "chunks/s",
-                                  "note": "encode+VQ forward only, 1 GPU, inputs resident"}
-        if not args.no_cpu_baseline:
-            extra["cpu_baseline"] = cpu_baseline()
+                             "hbm_frac": bytes_alg / sd / 1e3 / hbm, "share_of_step": sd / step_us,
+                             "rows_rescored_exactly": int(st[0]), "rows_uncertified_by_fp16_pass": int(st[1]),
+                             "l2": "flushed by writing 256 MB before every call"}
+        # --- the step-dominant kernel: the tensor-core linear layer (11 forward / dX launches + 6 dW launches per step).
+        #     Representative launch: encoder.2 (64 -> 128, GELU + derivative), HBM-bound by bytes ---
+        a1, a2, da2 = tr.bufs.t["a1"], tr.bufs.t["a2"], tr.bufs.t["da2_act"]
+        W, b = tr.p["encoder.2.weight"], tr.p["encoder.2.bias"]
+        lu, lu_min = _time_events(lambda: ops.linear_fwd_dual(a1, lipvq.ACT_NONE, W, b, lipvq.ACT_GELU, a2, da2), 20, flush)
+        lbytes = N_TOK * (64 + 128 + 128) * 4 + W.numel() * 4
+        extra["roofline_step"] = {"bound": "hbm", "kernel": "linear_tc_kernel (lipvq_linear_fwd_dual_f32, 64 -> 128, GELU and its "
+                                  "derivative in the epilogue)", "achieved": lbytes / lu / 1e3, "peak": hbm, "unit": "GB/s",
+                                  "frac": lbytes / lu / 1e3 / hbm, "traffic": None, "us_per_launch": lu, "us_per_launch_min": lu_min,
+                                  "algorithmic_bytes": lbytes, "peak_source": src + " (copy bandwidth)",
+                                  "launches_of_this_family_per_step": 17}
+        if not args.no_sweep:
+            extra["sweep"] = search_sweep(dev, hbm, tf_burst, flush)
+        del flush
 
     if world > 1:
         dist.barrier()
     if rank == 0:
-        line = {"metric": "action_chunks_per_sec", "value": world * CHUNKS * args.steps / (ms * 1e-3), "unit": "chunks/s",
+        chunks = world * CHUNKS * args.steps
+        line = {"metric": "action_chunks_per_sec", "value": chunks / (ms * 1e-3), "unit": "chunks/s",
                 "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
                 "config": {"workload": WORKLOAD, "tokens_per_gpu": N_TOK, "parallelism": f"dp{world}",
                            "l2": "per-step working set (activations+gradients ~0.3 GB) exceeds the 126 MB L2; "
-                                 "4 input batches rotate", "cuda_graph": True, "final_loss": loss_final},
-                "e2e": {"value": world * CHUNKS * args.steps / (ms_e2e * 1e-3), "unit": "chunks/s",
+                                 "4 input batches rotate", "cuda_graph": True, "final_loss": loss_final,
+                           "collective": tr.collective, "collective_check": collective_check},
+                "e2e": {"value": chunks / (ms_e2e * 1e-3), "unit": "chunks/s",
                         "h2d_bytes_per_step": N_TOK * F_ * 4, "d2h_bytes_per_step": 16},
+                "tokenize": {"value": chunks / (ms_tok * 1e-3), "unit": "chunks/s", "ms_per_step": ms_tok / args.steps,
+                             "note": "encode+VQ only (the metric's literal reading), every rank on its own shard, inputs resident"},
+                "tokenize_e2e": {"value": chunks / (ms_tok_e2e * 1e-3), "unit": "chunks/s", "ms_per_step": ms_tok_e2e / args.steps,
+                                 "h2d_bytes_per_step": N_TOK * F_ * 4, "d2h_bytes_per_step": N_TOK * 8,
+                                 "note": "TokenizerTrainer.tokenize(pinned host actions) -> int64 indices copied back to pinned "
+                                         "host memory, every step, every rank"},
                 "gpu_launches": int(launches_per_step) * args.steps, "clocks": clocks}
         line.update(extra)
+    _teardown(tr, world)
+    if rank == 0:
+        # The timed CPU legs run on rank 0 AFTER the process group is gone and the other ranks have left: no GPU sits in a
+        # device-side barrier while the host cores work (round 1 kept seven B200s spinning for half a minute here).
+        if not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline()
+            line["cpu_baseline_1thread"] = cpu_baseline(max_seconds=12.0, threads=1, sample_chunks=128)
+        print(json.dumps(line), flush=True)
+
+
+def _teardown(tr, world):
+    """Release the captured graphs BEFORE the communicator (NCCL's destructor can block while a live graph still holds
+    its kernels), then destroy the group.  The destroy runs in a helper thread with a deadline: ranks > 0 leave if it does
+    not finish, rank 0 carries on (it still has the CPU legs to time and the line to print)."""
+    import gc
+    import torch.distributed as dist
+    if world <= 1:
+        return
+    sys.stdout.flush()
+    torch.cuda.synchronize()
+    dist.barrier()
+    for name in ("_graph_full", "_graph_a", "_graph_b", "_graph_tok"):
+        setattr(tr, name, None)
+    gc.collect()
+    torch.cuda.synchronize()
+    th = threading.Thread(target=dist.destroy_process_group, daemon=True)
+    th.start()
+    th.join(30.0)
+    if th.is_alive() and int(os.environ.get("RANK", "0")) != 0:
+        os._exit(0)
+
+
+# ----------------------------------------------------------------------------------------------
+# BASELINE config 5: ICRT + LipVQ-VAE in-context policy training step (bf16 transformer, random-init weights, synthetic
+# multi-trajectory prompts).  Shipped shapes: B = 16 prompt + 16 query trajectories, T = 10, observation width 208,
+# A = 12, embed 512, 6 layers, 8 heads, 5-mode GMM (config/icl_config.py:118-135, train_config.json).
+# ----------------------------------------------------------------------------------------------
+C5 = dict(B=16, T=10, A=12, embed=512, layers=6, heads=8)
+C5_OBS = (("robot0_eef_pos", (3,)), ("robot0_eef_quat", (4,)), ("robot0_gripper_qpos", (2,)), ("lang_emb", (199,)))
+C5_WORKLOAD = ("ICRT in-context policy training step with the LipVQ-VAE tokenizer (T1 protocol: tokenizer AdamW step, then "
+               "policy Adam step, clip 100), 16 prompt + 16 query trajectories x T=10 per GPU, obs width 208, A=12, "
+               "GPT 6 x 512 x 8 heads, 5-mode GMM")
+
+
+def _c5_batch(seed, device=None, pin=False):
+    from collections import OrderedDict
+    g = torch.Generator().manual_seed(seed)
+    B2, T_, A_ = 2 * C5["B"], C5["T"], C5["A"]
+    obs = OrderedDict((k, torch.randn(B2, T_, *s, generator=g)) for k, s in C5_OBS)
+    act = torch.rand(B2, T_, A_, generator=g) * 2 - 1
+    if pin:
+        obs = OrderedDict((k, v.pin_memory()) for k, v in obs.items())
+        act = act.pin_memory()
+    if device is not None:
+        obs = OrderedDict((k, v.to(device)) for k, v in obs.items())
+        act = act.to(device)
+    return {"obs": obs, "actions": act}
+
+
+def _c5_policy(factory=None, dropout=0.1):
+    from collections import OrderedDict
+    from lipvq import icrt
+    return icrt.ICLTransformerGMMActorNetwork(
+        obs_shapes=OrderedDict(C5_OBS), ac_dim=C5["A"], transformer_embed_dim=C5["embed"], transformer_num_layers=C5["layers"],
+        transformer_num_heads=C5["heads"], transformer_context_length=C5["T"], transformer_vq_vae_enabled=True,
+        transformer_nn_parameter_for_timesteps=True, num_modes=5, min_std=0.0001, transformer_emb_dropout=dropout,
+        transformer_attn_dropout=dropout, transformer_block_output_dropout=dropout, action_network_factory=factory)
+
+
+def run_c5(args):
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (use --impl reference for the CPU leg)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    import lipvq
+    from lipvq import icl_algo
+    torch.manual_seed(0)
+    policy = _c5_policy().to(dev).train()
+    algo = icl_algo.ICLTransformerGMM(policy, bf16=True)
+    hosts = [_c5_batch(100 + 7 * rank + i, pin=True) for i in range(4)]
+    devs = [{"obs": {k: v.to(dev) for k, v in b["obs"].items()}, "actions": b["actions"].to(dev)} for b in hosts]
+    c0 = lipvq.launch_count()
+    for i in range(max(args.warmup, 3)):
+        algo.train_on_batch(devs[i % 4])
+    torch.cuda.synchronize()
+    launches_per_step = (lipvq.launch_count() - c0) // max(args.warmup, 3)
+    _sync_all(world)
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        info = algo.train_on_batch(devs[i % 4])
+    e1.record()
+    _sync_all(world)
+    ms = e0.elapsed_time(e1)
+    # e2e: pinned-host prompts in (H2D inside), the two losses read back, every step
+    to_dev = lambda b: {"obs": {k: v.to(dev, non_blocking=True) for k, v in b["obs"].items()},
+                        "actions": b["actions"].to(dev, non_blocking=True)}
+    e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e2.record()
+    for i in range(args.steps):
+        info = algo.train_on_batch(to_dev(hosts[i % 4]))
+        _ = (float(info["action_loss"]), float(info["vq_vae_loss"]))
+    e3.record()
+    _sync_all(world)
+    ms_e2e = e2.elapsed_time(e3)
+    # share of the step inside the tokenizer: its forward + backward + AdamW alone on the same prompt actions
+    tok = policy.vq_vae_model
+    opt = torch.optim.AdamW(tok.parameters(), lr=1e-3, weight_decay=1e-4)
+    pa = devs[0]["actions"][:C5["B"]].reshape(-1, C5["A"]).contiguous()
+    for _ in range(3):
+        opt.zero_grad(); tok(pa)[1].backward(); opt.step()
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(args.steps):
+        opt.zero_grad(); tok(pa)[1].backward(); opt.step()
+    t1.record()
+    torch.cuda.synchronize()
+    ms_tok = t0.elapsed_time(t1)
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([ms, ms_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(t[0]), float(t[1])
+    if rank == 0:
+        bytes_in = sum(v.numel() * 4 for v in hosts[0]["obs"].values()) + hosts[0]["actions"].numel() * 4
+        n_par = sum(p.numel() for p in policy.parameters())
+        line = {"metric": "policy_training_steps_per_sec", "value": world * args.steps / (ms * 1e-3) / world, "unit": "steps/s",
+                "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+                "config": {"workload": C5_WORKLOAD, "parallelism": f"dp{world}", "parameters": n_par,
+                           "trajectories_per_sec": world * 2 * C5["B"] * args.steps / (ms * 1e-3),
+                           "tokenizer": "lipvq.LLFQVAE_V4 (fp32 CUDA kernels; K=1024, D=208)", "transformer": "torch bf16 autocast + SDPA",
+                           "l2": "4 prompt batches rotate; launch-bound at this size", "final_action_loss": float(info["action_loss"])},
+                "e2e": {"value": args.steps / (ms_e2e * 1e-3), "unit": "steps/s", "h2d_bytes_per_step": bytes_in, "d2h_bytes_per_step": 8},
+                "tokenizer_share_of_step": ms_tok / ms, "tokenizer_ms_per_step": ms_tok / args.steps,
+                "gpu_launches": int(launches_per_step) * args.steps, "clocks": clocks}
         print(json.dumps(line), flush=True)
     if world > 1:
-        # Tear down without NCCL's own destructor: a communicator whose kernels were captured into a live CUDA graph
-        # can block in destroy_process_group; the line is printed, every rank is idle, so leave directly.
         sys.stdout.flush()
         torch.cuda.synchronize()
         dist.barrier()
-        os._exit(0)
+        dist.destroy_process_group()
+
+
+def run_reference_c5(args):
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    sys.path.insert(0, os.path.join(ROOT, "oracle"))
+    import lipvq_oracle as O
+    from lipvq import icl_algo  # pure torch (no kernel is touched on this arm: the tokenizer slot holds the oracle)
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    torch.manual_seed(0)
+    policy = _c5_policy(factory=lambda a, d: O.T1Module(a, d)).train()
+    algo = icl_algo.ICLTransformerGMM(policy, bf16=False)
+    batches = [_c5_batch(100 + i) for i in range(2)]
+    for i in range(max(1, min(args.warmup, 2))):
+        algo.train_on_batch(batches[i % 2])
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        algo.train_on_batch(batches[i % 2])
+    dt = (time.perf_counter() - t0) / args.steps
+    line = {"impl": "reference", "metric": "policy_training_steps_per_sec", "value": 1.0 / dt, "unit": "steps/s",
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": {"workload": C5_WORKLOAD},
+            "cpu_baseline": {"value": 1.0 / dt, "unit": "steps/s", "cores": threads, "kind": "port",
+                             "sample": "the same step on the host cores: restated ICRT policy (torch fp32) with the oracle "
+                                       "tokenizer in the action_network slot"},
+            "e2e": {"value": 1.0 / dt, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
 
 
 def main():
@@ -311,11 +593,14 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the timed CPU leg (profiling runs only)")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the codebook-size sweep (BASELINE config 3) in the line")
+    ap.add_argument("--config", default="c2", choices=["c2", "c5"],
+                    help="c2: tokenizer training step (default, the headline); c5: ICRT+LipVQ-VAE policy training step")
     args = ap.parse_args()
     if args.impl == "reference":
-        run_reference(args)
+        run_reference_c5(args) if args.config == "c5" else run_reference(args)
     else:
-        run_ours(args)
+        run_c5(args) if args.config == "c5" else run_ours(args)
 
 
 if __name__ == "__main__":

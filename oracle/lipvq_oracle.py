@@ -567,3 +567,27 @@ def bin_embedding_forward(p: Params, actions: torch.Tensor, running_min: torch.T
     h = F.gelu(F.linear(emb, p["output_layer.0.weight"], p["output_layer.0.bias"]))
     out = F.gelu(F.linear(h, p["output_layer.2.weight"], p["output_layer.2.bias"]))
     return out, idx, running_min, running_max
+
+
+
+class T1Module(torch.nn.Module):
+    """LLFQVAE_V4's parameter tree (backbone_lfqvae_v5.py:52-68) with this oracle's forward: the CPU stand-in for the
+    tokenizer inside the restated ICRT policy (tests/test_icrt_cpu.py, bench.py --impl reference --config c5)."""
+
+    def __init__(self, feature_dim, latent_dim, num_codes=1024, hidden_dim=128):
+        super().__init__()
+        nn = torch.nn
+        self.encoder = nn.Sequential(nn.Linear(feature_dim, 64), nn.GELU(), nn.Linear(64, hidden_dim), nn.GELU())
+        self.to_latent = nn.Module()
+        self.to_latent.W = nn.Parameter(torch.randn(latent_dim, hidden_dim))
+        self.to_latent.b = nn.Parameter(torch.zeros(latent_dim))
+        self.to_latent.ci = nn.Parameter(torch.ones(latent_dim))
+        self.quantizer = nn.Module()
+        self.quantizer.codebook = nn.Parameter(torch.randn(num_codes, latent_dim))
+        nn.init.kaiming_uniform_(self.quantizer.codebook)
+        self.decoder = nn.Sequential(nn.Linear(latent_dim, 64), nn.GELU(), nn.Linear(64, hidden_dim), nn.GELU())
+        self.to_output = nn.Linear(hidden_dim, feature_dim)
+
+    def forward(self, x):
+        out = t1_forward(dict(self.named_parameters()), x)
+        return out["z_latent"], out["loss"]

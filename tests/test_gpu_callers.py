@@ -59,7 +59,7 @@ def test_bin_action_embedding_vs_reference_fixture():
     m._update_enabled = False
     m.zero_grad()
     m(a).square().sum().backward()
-    p = {k: v.clone().requires_grad_(True) for k, v in m.state_dict().items() if k not in ("running_min", "running_max")}
+    p = {k: v.detach().cpu().clone().requires_grad_(True) for k, v in m.state_dict().items() if k not in ("running_min", "running_max")}
     ref, _, _, _ = O.bin_embedding_forward(p, a.cpu(), m.running_min.cpu(), m.running_max.cpu(), update=False)
     ref.square().sum().backward()
     for k, v in m.named_parameters():

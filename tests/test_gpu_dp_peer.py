@@ -17,3 +17,26 @@ def test_peer_allreduce_matches_nccl_two_ranks():
            "--master-port", "29541", os.path.join(ROOT, "tests", "dp_peer_worker.py")]
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "PEER_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-4000:]
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_module_on_second_device_with_current_device_zero():
+    """The reference's nn.Modules work on any device after .to(): so must these -- kernels, streams and the per-device
+    caches (SM count, shared-memory opt-in) follow the TENSORS' device, not torch's current device."""
+    import lipvq as L
+    import lipvq_oracle as O
+    torch.cuda.set_device(0)
+    torch.manual_seed(0)
+    m = L.LLFQVAE_V4(12, 64, 512)
+    p = {k: v.clone() for k, v in m.state_dict().items()}
+    x = torch.rand(8192, 12, generator=torch.Generator().manual_seed(1)) * 2 - 1
+    m.to("cuda:1")
+    z, loss = m(x.to("cuda:1"))
+    loss.backward()
+    assert z.device == torch.device("cuda:1") and torch.cuda.current_device() == 0
+    ref = O.t1_forward(p, x, row_chunk=1024)
+    assert abs(loss.item() - ref["loss"].item()) <= 1e-4 * abs(ref["loss"].item())
+    assert (m.last_indices.cpu() != ref["indices"]).sum().item() <= 4
+    with pytest.raises(RuntimeError, match="one device"):
+        L.ops.nn_search(torch.rand(64, 8, device="cuda:0"), torch.rand(16, 8, device="cuda:1"))

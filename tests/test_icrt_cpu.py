@@ -16,24 +16,7 @@ KW = dict(ac_dim=12, transformer_embed_dim=64, transformer_num_layers=2, transfo
           transformer_vq_vae_enabled=True, transformer_nn_parameter_for_timesteps=True, num_modes=5, min_std=0.0001)
 
 
-class OracleTokenizer(nn.Module):
-    """LLFQVAE_V4's parameter tree (backbone_lfqvae_v5.py:52-68) with the oracle's forward."""
-
-    def __init__(self, feature_dim, latent_dim, num_codes=1024, hidden_dim=128):
-        super().__init__()
-        self.encoder = nn.Sequential(nn.Linear(feature_dim, 64), nn.GELU(), nn.Linear(64, hidden_dim), nn.GELU())
-        self.to_latent = nn.Module()
-        self.to_latent.W = nn.Parameter(torch.randn(latent_dim, hidden_dim))
-        self.to_latent.b = nn.Parameter(torch.zeros(latent_dim))
-        self.to_latent.ci = nn.Parameter(torch.ones(latent_dim))
-        self.quantizer = nn.Module()
-        self.quantizer.codebook = nn.Parameter(torch.randn(num_codes, latent_dim))
-        self.decoder = nn.Sequential(nn.Linear(latent_dim, 64), nn.GELU(), nn.Linear(64, hidden_dim), nn.GELU())
-        self.to_output = nn.Linear(hidden_dim, feature_dim)
-
-    def forward(self, x):
-        out = O.t1_forward(dict(self.named_parameters()), x)
-        return out["z_latent"], out["loss"]
+OracleTokenizer = O.T1Module
 
 
 def _build():
