@@ -410,6 +410,7 @@ def run_ours(args):
         # The timed CPU legs run on rank 0 AFTER the process group is gone and the other ranks have left: no GPU sits in a
         # device-side barrier while the host cores work (round 1 kept seven B200s spinning for half a minute here).
         if not args.no_cpu_baseline:
+            print("[bench] GPU section done; timing the CPU legs on rank 0", file=sys.stderr, flush=True)
             line["cpu_baseline"] = cpu_baseline()
             line["cpu_baseline_1thread"] = cpu_baseline(max_seconds=12.0, threads=1, sample_chunks=128)
         print(json.dumps(line), flush=True)

@@ -107,6 +107,28 @@ __device__ __forceinline__ float act_grad(int act, float x) {
   }
 }
 
+// GELU (erf form, nn.GELU() default) and its derivative from ONE short evaluation, for the tensor-core epilogues, where the
+// library erff + expf (~77 instructions per element for value and derivative) was the bound of the whole layer:
+//   erf(t) = sign(t) (1 - P(k) exp(-t^2)),  k = 1 / (1 + 0.3275911 |t|),  P degree 5 (Abramowitz & Stegun 7.1.26,
+//   |error| <= 1.5e-7 absolute), exp through ex2.approx.  exp(-t^2) = exp(-x^2/2) is also the Gaussian density the
+//   derivative needs.  ~18 instructions.  Absolute error of value and derivative <= 2e-7 (|x| + 1), far inside the
+//   1e-4 relative parity gate on losses / reconstructions (tests compare against the reference's exact erf).
+__device__ __forceinline__ void gelu_value_grad_fast(float x, float& val, float& grad) {
+  const float t = x * 0.70710678118654752440f;
+  const float a = fabsf(t);
+  const float k = __frcp_rn(fmaf(0.3275911f, a, 1.f));
+  float poly = fmaf(1.061405429f, k, -1.453152027f);
+  poly = fmaf(poly, k, 1.421413741f);
+  poly = fmaf(poly, k, -0.284496736f);
+  poly = fmaf(poly, k, 0.254829592f);
+  poly *= k;
+  const float e = __expf(-a * a);            // exp(-x^2 / 2)
+  const float erf_abs = fmaf(-poly, e, 1.f);
+  const float cdf = fmaf(0.5f, copysignf(erf_abs, t), 0.5f);
+  val = x * cdf;
+  grad = fmaf(x * 0.39894228040143267794f, e, cdf);
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -765,20 +765,55 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
       if (row < p.N) {
         const int ilo = __float2int_rn(ma), ihi = __float2int_rn(mb);
         const bool exact = ((float)ilo == ma) && ((float)ihi == mb) && ((unsigned)ilo < 65536u) && ((unsigned)ihi < 65536u);
-        const uint32_t mask = (uint32_t)ilo | ((uint32_t)ihi << 16);
-        const int bidx = base + __ffs((int)mask) - 1;
-        // exactly one score of the winning chunk within the margin of the best, and it is a real code
-        bool ok = exact && (__popc(mask) == 1) && (bidx < p.K) && (margin_row < 3.0e38f);
+        uint32_t mask = (uint32_t)ilo | ((uint32_t)ihi << 16);
+        const int ncand = __popc(mask);
+        int bidx = base + __ffs((int)mask) - 1;
+        // every code OUTSIDE the winning chunk's near-best mask is provably not the nearest when (i) the best of the
+        // other chunks is beyond the margin and (ii) no excluded code can interfere
+        bool others_out = exact && ncand >= 1 && (margin_row < 3.0e38f);
         const float gap = second - best;
-        if (ok && !(gap > margin_row)) {
+        if (others_out && !(gap > margin_row)) {
           // refine: only codes that can still beat the candidate matter, ||e-mu|| <= ||z-mu|| + d_best (triangle inequality)
           const float dhat = sqrtf(fmaxf(best + zn * zn, 0.f));
           const float emax = dotm ? emax_g : fminf(emax_g, zn + 1.02f * dhat + 1e-30f);
-          ok = gap > fminf(margin_of(zn, emax, dhat), margin_row);
+          others_out = gap > fminf(margin_of(zn, emax, dhat), margin_row);
         }
         if (excl_inv > 0.f) {  // codes left out of the contraction: each is further than ||z-mu|| + d_best, or the row is queued
           const float dhat = sqrtf(fmaxf(best + zn * zn, 0.f));
-          ok = ok && !dotm && ((zn + 1.02f * dhat) * excl_inv < 0.999f);
+          others_out = others_out && !dotm && ((zn + 1.02f * dhat) * excl_inv < 0.999f);
+        }
+        bool ok = others_out && ncand == 1 && bidx < p.K;
+        if (others_out && ncand >= 2 && ncand <= 4 && base + 32 - __clz((int)mask) <= p.K) {
+          // A handful of codes of ONE chunk are within the margin of each other: settle it here, exactly -- fp32 direct
+          // differences in the reference's domain (sqrt for L2, first minimum on ties), as the exact scan would, instead
+          // of sending the row through two more launches (0.7 % of the rows of a training batch end up here).
+          const float* zr = p.z + row * (int64_t)p.D;
+          float bv = INFINITY;
+          int bk = -1;
+          while (mask) {  // ascending code index: a strict < keeps the lowest index on exact ties
+            const int c = __ffs((int)mask) - 1;
+            mask &= mask - 1;
+            const float* er = p.cb + (int64_t)(base + c) * p.D;
+            float acc = 0.f;
+            for (int d = 0; d < p.D; ++d) {
+              const float zv = __ldg(zr + d), ev = __ldg(er + d);
+              if (dotm) {
+                acc = fmaf(zv, ev, acc);
+              } else {
+                const float df = zv - ev;
+                acc = fmaf(df, df, acc);
+              }
+            }
+            const float val = (p.metric == LIPVQ_METRIC_L2) ? sqrtf(acc) : (dotm ? -acc : acc);
+            if (val < bv) {
+              bv = val;
+              bk = base + c;
+            }
+          }
+          if (bk >= 0) {  // (NaN distances leave bk = -1: the exact scan owns the reference's NaN semantics)
+            bidx = bk;
+            ok = true;
+          }
         }
         if (ok) {
           p.idx_out[row] = (int64_t)bidx;
