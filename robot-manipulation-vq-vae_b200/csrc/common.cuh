@@ -113,18 +113,28 @@ __device__ __forceinline__ float act_grad(int act, float x) {
 //   |error| <= 1.5e-7 absolute), exp through ex2.approx.  exp(-t^2) = exp(-x^2/2) is also the Gaussian density the
 //   derivative needs.  ~18 instructions.  Absolute error of value and derivative <= 2e-7 (|x| + 1), far inside the
 //   1e-4 relative parity gate on losses / reconstructions (tests compare against the reference's exact erf).
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// 17 instructions, two of them on the special-function pipe (MUFU.RCP, MUFU.EX2: 1 and 2 ulp) -- no range fix-ups, no
+// Newton step, no slow-path call (what __frcp_rn / __expf expand to)
 __device__ __forceinline__ void gelu_value_grad_fast(float x, float& val, float& grad) {
-  const float t = x * 0.70710678118654752440f;
-  const float a = fabsf(t);
-  const float k = __frcp_rn(fmaf(0.3275911f, a, 1.f));
+  const float k = rcp_approx(fmaf(0.3275911f * 0.70710678118654752440f, fabsf(x), 1.f));
   float poly = fmaf(1.061405429f, k, -1.453152027f);
   poly = fmaf(poly, k, 1.421413741f);
   poly = fmaf(poly, k, -0.284496736f);
   poly = fmaf(poly, k, 0.254829592f);
   poly *= k;
-  const float e = __expf(-a * a);            // exp(-x^2 / 2)
+  const float e = ex2_approx((x * x) * (-0.5f * 1.44269504088896340736f));  // exp(-x^2 / 2)
   const float erf_abs = fmaf(-poly, e, 1.f);
-  const float cdf = fmaf(0.5f, copysignf(erf_abs, t), 0.5f);
+  const float cdf = fmaf(copysignf(0.5f, x), erf_abs, 0.5f);
   val = x * cdf;
   grad = fmaf(x * 0.39894228040143267794f, e, cdf);
 }

@@ -17,8 +17,10 @@
 //
 // Reference ops replaced: nn.Linear + GELU/ReLU/sigmoid chains and their autograd (backbone_lfqvae_v5.py:54-68,71-76;
 // backbone.py:17-32).  The fp32 FFMA tiles of linear.cu remain the path for shapes outside this kernel's range.
+#include <cuda.h>
 #include <cuda_bf16.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "common.cuh"
 #include "tc_common.cuh"
@@ -63,6 +65,8 @@ struct LinTcParams {
   const float* Xpre; int64_t ldx; int act_in;  // mode 1
   int mode, NC, Nbp, nbufA;
   uint32_t tmem_cols;
+  int scr_banks;   // 16-warp scratch banks: 2 for the dual forward and for the staged Xpre tile of mode 1
+  int tma_store;   // output tiles leave through cp.async.bulk.tensor (needs 16-byte aligned C / C2 and row pitch)
 };
 
 // Three-way bf16 split of two values at once, packed as (x0 | x1 << 16) per term.  The packed conversion
@@ -81,6 +85,14 @@ __device__ __forceinline__ void split3_pair(float x0, float x1, uint32_t& h, uin
 }
 // Run body(tag) with the activation as a compile-time constant: the element loops then contain straight-line code
 // instead of a switch per element (branch latency is not hidden with this few warps per scheduler).
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tm), "r"(src), "r"(c0), "r"(c1)
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
 template <int ACT>
 struct ActTag { static constexpr int value = ACT; };
 template <typename F>
@@ -95,7 +107,9 @@ __device__ __forceinline__ void dispatch_act(int act, F&& body) {
 }
 
 
-__global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParams p) {
+template <bool FASTG>
+__global__ void __launch_bounds__(kThreads, 1)
+    linear_tc_kernel(const __grid_constant__ CUtensorMap tm_c, const __grid_constant__ CUtensorMap tm_c2, const LinTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int a_bytes = 3 * p.NC * kATile;          // [term][chunk]
@@ -104,7 +118,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
   uint8_t* sB = sA + p.nbufA * a_bytes;           // [term][chunk]
   float* bias_s = reinterpret_cast<float*>(sB + 3 * p.NC * b_tile);  // [256]
   float* epi_scr = bias_s + 256;                                     // [1 or 2 banks][16 epilogue warps][32 x 16] fp32
-  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_scr + (p.C2 != nullptr ? 2 : 1) * kEpiF * 512);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(epi_scr + p.scr_banks * kEpiF * 512);
   const uint32_t bar_a_full = smem_u32(bars + 0), bar_a_empty = smem_u32(bars + 2);
   const uint32_t bar_acc_full = smem_u32(bars + 4), bar_acc_empty = smem_u32(bars + 6);
   const uint32_t bar_w = smem_u32(bars + 8);  // weights and bias are in shared memory
@@ -309,7 +323,6 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
     const bool mulX = p.mode == 1 && p.act_in != LIPVQ_ACT_NONE;
     const bool dual = p.mode == 0 && p.C2 != nullptr;
     float* scr = epi_scr + warp * 512;           // [32 rows][4 chunks of 4 floats]; chunk j of row r sits at j ^ ((r >> 1) & 3)
-    float* scr2 = scr + kEpiF * 512;             // derivative tile of the dual forward
     const int gr = lane >> 2, gj = lane & 3;     // coalesced side: row 8 * it + gr, chunk gj
     const int rsw = (lane >> 1) & 3;             // row side: this lane's token row, chunk j at j ^ rsw
     float* my_row = scr + lane * 16;
@@ -332,14 +345,20 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
         xr[it] = t;
       }
     };
-    auto store_tile = [&](const float* tile, float* dst, int c0, int64_t row0) {
+    // coalesced side of the transpose: shared-space reads (32-bit addresses), one 64-bit row pointer stepped by 8 rows
+    const uint32_t scr_s = smem_u32(scr);
+    const uint32_t tile_rd = scr_s + (uint32_t)(gr * 16) * 4u;  // row 8 * it + gr: + it * 512 bytes; chunk (gj ^ ((r >> 1) & 3))
+    auto store_tile = [&](uint32_t tile_s, float* dst, int c0, int64_t row0) {
+      const int col = c0 + 4 * gj;
+      float* cp = dst + (row0 + gr) * p.ldc + col;
+      const bool full = vecC && col + 4 <= p.Nb;
 #pragma unroll
-      for (int it = 0; it < 4; ++it) {
-        const int r = 8 * it + gr, col = c0 + 4 * gj;
-        const float4 t = *reinterpret_cast<const float4*>(tile + r * 16 + ((gj ^ ((r >> 1) & 3)) << 2));
+      for (int it = 0; it < 4; ++it, cp += 8 * p.ldc) {
+        const int r = 8 * it + gr;
+        float4 t;
+        lds_f4(tile_s + (uint32_t)it * 512u + (uint32_t)((gj ^ ((r >> 1) & 3)) << 4), t);
         if (row0 + r < p.N && col < p.Nb) {
-          float* cp = dst + (row0 + r) * p.ldc + col;
-          if (vecC && col + 4 <= p.Nb) {
+          if (full) {
             *reinterpret_cast<float4*>(cp) = t;
           } else {
             cp[0] = t.x;
@@ -366,72 +385,117 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_kernel(const LinTcParam
         __syncwarp();
         if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
       }
-      for (int c0 = 16 * part; c0 < p.Nbp; c0 += 64) {
-        const bool last = c0 + 64 >= p.Nbp;
-        if (mulX) {
+      // The group loop is instantiated per (activation, kind) OUTSIDE the loop: inside it the activation switch was an
+      // indirect branch per four columns, and together with generic-space scratch accesses and per-iteration set-up it
+      // made the epilogue -- the long pole of every linear layer -- a branchy 200-instruction body per 4 columns.
+      // kind: 0 forward, 1 forward + derivative (dual), 2 input gradient, 3 input gradient * act_in'(X)
+      const uint32_t my_row_s = smem_u32(my_row);
+      const uint32_t xs_s = scr_s + kEpiF * 2048;  // second bank: staging of the Xpre tile (kind 3)
+      auto groups = [&](auto act_tag, auto kind_tag) {
+        constexpr int ACT = decltype(act_tag)::value;
+        constexpr int KIND = decltype(kind_tag)::value;
+        for (int c0 = 16 * part; c0 < p.Nbp; c0 += 64) {
+          const bool last = c0 + 64 >= p.Nbp;
+          if (KIND == 3) {
 #pragma unroll
-          for (int it = 0; it < 4; ++it) {
-            const int r = 8 * it + gr;
-            *reinterpret_cast<float4*>(scr + r * 16 + ((gj ^ ((r >> 1) & 3)) << 2)) = xr[it];
+            for (int it = 0; it < 4; ++it) {
+              const int r = 8 * it + gr;
+              sts_f4(xs_s + (uint32_t)(r * 16 + ((gj ^ ((r >> 1) & 3)) << 2)) * 4u, xr[it].x, xr[it].y, xr[it].z, xr[it].w);
+            }
+            __syncwarp();
+            if (!last) load_x(c0 + 64, row0, xr);  // next group's, in flight during this group's math
           }
-          __syncwarp();
-          if (!last) load_x(c0 + 64, row0, xr);  // next group's, in flight during this group's math
-        }
-        // four columns per iteration, rolled: the activation bodies (erf, exp) are long, and sixteen unrolled copies of
-        // each variant overflow the instruction cache of the scheduler
-#pragma unroll 1
-        for (int e4 = 0; e4 < 4; ++e4) {
-          uint32_t v[4];
-          tmem_ld4(trow + c0 + 4 * e4, v); tmem_ld_wait4(v);
-          if (e4 == 3) {
-            if (last) {  // this warp's last load: release the accumulator before the math
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {  // eight columns at a time: one TMEM load + one wait per half group
+            uint32_t v[8];
+            tmem_ld8(trow + c0 + 8 * h, v);
+            tmem_ld_wait8(v);
+            if (h == 1 && last) {  // this warp's last load: release the accumulator before the math
               fence_before();
               __syncwarp();
               if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
             }
-          }
-          float* slot = my_row + ((e4 ^ rsw) << 2);
-          float o[4];
-          if (dual) {  // value and derivative from one evaluation (erf is shared after inlining)
-            float d[4];
-            dispatch_act(p.act_out, [&](auto tag) {
-              constexpr int ACT = decltype(tag)::value;
+            float o[8], d[8];
+            if (KIND <= 1) {
+              const float4 b0 = *reinterpret_cast<const float4*>(bias_s + c0 + 8 * h);
+              const float4 b1 = *reinterpret_cast<const float4*>(bias_s + c0 + 8 * h + 4);
+              const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
 #pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float pre = __uint_as_float(v[e]) + bias_s[c0 + 4 * e4 + e];
-                o[e] = act_apply(ACT, pre);
-                d[e] = act_grad(ACT, pre);
+              for (int e = 0; e < 8; ++e) {
+                const float pre = __uint_as_float(v[e]) + bb[e];
+                if (ACT == LIPVQ_ACT_GELU && FASTG) {
+                  gelu_value_grad_fast(pre, o[e], d[e]);
+                } else {
+                  o[e] = act_apply(ACT, pre);
+                  if (KIND == 1) d[e] = act_grad(ACT, pre);
+                }
               }
-            });
-            *reinterpret_cast<float4*>(slot + kEpiF * 512) = make_float4(d[0], d[1], d[2], d[3]);
-          } else if (p.mode == 0) {
-            dispatch_act(p.act_out, [&](auto tag) {
-              constexpr int ACT = decltype(tag)::value;
+            } else {
 #pragma unroll
-              for (int e = 0; e < 4; ++e) o[e] = act_apply(ACT, __uint_as_float(v[e]) + bias_s[c0 + 4 * e4 + e]);
-            });
-          } else {
+              for (int e = 0; e < 8; ++e) o[e] = __uint_as_float(v[e]);
+              if (KIND == 3) {
 #pragma unroll
-            for (int e = 0; e < 4; ++e) o[e] = __uint_as_float(v[e]);
-            if (mulX) {
-              const float4 t = *reinterpret_cast<const float4*>(slot);
-              const float xv[4] = {t.x, t.y, t.z, t.w};
-              dispatch_act(p.act_in, [&](auto tag) {
-                constexpr int ACT = decltype(tag)::value;
+                for (int e4 = 0; e4 < 2; ++e4) {
+                  float4 t;
+                  lds_f4(my_row_s + kEpiF * 2048 + ((((2 * h + e4) ^ rsw) << 2) << 2), t);
+                  const float xv[4] = {t.x, t.y, t.z, t.w};
 #pragma unroll
-                for (int e = 0; e < 4; ++e) o[e] *= act_grad(ACT, xv[e]);
-              });
+                  for (int e = 0; e < 4; ++e) {
+                    float g;
+                    if (ACT == LIPVQ_ACT_GELU && FASTG) {
+                      float unused;
+                      gelu_value_grad_fast(xv[e], unused, g);
+                    } else {
+                      g = act_grad(ACT, xv[e]);
+                    }
+                    o[4 * e4 + e] *= g;
+                  }
+                }
+              }
+            }
+            if (h == 0 && p.tma_store) {  // the previous group's bulk store has finished READING this scratch tile
+              if (lane == 0) bulk_wait_read0();
+              __syncwarp();
+            }
+#pragma unroll
+            for (int e4 = 0; e4 < 2; ++e4) {
+              const uint32_t slot = my_row_s + ((((2 * h + e4) ^ rsw) << 2) << 2);  // chunk j of this lane's row at j ^ rsw
+              sts_f4(slot, o[4 * e4], o[4 * e4 + 1], o[4 * e4 + 2], o[4 * e4 + 3]);
+              if (KIND == 1) sts_f4(slot + kEpiF * 512 * 4, d[4 * e4], d[4 * e4 + 1], d[4 * e4 + 2], d[4 * e4 + 3]);
             }
           }
-          *reinterpret_cast<float4*>(slot) = make_float4(o[0], o[1], o[2], o[3]);  // the slot this lane just read
+          TR(12);
+          if (p.tma_store) {
+            // asynchronous tile store: the warp goes on to the next group while the copy engine drains this one
+            // (store_tile kept the LSU busy for ~2000 cycles per group -- as long as the math)
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+              tma_store_2d(&tm_c, scr_s, c0, (int)row0);
+              if (KIND == 1) tma_store_2d(&tm_c2, scr_s + kEpiF * 2048, c0, (int)row0);
+              bulk_commit();
+            }
+          } else {
+            __syncwarp();
+            store_tile(tile_rd, p.C, c0, row0);
+            if (KIND == 1) store_tile(tile_rd + kEpiF * 2048, p.C2, c0, row0);
+            __syncwarp();
+          }
+          TR(13);
         }
-        __syncwarp();
-        store_tile(scr, p.C, c0, row0);
-        if (dual) store_tile(scr2, p.C2, c0, row0);
-        __syncwarp();
+      };
+      if (dual) {
+        dispatch_act(p.act_out, [&](auto tag) { groups(tag, std::integral_constant<int, 1>{}); });
+      } else if (p.mode == 0) {
+        dispatch_act(p.act_out, [&](auto tag) { groups(tag, std::integral_constant<int, 0>{}); });
+      } else if (mulX) {
+        dispatch_act(p.act_in, [&](auto tag) { groups(tag, std::integral_constant<int, 3>{}); });
+      } else {
+        groups(std::integral_constant<int, LIPVQ_ACT_NONE>{}, std::integral_constant<int, 2>{});
       }
       TR(14);
     }
+    if (p.tma_store && lane == 0) bulk_wait_all();  // the tile stores are complete before the CTA retires
   }
 
   TR(2);
@@ -730,7 +794,35 @@ bool linear_tc_supported(int mode, int64_t N, int Ka, int Nb, bool dual) {
   (void)mode;
   const int NC = (Ka + kChunk - 1) / kChunk, Nbp = (Nb + 15) / 16 * 16;
   const size_t a_bytes = (size_t)3 * NC * kATile, b_bytes = (size_t)3 * NC * Nbp * kChunk * 2;
-  return 1024 + a_bytes + b_bytes + kMisc + (dual ? kDualScratch : 0) <= 227 * 1024;
+  return 1024 + a_bytes + b_bytes + kMisc + ((dual || mode == 1) ? kDualScratch : 0) <= 227 * 1024;
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn lin_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* ptr = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  return fn;
+}
+// [N, Nb] fp32 with row pitch ldc, box = one epilogue warp's tile (32 rows x 16 columns, 64-byte rows); the 64-byte
+// swizzle IS the scratch layout of the epilogue (16-byte chunk j of row r at j ^ ((r >> 1) & 3)); out-of-range rows and
+// columns of a box are clipped by the copy engine
+static bool make_out_map(CUtensorMap* tm, float* C, int64_t N, int Nb, int64_t ldc) {
+  EncodeTiledFn enc = lin_encode_fn();
+  if (!enc || C == nullptr || (reinterpret_cast<uintptr_t>(C) & 15) != 0 || ldc % 4 != 0 || N >= (int64_t)1 << 31) return false;
+  const cuuint64_t gdim[2] = {(cuuint64_t)Nb, (cuuint64_t)N};
+  const cuuint64_t gstride[1] = {(cuuint64_t)ldc * 4};
+  const cuuint32_t box[2] = {16, 32};
+  const cuuint32_t estr[2] = {1, 1};
+  return enc(tm, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, C, gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+             CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, int actA, const float* W, int64_t w_rs,
@@ -741,7 +833,13 @@ int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, i
   p.W = W; p.w_rs = w_rs; p.w_cs = w_cs; p.Nb = Nb;
   p.C = C; p.ldc = ldc; p.bias = bias; p.act_out = act_out;
   p.C2 = (mode == 0) ? C2 : nullptr;
-  const size_t misc = kMisc + (p.C2 ? kDualScratch : 0);
+  p.scr_banks = (p.C2 != nullptr || (mode == 1 && act_in != LIPVQ_ACT_NONE)) ? 2 : 1;
+  const size_t misc = kMisc + (p.scr_banks == 2 ? kDualScratch : 0);
+  CUtensorMap tm_c, tm_c2;
+  memset(&tm_c, 0, sizeof(tm_c));
+  memset(&tm_c2, 0, sizeof(tm_c2));
+  static const bool no_tma = getenv("LIPVQ_LINEAR_TMA_STORE") != nullptr && getenv("LIPVQ_LINEAR_TMA_STORE")[0] == '0';
+  p.tma_store = !no_tma && make_out_map(&tm_c, C, N, Nb, ldc) && (p.C2 == nullptr || make_out_map(&tm_c2, p.C2, N, Nb, ldc));
   p.Xpre = Xpre; p.ldx = ldx; p.act_in = act_in;
   p.mode = mode;
   p.NC = (Ka + kChunk - 1) / kChunk;
@@ -756,16 +854,24 @@ int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, i
     set_error("linear_tc: shape Ka=%d Nb=%d does not fit shared memory", Ka, Nb);
     return LIPVQ_ERR_INVALID;
   }
-  static size_t smem_set[kMaxDevices] = {};  // the attribute is per device
+  // GELU epilogues: the short A&S 7.1.26 form (default; |error| <= 2e-7 (|x| + 1)) or libm erff / expf (LIPVQ_EXACT_GELU=1)
+  static const bool fast_gelu = !(getenv("LIPVQ_EXACT_GELU") != nullptr && getenv("LIPVQ_EXACT_GELU")[0] == '1');
+  static size_t smem_set[2][kMaxDevices] = {};  // the attribute is per device
   const int dev_ = current_device();
-  if (smem > smem_set[dev_]) {
-    LIPVQ_CUDA(cudaFuncSetAttribute(linear_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    smem_set[dev_] = smem;
+  if (smem > smem_set[fast_gelu][dev_]) {
+    if (fast_gelu)
+      LIPVQ_CUDA(cudaFuncSetAttribute(linear_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else
+      LIPVQ_CUDA(cudaFuncSetAttribute(linear_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    smem_set[fast_gelu][dev_] = smem;
   }
   const int row_blocks = (int)ceil_div64(N, kBM);
   const int sms = sm_count();
   const int grid = row_blocks < sms ? row_blocks : sms;
-  LIPVQ_CUDA(launch_pdl(linear_tc_kernel, dim3(grid), dim3(kThreads), smem, stream, p));
+  if (fast_gelu)
+    LIPVQ_CUDA(launch_pdl(linear_tc_kernel<true>, dim3(grid), dim3(kThreads), smem, stream, tm_c, tm_c2, p));
+  else
+    LIPVQ_CUDA(launch_pdl(linear_tc_kernel<false>, dim3(grid), dim3(kThreads), smem, stream, tm_c, tm_c2, p));
   LIPVQ_LAUNCHED("linear_tc_kernel");
   return LIPVQ_OK;
 }

@@ -28,3 +28,20 @@ for _ in range(3):
 for _ in range(3):
     ops.linear_bwd_w(dY, X, lipvq.ACT_NONE, dW, db)                            # linear_tc_bwd_w launches 0-2
 torch.cuda.synchronize()
+if "--time" in sys.argv:
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    mode = next((a.split("=")[1] for a in sys.argv if a.startswith("--flush=")), "write")  # write | read | none
+    for name, fn in (("fwd_dual 64->128 gelu", lambda: ops.linear_fwd_dual(X, lipvq.ACT_NONE, W, b, lipvq.ACT_GELU, Y, dYd)),
+                     ("bwd_x given", lambda: ops.linear_bwd_x(dY, W, X, lipvq.ACT_GIVEN, out=dX)),
+                     ("bwd_w", lambda: ops.linear_bwd_w(dY, X, lipvq.ACT_NONE, dW, db))):
+        ds = []
+        for i in range(12):
+            if mode == "write":
+                flush.zero_()           # leaves L2 full of DIRTY lines: the timed kernel also pays their write-back
+            elif mode == "read":
+                flush.view(torch.int32).sum()   # leaves L2 full of clean lines
+            a, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); e.record(); torch.cuda.synchronize()
+            if i >= 2:
+                ds.append(a.elapsed_time(e) * 1e3)
+        print(f"[flush={mode}] {name}: mean {sum(ds) / len(ds):.1f} us  min {min(ds):.1f} us")

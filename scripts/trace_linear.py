@@ -24,11 +24,15 @@ def main():
         dW, db = torch.zeros(OUT, IN, device="cuda"), torch.zeros(OUT, device="cuda")
         for _ in range(3):
             ops.linear_bwd_w(dY, x, a_in, dW, db)
+    elif "dual" in sys.argv:  # training-time forward: value + derivative
+        y2 = torch.empty(N, OUT, device="cuda")
+        for _ in range(3):
+            ops.linear_fwd_dual(x, a_in, W, b, a_out, y, y2)
     else:
         for _ in range(3):
             ops.linear_fwd(x, a_in, W, b, a_out, out=y)
     torch.cuda.synchronize()
-    ts.NAMES.update({10: "epi:wait_acc", 11: "epi:acc_full", 14: "epi:stored", 20: "cvt:wait_a_empty", 21: "cvt:a_empty",
+    ts.NAMES.update({10: "epi:wait_acc", 11: "epi:acc_full", 12: "epi:group_math", 13: "epi:group_stored", 14: "epi:stored", 20: "cvt:wait_a_empty", 21: "cvt:a_empty",
                      23: "cvt:a_filled", 30: "mma:a_full", 31: "mma:acc_empty", 32: "mma:issued"})
     ts.report("lipvq_debug_trace_linear", 32, 1024, {0: "epi p0", 12: "epi p3", 16: "cvt", 23: "cvt last", 24: "mma"})
 
