@@ -66,6 +66,7 @@ struct LinTcParams {
   int mode, NC, Nbp, nbufA;
   uint32_t tmem_cols;
   int scr_banks;   // 16-warp scratch banks: 2 for the dual forward and for the staged Xpre tile of mode 1
+  int prefetch;    // L2 prefetch of the next row block's operands (LIPVQ_LINEAR_PREFETCH=1)
   int tma_store;   // output tiles leave through cp.async.bulk.tensor (needs 16-byte aligned C / C2 and row pitch)
 };
 
@@ -89,6 +90,7 @@ __device__ __forceinline__ void tma_store_2d(const CUtensorMap* tm, uint32_t src
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(tm), "r"(src), "r"(c0), "r"(c1)
                : "memory");
 }
+__device__ __forceinline__ void prefetch_l2(const void* ptr) { asm volatile("prefetch.global.L2 [%0];" ::"l"(ptr)); }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
@@ -119,10 +121,13 @@ __global__ void __launch_bounds__(kThreads, 1)
   float* bias_s = reinterpret_cast<float*>(sB + 3 * p.NC * b_tile);  // [256]
   float* epi_scr = bias_s + 256;                                     // [1 or 2 banks][16 epilogue warps][32 x 16] fp32
   uint64_t* bars = reinterpret_cast<uint64_t*>(epi_scr + p.scr_banks * kEpiF * 512);
-  const uint32_t bar_a_full = smem_u32(bars + 0), bar_a_empty = smem_u32(bars + 2);
-  const uint32_t bar_acc_full = smem_u32(bars + 4), bar_acc_empty = smem_u32(bars + 6);
-  const uint32_t bar_w = smem_u32(bars + 8);  // weights and bias are in shared memory
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 9);
+  // A-tile barriers are per (buffer, 64-column chunk): slot = buf * NC + c (nbufA * NC <= 4), so with two chunks the MMAs
+  // of chunk 0 run while chunk 1 is still being converted, and chunk 0 of the next row block is refilled as soon as its
+  // own MMAs retire (with one barrier per buffer the K = 128 layers ran convert -> MMA -> convert strictly in series)
+  const uint32_t bar_a_full = smem_u32(bars + 0), bar_a_empty = smem_u32(bars + 4);
+  const uint32_t bar_acc_full = smem_u32(bars + 8), bar_acc_empty = smem_u32(bars + 10);
+  const uint32_t bar_w = smem_u32(bars + 12);  // weights and bias are in shared memory
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 13);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row_blocks = (int)((p.N + kBM - 1) / kBM);
@@ -134,9 +139,11 @@ __global__ void __launch_bounds__(kThreads, 1)
 #endif
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < 2; ++s) {
+    for (int s = 0; s < 4; ++s) {
       mbar_init(bar_a_full + 8 * s, kCvtF);
       mbar_init(bar_a_empty + 8 * s, 1);
+    }
+    for (int s = 0; s < 2; ++s) {
       mbar_init(bar_acc_full + 8 * s, 1);
       mbar_init(bar_acc_empty + 8 * s, kEpiF);
     }
@@ -161,30 +168,50 @@ __global__ void __launch_bounds__(kThreads, 1)
       for (int i = 0; i < nblk; ++i) {
         const int buf = i % p.nbufA;
         const uint32_t ab = (uint32_t)i & 1;
-        mbar_wait(bar_a_full + 8 * buf, (uint32_t)(i / p.nbufA) & 1);
-        TR(30);
-        mbar_wait(bar_acc_empty + 8 * ab, (((uint32_t)i >> 1) & 1) ^ 1);
-        fence_after();
-        TR(31);
+        const uint32_t a_phase = (uint32_t)(i / p.nbufA) & 1;
         const uint32_t d_tmem = tmem_base + ab * (uint32_t)p.Nbp;
         const uint32_t a_base = smem_u32(sA + buf * a_bytes);
         uint32_t first = 0;
         for (int c = 0; c < p.NC; ++c) {
+          const int slot = buf * p.NC + c;
+          mbar_wait(bar_a_full + 8 * slot, a_phase);
+          if (c == 0) {
+            TR(30);
+            mbar_wait(bar_acc_empty + 8 * ab, (((uint32_t)i >> 1) & 1) ^ 1);
+            TR(31);
+          }
+          fence_after();
+          // k-steps that hold data: a 12-wide input needs one 16-deep MMA per product, not the chunk's four
+          const int krem = p.Ka - c * kChunk;
+          const int ksteps = krem >= kChunk ? kChunk / 16 : (krem + 15) / 16;
           // term index: 0 = h, 1 = m, 2 = l.  smallest products first.
           const int ta[6] = {1, 2, 0, 1, 0, 0}, tb[6] = {1, 0, 2, 0, 1, 0};
+          // (one thread issues every MMA: the full chunk is unrolled so its descriptors are immediates off two bases)
+          if (ksteps == kChunk / 16) {
 #pragma unroll
-          for (int combo = 0; combo < 6; ++combo) {
-            const uint32_t aa = a_base + (uint32_t)((ta[combo] * p.NC + c) * kATile);
-            const uint32_t bb = b_base + (uint32_t)((tb[combo] * p.NC + c) * b_tile);
+            for (int combo = 0; combo < 6; ++combo) {
+              const uint32_t aa = a_base + (uint32_t)((ta[combo] * p.NC + c) * kATile);
+              const uint32_t bb = b_base + (uint32_t)((tb[combo] * p.NC + c) * b_tile);
 #pragma unroll
-            for (int k = 0; k < kChunk / 16; ++k) {
-              umma_f16(d_tmem, desc_sw128(aa + 32 * k), desc_sw128(bb + 32 * k), idesc, first);
-              first = 1;
+              for (int k = 0; k < kChunk / 16; ++k) {
+                umma_f16(d_tmem, desc_sw128(aa + 32 * k), desc_sw128(bb + 32 * k), idesc, first);
+                first = 1;
+              }
+            }
+          } else {
+#pragma unroll
+            for (int combo = 0; combo < 6; ++combo) {
+              const uint32_t aa = a_base + (uint32_t)((ta[combo] * p.NC + c) * kATile);
+              const uint32_t bb = b_base + (uint32_t)((tb[combo] * p.NC + c) * b_tile);
+              for (int k = 0; k < ksteps; ++k) {
+                umma_f16(d_tmem, desc_sw128(aa + 32 * k), desc_sw128(bb + 32 * k), idesc, first);
+                first = 1;
+              }
             }
           }
+          umma_commit(bar_a_empty + 8 * slot);
         }
         umma_commit(bar_acc_full + 8 * ab);
-        umma_commit(bar_a_empty + 8 * buf);
         TR(32);
       }
     }
@@ -223,11 +250,18 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
           }
         }
-        if (c == 0) {  // the loads above are already in flight while this waits for the MMAs that read the buffer
-          TR(20);
-          mbar_wait(bar_a_empty + 8 * buf, (((uint32_t)(i / p.nbufA)) & 1) ^ 1);
-          TR(21);
+        // next row block's lines of this chunk -> L2 (one request per 128-byte line), so its loads do not pay DRAM latency
+        if (p.prefetch && i + 1 < nblk && col < p.Ka && (ch & 3) == 0) {
+#pragma unroll
+          for (int u = 0; u < kCvtItems; ++u) {
+            const int64_t row = (rb + gridDim.x) * kBM + r0 + 32 * u;
+            if (row < p.N) prefetch_l2(p.A + row * p.lda + col);
+          }
         }
+        // the loads above are already in flight while this waits for the MMAs that read this chunk's tiles
+        if (c == 0) TR(20);
+        mbar_wait(bar_a_empty + 8 * (buf * p.NC + c), (((uint32_t)(i / p.nbufA)) & 1) ^ 1);
+        if (c == 0) TR(21);
 #pragma unroll
         for (int u = 0; u < kCvtItems; ++u) {
           const float x[8] = {va[u].x, va[u].y, va[u].z, va[u].w, vb[u].x, vb[u].y, vb[u].z, vb[u].w};
@@ -250,10 +284,10 @@ __global__ void __launch_bounds__(kThreads, 1)
           *reinterpret_cast<uint4*>(a_buf + (1 * p.NC + c) * kATile + off) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
           *reinterpret_cast<uint4*>(a_buf + (2 * p.NC + c) * kATile + off) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
         }
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_a_full + 8 * (buf * p.NC + c));
       }
-      fence_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_a_full + 8 * buf);
       TR(23);
     }
   } else {
@@ -375,6 +409,11 @@ __global__ void __launch_bounds__(kThreads, 1)
       const int64_t row0 = rb * kBM + q * 32;
       float4 xr[4];
       if (mulX && 16 * part < p.Nbp) load_x(16 * part, row0, xr);  // independent of the MMA: in flight during the wait
+      if (p.prefetch && mulX && i + 1 < nblk) {  // the next row block's Xpre segments of this warp -> L2
+        const int64_t rn = row0 + (int64_t)gridDim.x * kBM + lane;
+        if (rn < p.N)
+          for (int c0 = 16 * part; c0 < p.Nb; c0 += 64) prefetch_l2(p.Xpre + rn * p.ldx + c0);
+      }
       TR(10);
       mbar_wait(bar_acc_full + 8 * ab, ((uint32_t)i >> 1) & 1);
       fence_after();
@@ -839,6 +878,8 @@ int linear_tc_launch(int mode, const float* A, int64_t N, int Ka, int64_t lda, i
   memset(&tm_c, 0, sizeof(tm_c));
   memset(&tm_c2, 0, sizeof(tm_c2));
   static const bool no_tma = getenv("LIPVQ_LINEAR_TMA_STORE") != nullptr && getenv("LIPVQ_LINEAR_TMA_STORE")[0] == '0';
+  static const bool pre = getenv("LIPVQ_LINEAR_PREFETCH") != nullptr && getenv("LIPVQ_LINEAR_PREFETCH")[0] == '1';
+  p.prefetch = pre;
   p.tma_store = !no_tma && make_out_map(&tm_c, C, N, Nb, ldc) && (p.C2 == nullptr || make_out_map(&tm_c2, p.C2, N, Nb, ldc));
   p.Xpre = Xpre; p.ldx = ldx; p.act_in = act_in;
   p.mode = mode;

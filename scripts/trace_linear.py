@@ -24,6 +24,11 @@ def main():
         dW, db = torch.zeros(OUT, IN, device="cuda"), torch.zeros(OUT, device="cuda")
         for _ in range(3):
             ops.linear_bwd_w(dY, x, a_in, dW, db)
+    elif "bwdx" in sys.argv:  # N IN OUT none none bwdx: dX[N, IN] = (dY[N, OUT] @ W) * given derivative
+        dY = torch.randn(N, OUT, generator=g).cuda()
+        dX = torch.empty(N, IN, device="cuda")
+        for _ in range(3):
+            ops.linear_bwd_x(dY, W, x, lipvq.ACT_GIVEN, out=dX)
     elif "dual" in sys.argv:  # training-time forward: value + derivative
         y2 = torch.empty(N, OUT, device="cuda")
         for _ in range(3):
