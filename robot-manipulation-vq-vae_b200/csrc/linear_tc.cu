@@ -192,9 +192,10 @@ __global__ void __launch_bounds__(kThreads, 1)
             for (int combo = 0; combo < 6; ++combo) {
               const uint32_t aa = a_base + (uint32_t)((ta[combo] * p.NC + c) * kATile);
               const uint32_t bb = b_base + (uint32_t)((tb[combo] * p.NC + c) * b_tile);
+              const uint32_t a_lo = desc_sw128_lo(aa), b_lo = desc_sw128_lo(bb);
 #pragma unroll
               for (int k = 0; k < kChunk / 16; ++k) {
-                umma_f16(d_tmem, desc_sw128(aa + 32 * k), desc_sw128(bb + 32 * k), idesc, first);
+                umma_f16_lo(d_tmem, a_lo + 2 * k, b_lo + 2 * k, kDescSw128Hi, idesc, first);
                 first = 1;
               }
             }

@@ -42,6 +42,19 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64
       "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same, with the descriptors given as their low words (address >> 4 | LBO) and one shared high word: stepping a
+// descriptor through a tile is then ONE 32-bit add per operand for the single issuing thread, whose instruction
+// latency -- not the tensor pipe -- is what spaces the MMAs of a small tile
+__device__ __forceinline__ void umma_f16_lo(uint32_t d_tmem, uint32_t a_lo, uint32_t b_lo, uint32_t desc_hi, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n .reg .pred p;\n .reg .b64 da, db;\n mov.b64 da, {%1, %3};\n mov.b64 db, {%2, %3};\n setp.ne.b32 p, %5, 0;\n"
+      " tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %4, p;\n}" ::"r"(d_tmem),
+      "r"(a_lo), "r"(b_lo), "r"(desc_hi), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ uint32_t desc_sw128_lo(uint32_t smem_addr) { return ((smem_addr & 0x3FFFF) >> 4) | (1u << 16); }
+constexpr uint32_t kDescSw128Hi = (uint32_t)(1024 >> 4) | (1u << 14) | (2u << 29);  // SBO, version (bit 46), swizzle (bits 61-63)
 // K-major, SWIZZLE_128B, 128-byte tile rows, 8-row atoms 1024 B apart (UMMA::SmemDescriptor, version 1)
 __device__ __forceinline__ uint64_t desc_sw128(uint32_t smem_addr) {
   return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
