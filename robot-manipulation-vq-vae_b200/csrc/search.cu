@@ -296,18 +296,21 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// Exact scan for queued rows: one CTA (8 warps) per row, grid-stride over the queue.  A group of LPC lanes owns one
-// code at a time and walks its row with coalesced float4 loads; each code's fp32 direct-difference sum (the reference's
-// expression, backbone_lfqvae_v5.py:41-45) is reduced over the group in a fixed butterfly order, so the result is
-// deterministic.  Winner = smallest value, lowest index on exact ties (torch.argmin's first-min rule).
+// Exact scan for queued rows: one CTA (8 warps) per batch of R rows, grid-stride over the queue.  A group of LPC lanes
+// owns one code at a time and walks its row with coalesced float4 loads; each code's fp32 direct-difference sum (the
+// reference's expression, backbone_lfqvae_v5.py:41-45) is reduced over the group in a fixed butterfly order, so the
+// result is deterministic and does not depend on UN or R.  Winner = smallest value, lowest index on exact ties
+// (torch.argmin's first-min rule).  Every row needs the WHOLE codebook: with one row per CTA the scan was bound by L2
+// bandwidth (3000 queued rows x 128 KB = 393 MB -> 100 us); R rows share each code load.
+template <int UN, int R>
 __global__ void __launch_bounds__(256)
     rescore_kernel(const float* __restrict__ z, int D, const float* __restrict__ cb, int K, int metric,
                    const int* __restrict__ count, const int* __restrict__ first_count, const int* __restrict__ work,
                    const int* __restrict__ work_first, int skip_rows, int64_t* __restrict__ idx_out, float* __restrict__ best_out, int32_t* __restrict__ stats_out, int vec,
                    int lpc) {
-  extern __shared__ __align__(16) float zs[];
-  __shared__ float s_bv[8];
-  __shared__ int s_bk[8];
+  extern __shared__ __align__(16) float zs[];  // [R][D]
+  __shared__ float s_bv[R][8];
+  __shared__ int s_bk[R][8];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   grid_dep_wait();  // launched as a programmatic dependent of the last search pass
   int nflag = *count;
@@ -320,69 +323,226 @@ __global__ void __launch_bounds__(256)
     stats_out[1] = *first_count;  // rows the first (fastest) level could not certify
   }
   const int sub = lane & (lpc - 1), grp = lane / lpc, groups = 32 / lpc;
-  for (int w = blockIdx.x; w < nflag; w += gridDim.x) {
-    const int64_t row = work[w];
-    const float* zr = z + row * (int64_t)D;
-    __syncthreads();  // previous row fully consumed
-    for (int d = threadIdx.x; d < D; d += blockDim.x) zs[d] = __ldg(zr + d);
+  for (int w0 = blockIdx.x * R; w0 < nflag; w0 += gridDim.x * R) {
+    const int nr = (nflag - w0 < R) ? nflag - w0 : R;
+    __syncthreads();  // previous batch fully consumed
+    for (int i = threadIdx.x; i < R * D; i += blockDim.x) {
+      const int r = i / D, d = i - r * D;
+      zs[i] = (r < nr) ? __ldg(z + (int64_t)work[w0 + r] * D + d) : 0.f;
+    }
     __syncthreads();
-    float bv = INFINITY;
-    int bk = 0x7fffffff;
-    // four codes per group and iteration, independent accumulators: the loads of all four are in flight together
-    for (int k0 = warp * groups; k0 < K; k0 += 8 * groups * 4) {
-      float a[4] = {0.f, 0.f, 0.f, 0.f};
+    float bv[R];
+    int bk[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      bv[r] = INFINITY;
+      bk[r] = 0x7fffffff;
+    }
+    // UN codes per group and iteration, independent accumulators: the loads of all of them are in flight together
+    for (int k0 = warp * groups; k0 < K; k0 += 8 * groups * UN) {
+      float a[UN][R];
+#pragma unroll
+      for (int u = 0; u < UN; ++u)
+#pragma unroll
+        for (int r = 0; r < R; ++r) a[u][r] = 0.f;
       if (vec) {
         for (int d = 4 * sub; d < D; d += 4 * lpc) {
-          float4 e4[4];
+          float4 e4[UN];
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
+          for (int u = 0; u < UN; ++u) {
             const int k = k0 + grp + u * 8 * groups;
             e4[u] = (k < K) ? __ldg(reinterpret_cast<const float4*>(cb + (int64_t)k * D + d)) : make_float4(0.f, 0.f, 0.f, 0.f);
           }
-          const float4 z4 = *reinterpret_cast<const float4*>(zs + d);
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            if (metric == LIPVQ_METRIC_DOT) {
-              a[u] = fmaf(z4.x, e4[u].x, a[u]); a[u] = fmaf(z4.y, e4[u].y, a[u]);
-              a[u] = fmaf(z4.z, e4[u].z, a[u]); a[u] = fmaf(z4.w, e4[u].w, a[u]);
-            } else {
-              float df;
-              df = z4.x - e4[u].x; a[u] = fmaf(df, df, a[u]);
-              df = z4.y - e4[u].y; a[u] = fmaf(df, df, a[u]);
-              df = z4.z - e4[u].z; a[u] = fmaf(df, df, a[u]);
-              df = z4.w - e4[u].w; a[u] = fmaf(df, df, a[u]);
+          for (int r = 0; r < R; ++r) {
+            const float4 z4 = *reinterpret_cast<const float4*>(zs + r * D + d);
+#pragma unroll
+            for (int u = 0; u < UN; ++u) {
+              if (metric == LIPVQ_METRIC_DOT) {
+                a[u][r] = fmaf(z4.x, e4[u].x, a[u][r]); a[u][r] = fmaf(z4.y, e4[u].y, a[u][r]);
+                a[u][r] = fmaf(z4.z, e4[u].z, a[u][r]); a[u][r] = fmaf(z4.w, e4[u].w, a[u][r]);
+              } else {
+                float df;
+                df = z4.x - e4[u].x; a[u][r] = fmaf(df, df, a[u][r]);
+                df = z4.y - e4[u].y; a[u][r] = fmaf(df, df, a[u][r]);
+                df = z4.z - e4[u].z; a[u][r] = fmaf(df, df, a[u][r]);
+                df = z4.w - e4[u].w; a[u][r] = fmaf(df, df, a[u][r]);
+              }
             }
           }
         }
       } else {
         for (int d = sub; d < D; d += lpc) {
-          float ev[4];
+          float ev[UN];
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
+          for (int u = 0; u < UN; ++u) {
             const int k = k0 + grp + u * 8 * groups;
             ev[u] = (k < K) ? __ldg(cb + (int64_t)k * D + d) : 0.f;
           }
 #pragma unroll
-          for (int u = 0; u < 4; ++u) {
-            if (metric == LIPVQ_METRIC_DOT) {
-              a[u] = fmaf(zs[d], ev[u], a[u]);
-            } else {
-              const float df = zs[d] - ev[u];
-              a[u] = fmaf(df, df, a[u]);
+          for (int r = 0; r < R; ++r) {
+            const float zv = zs[r * D + d];
+#pragma unroll
+            for (int u = 0; u < UN; ++u) {
+              if (metric == LIPVQ_METRIC_DOT) {
+                a[u][r] = fmaf(zv, ev[u], a[u][r]);
+              } else {
+                const float df = zv - ev[u];
+                a[u][r] = fmaf(df, df, a[u][r]);
+              }
             }
           }
         }
       }
 #pragma unroll
-      for (int u = 0; u < 4; ++u) {  // ascending k within the group, so a strict < keeps the lowest index on ties
+      for (int u = 0; u < UN; ++u) {  // ascending k within the group, so a strict < keeps the lowest index on ties
         const int k = k0 + grp + u * 8 * groups;
-        float av = a[u];
-        for (int o = lpc >> 1; o > 0; o >>= 1) av += __shfl_xor_sync(0xffffffffu, av, o);
-        const float val = (metric == LIPVQ_METRIC_L2) ? sqrtf(av) : (metric == LIPVQ_METRIC_DOT ? -av : av);
-        if (k < K && val < bv) {
-          bv = val;
-          bk = k;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+          float av = a[u][r];
+          for (int o = lpc >> 1; o > 0; o >>= 1) av += __shfl_xor_sync(0xffffffffu, av, o);
+          const float val = (metric == LIPVQ_METRIC_L2) ? sqrtf(av) : (metric == LIPVQ_METRIC_DOT ? -av : av);
+          if (k < K && val < bv[r]) {
+            bv[r] = val;
+            bk[r] = k;
+          }
         }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ov = __shfl_xor_sync(0xffffffffu, bv[r], o);
+        const int ok = __shfl_xor_sync(0xffffffffu, bk[r], o);
+        if (ov < bv[r] || (ov == bv[r] && ok < bk[r])) {
+          bv[r] = ov;
+          bk[r] = ok;
+        }
+      }
+      if (lane == 0) {
+        s_bv[r][warp] = bv[r];
+        s_bk[r][warp] = bk[r];
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x < nr) {
+      const int r = threadIdx.x;
+      float v = s_bv[r][0];
+      int k = s_bk[r][0];
+      for (int i = 1; i < 8; ++i)
+        if (s_bv[r][i] < v || (s_bv[r][i] == v && s_bk[r][i] < k)) {
+          v = s_bv[r][i];
+          k = s_bk[r][i];
+        }
+      if (k == 0x7fffffff) k = 0;  // all-NaN row: torch would return the NaN's index; we return 0
+      const int64_t row = work[w0 + r];
+      idx_out[row] = (int64_t)k;
+      if (best_out) best_out[row] = (metric == LIPVQ_METRIC_DOT) ? -v : v;
+    }
+  }
+}
+
+// Exact scan, small codebooks (D % 4 == 0, D <= 256, K * (D + 4) * 4 bytes <= 200 KB): the fp32 codebook is staged in
+// shared memory ONCE per CTA and every queued row of the CTA scans it there, one LANE per code.
+//   * With the codebook in global memory every row re-read all of it from L2, and because every SM reads the SAME
+//     K * D * 4 bytes the requests pile up on the few L2 slices that own those lines: 3000 queued rows took 137 us
+//     (~2.9 TB/s) however the scan was arranged (group butterfly, sixteen codes in flight, eight rows per batch).
+//   * Rows are padded to D + 4 floats: lane k reads 16 bytes at k * (D + 4) * 4, an odd multiple of 16 bytes apart, so
+//     the eight lanes of a quarter-warp request hit distinct banks.
+//   * No cross-lane reduction per code; each code's sum runs over four interleaved partial sums in a fixed order, so the
+//     result is deterministic.  Winner = smallest value, lowest index on exact ties (torch.argmin's first-min rule).
+__global__ void __launch_bounds__(256, 1)
+    rescore_smem_kernel(const float* __restrict__ z, int D, const float* __restrict__ cb, int K, int metric,
+                        const int* __restrict__ count, const int* __restrict__ first_count, const int* __restrict__ work,
+                        const int* __restrict__ work_first, int skip_rows, int64_t* __restrict__ idx_out,
+                        float* __restrict__ best_out, int32_t* __restrict__ stats_out) {
+  extern __shared__ __align__(16) float cs[];  // [K][D + 4] codebook, then [D] the row
+  __shared__ float s_bv[8];
+  __shared__ int s_bk[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nv = D >> 2, ldc = D + 4;
+  float* zs = cs + (size_t)K * ldc;
+  grid_dep_wait();
+  int nflag = *count;
+  if (work_first != nullptr && *first_count <= skip_rows) {
+    nflag = *first_count;
+    work = work_first;
+  }
+  if (stats_out && blockIdx.x == 0 && threadIdx.x == 0) {
+    stats_out[0] = nflag;
+    stats_out[1] = *first_count;
+  }
+  if ((int)blockIdx.x >= nflag) return;  // the common case: nothing queued, nothing staged
+  {  // every CTA stages the same lines: each starts at its own offset so the L2 slices are not hit in lock step
+    const int total = K * nv;
+    const int start = (int)(((int64_t)total * blockIdx.x) / gridDim.x) & ~255;
+    for (int i0 = threadIdx.x; i0 < total; i0 += 8 * 256) {  // eight independent loads in flight per thread
+      float4 t[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        int i = i0 + u * 256 + start;
+        if (i >= total) i -= total;
+        t[u] = (i0 + u * 256 < total) ? __ldg(reinterpret_cast<const float4*>(cb) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        int i = i0 + u * 256 + start;
+        if (i >= total) i -= total;
+        const int k = i / nv, v = i - k * nv;
+        if (i0 + u * 256 < total) *reinterpret_cast<float4*>(cs + (size_t)k * ldc + 4 * v) = t[u];
+      }
+    }
+  }
+  // the row of the NEXT trip is requested before the current one is scanned (index, then row: two dependent loads)
+  float znext = ((int)threadIdx.x < D) ? __ldg(z + (int64_t)work[blockIdx.x] * D + threadIdx.x) : 0.f;
+  for (int w = blockIdx.x; w < nflag; w += gridDim.x) {
+    const int64_t row = work[w];
+    __syncthreads();  // codebook staged / previous row consumed
+    if ((int)threadIdx.x < D) zs[threadIdx.x] = znext;
+    __syncthreads();
+    if (w + (int)gridDim.x < nflag && (int)threadIdx.x < D)
+      znext = __ldg(z + (int64_t)work[w + gridDim.x] * D + threadIdx.x);
+    float bv = INFINITY;
+    int bk = 0x7fffffff;
+    // two codes per trip (k and k + 256) share every load of the row; ascending k per thread, so a strict < keeps the
+    // lowest index on ties
+    for (int k = threadIdx.x; k < K; k += 512) {
+      const bool two = k + 256 < K;
+      const float4* e0 = reinterpret_cast<const float4*>(cs + (size_t)k * ldc);
+      const float4* e1 = reinterpret_cast<const float4*>(cs + (size_t)(two ? k + 256 : k) * ldc);
+      float a[4] = {0.f, 0.f, 0.f, 0.f}, b[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll 4
+      for (int v = 0; v < nv; ++v) {
+        const float4 x = e0[v], y = e1[v];
+        const float4 z4 = *reinterpret_cast<const float4*>(zs + 4 * v);
+        float& accA = a[v & 3];
+        float& accB = b[v & 3];
+        if (metric == LIPVQ_METRIC_DOT) {
+          accA = fmaf(z4.x, x.x, accA); accA = fmaf(z4.y, x.y, accA); accA = fmaf(z4.z, x.z, accA); accA = fmaf(z4.w, x.w, accA);
+          accB = fmaf(z4.x, y.x, accB); accB = fmaf(z4.y, y.y, accB); accB = fmaf(z4.z, y.z, accB); accB = fmaf(z4.w, y.w, accB);
+        } else {
+          float df;
+          df = z4.x - x.x; accA = fmaf(df, df, accA);
+          df = z4.y - x.y; accA = fmaf(df, df, accA);
+          df = z4.z - x.z; accA = fmaf(df, df, accA);
+          df = z4.w - x.w; accA = fmaf(df, df, accA);
+          df = z4.x - y.x; accB = fmaf(df, df, accB);
+          df = z4.y - y.y; accB = fmaf(df, df, accB);
+          df = z4.z - y.z; accB = fmaf(df, df, accB);
+          df = z4.w - y.w; accB = fmaf(df, df, accB);
+        }
+      }
+      const float av = (a[0] + a[1]) + (a[2] + a[3]), bvv = (b[0] + b[1]) + (b[2] + b[3]);
+      const float val = (metric == LIPVQ_METRIC_L2) ? sqrtf(av) : (metric == LIPVQ_METRIC_DOT ? -av : av);
+      const float val2 = (metric == LIPVQ_METRIC_L2) ? sqrtf(bvv) : (metric == LIPVQ_METRIC_DOT ? -bvv : bvv);
+      if (val < bv) {
+        bv = val;
+        bk = k;
+      }
+      if (two && val2 < bv) {
+        bv = val2;
+        bk = k + 256;
       }
     }
 #pragma unroll
@@ -409,6 +569,143 @@ __global__ void __launch_bounds__(256)
       idx_out[row] = (int64_t)bk;
       if (best_out) best_out[row] = (metric == LIPVQ_METRIC_DOT) ? -bv : bv;
     }
+  }
+}
+
+// Exact scan, the tokenizer's own shape class (K <= 512, D <= 64, D % 4 == 0): thread k keeps code k in REGISTERS for
+// the whole kernel and every queued row of the CTA is scanned against them -- per row one broadcast read of z from
+// shared memory and ~130 arithmetic instructions per thread (the shared-memory variant above re-reads 128 KB of codes
+// per row and runs at ~2 us per row and CTA).  Same fixed summation order as rescore_smem_kernel.
+__global__ void __launch_bounds__(512, 1)
+    rescore_reg_kernel(const float* __restrict__ z, int D, const float* __restrict__ cb, int K, int metric,
+                       const int* __restrict__ count, const int* __restrict__ first_count, const int* __restrict__ work,
+                       const int* __restrict__ work_first, int skip_rows, int64_t* __restrict__ idx_out,
+                       float* __restrict__ best_out, int32_t* __restrict__ stats_out) {
+  __shared__ __align__(16) float zs[8][64];
+  __shared__ int s_rows[32];
+  __shared__ float s_bv[4][16];
+  __shared__ int s_bk[4][16];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int k = threadIdx.x;
+  grid_dep_wait();
+  int nflag = *count;
+  if (work_first != nullptr && *first_count <= skip_rows) {
+    nflag = *first_count;
+    work = work_first;
+  }
+  if (stats_out && blockIdx.x == 0 && threadIdx.x == 0) {
+    stats_out[0] = nflag;
+    stats_out[1] = *first_count;
+  }
+  if ((int)blockIdx.x >= nflag) return;  // the common case: nothing queued
+  // (loading the codes above the dependency wait was tried: the 128 KB per CTA are then read even when nothing is queued,
+  //  and the search without queued rows went from 29.7 to 37.9 us)
+  const int nv = D >> 2;
+  float4 e[16];
+#pragma unroll
+  for (int v = 0; v < 16; ++v)
+    e[v] = (k < K && v < nv) ? __ldg(reinterpret_cast<const float4*>(cb + (size_t)k * D) + v) : make_float4(0.f, 0.f, 0.f, 0.f);
+  // Rows are scanned FOUR per trip (the per-row chain -- shared-memory reads, FMA chain, ten shuffles, two barriers, the
+  // final warp -- is latency, so four independent rows share it) and reach shared memory through cp.async one trip
+  // ahead; the CTA's row numbers are fetched 32 at a time so a row is one L2 round trip, not two dependent ones.
+  constexpr int RB = 4;
+  for (int i = threadIdx.x; i < 2 * RB * 64; i += 512) (&zs[0][0])[i] = 0.f;  // padded dims read as zero
+  const int mine = (nflag - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // rows of this CTA
+  for (int base = 0; base < mine; base += 32) {
+    const int cnt = (mine - base < 32) ? mine - base : 32;
+    __syncthreads();  // previous batch done with s_rows and the ring; the zero fill above is visible
+    if ((int)threadIdx.x < cnt) s_rows[threadIdx.x] = __ldg(work + blockIdx.x + (size_t)(base + threadIdx.x) * gridDim.x);
+    __syncthreads();
+    auto issue = [&](int t) {  // trip t: rows 4 t .. 4 t + 3 of this batch -> ring half t & 1
+      const int r = (int)threadIdx.x >> 6, d = (int)threadIdx.x & 63, j = RB * t + r;
+      if (r < RB && j < cnt && d < D) {
+        const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&zs[(t & 1) * RB + r][d]);
+        const float* src = z + (int64_t)s_rows[j] * D + d;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+      }
+      asm volatile("cp.async.commit_group;" ::: "memory");  // (possibly empty: keeps the group count uniform)
+    };
+    const int trips = (cnt + RB - 1) / RB;
+    issue(0);
+    for (int t = 0; t < trips; ++t) {
+      issue(t + 1);
+      asm volatile("cp.async.wait_group 1;" ::: "memory");  // trip t has landed (this thread's part)
+      __syncthreads();                                       // ... everyone's part; s_bv / s_bk of the previous trip consumed
+      float a[RB][4];
+#pragma unroll
+      for (int r = 0; r < RB; ++r)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) a[r][q] = 0.f;
+#pragma unroll
+      for (int v = 0; v < 16; ++v) {  // padded dims hold zeros on both sides
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+          const float4 z4 = *reinterpret_cast<const float4*>(&zs[(t & 1) * RB + r][4 * v]);
+          float& acc = a[r][v & 3];
+          if (metric == LIPVQ_METRIC_DOT) {
+            acc = fmaf(z4.x, e[v].x, acc); acc = fmaf(z4.y, e[v].y, acc); acc = fmaf(z4.z, e[v].z, acc); acc = fmaf(z4.w, e[v].w, acc);
+          } else {
+            float df;
+            df = z4.x - e[v].x; acc = fmaf(df, df, acc);
+            df = z4.y - e[v].y; acc = fmaf(df, df, acc);
+            df = z4.z - e[v].z; acc = fmaf(df, df, acc);
+            df = z4.w - e[v].w; acc = fmaf(df, df, acc);
+          }
+        }
+      }
+      float bv[RB];
+      int bk[RB];
+#pragma unroll
+      for (int r = 0; r < RB; ++r) {
+        const float av = (a[r][0] + a[r][1]) + (a[r][2] + a[r][3]);
+        bv[r] = (metric == LIPVQ_METRIC_L2) ? sqrtf(av) : (metric == LIPVQ_METRIC_DOT ? -av : av);
+        bk[r] = k;
+        if (k >= K || !(bv[r] == bv[r])) {  // NaN never wins (as in the other scans: val < best is false for NaN)
+          bv[r] = INFINITY;
+          bk[r] = 0x7fffffff;
+        }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+          const float ov = __shfl_xor_sync(0xffffffffu, bv[r], o);
+          const int ok = __shfl_xor_sync(0xffffffffu, bk[r], o);
+          if (ov < bv[r] || (ov == bv[r] && ok < bk[r])) {
+            bv[r] = ov;
+            bk[r] = ok;
+          }
+        }
+      }
+      if (lane == 0) {
+#pragma unroll
+        for (int r = 0; r < RB; ++r) {
+          s_bv[r][warp] = bv[r];
+          s_bk[r][warp] = bk[r];
+        }
+      }
+      __syncthreads();  // partial winners visible; every thread is done reading this ring half (refilled by issue(t + 2))
+      if (warp < RB && RB * t + warp < cnt) {  // warp r finishes row r of the trip
+        float fv = lane < 16 ? s_bv[warp][lane] : INFINITY;
+        int fk = lane < 16 ? s_bk[warp][lane] : 0x7fffffff;
+#pragma unroll
+        for (int o = 8; o > 0; o >>= 1) {
+          const float ov = __shfl_xor_sync(0xffffffffu, fv, o);
+          const int ok = __shfl_xor_sync(0xffffffffu, fk, o);
+          if (ov < fv || (ov == fv && ok < fk)) {
+            fv = ov;
+            fk = ok;
+          }
+        }
+        if (lane == 0) {
+          if (fk == 0x7fffffff) fk = 0;  // all-NaN row: torch would return the NaN's index; we return 0
+          const int64_t row = s_rows[RB * t + warp];
+          idx_out[row] = (int64_t)fk;
+          if (best_out) best_out[row] = (metric == LIPVQ_METRIC_DOT) ? -fv : fv;
+        }
+      }
+    }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
   }
 }
 
@@ -535,9 +832,21 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
   float* mu = (float*)(ws + plan.off_mu);
   const int vec = (D % 4 == 0) && aligned16(z) && aligned16(codebook);
   const int rs_blocks = 4 * sm_count();
-  const size_t rs_smem = (size_t)D * sizeof(float);
   int lpc = 1;  // lanes per code: enough to cover the row with one float4 (or one float) each, at most a warp
   while (lpc < 32 && lpc * (vec ? 4 : 1) < D) lpc <<= 1;
+  // small codebooks: staged in shared memory, one lane per code (rescore_smem_kernel)
+  const size_t rs_wide_smem = ((size_t)K * (D + 4) + D) * sizeof(float);
+  const bool rs_wide = vec && D <= 256 && rs_wide_smem <= 200 * 1024;
+  const size_t rs_smem = (size_t)D * sizeof(float);
+  const bool rs_reg = vec && D <= 64 && K <= 512;  // one code per thread, held in registers (rescore_reg_kernel)
+  if (rs_wide) {
+    static size_t smem_set[kMaxDevices] = {};  // the attribute is per device
+    const int dev_ = current_device();
+    if (rs_wide_smem > smem_set[dev_]) {
+      LIPVQ_CUDA(cudaFuncSetAttribute(rescore_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rs_wide_smem));
+      smem_set[dev_] = rs_wide_smem;
+    }
+  }
   LIPVQ_REQUIRE(rs_smem <= 48 * 1024, "nn_search: D=%d too large for the rescore kernel", D);
 
   if (plan.algo == LIPVQ_ALGO_TCGEN05) {
@@ -548,9 +857,18 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
     if (rc != LIPVQ_OK) return rc;
     static const bool dbg_no_tails = getenv("LIPVQ_DEBUG_NO_TAILS") != nullptr;  // timing experiments only
     if (dbg_no_tails) return LIPVQ_OK;
-    LIPVQ_CUDA(launch_pdl(rescore_kernel, dim3(rs_blocks), dim3(256), rs_smem, stream, z, D, codebook, K, metric, count,
-                          (const int*)&hdr->flagged, queue, (const int*)(queue == work ? nullptr : work),
-                          search_skip_rows(N, D, K), idx_out, (float*)nullptr, stats_out, vec, lpc));
+    if (rs_reg)
+      LIPVQ_CUDA(launch_pdl(rescore_reg_kernel, dim3(sm_count()), dim3(512), 0, stream, z, D, codebook, K, metric, count,
+                            (const int*)&hdr->flagged, queue, (const int*)(queue == work ? nullptr : work),
+                            search_skip_rows(N, D, K), idx_out, (float*)nullptr, stats_out));
+    else if (rs_wide)
+      LIPVQ_CUDA(launch_pdl(rescore_smem_kernel, dim3(sm_count()), dim3(256), rs_wide_smem, stream, z, D, codebook, K, metric, count,
+                            (const int*)&hdr->flagged, queue, (const int*)(queue == work ? nullptr : work),
+                            search_skip_rows(N, D, K), idx_out, (float*)nullptr, stats_out));
+    else
+      LIPVQ_CUDA(launch_pdl(rescore_kernel<4, 1>, dim3(rs_blocks), dim3(256), rs_smem, stream, z, D, codebook, K, metric, count,
+                            (const int*)&hdr->flagged, queue, (const int*)(queue == work ? nullptr : work),
+                            search_skip_rows(N, D, K), idx_out, (float*)nullptr, stats_out, vec, lpc));
     LIPVQ_LAUNCHED("rescore_kernel");
     if (best_out) return search_best_values(z, N, D, codebook, metric, idx_out, best_out, stream);
     return LIPVQ_OK;
@@ -575,8 +893,15 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
                                                                          psecond, pidx, gamma_en, gamma, gamma_ref, hdr, work,
                                                                          idx_out, best_out);
   LIPVQ_LAUNCHED("finalize_kernel");
-  rescore_kernel<<<rs_blocks, 256, rs_smem, stream>>>(z, D, codebook, K, metric, &hdr->flagged, &hdr->flagged, work,
-                                                      (const int*)nullptr, 0, idx_out, best_out, stats_out, vec, lpc);
+  if (rs_reg)
+    rescore_reg_kernel<<<sm_count(), 512, 0, stream>>>(z, D, codebook, K, metric, &hdr->flagged, &hdr->flagged, work,
+                                                      (const int*)nullptr, 0, idx_out, best_out, stats_out);
+  else if (rs_wide)
+    rescore_smem_kernel<<<sm_count(), 256, rs_wide_smem, stream>>>(z, D, codebook, K, metric, &hdr->flagged, &hdr->flagged, work,
+                                                      (const int*)nullptr, 0, idx_out, best_out, stats_out);
+  else
+    rescore_kernel<4, 1><<<rs_blocks, 256, rs_smem, stream>>>(z, D, codebook, K, metric, &hdr->flagged, &hdr->flagged, work,
+                                                          (const int*)nullptr, 0, idx_out, best_out, stats_out, vec, lpc);
   LIPVQ_LAUNCHED("rescore_kernel");
   return LIPVQ_OK;
 }

@@ -17,6 +17,12 @@ iters = int(sys.argv[5]) if len(sys.argv) > 5 and sys.argv[5].isdigit() else 6
 g = torch.Generator().manual_seed(0)
 cb = ((torch.rand(K, D, generator=g) * 2 - 1) * math.sqrt(6.0 / D)).cuda()
 z = (torch.rand(N, D, generator=g) if mode == "uniform" else torch.sigmoid(0.05 * torch.randn(N, D, generator=g))).cuda()
+nt = next((int(a.split("=")[1]) for a in sys.argv if a.startswith("--ties=")), 0)
+if nt:  # nt rows sit (almost) midway between two codes: the fp16 pass cannot certify them (the cliff case of the N >= 2 runs)
+    rows = torch.randperm(N, generator=g)[:nt]
+    a_, b_ = torch.randint(0, K, (nt,), generator=g), torch.randint(0, K, (nt,), generator=g)
+    mid = 0.5 * (cb.cpu()[a_] + cb.cpu()[b_]) + 1e-7 * torch.randn(nt, D, generator=g)
+    z[rows.cuda()] = mid.cuda()
 ws = torch.empty(ops.search_workspace_bytes(N, D, K, lipvq.METRIC_L2, lipvq.ALGO_TCGEN05), dtype=torch.uint8, device="cuda")
 idx = torch.empty(N, dtype=torch.int64, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
