@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 3
+#define LIPVQ_ABI_VERSION 4
 #define LIPVQ_API __attribute__((visibility("default")))
 
 enum {
@@ -138,6 +138,24 @@ LIPVQ_API int lipvq_gather_ste_loss_bwd_f32(const float* z, const float* z_q, co
  * --------------------------------------------------------------------------------------------- */
 LIPVQ_API int lipvq_ema_stats_f32(const float* z, const int64_t* idx, int64_t N, int D, int K, float* counts, float* sums,
                         void* stream);
+/* Deterministic variants of the two per-code sums above (scatter_det.cu).  lipvq_code_sort_i64 puts the tokens in code
+ * order with a STABLE counting sort (integer work only); the *_sorted calls then add every code's rows in ascending token
+ * order, one writer per output row: bit-identical results run to run, no floating-point atomics.  The legacy calls above
+ * accumulate with atomics (sums correct to rounding, order varies).  Semantics are otherwise the same (ACCUMULATE into
+ * counts / sums / dcodebook; out-of-range codes are clamped to [0, K)).
+ * workspace: lipvq_code_sort_workspace_bytes(N, D, K) bytes of device memory, 16-byte aligned, owned by the caller; it
+ * must be passed unchanged from the sort to the sums, and re-sorted whenever idx changes.  Shapes: 1 <= N < 2^31,
+ * D % 4 == 0, 4 <= D <= 128, 1 <= K <= 8192 (workspace_bytes returns 0 otherwise).  Replaces the same reference lines as
+ * lipvq_ema_stats_f32 / lipvq_gather_ste_loss_bwd_f32 (hq_vae.py:262-275; algo/heirarchical_vqvae.py:518-530). */
+LIPVQ_API size_t lipvq_code_sort_workspace_bytes(int64_t N, int D, int K);
+LIPVQ_API int lipvq_code_sort_i64(const int64_t* idx, int64_t N, int D, int K, void* workspace, size_t workspace_bytes,
+                                  void* stream);
+LIPVQ_API int lipvq_ema_stats_sorted_f32(const float* z, int64_t N, int D, int K, void* workspace, size_t workspace_bytes,
+                                         float* counts, float* sums, void* stream);
+LIPVQ_API int lipvq_gather_ste_loss_bwd_sorted_f32(const float* z, const float* z_q, const float* dzq_up,
+                                                   const float* gscale_dev, float w_commit, float w_codebook, int ste,
+                                                   const float* sigmoid_out, int64_t N, int D, int K, void* workspace,
+                                                   size_t workspace_bytes, float* dz_out, float* dcodebook, void* stream);
 /* size <- decay*size + (1-decay)*counts ; ema_sum <- decay*ema_sum + (1-decay)*sums ;
  * codebook <- variant(ema_sum, size).  one_minus_decay is passed separately so the host can form
  * it in double like the reference does (1 - self.decay).  scratch: >= 8 bytes device. */

@@ -151,6 +151,34 @@ def ema_stats(z, idx, counts, sums):
                                     _chk(sums, F32, "sums"), _stream())
 
 
+def code_sort_workspace_bytes(N: int, D: int, K: int) -> int:
+    """0 when the shape is outside the deterministic path (D % 4, D <= 128, K <= 8192)."""
+    return int(lib.lipvq_code_sort_workspace_bytes(N, D, K))
+
+
+def code_sort(idx, D: int, K: int, workspace):
+    """Stable counting sort of the tokens by code into ``workspace`` (uint8, code_sort_workspace_bytes): the input of
+    ema_stats_sorted / gather_bwd_sorted.  Re-run whenever ``idx`` changes."""
+    _call(lib.lipvq_code_sort_i64, "code_sort", _chk(idx, I64, "idx"), idx.numel(), D, K, _chk(workspace, U8, "workspace"),
+          workspace.numel(), _stream())
+
+
+def ema_stats_sorted(z, workspace, counts, sums):
+    N, D = z.shape
+    K = counts.numel()
+    _call(lib.lipvq_ema_stats_sorted_f32, "ema_stats_sorted", _chk(z, F32, "z"), N, D, K, _chk(workspace, U8, "workspace"),
+          workspace.numel(), _chk(counts, F32, "counts"), _chk(sums, F32, "sums"), _stream())
+
+
+def gather_bwd_sorted(z, z_q, dzq_up, gscale, w_commit: float, w_codebook: float, ste: bool, sigmoid_out, K: int, workspace,
+                      dz_out, dcodebook):
+    N, D = z.shape
+    _call(lib.lipvq_gather_ste_loss_bwd_sorted_f32, "gather_bwd_sorted", _chk(z, F32, "z"), _chk(z_q, F32, "z_q"),
+          _chk(dzq_up, F32, "dzq_up", True), _chk(gscale, F32, "gscale", True), w_commit, w_codebook, int(ste),
+          _chk(sigmoid_out, F32, "sigmoid_out", True), N, D, K, _chk(workspace, U8, "workspace"), workspace.numel(),
+          _chk(dz_out, F32, "dz_out", True), _chk(dcodebook, F32, "dcodebook"), _stream())
+
+
 def ema_apply(counts, sums, ema_size, ema_sum, codebook, decay: float, eps: float, variant: int, scratch):
     K, D = ema_sum.shape
     _call(lib.lipvq_ema_apply_f32, "ema_apply", _chk(counts, F32, "counts"), _chk(sums, F32, "sums"), K, D, decay, 1.0 - decay, eps,

@@ -54,6 +54,13 @@ class T1Buffers:
             "stats": torch.zeros(4, dtype=torch.int32, device=dev),
             "ws": torch.empty(max(1, ops.search_workspace_bytes(N, D, K)), dtype=torch.uint8, device=dev),
         }
+        # deterministic per-code sums (stable counting sort + ordered segment sums, csrc/scatter_det.cu): opt-in with
+        # LIPVQ_SCATTER=sorted -- bit-identical run to run, but measured slower than the shared-memory atomics of
+        # quantize.cu (spread codes: 70 vs 47 us for the two sums; a collapsed codebook: 240 vs 48 us), so not the default
+        import os
+        nbytes = ops.code_sort_workspace_bytes(N, D, K) if (N >= 4096 and os.environ.get("LIPVQ_SCATTER", "atomic") == "sorted") else 0
+        self.sort_ws = torch.empty(nbytes, dtype=torch.uint8, device=dev) if nbytes else None
+        self.sorted_ok = False  # sort_ws holds the order of the CURRENT t["idx"]
 
     def alloc_derivatives(self):
         N, H, dev = self.N, self.H, self.device
@@ -85,6 +92,7 @@ def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: 
         ops.linear_fwd_dual(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, t["a2"], t["da2_act"])
     ops.linear_fwd(t["a2"], A.ACT_NONE, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"])
     ops.nn_search(t["z_e"], p["quantizer.codebook"], A.METRIC_L2, algo, out=t["idx"], workspace=t["ws"])
+    b.sorted_ok = False
     if encode_only:
         return
     if not getattr(b, "zeroed_by_caller", False):  # the trainer clears sq and G with one fill at the start of the step
@@ -119,8 +127,15 @@ def backward(p: Dict[str, torch.Tensor], g: Dict[str, torch.Tensor], x: torch.Te
     ops.linear_bwd_x(t["dc1"], p["decoder.0.weight"], None, A.ACT_NONE, out=t["dzq"])
     # quantizer: codebook rows get recon grad + 0.25*codebook-loss grad; encoder gets 0.25*commitment grad,
     # already multiplied by sigmoid'(.) so it is the gradient at the Lipschitz layer's pre-activation
-    ops.gather_bwd(t["z_e"], t["z_q"], t["idx"], t["dzq"], gscale, 0.25, 0.25, False, t["z_e"], b.K, t["dzpre"],
-                   g["quantizer.codebook"])
+    if b.sort_ws is not None:
+        if not b.sorted_ok:
+            ops.code_sort(t["idx"], b.D, b.K, b.sort_ws)
+            b.sorted_ok = True
+        ops.gather_bwd_sorted(t["z_e"], t["z_q"], t["dzq"], gscale, 0.25, 0.25, False, t["z_e"], b.K, b.sort_ws, t["dzpre"],
+                              g["quantizer.codebook"])
+    else:
+        ops.gather_bwd(t["z_e"], t["z_q"], t["idx"], t["dzq"], gscale, 0.25, 0.25, False, t["z_e"], b.K, t["dzpre"],
+                       g["quantizer.codebook"])
     # Lipschitz layer: G = dL/dW_norm, then through min(1, softplus(ci)/||W_i||_1)
     if not getattr(b, "zeroed_by_caller", False):
         t["G"].zero_()
@@ -135,4 +150,10 @@ def backward(p: Dict[str, torch.Tensor], g: Dict[str, torch.Tensor], x: torch.Te
 
 def ema_stats(b: T1Buffers, counts: torch.Tensor, sums: torch.Tensor) -> None:
     """counts[K] += bincount(idx); sums[K,D] += onehot^T z_e  (hq_vae.py:264-271)."""
-    ops.ema_stats(b.t["z_e"], b.t["idx"], counts, sums)
+    if b.sort_ws is not None:
+        if not b.sorted_ok:
+            ops.code_sort(b.t["idx"], b.D, b.K, b.sort_ws)
+            b.sorted_ok = True
+        ops.ema_stats_sorted(b.t["z_e"], b.sort_ws, counts, sums)
+    else:
+        ops.ema_stats(b.t["z_e"], b.t["idx"], counts, sums)

@@ -185,6 +185,57 @@ def test_gather_bwd_and_stats_shared_memory_path(L):
         assert torch.allclose(sums.cpu(), ref, rtol=1e-4, atol=1e-3)
 
 
+def test_scatter_deterministic_sorted_path(L):
+    """D % 4 == 0, D <= 128, K <= 8192: the stable counting sort + ordered segment sums (scatter_det.cu).  Sums must be
+    bit-identical run to run (torch.equal), match index_add, and handle a collapsed assignment (one code owns everything:
+    its segment spans every piece), empty codes, out-of-range indices (clamped) and N not a multiple of the piece size."""
+    for case in ("spread", "collapsed", "one", "ragged"):
+        N, K, D = {"spread": (65536, 512, 64), "collapsed": (8192 + 37, 512, 64), "one": (5000, 64, 32),
+                   "ragged": (4097, 1000, 128)}[case]
+        g = torch.Generator().manual_seed(77)
+        z = torch.rand(N, D, generator=g)
+        cb = torch.randn(K, D, generator=g)
+        if case == "spread":
+            idx = torch.randint(0, K, (N,), generator=g)
+        elif case == "collapsed":
+            idx = torch.randint(0, 5, (N,), generator=g) * 100
+        elif case == "one":
+            idx = torch.full((N,), 7, dtype=torch.int64)
+        else:
+            idx = torch.randint(-3, K + 3, (N,), generator=g)
+        idc = idx.clamp(0, K - 1)
+        up = torch.randn(N, D, generator=g)
+        zd, id_, upd = z.to(DEV), idx.to(DEV), up.to(DEV)
+        zq = cb[idc].to(DEV)
+        outs = []
+        ws = torch.empty(L.ops.code_sort_workspace_bytes(N, D, K), dtype=torch.uint8, device=DEV)
+        assert ws.numel() > 0
+        for _ in range(2):
+            ws.fill_(0xAB)  # nothing may depend on the scratch's previous contents
+            counts, sums = torch.zeros(K, device=DEV), torch.zeros(K, D, device=DEV)
+            L.ops.code_sort(id_, D, K, ws)
+            L.ops.ema_stats_sorted(zd, ws, counts, sums)
+            dz, dcb = torch.empty_like(zd), torch.zeros(K, D, device=DEV)
+            L.ops.gather_bwd_sorted(zd, zq, upd, None, 0.25, 0.25, False, None, K, ws, dz, dcb)
+            outs.append((counts.cpu(), sums.cpu(), dz.cpu(), dcb.cpu()))
+        for a, b in zip(*outs):
+            assert torch.equal(a, b), case
+        counts, sums, dz, dcb = outs[0]
+        assert torch.equal(counts, torch.bincount(idc, minlength=K).float()), case
+        ref = torch.zeros(K, D, dtype=torch.float64).index_add_(0, idc, z.double())
+        assert torch.allclose(sums.double(), ref, rtol=1e-5, atol=1e-4 * max(1.0, float(counts.max()) / 1000)), case
+        coef = 2.0 / (N * D)
+        q = cb[idc]
+        assert torch.allclose(dz, 0.25 * coef * (z - q), rtol=1e-5, atol=1e-9), case
+        refg = torch.zeros(K, D, dtype=torch.float64).index_add_(0, idc, (0.25 * coef * (q - z) + up).double())
+        assert torch.allclose(dcb.double(), refg, rtol=1e-4, atol=2e-3 if case in ("collapsed", "one") else 1e-4), case
+        # accumulate semantics: a second call adds on top
+        counts2, sums2 = counts.clone().to(DEV), sums.clone().to(DEV)
+        L.ops.ema_stats_sorted(zd, ws, counts2, sums2)
+        assert torch.equal(counts2.cpu(), 2 * counts), case
+        assert torch.allclose(sums2.cpu(), 2 * sums, rtol=1e-6, atol=1e-6), case
+
+
 # ------------------------------------------------------------------------------------------------ K5 / K6
 @pytest.mark.parametrize("N,K,D", [(256, 64, 32), (4096, 512, 64), (333, 20, 208), (100, 9, 7)])
 def test_ema_stats_and_apply(L, N, K, D):
