@@ -156,6 +156,19 @@ LIPVQ_API int lipvq_gather_ste_loss_bwd_sorted_f32(const float* z, const float* 
                                                    const float* gscale_dev, float w_commit, float w_codebook, int ste,
                                                    const float* sigmoid_out, int64_t N, int D, int K, void* workspace,
                                                    size_t workspace_bytes, float* dz_out, float* dcodebook, void* stream);
+/* Allocation-free variant of code_sort + ema_stats_sorted.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  One call sorts idx and ACCUMULATES counts[k] += #tokens of code k, sums[k,:] += their z rows in
+ * ascending token order (bit-identical to the two-call sequence above).  Its scratch is a file-scope __device__ array of
+ * lipvq_ema_stats_static_max_bytes() = 8 MiB inside the library (held by every GPU that loads the library until exit);
+ * the call performs no cudaMalloc / cudaFree / cudaMallocAsync, only kernel launches.  Shapes as for lipvq_code_sort_i64
+ * AND lipvq_code_sort_workspace_bytes(N, D, K) <= 8 MiB (e.g. N = 65536, D = 64, K = 512 needs 2.9 MB), otherwise
+ * LIPVQ_ERR_INVALID with the sizes in lipvq_last_error().  Every call on a device shares the one array, which keeps the
+ * last call's contents (nothing in it needs to start at zero): calls that overlap on the GPU -- two streams, or two
+ * threads on one device -- race; serialise them. */
+LIPVQ_API size_t lipvq_ema_stats_static_max_bytes(void);
+LIPVQ_API int lipvq_ema_stats_static_f32(const float* z, const int64_t* idx, int64_t N, int D, int K, float* counts,
+                                         float* sums, void* stream);
 /* size <- decay*size + (1-decay)*counts ; ema_sum <- decay*ema_sum + (1-decay)*sums ;
  * codebook <- variant(ema_sum, size).  one_minus_decay is passed separately so the host can form
  * it in double like the reference does (1 - self.decay).  scratch: >= 8 bytes device. */

@@ -28,6 +28,12 @@
 
 #include "common.cuh"
 
+// Scratch of lipvq_ema_stats_static_f32 (end of this file): lives in the module image, so every GPU that loads the
+// library holds these 8 MiB until the process exits.  In HOST code this name is only a stand-in for the symbol -- the
+// device address comes from cudaGetSymbolAddress (static_scratch_ptr below), once per device.
+constexpr size_t kStaticScratchBytes = (size_t)8 << 20;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
 namespace lipvq {
 namespace {
 
@@ -354,6 +360,28 @@ bool det_shape_ok(int64_t N, int D, int K) {
   return N >= 1 && N < ((int64_t)1 << 31) && D >= 4 && D % 4 == 0 && D <= 128 && K >= 1 && K <= 8192;
 }
 
+// device address of g_static_scratch on the CURRENT device (looked up once per device, with that device current)
+int static_scratch_ptr(uint8_t** out) {
+  static uint8_t* ptrs[kMaxDevices] = {};
+  const int dev = current_device();
+  if (dev < 0 || dev >= kMaxDevices) {
+    set_error("ema_stats_static: device ordinal %d out of range", dev);
+    return LIPVQ_ERR_INVALID;
+  }
+  if (ptrs[dev] == nullptr) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+    if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_static_scratch)");
+    if (p == nullptr) {
+      set_error("ema_stats_static: cudaGetSymbolAddress returned a null address");
+      return LIPVQ_ERR_CUDA;
+    }
+    ptrs[dev] = (uint8_t*)p;
+  }
+  *out = ptrs[dev];
+  return LIPVQ_OK;
+}
+
 }  // namespace
 }  // namespace lipvq
 
@@ -411,6 +439,38 @@ int lipvq_gather_ste_loss_bwd_sorted_f32(const float* z, const float* z_q, const
   BwdFn f{z, z_q, dzq_up, sigmoid_out, dz_out, gscale_dev, (float)(2.0 / ((double)N * (double)D)), w_commit, w_codebook, ste, D,
           sigmoid_out == z ? 1 : 0};
   return det_sum<BwdFn, 4>(f, N, D, K, pl, dcodebook, (float*)nullptr, stream);
+}
+
+size_t lipvq_ema_stats_static_max_bytes(void) { return kStaticScratchBytes; }
+
+// Sort + ordered sums in one call, scratch in g_static_scratch: no cudaMalloc / cudaFree / stream-ordered allocation,
+// only kernel launches.  Nothing in the scratch has to start at zero (every word the kernels read is written earlier in
+// the same call), so it is not cleared; it keeps the last call's contents, and calls that overlap on the GPU race.
+int lipvq_ema_stats_static_f32(const float* z, const int64_t* idx, int64_t N, int D, int K, float* counts, float* sums,
+                               void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(det_shape_ok(N, D, K), "ema_stats_static: needs 1 <= N < 2^31, D %% 4 == 0, 4 <= D <= 128, 1 <= K <= 8192 (N=%lld D=%d K=%d)",
+                (long long)N, D, K);
+  LIPVQ_REQUIRE(z && idx && counts && sums && aligned16(z) && aligned16(sums), "ema_stats_static: null or misaligned pointer");
+  const size_t need = det_plan(N, D, K, nullptr).bytes;
+  LIPVQ_REQUIRE(need <= kStaticScratchBytes,
+                "ema_stats_static: N=%lld D=%d K=%d needs %zu bytes of scratch, the built-in array holds %zu; use "
+                "lipvq_code_sort_i64 + lipvq_ema_stats_sorted_f32 with a caller-owned workspace",
+                (long long)N, D, K, need, kStaticScratchBytes);
+  uint8_t* base = nullptr;
+  const int rc = static_scratch_ptr(&base);
+  if (rc != LIPVQ_OK) return rc;
+  const DetPlan pl = det_plan(N, D, K, base);
+  LIPVQ_CUDA(launch_pdl(code_hist_kernel, dim3(pl.G), dim3(kSortThreads), (size_t)K * 4, stream, idx, N, K, pl.hist));
+  LIPVQ_LAUNCHED("code_hist_kernel");
+  LIPVQ_CUDA(launch_pdl(code_scan_kernel, dim3((unsigned)ceil_div64((int64_t)K * 32, 128)), dim3(128), 0, stream, pl.hist, pl.G, K,
+                        pl.total));
+  LIPVQ_LAUNCHED("code_scan_kernel");
+  LIPVQ_CUDA(launch_pdl(code_place_kernel, dim3(pl.G), dim3(kSortThreads), (size_t)(K + 1) * 4, stream, idx, N, K,
+                        (const int*)pl.hist, (const int*)pl.total, pl.seg, pl.perm, pl.skey));
+  LIPVQ_LAUNCHED("code_place_kernel");
+  StatsFn f{z, D};
+  return det_sum<StatsFn, 8>(f, N, D, K, pl, sums, counts, stream);
 }
 
 }  // extern "C"

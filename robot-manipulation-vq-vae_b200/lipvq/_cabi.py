@@ -39,6 +39,8 @@ SIGNATURES = {
     "lipvq_code_sort_i64": (_i, [_p, _i64, _i, _i, _p, _sz, _p]),
     "lipvq_ema_stats_sorted_f32": (_i, [_p, _i64, _i, _i, _p, _sz, _p, _p, _p]),
     "lipvq_gather_ste_loss_bwd_sorted_f32": (_i, [_p, _p, _p, _p, _f, _f, _i, _p, _i64, _i, _i, _p, _sz, _p, _p, _p]),
+    "lipvq_ema_stats_static_max_bytes": (_sz, []),
+    "lipvq_ema_stats_static_f32": (_i, [_p, _p, _i64, _i, _i, _p, _p, _p]),
     "lipvq_ema_apply_f32": (_i, [_p, _p, _i, _i, _f, _f, _f, _i, _p, _p, _p, _p, _p]),
     "lipvq_usage_stats_f32": (_i, [_p, _i, _p, _p, _p, _p]),
     "lipvq_codebook_usage_f32": (_i, [_p, _i, _f, _p, _p]),
