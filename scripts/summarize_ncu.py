@@ -43,12 +43,12 @@ def full(path, out):
     hdr, units = rows[0], rows[1]
     import json
     for r in rows[2:]:
-        if "search_fused_kernel<1>" in r[hdr.index("Kernel Name")] or "search_fused_kernel<(int)1>" in r[hdr.index("Kernel Name")]:
+        if "search_p1_kernel" in r[hdr.index("Kernel Name")]:
             def gb(k):
                 v, u = float(r[hdr.index(k)].replace(",", "")), units[hdr.index(k)]
                 return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}.get(u, 1)
             with open("profiles/search_traffic.json", "w") as tf:
-                json.dump({"kernel": "search_fused_kernel<1>", "source": path,
+                json.dump({"kernel": "search_p1_kernel", "source": path,
                            "dram_bytes_per_launch": gb("dram__bytes_read.sum") + gb("dram__bytes_write.sum")}, tf)
     for r in rows[2:]:
         out.write(f"\n### {r[hdr.index('Kernel Name')][:120]}\n")
