@@ -192,6 +192,53 @@ def _time_events(fn, iters, flush=None):
     return statistics.mean(durs), min(durs)
 
 
+def _time_rotating(fn, bufs, iters, streamed=False):
+    """mean / min duration in us of fn(buf) over calls that walk through `bufs` (together larger than the L2, so every
+    call finds its input in HBM; nothing is flushed, small per-launch state such as a prepared codebook stays in L2 as it
+    does in a real run).
+    streamed=False: an event pair and a synchronize around every single call; a short spin kernel is queued first so the
+    host has issued the launch before the GPU reaches the first event (otherwise the event pair times the Python call).
+    streamed=True: the len(bufs) calls are captured once as a CUDA graph (no host time between launches) and replayed
+    back to back between ONE event pair: mean = total / launches."""
+    n = len(bufs)
+    for i in range(n):
+        fn(bufs[i])
+    torch.cuda.synchronize()
+    if streamed:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for i in range(n):
+                fn(bufs[i])
+        torch.cuda.current_stream().wait_stream(side)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for i in range(n):
+                fn(bufs[i])
+        reps = max(1, iters // n)
+        g.replay()
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(reps):
+            g.replay()
+        b.record()
+        torch.cuda.synchronize()
+        t = a.elapsed_time(b) * 1e3 / (reps * n)
+        del g
+        return t, t
+    durs = []
+    for i in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda._sleep(200000)
+        a.record()
+        fn(bufs[i % n])
+        b.record()
+        torch.cuda.synchronize()
+        durs.append(a.elapsed_time(b) * 1e3)
+    return statistics.mean(durs), min(durs)
+
+
 def search_sweep(dev, hbm, tf_burst, flush, cpu_rows=256):
     """BASELINE config 3: K in {512, 4096, 65536} x D in {64, 256}, N = 65536, raw latents z ~ U(0,1), with the
     two baselines the config names: torch.cdist + argmin on the host cores and eager on the same B200."""
@@ -209,6 +256,10 @@ def search_sweep(dev, hbm, tf_burst, flush, cpu_rows=256):
         iters = 3 if K * D >= 65536 * 64 else 8
         us, mn = _time_events(lambda: ops.nn_search(z, cb, lipvq.METRIC_L2, algo, out=idx, workspace=ws), iters, flush)
         _, st = ops.nn_search(z, cb, lipvq.METRIC_L2, algo, want_stats=True, workspace=ws)
+        us_prep = None
+        if ops.search_prepared_supported(N, D, K):  # resident codebook: the prepared pair (one launch per search)
+            ops.nn_search_prepare(cb, ws, lipvq.METRIC_L2, center=z)
+            us_prep, _ = _time_events(lambda: ops.nn_search_prepared(z, cb, ws, lipvq.METRIC_L2, out=idx), iters, flush)
         eager_us, _ = _time_events(lambda: torch.cdist(z, cb).argmin(dim=1), 2 if K >= 65536 else 4, flush)
         ref_idx = torch.cdist(z[:2048], cb, compute_mode="donot_use_mm_for_euclid_dist").argmin(dim=1)
         flops = 2.0 * N * K * D
@@ -217,6 +268,7 @@ def search_sweep(dev, hbm, tf_burst, flush, cpu_rows=256):
                     "frac_hbm": round((N * (4 * D + 8) + K * D * 4) / us / 1e3 / hbm, 4),
                     "rows_uncertified_by_fp16_pass": int(st[1]), "rows_exact_scan": int(st[0]),
                     "index_mismatch_vs_eager_direct_2048": int((idx[:2048] != ref_idx).sum()),
+                    "us_prepared_codebook": None if us_prep is None else round(us_prep, 1),
                     "baseline_gpu_eager_us": round(eager_us, 1),
                     "baseline_cpu_us": round(cpu_cdist_argmin_us(N, K, D, rows=cpu_rows if K < 65536 else 64), 0)})
         del z, cb, ws, idx
@@ -312,23 +364,26 @@ def run_ours(args):
     # bulk tokenisation (encode + VQ), the metric's literal reading, on EVERY rank (the dataset shards over ranks, no
     # collective): resident inputs, and end to end = pinned-host actions in, int64 indices back to pinned host memory
     idx_host = torch.empty(N_TOK, dtype=torch.int64).pin_memory()
+    # (the weights are fixed while a dataset is tokenised: the first call derives the clamped to_latent weight and
+    #  prepares the codebook for the search, the following calls -- prepared=True -- are three linear layers + one search)
+    tr.tokenize(xs_dev[0])
     for i in range(3):
-        tr.tokenize(xs_dev[i % n_in])
+        tr.tokenize(xs_dev[i % n_in], prepared=True)
     _sync_all(world)
     t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record()
     for i in range(args.steps):
-        tr.tokenize(xs_dev[i % n_in])
+        tr.tokenize(xs_dev[i % n_in], prepared=True)
     t1.record()
     _sync_all(world)
     ms_tok = t0.elapsed_time(t1)
     for i in range(2):
-        idx_host.copy_(tr.tokenize(xs_host[i % n_in]), non_blocking=True)
+        idx_host.copy_(tr.tokenize(xs_host[i % n_in], prepared=True), non_blocking=True)
     _sync_all(world)
     t2, t3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t2.record()
     for i in range(args.steps):
-        idx_host.copy_(tr.tokenize(xs_host[i % n_in]), non_blocking=True)
+        idx_host.copy_(tr.tokenize(xs_host[i % n_in], prepared=True), non_blocking=True)
     t3.record()
     _sync_all(world)
     ms_tok_e2e = t2.elapsed_time(t3)
@@ -346,9 +401,31 @@ def run_ours(args):
         #     z_e / codebook, L2 flushed (written) before every call ---
         z_e, cb = tr.bufs.t["z_e"], tr.p["quantizer.codebook"]
         algo = ops.pick_algo(N_TOK, D, K)
-        sd, sd_min = _time_events(lambda: ops.nn_search(z_e, cb, lipvq.METRIC_L2, algo, out=tr.bufs.t["idx"],
-                                                        workspace=tr.bufs.t["ws"]), 20, flush)
-        _, st = ops.nn_search(z_e, cb, lipvq.METRIC_L2, algo, want_stats=True, workspace=tr.bufs.t["ws"])
+        ws = tr.bufs.t["ws"]
+        idx_buf = tr.bufs.t["idx"]
+        un, un_min = _time_events(lambda: ops.nn_search(z_e, cb, lipvq.METRIC_L2, algo, out=idx_buf, workspace=ws), 20, flush)
+        # ten copies of the step's latents (10 x 16.8 MB > the 126 MB L2), used in turn: every call reads its rows from HBM
+        zrot = [z_e.clone() for _ in range(10)]
+        if tr.search_prepared:
+            # the product path: the codebook is prepared once per codebook version (after each training step's update,
+            # once for a tokenisation run); a search is then ONE launch
+            pu, _ = _time_events(lambda: ops.nn_search_prepare(cb, ws, lipvq.METRIC_L2, center=z_e), 20, flush)
+            call = lambda zz: ops.nn_search_prepared(zz, cb, ws, lipvq.METRIC_L2, out=idx_buf)
+            wf, wf_min = _time_events(lambda: call(z_e), 20, flush)
+            _, st = ops.nn_search_prepared(z_e, cb, ws, lipvq.METRIC_L2, want_stats=True)
+            kname = ("lipvq_nn_search_prepared_f32 = search_p1_kernel, ONE launch (bulk copy of the prepared code image, fp16 "
+                     "tcgen05 pass with a best-only fold + exact near-best mask, certification, in-kernel settling of "
+                     "uncertified rows); the codebook-only preparation (search_prep_kernel, once per codebook version) is "
+                     "timed separately as us_prepare; us_unprepared = lipvq_nn_search_f32 (one call doing both)")
+        else:
+            pu = None
+            call = lambda zz: ops.nn_search(zz, cb, lipvq.METRIC_L2, algo, out=idx_buf, workspace=ws)
+            wf, wf_min = un, un_min
+            _, st = ops.nn_search(z_e, cb, lipvq.METRIC_L2, algo, want_stats=True, workspace=ws)
+            kname = "lipvq_nn_search_f32; algo=" + {1: "simt_f32", 2: "tcgen05"}[algo]
+        iso, iso_min = _time_rotating(call, zrot, 40)
+        sd, sd_min = _time_rotating(call, zrot, 200, streamed=True)
+        del zrot
         flops = 2.0 * N_TOK * K * D
         bytes_alg = N_TOK * (4 * D + 8) + K * D * 4
         traffic = None
@@ -358,17 +435,25 @@ def run_ours(args):
         except Exception:
             pass
         step_us = ms / args.steps * 1e3
-        extra["roofline"] = {"bound": "tensor", "kernel": "lipvq_nn_search_f32 = search_p1_kernel (one launch: cooperative codebook "
-                             "preparation + fp16 tcgen05 pass, best-only fold + exact near-best mask, certification) + "
-                             "search_fused<3> / exact scan (both empty unless rows stay uncertified); algo="
-                             + {1: "simt_f32", 2: "tcgen05"}[algo],
+        extra["roofline"] = {"bound": "tensor", "kernel": kname,
                              "achieved": flops / sd / 1e6, "peak": tf_burst, "unit": "TFLOP/s",
                              "frac": flops / sd / 1e6 / tf_burst, "traffic": traffic,
                              "peak_source": src + " (bf16 dense burst)", "us_per_launch": sd, "us_per_launch_min": sd_min,
+                             "timing": "us_per_launch: 200 back-to-back launches (a captured graph of ten, replayed twenty times) "
+                                       "between ONE CUDA-event pair, total / 200, the inputs rotating through ten copies of the "
+                                       "step's latents (168 MB > L2: every launch reads its rows from HBM; no flush); us_per_launch_isolated: the same rotation with an "
+                                       "event pair and a synchronize around every single launch (adds the launch latency of a "
+                                       "lone kernel); us_per_launch_writeflush: isolated, with 256 MB written through the L2 "
+                                       "before every launch (the L2 is then full of dirty lines that every miss must evict "
+                                       "first; the r1 / r2a way of measuring)",
+                             "us_per_launch_isolated": iso, "us_per_launch_isolated_min": iso_min,
+                             "us_per_launch_writeflush": wf, "us_per_launch_writeflush_min": wf_min,
+                             "frac_isolated": flops / iso / 1e6 / tf_burst, "frac_writeflush": flops / wf / 1e6 / tf_burst,
+                             "us_prepare": pu, "us_unprepared": un, "us_unprepared_min": un_min,
                              "algorithmic_flops": flops, "algorithmic_bytes": bytes_alg,
                              "hbm_frac": bytes_alg / sd / 1e3 / hbm, "share_of_step": sd / step_us,
                              "rows_rescored_exactly": int(st[0]), "rows_uncertified_by_fp16_pass": int(st[1]),
-                             "l2": "flushed by writing 256 MB before every call"}
+                             "l2": "inputs larger than L2 (ten 16.8 MB latent buffers in turn); see timing"}
         # --- the step-dominant kernel: the tensor-core linear layer (11 forward / dX launches + 6 dW launches per step).
         #     Representative launch: encoder.2 (64 -> 128, GELU + derivative), HBM-bound by bytes ---
         a1, a2, da2 = tr.bufs.t["a1"], tr.bufs.t["a2"], tr.bufs.t["da2_act"]
@@ -398,7 +483,8 @@ def run_ours(args):
                 "e2e": {"value": chunks / (ms_e2e * 1e-3), "unit": "chunks/s",
                         "h2d_bytes_per_step": N_TOK * F_ * 4, "d2h_bytes_per_step": 16},
                 "tokenize": {"value": chunks / (ms_tok * 1e-3), "unit": "chunks/s", "ms_per_step": ms_tok / args.steps,
-                             "note": "encode+VQ only (the metric's literal reading), every rank on its own shard, inputs resident"},
+                             "note": "encode+VQ only (the metric's literal reading), every rank on its own shard, inputs resident; "
+                                     "fixed weights: clamped to_latent weight and prepared codebook derived once before the loop"},
                 "tokenize_e2e": {"value": chunks / (ms_tok_e2e * 1e-3), "unit": "chunks/s", "ms_per_step": ms_tok_e2e / args.steps,
                                  "h2d_bytes_per_step": N_TOK * F_ * 4, "d2h_bytes_per_step": N_TOK * 8,
                                  "note": "TokenizerTrainer.tokenize(pinned host actions) -> int64 indices copied back to pinned "
@@ -427,7 +513,7 @@ def _teardown(tr, world):
     sys.stdout.flush()
     torch.cuda.synchronize()
     dist.barrier()
-    for name in ("_graph_full", "_graph_a", "_graph_b", "_graph_tok"):
+    for name in ("_graph_full", "_graph_a", "_graph_b", "_graph_tok", "_graph_tok_fast"):
         setattr(tr, name, None)
     gc.collect()
     torch.cuda.synchronize()

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 4
+#define LIPVQ_ABI_VERSION 5
 #define LIPVQ_API __attribute__((visibility("default")))
 
 enum {
@@ -102,6 +102,29 @@ LIPVQ_API int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float*
                         size_t workspace_bytes, void* stream);
 /* which algorithm AUTO resolves to for a shape (host-side, no launch) */
 LIPVQ_API int lipvq_nn_search_pick_algo(int64_t N, int D, int K, int metric);
+
+/* The same search split in two for callers whose codebook changes less often than they search it (bulk tokenisation:
+ * LFQQuantizer.forward under torch.no_grad with fixed weights, backbone_lfqvae_v5.py:39-46; a training step: the
+ * codebook changes once per step, hq_vae.py:277-279, and is prepared right after that update, off the search's
+ * critical path).  prepare: everything that depends on the codebook only -- centre, centred fp16 code tiles in the
+ * tensor core's shared-memory layout, the fp16 split of the code norms, the maxima the certification margin uses --
+ * is written into the workspace (one small launch).  prepared: ONE launch per search; it bulk-copies that image,
+ * runs the fp16 tcgen05 pass over all rows and settles the rows it cannot certify itself (exact fp32 scan, same
+ * arithmetic and tie rule as lipvq_nn_search_f32), so results are identical to lipvq_nn_search_f32's.
+ *   center_rows [n_center_rows, D] or NULL: rows whose mean becomes the centre (a batch of latents of the kind that
+ *   will be searched; <= 32 evenly spaced rows are read).  NULL: the codebook's own rows.  Any centre is valid.
+ *   The workspace is lipvq_nn_search_workspace_bytes(N, D, K, metric, LIPVQ_ALGO_TCGEN05) bytes for the largest N
+ *   searched; the prepared state sits at an offset that does not depend on N.  lipvq_nn_search_f32 on the same
+ *   workspace leaves the prepared state intact.
+ *   CONTRACT: `codebook` must hold the values it held when prepare ran (it is re-read only for near-ties); searching
+ *   a workspace that was never prepared for (K, D, metric) is detected on the device and costs an exact scan of every
+ *   row, not a wrong result.  supported(): 1 when the shape takes this path (codebook resident in shared memory and
+ *   N * K large enough for the tensor path), else 0 -- use lipvq_nn_search_f32. */
+LIPVQ_API int lipvq_nn_search_prepared_supported(int64_t N, int D, int K, int metric);
+LIPVQ_API int lipvq_nn_search_prepare_f32(const float* codebook, int K, int D, int metric, const float* center_rows,
+                        int64_t n_center_rows, void* workspace, size_t workspace_bytes, void* stream);
+LIPVQ_API int lipvq_nn_search_prepared_f32(const float* z, int64_t N, int D, const float* codebook, int K, int metric,
+                        int64_t* idx_out, int32_t* stats_out, void* workspace, size_t workspace_bytes, void* stream);
 
 /* row-wise F.normalize(x, dim=-1, eps=1e-12) (heirarchical_vqvae.py:441-445). y may alias x. */
 LIPVQ_API int lipvq_l2_normalize_rows_f32(const float* x, int64_t rows, int D, float* y, void* stream);

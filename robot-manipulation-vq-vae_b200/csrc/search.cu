@@ -762,10 +762,14 @@ SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo) {
   p.off_pbest = o;    o = align_up(o + sizeof(float) * (size_t)p.ksplit * N, 256);
   p.off_psecond = o;  o = align_up(o + sizeof(float) * (size_t)p.ksplit * N, 256);
   p.off_pidx = o;     o = align_up(o + sizeof(int) * (size_t)p.ksplit * N, 256);
-  p.off_work = o;     o = align_up(o + sizeof(int) * (size_t)(N > 0 ? N : 1), 256);
+  if (algo == LIPVQ_ALGO_TCGEN05) {  // prepared codebook state: before every N-dependent array, so prepare() needs no N
+    p.off_prep = o;   o = align_up(o + (search_p1_fits(N > 0 ? N : 1, D, K) ? search_p1_state_bytes(D, K) : 0), 1024);
+  }
+  const int64_t work_rows = (algo == LIPVQ_ALGO_TCGEN05 && search_p1_fits(N > 0 ? N : 1, D, K)) ? search_p1_queue_rows(N) : (N > 0 ? N : 1);
+  p.off_work = o;     o = align_up(o + sizeof(int) * (size_t)work_rows, 256);
   if (algo == LIPVQ_ALGO_TCGEN05) {
     const size_t eb = sizeof(uint16_t) * (size_t)p.Kp * p.Dp;
-    p.off_work2 = o; o = align_up(o + sizeof(int) * (size_t)(N > 0 ? N : 1), 256);
+    p.off_work2 = o; o = align_up(o + sizeof(int) * (size_t)work_rows, 256);
     p.off_ehi = o;  o = align_up(o + eb, 1024);
     p.off_elo = o;  o = align_up(o + eb, 1024);
     p.off_img = o;  o = align_up(o + (search_p1_fits(N, D, K) ? search_p1_image_bytes(D, K) : 0), 1024);
@@ -853,8 +857,12 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
     // prep + fp16 pass + 3-term pass (search_fused.cu); whatever is still queued gets the exact scan
     const int* queue = nullptr;
     const int* count = nullptr;
-    const int rc = search_fused_launch(z, N, D, codebook, K, metric, plan, ws, idx_out, stream, &queue, &count);
+    const int rc = search_fused_launch(z, N, D, codebook, K, metric, plan, ws, idx_out, stream, &queue, &count, stats_out);
     if (rc != LIPVQ_OK) return rc;
+    if (count == nullptr) {  // single-launch pass with its own exact scan: every row is settled
+      if (best_out) return search_best_values(z, N, D, codebook, metric, idx_out, best_out, stream);
+      return LIPVQ_OK;
+    }
     static const bool dbg_no_tails = getenv("LIPVQ_DEBUG_NO_TAILS") != nullptr;  // timing experiments only
     if (dbg_no_tails) return LIPVQ_OK;
     if (rs_reg)
@@ -904,6 +912,53 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
                                                           (const int*)nullptr, 0, idx_out, best_out, stats_out, vec, lpc);
   LIPVQ_LAUNCHED("rescore_kernel");
   return LIPVQ_OK;
+}
+
+int lipvq_nn_search_prepared_supported(int64_t N, int D, int K, int metric) {
+  if (N < 1 || D <= 0 || K <= 0) return 0;
+  if (const char* e = getenv("LIPVQ_SEARCH_PREPARED"))  // A/B switch: 0 = callers fall back to lipvq_nn_search_f32
+    if (e[0] == '0') return 0;
+  return lipvq_nn_search_pick_algo(N, D, K, metric) == LIPVQ_ALGO_TCGEN05 && search_p1_supported(N, D, K) ? 1 : 0;
+}
+
+int lipvq_nn_search_prepare_f32(const float* codebook, int K, int D, int metric, const float* center_rows,
+                                int64_t n_center_rows, void* workspace, size_t workspace_bytes, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(D > 0 && K > 0, "nn_search_prepare: bad shape D=%d K=%d", D, K);
+  LIPVQ_REQUIRE(metric >= LIPVQ_METRIC_L2 && metric <= LIPVQ_METRIC_DOT, "nn_search_prepare: bad metric %d", metric);
+  LIPVQ_REQUIRE(codebook && workspace, "nn_search_prepare: null pointer");
+  LIPVQ_REQUIRE(center_rows == nullptr || n_center_rows >= 1, "nn_search_prepare: center_rows given with %lld rows",
+                (long long)n_center_rows);
+  if (!search_p1_fits(1, D, K)) {
+    set_error("nn_search_prepare: codebook K=%d D=%d is streamed, not resident: use lipvq_nn_search_f32", K, D);
+    return LIPVQ_ERR_UNSUPPORTED;
+  }
+  const SearchPlan plan = make_search_plan(1, D, K, metric, LIPVQ_ALGO_TCGEN05);
+  LIPVQ_REQUIRE(workspace_bytes >= plan.off_prep + search_p1_state_bytes(D, K), "nn_search_prepare: workspace %zu too small",
+                workspace_bytes);
+  LIPVQ_REQUIRE(aligned16(workspace), "nn_search_prepare: workspace must be 16-byte aligned");
+  return search_prep_launch(codebook, K, D, metric, center_rows, n_center_rows, (char*)workspace + plan.off_prep, stream);
+}
+
+int lipvq_nn_search_prepared_f32(const float* z, int64_t N, int D, const float* codebook, int K, int metric,
+                                 int64_t* idx_out, int32_t* stats_out, void* workspace, size_t workspace_bytes,
+                                 void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(N >= 1 && D > 0 && K > 0, "nn_search_prepared: bad shape N=%lld D=%d K=%d", (long long)N, D, K);
+  LIPVQ_REQUIRE(N < ((int64_t)1 << 31), "nn_search_prepared: N=%lld exceeds int32 row ids", (long long)N);
+  LIPVQ_REQUIRE(metric >= LIPVQ_METRIC_L2 && metric <= LIPVQ_METRIC_DOT, "nn_search_prepared: bad metric %d", metric);
+  LIPVQ_REQUIRE(z && codebook && idx_out && workspace, "nn_search_prepared: null pointer");
+  if (!search_p1_fits(N, D, K)) {
+    set_error("nn_search_prepared: codebook K=%d D=%d is streamed, not resident: use lipvq_nn_search_f32", K, D);
+    return LIPVQ_ERR_UNSUPPORTED;
+  }
+  const SearchPlan plan = make_search_plan(N, D, K, metric, LIPVQ_ALGO_TCGEN05);
+  LIPVQ_REQUIRE(workspace_bytes >= plan.total, "nn_search_prepared: workspace %zu < required %zu", workspace_bytes, plan.total);
+  LIPVQ_REQUIRE(aligned16(workspace), "nn_search_prepared: workspace must be 16-byte aligned");
+  char* ws = (char*)workspace;
+  return search_p1_launch(z, N, D, codebook, K, metric, 0, nullptr, nullptr, nullptr, nullptr, nullptr,
+                          (SearchHdr*)(ws + plan.off_hdr), (int*)(ws + plan.off_work), nullptr, idx_out, stream,
+                          ws + plan.off_prep, 1, stats_out, (float*)(ws + plan.off_work2));
 }
 
 int lipvq_l2_normalize_rows_f32(const float* x, int64_t rows, int D, float* y, void* stream_) {

@@ -12,7 +12,9 @@ struct SearchHdr {
   unsigned excl_inv_bits;  // fused path: max over codes excluded from the fp16 contraction of 1/||e_k-mu|| (0 = none)
   int flagged2;         // fused path: rows the 3-term pass could not certify either -> exact rescore
   int arrived;          // single-launch first pass: CTAs that have published their slice of the prepared codebook
-  int pad[10];
+  int done;             // single-launch first pass with its own exact scan: CTAs that have finished (statistics ticket)
+  int ncand, nall;      // ... its statistics: codes evaluated exactly / rows whose every code was a candidate
+  int pad[7];
 };
 
 struct SearchPlan {
@@ -27,6 +29,7 @@ struct SearchPlan {
   size_t off_work2;                  // tcgen05 path: second-level queue
   size_t off_ehi, off_elo;           // tcgen05 path: fp16 hi/lo of -2(e-mu), [Kp][Dp]
   size_t off_img;                    // single-launch first pass: image of its shared-memory code tiles + norm slab
+  size_t off_prep;                   // prepared codebook state (search_prep_kernel); its position does not depend on N
   size_t total;
 };
 
@@ -36,18 +39,26 @@ SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo);
 // Writes idx_out for every certified row; *final_queue / *final_count name the rows left for the exact scan.
 bool search_fused_supported(int64_t N, int D, int K);
 void search_fused_plan(int D, int K, int* Kp, int* Dp);
+// (*final_count == nullptr: every row has been settled, nothing is left for the exact scan)
 int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, const SearchPlan& plan,
                         char* ws, int64_t* idx_out, cudaStream_t stream, const int** final_queue,
-                        const int** final_count);
+                        const int** final_count, int32_t* stats_out);
 // Single-launch first pass for codebooks that fit shared memory (search_p1.cu): codebook preparation + fp16 tcgen05 pass
 // with the packed-key fold.  Uncertified rows are appended to queue (*queue_count must be zero on entry); mu / enorm /
 // ehi / elo ([Kp_pub][Dp] fp16) / hdr are published for the later passes.
 bool search_p1_supported(int64_t N, int D, int K);
 bool search_p1_fits(int64_t N, int D, int K);  // geometry only (workspace planning)
 size_t search_p1_image_bytes(int D, int K);
+// prepared_state: nullptr (the kernel prepares the codebook itself) or the state search_prep_launch wrote for this codebook.
+// tail: the kernel settles its own uncertified rows (exact scan); queue then needs search_p1_queue_rows(N) ints.
 int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, int Kp_pub, float* mu,
                      float* enorm, void* ehi, void* elo, void* img, SearchHdr* hdr, int* queue, int* queue_count, int64_t* idx_out,
-                     cudaStream_t stream);
+                     cudaStream_t stream, void* prepared_state, int tail, int32_t* stats_out, float* queue_thr);
+size_t search_p1_state_bytes(int D, int K);
+int64_t search_p1_queue_rows(int64_t N);
+int search_prep_launch(const float* cb, int K, int D, int metric, const float* center, int64_t n_center, void* state,
+                       cudaStream_t stream);
+bool search_p1_tail();  // the single-launch pass settles its own rows (default; LIPVQ_P1_TAIL=0: later passes as in round 1)
 int search_skip_rows(int64_t N, int D, int K);
 int search_best_values(const float* z, int64_t N, int D, const float* cb, int metric, const int64_t* idx, float* best_out,
                        cudaStream_t stream);

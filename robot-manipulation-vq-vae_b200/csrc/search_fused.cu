@@ -931,7 +931,7 @@ void search_fused_plan(int D, int K, int* Kp, int* Dp) {
 // the exact scan in *final_queue / *final_count (device pointers inside the workspace).
 int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, const SearchPlan& plan,
                         char* ws, int64_t* idx_out, cudaStream_t stream, const int** final_queue,
-                        const int** final_count) {
+                        const int** final_count, int32_t* stats_out) {
   const int Kp = fused_kp(K);
   const bool staged = (D % 4 == 0) && aligned16(z);
   FusedGeom g1 = fused_geom(D, Kp, 1, staged);
@@ -980,9 +980,15 @@ int search_fused_launch(const float* z, int64_t N, int D, const float* cb, int K
     memset(&tm_z, 0, sizeof(tm_z));
   }
   if (use_p1) {
-    if ((rc = search_p1_launch(z, N, D, cb, K, metric, Kp, mu, enorm, ehi, elo, ws + plan.off_img, hdr, work, &hdr->flagged, idx_out, stream)) !=
-        LIPVQ_OK)
+    const int tail = search_p1_tail() ? 1 : 0;
+    if ((rc = search_p1_launch(z, N, D, cb, K, metric, Kp, mu, enorm, ehi, elo, ws + plan.off_img, hdr, work, &hdr->flagged, idx_out, stream,
+                               nullptr, tail, stats_out, reinterpret_cast<float*>(work2))) != LIPVQ_OK)
       return rc;
+    if (tail) {  // the kernel has settled its own uncertified rows: no later passes
+      *final_queue = nullptr;
+      *final_count = nullptr;
+      return LIPVQ_OK;
+    }
   } else {
     CUtensorMap tm_hi, tm_lo;
     if ((rc = make_map(&tm_hi, ehi, Kp, g1.Dp, g1.BN)) != LIPVQ_OK) return rc;

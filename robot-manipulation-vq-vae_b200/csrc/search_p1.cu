@@ -61,6 +61,23 @@ __device__ int g_trace_p1_n[16];
 #define TR(ev) do {} while (0)
 #endif
 
+// Prepared state of one codebook (search_prep_kernel -> search_p1_kernel, "prepared" mode): everything the search needs
+// that depends on the codebook only.  Lives in the search workspace, followed (at kStateHdr bytes) by the image of the
+// shared-memory code tiles + norm slab.
+constexpr int kStateParts = 64;
+constexpr int kStateHdr = 2048;
+constexpr int kStateMagic = 0x4c505631;
+struct P1State {
+  float mu[256];
+  float emax2_part[kStateParts];     // per prep CTA: max ||e-mu||^2 over its codes
+  float excl_inv_part[kStateParts];  // per prep CTA: max 1/||e-mu|| over its codes left out of the contraction (0 = none)
+  float mu_norm;
+  int nparts, magic, K, D, metric;
+  int flagged, done;                 // per-call counters of the search kernel; the last CTA of a call clears them
+  int ncand, nall;                   // statistics: candidates evaluated exactly / rows whose every code was a candidate
+};
+static_assert(sizeof(P1State) <= kStateHdr, "state header");
+
 struct P1Params {
   const float* z;
   const float* cb;
@@ -71,6 +88,16 @@ struct P1Params {
   int Kp_pub;     // rows of the published arrays (the later passes' padded code count)
   int early_trigger;  // griddepcontrol.launch_dependents right after set-up instead of at the end
   int slab_swap;  // debug: swap LBO/SBO of the no-swizzle descriptors
+  int prepared;   // the code image, mu and the code maxima come from a P1State written by search_prep_kernel
+  int tail;       // rows this pass cannot certify are settled HERE (exact fp32 scan at the end of the CTA): no later launches
+  int qcap;       // tail: queue_out / queue_thr are cut into per-CTA segments of qcap entries
+  float* queue_thr;  // tail: per queued row, the score threshold of the candidate filter
+  P1State* st;    // prepared
+  int* flagged_ctr;  // tail: grid-wide count of queued rows (statistics only) and the ticket that resets both
+  int* done_ctr;
+  int* ncand_ctr;    // tail statistics (only when stats_out is given): exact evaluations, rows scanned in full
+  int* nall_ctr;
+  int32_t* stats_out;
   // outputs for the later passes (search_fused_kernel<3>, rescore): published by slices of the grid
   float* mu_g;
   float* enorm_g;
@@ -158,6 +185,343 @@ struct RowBest {  // partial result of one epilogue group for one row, handed to
   int pad[3];
 };
 
+// Rows a CTA of search_p1_kernel could not certify are settled by the same CTA (one warp per row when there are many,
+// all warps per row when there are few: p1_tail_scan / p1_tail_coop below), in two steps:
+//   filter   the row's scores against ALL codes are recomputed on the CUDA cores from what is still in shared memory --
+//            the fp16 code tiles -2(e-mu), the fp16 split of ||e-mu||^2 -- with the row centred in fp32.  Each score is
+//            within the contraction's error bound of the true value (one operand is exact now), so every code that can be
+//            the nearest -- or tie with it inside the reference's own fp32 noise -- has a score <= thr, where thr = the
+//            row's best tensor-core score + 1.25 x the certification margin (written next to the row number; the margin
+//            is twice the error bound of a score, which is what the argument needs).  Codes
+//            that were left out of the contraction (sentinel norm) are always candidates; a non-finite thr (NaN rows,
+//            unusable row statistics, a workspace that was never prepared) makes every code a candidate.
+//   exact    the candidates (usually two or three) are evaluated as the stand-alone exact scan does: fp32 direct
+//            differences, four interleaved partial sums in a fixed order, sqrt for L2, lowest index on exact ties
+//            (torch.argmin's first-minimum rule), NaN never wins, an all-NaN row gets index 0.
+// No codebook traffic: staging the fp32 codebook per CTA (128 KB from L2, the same lines for all 148 CTAs) cost 18 us for
+// a few hundred rows.  Not inlined: its registers must not weigh on the fold loop of the kernel.
+// score of code k for the candidate filter: ||e_k-mu||^2 (fp16 split in the norm slab) + (z-mu) . (-2(e_k-mu)) (fp16 tile
+// row), fp32 accumulation in four interleaved partial sums.  Explicit shared-space loads: through generic pointers each
+// 16-byte load of 32 different tile rows was handled like a scattered global access.  The tiles do not change during the
+// scan, so their loads carry no ordering (volatile loads exposed one shared-memory latency per 16 bytes).
+template <bool ONE>
+__device__ __forceinline__ float tail_score(int k, int NC, uint32_t sB_s, uint32_t sE_s, uint32_t zc_s, const float (&zreg)[64],
+                                            float& en) {
+  constexpr int b_tile = kBN * kChunk * 2;
+  const int jt = k >> 8, r = k & 255;  // kBN = 256
+  uint2 nh;
+  asm("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(nh.x), "=r"(nh.y) : "r"(sE_s + slab_off(k, 0)));
+  const float2 n01 = __half22float2(*reinterpret_cast<const __half2*>(&nh.x));
+  const float2 n2 = __half22float2(*reinterpret_cast<const __half2*>(&nh.y));
+  en = (n01.x + n01.y) + n2.x;
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  if (ONE) {  // one 64-wide chunk (the tokenizer's own width): the centred row sits in registers
+    const uint32_t trow = sB_s + (uint32_t)(jt * b_tile + r * 128);
+    uint4 h[8];
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(h[q].x), "=r"(h[q].y), "=r"(h[q].z), "=r"(h[q].w) : "r"(trow + ((q ^ (r & 7)) << 4)));
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&h[q].x));
+      const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&h[q].y));
+      const float2 f2 = __half22float2(*reinterpret_cast<const __half2*>(&h[q].z));
+      const float2 f3 = __half22float2(*reinterpret_cast<const __half2*>(&h[q].w));
+      a0 = fmaf(zreg[8 * q + 0], f0.x, a0); a1 = fmaf(zreg[8 * q + 1], f0.y, a1); a2 = fmaf(zreg[8 * q + 2], f1.x, a2); a3 = fmaf(zreg[8 * q + 3], f1.y, a3);
+      a0 = fmaf(zreg[8 * q + 4], f2.x, a0); a1 = fmaf(zreg[8 * q + 5], f2.y, a1); a2 = fmaf(zreg[8 * q + 6], f3.x, a2); a3 = fmaf(zreg[8 * q + 7], f3.y, a3);
+    }
+  } else {
+    for (int c = 0; c < NC; ++c) {
+      const uint32_t trow = sB_s + (uint32_t)((jt * NC + c) * b_tile + r * 128);
+      const uint32_t zq = zc_s + (uint32_t)(c * kChunk * 4);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        uint4 h;
+        asm("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(h.x), "=r"(h.y), "=r"(h.z), "=r"(h.w) : "r"(trow + ((q ^ (r & 7)) << 4)));
+        float4 za, zb;  // (the centred row was written by this warp before a __syncwarp: ordered loads)
+        lds_f4(zq + 32 * q, za);
+        lds_f4(zq + 32 * q + 16, zb);
+        const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&h.x));
+        const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&h.y));
+        const float2 f2 = __half22float2(*reinterpret_cast<const __half2*>(&h.z));
+        const float2 f3 = __half22float2(*reinterpret_cast<const __half2*>(&h.w));
+        a0 = fmaf(za.x, f0.x, a0); a1 = fmaf(za.y, f0.y, a1); a2 = fmaf(za.z, f1.x, a2); a3 = fmaf(za.w, f1.y, a3);
+        a0 = fmaf(zb.x, f2.x, a0); a1 = fmaf(zb.y, f2.y, a1); a2 = fmaf(zb.z, f3.x, a2); a3 = fmaf(zb.w, f3.y, a3);
+      }
+    }
+  }
+  return en + ((a0 + a1) + (a2 + a3));
+}
+
+// exact value of code k for the row in zs (zeros past D), as the stand-alone exact scan computes it
+__device__ __forceinline__ float tail_exact(int k, const float* __restrict__ cb, const float* zs, int D, int metric, bool vec) {
+  const bool dotm = (metric == LIPVQ_METRIC_DOT);
+  const float* er = cb + (size_t)k * D;
+  float a[4] = {0.f, 0.f, 0.f, 0.f};
+  if (vec && D <= 64) {  // the tokenizer's own width: the code row in two batches of eight loads in flight together
+    const int nv = D >> 2;
+#pragma unroll
+    for (int hb = 0; hb < 2; ++hb) {
+      float4 x[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        x[u] = (8 * hb + u < nv) ? __ldg(reinterpret_cast<const float4*>(er) + 8 * hb + u) : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int v = 8 * hb + u;
+        if (v < nv) {
+          const float4 z4 = *reinterpret_cast<const float4*>(zs + 4 * v);
+          const int j = v & 3;
+          if (dotm) {
+            a[j] = fmaf(z4.x, x[u].x, a[j]); a[j] = fmaf(z4.y, x[u].y, a[j]); a[j] = fmaf(z4.z, x[u].z, a[j]); a[j] = fmaf(z4.w, x[u].w, a[j]);
+          } else {
+            float df;
+            df = z4.x - x[u].x; a[j] = fmaf(df, df, a[j]);
+            df = z4.y - x[u].y; a[j] = fmaf(df, df, a[j]);
+            df = z4.z - x[u].z; a[j] = fmaf(df, df, a[j]);
+            df = z4.w - x[u].w; a[j] = fmaf(df, df, a[j]);
+          }
+        }
+      }
+    }
+  } else if (vec) {
+    const int nv = D >> 2;
+    for (int v0 = 0; v0 < nv; v0 += 4) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int v = v0 + j;
+        if (v < nv) {
+          const float4 x = __ldg(reinterpret_cast<const float4*>(er) + v);
+          const float4 z4 = *reinterpret_cast<const float4*>(zs + 4 * v);
+          if (dotm) {
+            a[j] = fmaf(z4.x, x.x, a[j]); a[j] = fmaf(z4.y, x.y, a[j]); a[j] = fmaf(z4.z, x.z, a[j]); a[j] = fmaf(z4.w, x.w, a[j]);
+          } else {
+            float df;
+            df = z4.x - x.x; a[j] = fmaf(df, df, a[j]);
+            df = z4.y - x.y; a[j] = fmaf(df, df, a[j]);
+            df = z4.z - x.z; a[j] = fmaf(df, df, a[j]);
+            df = z4.w - x.w; a[j] = fmaf(df, df, a[j]);
+          }
+        }
+      }
+    }
+  } else {
+    for (int d0 = 0; d0 < D; d0 += 16) {  // the same partial-sum assignment: float4 v -> a[v & 3]
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int d = d0 + 4 * j + e;
+          if (d < D) {
+            const float zv = zs[d], ev = __ldg(er + d);
+            if (dotm) {
+              a[j] = fmaf(zv, ev, a[j]);
+            } else {
+              const float df = zv - ev;
+              a[j] = fmaf(df, df, a[j]);
+            }
+          }
+        }
+    }
+  }
+  const float av = (a[0] + a[1]) + (a[2] + a[3]);
+  return (metric == LIPVQ_METRIC_L2) ? sqrtf(av) : (dotm ? -av : av);
+}
+
+constexpr int kTailWarps = kThreads / 32;      // 13: every warp of the CTA takes part
+constexpr int kTailCoopRows = 8;               // up to this many queued rows a CTA works on each row with ALL its warps
+constexpr int kTailList = 64;                  // candidate list entries (per warp / per row)
+// per-warp scratch: centred row, row, candidate list; then the two row-level lists + counters of the cooperative form
+__device__ __forceinline__ int tail_warp_floats(int Dp) { return 2 * Dp + kTailList; }
+
+// One warp per row (many queued rows per CTA: the CTA is throughput-bound, rows are independent).
+__device__ __noinline__ void p1_tail_scan(const float* __restrict__ z, const float* __restrict__ cb, const int* __restrict__ rows,
+                                          const float* __restrict__ thrs, int64_t* __restrict__ idx_out, int D, int K, int Kp,
+                                          int NC, int metric, const uint8_t* sB, const uint8_t* sE, const float* mu_s,
+                                          float* scratch, int nq, int* ncand_ctr, int* nall_ctr) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Dp = NC * kChunk;
+  int n_eval = 0, n_all = 0;
+  float* zc = scratch + warp * tail_warp_floats(Dp);  // centred row, zeros past D
+  float* zs = zc + Dp;                                // the row itself, zeros past D
+  int* clist = reinterpret_cast<int*>(zs + Dp);       // candidates found by the filter, evaluated 32 at a time
+  const uint32_t sB_s = smem_u32(sB), sE_s = smem_u32(sE), zc_s = smem_u32(zc);
+  const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(cb) & 15) == 0);
+  for (int w = warp; w < nq; w += kTailWarps) {
+    const int64_t row = rows[w];
+    const float thr = thrs[w];
+    const bool all = !(thr < 3.0e38f);
+    const float* zr = z + row * (int64_t)D;
+    for (int d = lane; d < Dp; d += 32) {
+      const float v = (d < D) ? __ldg(zr + d) : 0.f;
+      zs[d] = v;
+      zc[d] = (d < D) ? v - mu_s[d] : 0.f;
+    }
+    __syncwarp();
+    float zreg[64];
+    if (NC == 1) {
+#pragma unroll
+      for (int v = 0; v < 16; ++v) {
+        float4 t;
+        lds_f4(zc_s + 16 * v, t);
+        zreg[4 * v] = t.x; zreg[4 * v + 1] = t.y; zreg[4 * v + 2] = t.z; zreg[4 * v + 3] = t.w;
+      }
+    }
+    float bv = INFINITY;
+    int bk = 0x7fffffff;
+    // exact evaluation of one candidate per lane: all lanes' code rows are in flight together (evaluating a candidate
+    // where the filter finds it serialised one L2 round trip per candidate)
+    auto evaluate = [&](int k) {
+      const float val = tail_exact(k, cb, zs, D, metric, vec);
+      if (val < bv || (val == bv && k < bk)) {  // lowest index on exact ties, whatever the order of evaluation
+        bv = val;
+        bk = k;
+      }
+    };
+    n_all += all ? 1 : 0;
+#ifdef LIPVQ_TAILPROF
+    const long long tp0 = clock64();
+#endif
+    int cnt = 0;  // candidates waiting in this warp's list (warp-uniform)
+    for (int k = lane; k < Kp; k += 32) {
+      bool cand = all;
+      if (!all) {
+        float en;
+        const float sc = (NC == 1) ? tail_score<true>(k, NC, sB_s, sE_s, zc_s, zreg, en) : tail_score<false>(k, NC, sB_s, sE_s, zc_s, zreg, en);
+        cand = (sc <= thr) || (en > 1.0e5f) || !(sc == sc);  // (sentinel norms: 3 x 65504)
+      }
+      cand = cand && k < K;
+      const unsigned m = __ballot_sync(0xffffffffu, cand);
+      if (cand) clist[cnt + __popc(m & ((1u << lane) - 1u))] = k;
+      cnt += __popc(m);
+      n_eval += __popc(m);
+      __syncwarp();
+      if (cnt >= 32) {  // a full batch: one candidate per lane
+        evaluate(clist[lane]);
+        const int rest = cnt - 32;
+        const int moved = (lane < rest) ? clist[32 + lane] : 0;
+        __syncwarp();
+        if (lane < rest) clist[lane] = moved;
+        cnt = rest;
+        __syncwarp();
+      }
+    }
+#ifdef LIPVQ_TAILPROF
+    const long long tp1 = clock64();
+#endif
+    if (lane < cnt) evaluate(clist[lane]);
+#ifdef LIPVQ_TAILPROF
+    const long long tp2 = clock64();
+    n_eval += (int)(tp1 - tp0);  // (profiling build: stats[2] = filter cycles, stats[3] = evaluation cycles)
+    n_all += (int)(tp2 - tp1);
+#endif
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int ok = __shfl_xor_sync(0xffffffffu, bk, o);
+      if (ov < bv || (ov == bv && ok < bk)) {
+        bv = ov;
+        bk = ok;
+      }
+    }
+    if (lane == 0) idx_out[row] = (int64_t)(bk == 0x7fffffff ? 0 : bk);
+    __syncwarp();  // the row buffers are rewritten by the next trip
+  }
+  if (ncand_ctr != nullptr && lane == 0) {
+    atomicAdd(ncand_ctr, n_eval);
+    if (n_all) atomicAdd(nall_ctr, n_all);
+  }
+}
+
+// A handful of queued rows per CTA (the usual case when there are any: a few hundred near-ties in a 65 536-token batch):
+// with one warp per row a lone warp walks all K codes -- ~10 000 cycles of dependent work while twelve warps idle -- and
+// every row pays its own chain of dependent loads (row number -> row -> candidates' code rows).  Here
+//   0. the rows are fetched together into CTA-level buffers (one chain of dependent loads for all of them),
+//   1. ALL warps filter every row (warp w takes codes 32 w .., 32 (w + 13) ..; the centred row is read from the shared
+//      buffer into registers), candidates go to the row's list in shared memory -- no barrier between rows,
+//   2. after one barrier warp r evaluates the candidates of row r: the rows' exact evaluations run side by side.
+// Called by every thread of the CTA, nq <= kTailCoopRows.  More candidates than a list holds: every code is evaluated.
+__device__ __noinline__ void p1_tail_coop(const float* __restrict__ z, const float* __restrict__ cb, const int* __restrict__ rows,
+                                          const float* __restrict__ thrs, int64_t* __restrict__ idx_out, int D, int K, int Kp,
+                                          int NC, int metric, const uint8_t* sB, const uint8_t* sE, const float* mu_s,
+                                          float* scratch, int nq, int* ncand_ctr, int* nall_ctr) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Dp = NC * kChunk;
+  float* zc_all = scratch;                          // [kTailCoopRows][Dp] centred rows, zeros past D
+  float* zs_all = zc_all + kTailCoopRows * Dp;      // [kTailCoopRows][Dp] the rows themselves
+  int* rlist = reinterpret_cast<int*>(zs_all + kTailCoopRows * Dp);  // [kTailCoopRows][kTailList]
+  int* rcnt = rlist + kTailCoopRows * kTailList;                       // [kTailCoopRows]
+  const uint32_t sB_s = smem_u32(sB), sE_s = smem_u32(sE);
+  const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(cb) & 15) == 0);
+  if ((int)threadIdx.x < nq) rcnt[threadIdx.x] = 0;
+  for (int i = threadIdx.x; i < nq * Dp; i += kThreads) {
+    const int w = i / Dp, d = i - w * Dp;
+    const float v = (d < D) ? __ldg(z + (int64_t)rows[w] * D + d) : 0.f;
+    zs_all[i] = v;
+    zc_all[i] = (d < D) ? v - mu_s[d] : 0.f;
+  }
+  __syncthreads();
+  for (int w = 0; w < nq; ++w) {
+    const float thr = thrs[w];
+    if (!(thr < 3.0e38f)) continue;  // every code is a candidate: left to the evaluation below
+    const uint32_t zc_s = smem_u32(zc_all + w * Dp);
+    float zreg[64];
+    if (NC == 1) {
+#pragma unroll
+      for (int v = 0; v < 16; ++v) {
+        float4 t;
+        lds_f4(zc_s + 16 * v, t);
+        zreg[4 * v] = t.x; zreg[4 * v + 1] = t.y; zreg[4 * v + 2] = t.z; zreg[4 * v + 3] = t.w;
+      }
+    }
+    for (int k = warp * 32 + lane; k < Kp; k += kTailWarps * 32) {
+      float en;
+      const float sc = (NC == 1) ? tail_score<true>(k, NC, sB_s, sE_s, zc_s, zreg, en) : tail_score<false>(k, NC, sB_s, sE_s, zc_s, zreg, en);
+      if (((sc <= thr) || (en > 1.0e5f) || !(sc == sc)) && k < K) {
+        const int pos = atomicAdd(&rcnt[w], 1);
+        if (pos < kTailList) rlist[w * kTailList + pos] = k;
+      }
+    }
+  }
+  __syncthreads();
+  if (warp < nq) {
+    const int w = warp;
+    const bool all = !(thrs[w] < 3.0e38f);
+    const int cnt = all ? kTailList + 1 : rcnt[w];
+    const float* zs = zs_all + w * Dp;
+    float bv = INFINITY;
+    int bk = 0x7fffffff;
+    auto evaluate = [&](int k) {
+      const float val = tail_exact(k, cb, zs, D, metric, vec);
+      if (val < bv || (val == bv && k < bk)) {  // lowest index on exact ties, whatever the order of evaluation
+        bv = val;
+        bk = k;
+      }
+    };
+    if (cnt > kTailList) {  // every code (non-finite threshold), or more candidates than the list holds
+      for (int k = lane; k < K; k += 32) evaluate(k);
+    } else {
+      for (int i = lane; i < cnt; i += 32) evaluate(rlist[w * kTailList + i]);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int ok = __shfl_xor_sync(0xffffffffu, bk, o);
+      if (ov < bv || (ov == bv && ok < bk)) {
+        bv = ov;
+        bk = ok;
+      }
+    }
+    if (lane == 0) {
+      idx_out[rows[w]] = (int64_t)(bk == 0x7fffffff ? 0 : bk);
+      if (ncand_ctr != nullptr) {
+        atomicAdd(ncand_ctr, cnt > kTailList ? K : cnt);
+        if (all) atomicAdd(nall_ctr, 1);
+      }
+    }
+  }
+}
+
 // Warp roles (416 threads, one CTA per SM):
 //   0-7   epilogue: warp w owns TMEM lanes 32*(w&3).. (= rows); group w>>2 drains every second code tile
 //   8-11  converters: fp32 z rows -> centred fp16 -> swizzled A tiles (+ per-row ||z-mu||^2, ||z||^2)
@@ -184,6 +548,7 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
   const uint32_t bar_x_full = smem_u32(bars + 16), bar_x_empty = smem_u32(bars + 18);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
   const uint32_t bar_img = smem_u32(bars + 21), bar_mu = smem_u32(bars + 22);
+  int* s_qn = reinterpret_cast<int*>(bars + 23);  // tail: rows this CTA has queued for its exact scan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 #ifdef LIPVQ_TRACE
@@ -206,6 +571,7 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
     }
     mbar_init(bar_img, 1);
     mbar_init(bar_mu, 1);
+    *s_qn = 0;
     for (int s = 0; s < 4; ++s) {
       mbar_init(bar_z_full + 8 * s, 1);
       mbar_init(bar_z_empty + 8 * s, kCvtWarps);
@@ -233,7 +599,25 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
       const uint32_t lbo = p.slab_swap ? 256u : 128u, sbo = p.slab_swap ? 128u : 256u;
       const uint64_t a1desc = desc_noswz(smem_u32(sA1), lbo, sbo);
       uint32_t t = 0;
-      mbar_wait(bar_img, 0);  // code tiles + norm slab (bulk copies) and the ones slab are in place
+      if (p.prepared) {
+        // the prepared image is copied by this thread (idle until it lands): twenty bulk copies issued from an epilogue
+        // thread held up that role's prologue barrier for 3 000 cycles
+        const size_t img_tiles_bytes = (size_t)p.T * p.NC * b_tile;
+        // 4 KB pieces, every CTA starting at a different piece: all CTAs copy the SAME 80 KB, and 148 of them asking for
+        // the same lines at the same moment queue up at the L2 slices that own those lines (measured ~3 TB/s, 4 us)
+        const uint32_t slab_bytes = (uint32_t)p.Kp * 32u;
+        mbar_expect_tx(bar_img, (uint32_t)img_tiles_bytes + slab_bytes);
+        const uint32_t n_tile = (uint32_t)(img_tiles_bytes >> 12), n_all = n_tile + (slab_bytes >> 12);
+        uint32_t j = ((uint32_t)blockIdx.x * 7u) % n_all;
+  #pragma unroll 1
+        for (uint32_t i = 0; i < n_all; ++i) {
+          const uint32_t off = j << 12;
+          const uint32_t dst = (j < n_tile) ? smem_u32(sB) + off : smem_u32(sE) + (off - (uint32_t)img_tiles_bytes);
+          bulk_load_1d(dst, p.img + off, 4096u, bar_img);
+          if (++j == n_all) j = 0;
+        }
+      }
+      mbar_wait(bar_img, 0);  // code tiles + norm slab (bulk copies) are in place (the ones slab: ordered through bar_mu -> bar_a_full)
       fence_after();
       for (int i = 0; i < nblk; ++i) {
         const int buf = i % p.nbufA;
@@ -411,6 +795,42 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
     // itself, with the sample loads and the slice's code rows requested together (one round trip).
     // item = (code k, 16-byte output chunk of its row): 8 latent dims = two float4 loads; the items of one row sit in
     // consecutive lanes (Dp/8 = 8, 16 or 32 of them), so ||e-mu||^2 is a fixed-order shuffle reduction.
+    const size_t img_tiles_bytes = (size_t)p.T * p.NC * b_tile;
+    float emax2 = 0.f, excl_inv = 0.f, mu_norm = 0.f;
+    if (p.prepared) {
+      // ---- prepared codebook (search_prep_kernel ran earlier in the stream, once per codebook version): the image is
+      // bulk-copied straight away (by the MMA thread), mu and the code maxima are read from the state header -- no
+      // grid-wide meeting
+      const P1State* st = p.st;
+      mu_s[threadIdx.x] = __ldg(st->mu + threadIdx.x);  // 256 epilogue threads, 256 entries (zeros past D)
+      const int np = __ldg(&st->nparts);
+      const bool valid = __ldg(&st->magic) == kStateMagic && __ldg(&st->K) == p.K && __ldg(&st->D) == p.D &&
+                         __ldg(&st->metric) == p.metric && np >= 1 && np <= kStateParts;
+      // (all kStateParts entries: the preparation zero-fills the unused ones, so no load waits for nparts -- with a cold
+      //  L2 every dependent load here is a DRAM round trip in front of the first MMA)
+      float e2 = fmaxf(__ldg(st->emax2_part + lane), __ldg(st->emax2_part + lane + 32));
+      float xi = fmaxf(__ldg(st->excl_inv_part + lane), __ldg(st->excl_inv_part + lane + 32));
+      mu_norm = __ldg(&st->mu_norm);
+      for (int r = threadIdx.x; r < kBM; r += kEpiWarps * 32) {  // ones slab: columns 0..2 = 1.0 for every row
+        *reinterpret_cast<uint4*>(sA1 + slab_off(r, 0)) = make_uint4(0x3C003C00u, 0x00003C00u, 0u, 0u);
+        *reinterpret_cast<uint4*>(sA1 + slab_off(r, 8)) = make_uint4(0u, 0u, 0u, 0u);
+      }
+      fence_async_smem();  // (the ones slab, for the tensor core)
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (threadIdx.x == 0) mbar_arrive(bar_mu);  // the z converters may start
+      TR(43);
+  #pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        e2 = fmaxf(e2, __shfl_xor_sync(0xffffffffu, e2, o));
+        xi = fmaxf(xi, __shfl_xor_sync(0xffffffffu, xi, o));
+      }
+      // a workspace that was never prepared for this (K, D, metric): nothing is certified, every row takes the exact scan
+      emax2 = valid ? e2 : INFINITY;
+      excl_inv = xi;
+      TR(46);
+      mbar_wait(bar_img, 0);
+      TR(47);
+    } else {
     const int ipr = Dp / 8;  // items per row: 8 (D <= 64), 16, 24 (-> handled as 32 with idle lanes), 32
     const int ipr_p2 = ipr <= 8 ? 8 : (ipr <= 16 ? 16 : 32);
     const int rpp = (kEpiWarps * 32) / ipr_p2;  // whole rows per pass over the 256 epilogue threads
@@ -420,7 +840,6 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
     const bool vec = (p.D % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.cb) & 15) == 0) && (d0 + 8 <= p.D);
     const int slice_n = (p.Kp + (int)gridDim.x - 1) / (int)gridDim.x;
     const int slice_lo = (int)blockIdx.x * slice_n, slice_hi = min(slice_lo + slice_n, p.Kp);
-    const size_t img_tiles_bytes = (size_t)p.T * p.NC * b_tile;
     auto load_item = [&](int k, float (&x)[8]) {
   #pragma unroll
       for (int e = 0; e < 8; ++e) x[e] = 0.f;
@@ -612,7 +1031,6 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
     TR(46);
     mbar_wait(bar_img, 0);  // every thread: code tiles + norm slab have landed (async-proxy writes, visible to the MMA)
     TR(47);
-    float emax2, excl_inv;
     {
       unsigned a, b;
       asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(a) : "l"(&p.hdr->emax2_bits) : "memory");
@@ -620,11 +1038,12 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
       emax2 = __uint_as_float(a);
       excl_inv = __uint_as_float(b);
     }
-    const float mu_norm = sqrtf(red_s[31]);
+    mu_norm = sqrtf(red_s[31]);
     if (blockIdx.x == 0) {  // what the later passes read
       for (int d = threadIdx.x; d < Dp; d += kEpiWarps * 32) p.mu_g[d] = mu_s[d];
       if (threadIdx.x == 0) p.hdr->mu_norm = mu_norm;
     }
+    }  // !prepared
 
     // TMEM lane = row; group g = warp >> 2 drains every second code tile.  Per 32-column chunk and row:
     //   best of the chunk      plain fp32 minimum, half an ALU instruction per score (FMNMX3)
@@ -818,8 +1237,14 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
         if (ok) {
           p.idx_out[row] = (int64_t)bidx;
         } else {
-          const int pos = atomicAdd(p.queue_count, 1);
-          p.queue_out[pos] = (int)row;
+          if (p.tail) {  // this CTA's own segment: scanned at the end of this kernel
+            const int pos = atomicAdd(s_qn, 1);
+            p.queue_out[(size_t)blockIdx.x * p.qcap + pos] = (int)row;
+            p.queue_thr[(size_t)blockIdx.x * p.qcap + pos] = best + 1.25f * margin_row;  // (NaN / inf: every code is a candidate)
+          } else {
+            const int pos = atomicAdd(p.queue_count, 1);
+            p.queue_out[pos] = (int)row;
+          }
         }
       }
       best = INFINITY; second = INFINITY; ma = 0.f; mb = 0.f; base = 0;
@@ -834,10 +1259,216 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
     fence_after();
     tmem_dealloc(tmem_base, 512);
   }
+  if (p.tail) {
+    // ===== the rows this CTA could not certify (usually none): candidate filter + exact evaluation, see p1_tail_scan.
+    // Every MMA, TMA load and bulk copy of this CTA has completed (each was waited for by its consumer); the code tiles
+    // and the norm slab are still in place, the A buffers hold the row buffers and candidate lists (13 x (2 Dp + 64) words, or 8 x (2 Dp + 65): <= 16 KB x NC).
+    const int nq = *s_qn;
+    if (nq > 0) {
+      fence_async_smem();  // the A buffers (written by the converters, read by the MMAs) become scratch
+      const int* qrows = p.queue_out + (size_t)blockIdx.x * p.qcap;
+      const float* qthr = p.queue_thr + (size_t)blockIdx.x * p.qcap;
+      if (nq <= kTailCoopRows)
+        p1_tail_coop(p.z, p.cb, qrows, qthr, p.idx_out, p.D, p.K, p.Kp, p.NC, p.metric, sB, sE, mu_s, reinterpret_cast<float*>(sA),
+                     nq, p.stats_out ? p.ncand_ctr : nullptr, p.nall_ctr);
+      else
+        p1_tail_scan(p.z, p.cb, qrows, qthr, p.idx_out, p.D, p.K, p.Kp, p.NC, p.metric, sB, sE, mu_s, reinterpret_cast<float*>(sA),
+                     nq, p.stats_out ? p.ncand_ctr : nullptr, p.nall_ctr);
+      __syncthreads();  // (the statistics below read what the warps added)
+    }
+    // statistics: the last CTA of the call publishes the grid-wide count and clears the counters for the next call
+    if (threadIdx.x == 0 && p.stats_out != nullptr) {  // (two grid-wide round trips at the very end: only when asked for)
+      if (nq > 0) atomicAdd(p.flagged_ctr, nq);
+      __threadfence();
+      const int ticket = atomicAdd(p.done_ctr, 1);
+      if (ticket == (int)gridDim.x - 1) {
+        __threadfence();
+        const int tot = atomicExch(p.flagged_ctr, 0);
+        if (p.stats_out) {
+          p.stats_out[0] = tot;  // rows settled by the exact evaluation of their candidates
+          p.stats_out[1] = tot;  // rows the fp16 pass left uncertified
+          p.stats_out[2] = atomicExch(p.ncand_ctr, 0);  // codes evaluated exactly for those rows
+          p.stats_out[3] = atomicExch(p.nall_ctr, 0);   // rows for which every code was a candidate (non-finite threshold)
+        }
+        atomicExch(p.done_ctr, 0);
+      }
+    }
+  }
 #ifdef LIPVQ_TRACE
   TR(3);
   if (blockIdx.x == 0 && lane == 0) g_trace_p1_n[warp] = tr_n;
 #endif
+}
+
+// Codebook preparation as a launch of its own: everything search_p1_kernel needs that depends on the codebook only -- the
+// centre mu, -2(e-mu) as swizzled fp16 tiles, the fp16 split of ||e-mu||^2 (norm slab), the maxima the certification
+// margin uses.  Run once per codebook VERSION (bulk tokenisation: once; training: after the codebook update, off the
+// search's critical path); the search itself then starts with one bulk copy instead of an 18 000-cycle prologue.
+// mu = mean of <= 32 evenly spaced rows of `center` (e.g. a batch of latents; any centre is valid -- the bounds are
+// evaluated for the centre that was used -- a centre near the latents certifies the most rows) or, without one, of the
+// codebook itself.  Each CTA owns cpc codes; every CTA derives the same mu (fixed summation order).
+__global__ void __launch_bounds__(256, 1)
+    search_prep_kernel(const float* __restrict__ cb, int K, int D, int Kp, int NC, int metric, const float* __restrict__ center,
+                       int64_t n_center, int cpc, P1State* st, uint8_t* img) {
+  __shared__ float samp[32 * 256];
+  __shared__ float mu_s[256];
+  __shared__ float red_a[8], red_b[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Dp = NC * kChunk;
+  const int b_tile = kBN * kChunk * 2;
+  const int T = Kp / kBN;
+  grid_dep_wait();
+  {
+    constexpr int RMAX = 32;
+    const float* src = center ? center : cb;
+    const int64_t n = center ? n_center : (int64_t)K;
+    const int R = (int)(n < RMAX ? n : RMAX);
+    const int64_t stride = n / R;
+    const bool want_mu = metric != LIPVQ_METRIC_DOT;
+    const int dl = (int)threadIdx.x & 63, il = (int)threadIdx.x >> 6;
+    for (int db = 0; db < 256; db += 64) {
+      const int d = db + dl;
+      float v[8];
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const int i = il + 4 * q;
+        v[q] = (want_mu && d < D && i < R) ? __ldg(src + (int64_t)i * stride * D + d) : 0.f;
+      }
+#pragma unroll
+      for (int q = 0; q < 8; ++q) samp[(il + 4 * q) * 256 + d] = v[q];
+    }
+    __syncthreads();
+    const int d = (int)threadIdx.x;
+    float sum = 0.f;
+#pragma unroll 8
+    for (int i = 0; i < RMAX; ++i) sum += samp[i * 256 + d];  // rows >= R hold zeros; fixed order
+    mu_s[d] = sum / (float)R;
+    __syncthreads();
+  }
+  const int ipr = Dp / 8;
+  const int ipr_p2 = ipr <= 8 ? 8 : (ipr <= 16 ? 16 : 32);
+  const int rpp = 256 / ipr_p2;
+  const int sub = (int)threadIdx.x % ipr_p2, rslot = (int)threadIdx.x / ipr_p2;
+  const int d0 = sub * 8;
+  const bool col_live = sub < ipr && d0 < D;
+  const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(cb) & 15) == 0) && (d0 + 8 <= D);
+  const int lo = (int)blockIdx.x * cpc, hi = min(lo + cpc, Kp);
+  const bool dot = (metric == LIPVQ_METRIC_DOT);
+  const size_t img_tiles_bytes = (size_t)T * NC * b_tile;
+  float mu8[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) mu8[e] = (col_live && d0 + e < D) ? mu_s[d0 + e] : 0.f;
+  const int ch = sub & 7;
+  float emax2_loc = 0.f, excl_inv_loc = 0.f;
+  for (int k0 = lo; k0 < hi; k0 += rpp) {
+    const int k = k0 + rslot;
+    float x[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) x[e] = 0.f;
+    if (k < hi && k < K && col_live) {
+      const float* src = cb + (size_t)k * D + d0;
+      if (vec) {
+        const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
+        x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w; x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
+      } else {
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          if (d0 + e < D) x[e] = __ldg(src + e);
+      }
+    }
+    float c[8];
+    float s = 0.f, am = 0.f;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      c[e] = x[e] - mu8[e];
+      s = fmaf(c[e], c[e], s);
+    }
+#pragma unroll
+    for (int e = 0; e < 8; e += 2) am = fmaxf(am, fmaxf(fabsf(c[e]), fabsf(c[e + 1])));
+    for (int o = 1; o < ipr_p2; o <<= 1) {
+      s += __shfl_xor_sync(0xffffffffu, s, o);
+      am = fmaxf(am, __shfl_xor_sync(0xffffffffu, am, o));
+    }
+    if (k >= hi || sub >= ipr) continue;  // (after the shuffles: every lane of the warp takes part in them)
+    // a code whose centred entries or norm do not fit fp16 (or that holds inf / NaN) is left out of the contraction
+    const bool excluded = k < K && (!(am < kF16Safe) || (dot ? !(s < 3.0e38f) : !(s <= kEnormMax)));
+    const bool zero_row = k >= K || excluded;
+    uint32_t hh[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float va = zero_row ? 0.f : -2.f * c[2 * e], vb = zero_row ? 0.f : -2.f * c[2 * e + 1];
+      const __half2 hp = __floats2half2_rn(va, vb);
+      hh[e] = *reinterpret_cast<const uint32_t*>(&hp);
+    }
+    const int j = k >> 8, r = k & 255;  // kBN = 256
+    *reinterpret_cast<uint4*>(img + ((size_t)j * NC + (sub >> 3)) * b_tile + r * 128 + ((ch ^ (r & 7)) << 4)) =
+        make_uint4(hh[0], hh[1], hh[2], hh[3]);
+    if (sub == 0) {
+      const float en = dot ? 0.f : s;
+      float h0, h1, h2;
+      if (zero_row) {
+        h0 = h1 = h2 = kSentinel;
+      } else {
+        h0 = __half2float(__float2half_rn(en));
+        h1 = __half2float(__float2half_rn(en - h0));
+        h2 = __half2float(__float2half_rn(en - h0 - h1));
+        emax2_loc = fmaxf(emax2_loc, s);
+      }
+      if (excluded) {
+        const float inv = (s < 3.0e38f) ? rsqrtf(s) * 1.0001f : 3.0e38f;  // 1/||e-mu|| rounded up (NaN/inf: unusable)
+        excl_inv_loc = fmaxf(excl_inv_loc, inv);
+      }
+      const __half2 a = __floats2half2_rn(h0, h1), b = __floats2half2_rn(h2, 0.f);
+      uint8_t* slab = img + img_tiles_bytes;
+      *reinterpret_cast<uint4*>(slab + slab_off(k, 0)) =
+          make_uint4(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b), 0u, 0u);
+      *reinterpret_cast<uint4*>(slab + slab_off(k, 8)) = make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    emax2_loc = fmaxf(emax2_loc, __shfl_xor_sync(0xffffffffu, emax2_loc, o));
+    excl_inv_loc = fmaxf(excl_inv_loc, __shfl_xor_sync(0xffffffffu, excl_inv_loc, o));
+  }
+  if (lane == 0) {
+    red_a[warp] = emax2_loc;
+    red_b[warp] = excl_inv_loc;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float a = red_a[0], b = red_b[0];
+    for (int i = 1; i < 8; ++i) {
+      a = fmaxf(a, red_a[i]);
+      b = fmaxf(b, red_b[i]);
+    }
+    st->emax2_part[blockIdx.x] = a;
+    st->excl_inv_part[blockIdx.x] = b;
+  }
+  if (blockIdx.x == 0 && (int)threadIdx.x >= (int)gridDim.x && threadIdx.x < kStateParts) {  // unused parts read as zero
+    st->emax2_part[threadIdx.x] = 0.f;
+    st->excl_inv_part[threadIdx.x] = 0.f;
+  }
+  if (blockIdx.x == 0) {
+    st->mu[threadIdx.x] = (int)threadIdx.x < Dp ? mu_s[threadIdx.x] : 0.f;
+    if (warp == 0) {
+      float t = 0.f;
+      for (int dd = lane; dd < 256; dd += 32) t = fmaf(mu_s[dd], mu_s[dd], t);
+      t = warp_sum(t);
+      if (lane == 0) {
+        st->mu_norm = sqrtf(t);
+        st->nparts = (int)gridDim.x;
+        st->K = K;
+        st->D = D;
+        st->metric = metric;
+        st->flagged = 0;
+        st->done = 0;
+        st->ncand = 0;
+        st->nall = 0;
+        st->magic = kStateMagic;
+      }
+    }
+  }
+  grid_dep_launch();
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
@@ -919,16 +1550,47 @@ bool search_p1_supported(int64_t N, int D, int K) {
   return search_p1_fits(N, D, K);
 }
 
+bool search_p1_tail() {
+  if (const char* e = getenv("LIPVQ_P1_TAIL")) return e[0] != '0';
+  return true;
+}
+
 size_t search_p1_image_bytes(int D, int K) {
   const size_t Dp = (size_t)(D + kChunk - 1) / kChunk * kChunk, Kp = (size_t)(K + kBN - 1) / kBN * kBN;
   return Kp * Dp * 2 + Kp * 32;
 }
 
-// One launch: codebook preparation + fp16 pass over all rows.  Uncertified rows are appended to `queue` (count at
-// *queue_count, which must be zero on entry); mu / enorm / ehi / elo / hdr are published for the later passes.
+size_t search_p1_state_bytes(int D, int K) { return (size_t)kStateHdr + search_p1_image_bytes(D, K); }
+
+// rows of the per-CTA queue segments the in-kernel exact scan needs (N + one row block of slack per CTA)
+int64_t search_p1_queue_rows(int64_t N) { return N + (int64_t)kBM * 257; }
+
+// Codebook preparation for the "prepared" mode (see search_prep_kernel).  state = search_p1_state_bytes(D, K) bytes.
+int search_prep_launch(const float* cb, int K, int D, int metric, const float* center, int64_t n_center, void* state,
+                       cudaStream_t stream) {
+  const P1Geom g = p1_geom(D, K, false);
+  if (!g.ok) {
+    set_error("search_prep: codebook K=%d D=%d does not stay resident in shared memory", K, D);
+    return LIPVQ_ERR_UNSUPPORTED;
+  }
+  int cpc = 32;
+  while ((g.Kp + cpc - 1) / cpc > kStateParts) cpc += 32;
+  const int grid = (g.Kp + cpc - 1) / cpc;
+  uint8_t* base = reinterpret_cast<uint8_t*>(state);
+  LIPVQ_CUDA(launch_pdl(search_prep_kernel, dim3(grid), dim3(256), 0, stream, cb, K, D, g.Kp, g.NC, metric, center, n_center, cpc,
+                        reinterpret_cast<P1State*>(base), base + kStateHdr));
+  LIPVQ_LAUNCHED("search_prep_kernel");
+  return LIPVQ_OK;
+}
+
+// The fp16 pass over all rows.  prepared_state == nullptr: ONE launch that also prepares the codebook (cooperatively,
+// in its prologue) and publishes mu / enorm / ehi / elo / hdr for the later passes; otherwise the state written by
+// search_prep_launch for this codebook.  tail != 0: rows the pass cannot certify are settled by the same kernel (exact
+// scan; `queue` and `queue_thr` then hold search_p1_queue_rows(N) entries each and nothing is left for later passes); tail == 0: they are
+// appended to `queue` (count at *queue_count, which must be zero on entry).
 int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, int Kp_pub, float* mu,
                      float* enorm, void* ehi_, void* elo_, void* img, SearchHdr* hdr, int* queue, int* queue_count, int64_t* idx_out,
-                     cudaStream_t stream) {
+                     cudaStream_t stream, void* prepared_state, int tail, int32_t* stats_out, float* queue_thr) {
   __half* ehi = reinterpret_cast<__half*>(ehi_);
   __half* elo = reinterpret_cast<__half*>(elo_);
   const bool staged = (D % 4 == 0) && aligned16(z);
@@ -936,6 +1598,10 @@ int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, i
   if (!g.ok) g = p1_geom(D, K, false);
   if (!g.ok) {
     set_error("search_p1: shape N=%lld D=%d K=%d does not fit", (long long)N, D, K);
+    return LIPVQ_ERR_INVALID;
+  }
+  if (prepared_state != nullptr && !tail) {
+    set_error("search_p1: the prepared mode settles its own rows (tail)");
     return LIPVQ_ERR_INVALID;
   }
   P1Params p{};
@@ -949,6 +1615,27 @@ int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, i
   p.mu_g = mu; p.enorm_g = enorm; p.ehi_g = ehi; p.elo_g = elo; p.hdr = hdr;
   p.img = reinterpret_cast<uint8_t*>(img);
   p.queue_out = queue; p.queue_count = queue_count; p.idx_out = idx_out;
+  p.prepared = prepared_state != nullptr;
+  p.tail = tail;
+  p.stats_out = stats_out;
+  p.queue_thr = queue_thr;
+  if (tail && queue_thr == nullptr) {
+    set_error("search_p1: the in-kernel exact scan needs the threshold queue");
+    return LIPVQ_ERR_INVALID;
+  }
+  if (p.prepared) {
+    p.st = reinterpret_cast<P1State*>(prepared_state);
+    p.img = reinterpret_cast<uint8_t*>(prepared_state) + kStateHdr;
+    p.flagged_ctr = &p.st->flagged;
+    p.done_ctr = &p.st->done;
+    p.ncand_ctr = &p.st->ncand;
+    p.nall_ctr = &p.st->nall;
+  } else {
+    p.flagged_ctr = &hdr->flagged;
+    p.done_ctr = &hdr->done;
+    p.ncand_ctr = &hdr->ncand;
+    p.nall_ctr = &hdr->nall;
+  }
   const float u22 = 2.3841858e-7f;
   const float steps = (float)(g.Dp / 16 + 1);  // + the norm-slab MMA
   p.gamma_en = (float)(D + 4) * 5.9604645e-8f + (steps + 1.f) * u22;
@@ -968,8 +1655,10 @@ int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, i
     smem_set[dev_] = g.smem;
   }
   const int row_blocks = (int)ceil_div64(N, kBM);
-  const int sms = sm_count();
+  int sms = sm_count();
+  if (sms > 256) sms = 256;  // (search_p1_queue_rows)
   const int grid = row_blocks < sms ? row_blocks : sms;
+  p.qcap = (row_blocks + grid - 1) / grid * kBM;
   LIPVQ_CUDA(launch_pdl(search_p1_kernel, dim3(grid), dim3(kThreads), g.smem, stream, tm_z, p));
   LIPVQ_LAUNCHED("search_p1_kernel");
   return LIPVQ_OK;

@@ -19,7 +19,7 @@ METRIC_L2, METRIC_L2SQ, METRIC_DOT = 0, 1, 2
 ALGO_AUTO, ALGO_SIMT_F32, ALGO_TCGEN05 = 0, 1, 2
 ACT_NONE, ACT_RELU, ACT_GELU, ACT_SIGMOID, ACT_GIVEN = 0, 1, 2, 3, 4
 EMA_SIMPLE, EMA_LAPLACE, EMA_NORMALIZE = 0, 1, 2
-ABI_VERSION = 4
+ABI_VERSION = 5
 
 _p, _i, _i64, _f, _d, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double, C.c_size_t
 
@@ -31,6 +31,9 @@ SIGNATURES = {
     "lipvq_nn_search_workspace_bytes": (_sz, [_i64, _i, _i, _i, _i]),
     "lipvq_nn_search_f32": (_i, [_p, _i64, _i, _p, _i, _i, _i, _p, _p, _p, _p, _sz, _p]),
     "lipvq_nn_search_pick_algo": (_i, [_i64, _i, _i, _i]),
+    "lipvq_nn_search_prepared_supported": (_i, [_i64, _i, _i, _i]),
+    "lipvq_nn_search_prepare_f32": (_i, [_p, _i, _i, _i, _p, _i64, _p, _sz, _p]),
+    "lipvq_nn_search_prepared_f32": (_i, [_p, _i64, _i, _p, _i, _i, _p, _p, _p, _sz, _p]),
     "lipvq_l2_normalize_rows_f32": (_i, [_p, _i64, _i, _p, _p]),
     "lipvq_gather_ste_loss_fwd_f32": (_i, [_p, _p, _p, _i64, _i, _i, _p, _p, _p, _p]),
     "lipvq_gather_ste_loss_bwd_f32": (_i, [_p, _p, _p, _p, _p, _f, _f, _i, _p, _i64, _i, _i, _p, _p, _p]),

@@ -105,6 +105,41 @@ def nn_search(z: torch.Tensor, codebook: torch.Tensor, metric: int = A.METRIC_L2
     return res[0] if len(res) == 1 else res
 
 
+def search_prepared_supported(N: int, D: int, K: int, metric: int = A.METRIC_L2) -> bool:
+    """True when (N, D, K) takes the prepare / prepared pair (codebook resident in shared memory, tensor path)."""
+    return bool(lib.lipvq_nn_search_prepared_supported(N, D, K, metric))
+
+
+def nn_search_prepare(codebook: torch.Tensor, workspace: torch.Tensor, metric: int = A.METRIC_L2,
+                      center: Optional[torch.Tensor] = None) -> None:
+    """Prepare ``workspace`` for nn_search_prepared on this codebook (once per codebook VERSION).  ``center``: rows
+    [n, D] whose mean centres the contraction (a batch of latents); None: the codebook's own rows."""
+    K, D = codebook.shape
+    if center is not None and center.shape[-1] != D:
+        raise RuntimeError(f"shape mismatch: center has dim {center.shape[-1]}, codebook {D}")
+    n = 0 if center is None else center.numel() // D
+    _chk(workspace, torch.uint8, "workspace")
+    _call(lib.lipvq_nn_search_prepare_f32, "nn_search_prepare", _chk(codebook, F32, "codebook"), K, D, metric,
+          _chk(center, F32, "center", True) if n > 0 else None, n, workspace.data_ptr(),
+          workspace.numel() * workspace.element_size(), _stream())
+
+
+def nn_search_prepared(z: torch.Tensor, codebook: torch.Tensor, workspace: torch.Tensor, metric: int = A.METRIC_L2,
+                       out: Optional[torch.Tensor] = None, want_stats: bool = False):
+    """nn_search on a workspace that nn_search_prepare filled for this codebook (which must not have changed since)."""
+    N, D = z.shape
+    K, D2 = codebook.shape
+    if D != D2:
+        raise RuntimeError(f"shape mismatch: z has dim {D}, codebook {D2}")
+    idx = out if out is not None else torch.empty(N, dtype=I64, device=z.device)
+    stats = torch.empty(4, dtype=I32, device=z.device) if want_stats else None
+    _chk(workspace, torch.uint8, "workspace")
+    _call(lib.lipvq_nn_search_prepared_f32, "nn_search_prepared", _chk(z, F32, "z"), N, D, _chk(codebook, F32, "codebook"),
+          K, metric, _chk(idx, I64, "idx"), _chk(stats, I32, "stats", True), workspace.data_ptr(),
+          workspace.numel() * workspace.element_size(), _stream())
+    return (idx, stats) if want_stats else idx
+
+
 def search_workspace_bytes(N: int, D: int, K: int, metric: int = A.METRIC_L2, algo: int = A.ALGO_AUTO) -> int:
     return int(lib.lipvq_nn_search_workspace_bytes(N, D, K, metric, algo))
 

@@ -61,6 +61,8 @@ class T1Buffers:
         nbytes = ops.code_sort_workspace_bytes(N, D, K) if (N >= 4096 and os.environ.get("LIPVQ_SCATTER", "atomic") == "sorted") else 0
         self.sort_ws = torch.empty(nbytes, dtype=torch.uint8, device=dev) if nbytes else None
         self.sorted_ok = False  # sort_ws holds the order of the CURRENT t["idx"]
+        # the search can run on a codebook prepared once per codebook version (ops.nn_search_prepare -> t["ws"])
+        self.search_prepared_ok = ops.search_prepared_supported(N, D, K)
 
     def alloc_derivatives(self):
         N, H, dev = self.N, self.H, self.device
@@ -77,12 +79,22 @@ class T1Buffers:
                            "scratch": torch.zeros(1, dtype=torch.float64, device=dev)})
 
 
+def prepare_search(p: Dict[str, torch.Tensor], b: T1Buffers, center: Optional[torch.Tensor] = None) -> None:
+    """Codebook-dependent half of the search, once per codebook version (see include/lipvq.h, K3)."""
+    ops.nn_search_prepare(p["quantizer.codebook"], b.t["ws"], A.METRIC_L2, center=center)
+
+
 def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: int = A.ALGO_AUTO,
-            encode_only: bool = False) -> None:
+            encode_only: bool = False, search_prepared: bool = False, weights_prepared: bool = False,
+            prepare_search_here: bool = False) -> None:
     """x [N,F] -> b.t[...]: z_e, idx, z_q, x_recon, losses.  ``encode_only`` stops after the search
-    (the bulk-tokenisation path: encode + VQ)."""
+    (the bulk-tokenisation path: encode + VQ).  ``search_prepared``: b.t["ws"] was prepared for the current codebook
+    (prepare_search); ``weights_prepared``: b.t["Wn"] already holds the clamped to_latent weight of the current
+    parameters (bulk tokenisation with fixed weights); ``prepare_search_here``: prepare the codebook inside this call,
+    centred on this batch's latents, right before the search (then ``search_prepared`` applies)."""
     t = b.t
-    ops.lipschitz_scale_fwd(p["to_latent.W"], p["to_latent.ci"], t["Wn"])
+    if not weights_prepared:
+        ops.lipschitz_scale_fwd(p["to_latent.W"], p["to_latent.ci"], t["Wn"])
     if encode_only:
         ops.linear_fwd(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, out=t["a1"])
         ops.linear_fwd(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, out=t["a2"])
@@ -91,7 +103,12 @@ def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: 
         ops.linear_fwd_dual(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, t["a1"], t["da1_act"])
         ops.linear_fwd_dual(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, t["a2"], t["da2_act"])
     ops.linear_fwd(t["a2"], A.ACT_NONE, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"])
-    ops.nn_search(t["z_e"], p["quantizer.codebook"], A.METRIC_L2, algo, out=t["idx"], workspace=t["ws"])
+    if prepare_search_here:
+        prepare_search(p, b, center=t["z_e"])
+    if search_prepared or prepare_search_here:
+        ops.nn_search_prepared(t["z_e"], p["quantizer.codebook"], t["ws"], A.METRIC_L2, out=t["idx"])
+    else:
+        ops.nn_search(t["z_e"], p["quantizer.codebook"], A.METRIC_L2, algo, out=t["idx"], workspace=t["ws"])
     b.sorted_ok = False
     if encode_only:
         return

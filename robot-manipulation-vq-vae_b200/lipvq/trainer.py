@@ -110,11 +110,20 @@ class TokenizerTrainer:
         self.bufs.zeroed_by_caller = True
         self.bufs.t["losses"] = self.losses_in
         self.x_static = torch.empty(self.N, F_, dtype=torch.float32, device=dev)
+        # The codebook changes once per step (EMA overwrite + AdamW, phase B): its search-side preparation runs right
+        # there, centred on that step's latents, and the next step's search starts from the prepared image.  Anything
+        # that changes the parameters behind the trainer's back (load_state_dict, manual edits) must call refresh().
+        self.search_prepared = (self.bufs.search_prepared_ok and search_algo in (A.ALGO_AUTO, A.ALGO_TCGEN05)
+                                and os.environ.get("LIPVQ_TRAINER_PREPARED", "1") != "0")
+        # (the centre of the prepared contraction is a batch of latents: until the first step has produced one, the step
+        #  uses the self-contained search, which takes its centre from the rows it is given)
+        self._centre_ok = False
         self.use_graph = use_graph
         self._graph_a = None  # zero grads, forward, EMA statistics, backward
         self._graph_b = None  # EMA apply + AdamW
         self._graph_full = None  # world > 1: phase a + all-reduce + phase b in one graph
         self._graph_tok = None
+        self._graph_tok_fast = None
         self.graph_collective = os.environ.get("LIPVQ_GRAPH_COLLECTIVE", "1") != "0"
         # input prefetch (step(x, prefetch=x_next)): the next batch's H2D copy runs on its own stream under this step
         self._stage = None
@@ -128,7 +137,8 @@ class TokenizerTrainer:
     def _phase_a(self):
         self.red.zero_()
         self._arena.zero_()
-        t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo)
+        t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo,
+                   search_prepared=self.search_prepared and self._centre_ok)
         if self.ema:
             t1.ema_stats(self.bufs, self.counts, self.sums)
         t1.backward(self.p, self.g, self.x_static, self.bufs)
@@ -147,6 +157,17 @@ class TokenizerTrainer:
         ops.counter_add(self.step_dev, 1)
         ops.adamw_step(self.flat_p, self.flat_g, self.flat_m, self.flat_v, 0, self.step_dev, self.lr, self.betas,
                        self.eps, self.wd, 1.0 / self.world)
+        if self.search_prepared:  # the codebook has its final value of this step
+            t1.prepare_search(self.p, self.bufs, center=self.bufs.t["z_e"])
+            self._centre_ok = True
+
+    def refresh(self) -> None:
+        """Call after changing parameters outside step() (load_state_dict, ...): re-derives what is cached per
+        parameter version (the prepared codebook of the search)."""
+        self._tok_ready = False
+        with torch.cuda.device(self.device):
+            if self.search_prepared and self._centre_ok:  # (the latents of the last batch are still a good centre)
+                t1.prepare_search(self.p, self.bufs, center=self.bufs.t["z_e"])
 
     def _snapshot(self):
         st = [self.flat_p.clone(), self.flat_m.clone(), self.flat_v.clone(), self.step_dev.clone()]
@@ -160,6 +181,8 @@ class TokenizerTrainer:
         if self.ema:
             q = self.model.quantizer
             q.ema_cluster_size.copy_(st[4]); q.ema_codebook.copy_(st[5])
+        if self.search_prepared and self._centre_ok:
+            t1.prepare_search(self.p, self.bufs, center=self.bufs.t["z_e"])
 
     def _capture(self):
         # one eager pass on a side stream first (lazy module loading, allocator), then capture both halves;
@@ -231,6 +254,7 @@ class TokenizerTrainer:
             return self._step(x, prefetch)
 
     def _step(self, x: torch.Tensor, prefetch: Optional[torch.Tensor]) -> torch.Tensor:
+        self._tok_ready = False  # the step updates the parameters after it clamped to_latent.W
         self._load_input(x, prefetch)
         if self.use_graph and self._graph_a is None:
             self._capture()
@@ -256,27 +280,43 @@ class TokenizerTrainer:
         return self.bufs.t["idx"]
 
     @torch.no_grad()
-    def tokenize(self, x: torch.Tensor) -> torch.Tensor:
-        """encode + VQ only on x [N,F] (bulk tokenisation) -> int64 [N] (a buffer the next call overwrites)."""
+    def tokenize(self, x: torch.Tensor, prepared: bool = False) -> torch.Tensor:
+        """encode + VQ only on x [N,F] (bulk tokenisation) -> int64 [N] (a buffer the next call overwrites).
+        ``prepared=True``: the parameters have not changed since the last step() / tokenize() / refresh() of this
+        trainer -- the clamped to_latent weight and the prepared codebook of that call are reused (bulk tokenisation
+        of a dataset with fixed weights: three linear layers + one search launch per call)."""
         if tuple(x.shape) != tuple(self.x_static.shape):
             raise RuntimeError(f"expected input of shape {tuple(self.x_static.shape)}, got {tuple(x.shape)}")
         with torch.cuda.device(self.device):
-            return self._tokenize(x)
+            return self._tokenize(x, prepared and self.search_prepared and self._tok_ready)
 
-    def _tokenize(self, x: torch.Tensor) -> torch.Tensor:
+    _tok_ready = False  # Wn and the prepared codebook in bufs are those of the current parameters
+
+    def _tok_forward(self, fast: bool) -> None:
+        if fast:
+            t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True, search_prepared=True,
+                       weights_prepared=True)
+            return
+        t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True,
+                   prepare_search_here=self.search_prepared)
+
+    def _tokenize(self, x: torch.Tensor, fast: bool) -> torch.Tensor:
         self.x_static.copy_(x, non_blocking=True)
         if not self.use_graph:
-            t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True)
+            self._tok_forward(fast)
+            self._tok_ready = True
             return self.bufs.t["idx"]
-        if self._graph_tok is None:
+        attr = "_graph_tok_fast" if fast else "_graph_tok"
+        if getattr(self, attr) is None:
             s = torch.cuda.Stream(device=self.device)
             s.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(s):
-                t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True)
+                self._tok_forward(fast)
             torch.cuda.current_stream(self.device).wait_stream(s)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True)
-            self._graph_tok = g
-        self._graph_tok.replay()
+                self._tok_forward(fast)
+            setattr(self, attr, g)
+        getattr(self, attr).replay()
+        self._tok_ready = True
         return self.bufs.t["idx"]

@@ -29,6 +29,9 @@ flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 rot = "--rotate" in sys.argv
 if rot:  # inputs larger than L2: 16 different z buffers (268 MB) used in turn, no flush
     zs = [z.clone() + 0 * i for i in range(16)]
+prep = "--prepared" in sys.argv  # codebook prepared once, then one launch per search (lipvq_nn_search_prepared_f32)
+if prep:
+    ops.nn_search_prepare(cb, ws, lipvq.METRIC_L2, center=z)
 for i in range(iters):
     if rot:
         z = zs[i % 16]
@@ -38,7 +41,15 @@ for i in range(iters):
         flush.zero_()
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
-    ops.nn_search(z, cb, lipvq.METRIC_L2, lipvq.ALGO_TCGEN05, out=idx, workspace=ws)
+    if prep:
+        ops.nn_search_prepared(z, cb, ws, lipvq.METRIC_L2, out=idx)
+    else:
+        ops.nn_search(z, cb, lipvq.METRIC_L2, lipvq.ALGO_TCGEN05, out=idx, workspace=ws)
     b.record()
     torch.cuda.synchronize()
     print(f"iter {i}: {a.elapsed_time(b) * 1e3:.1f} us")
+if prep:
+    _, st = ops.nn_search_prepared(z, cb, ws, lipvq.METRIC_L2, want_stats=True)
+else:
+    _, st = ops.nn_search(z, cb, lipvq.METRIC_L2, lipvq.ALGO_TCGEN05, want_stats=True, workspace=ws)
+print("stats", st.tolist())

@@ -51,14 +51,26 @@ def main():
     N, K, D = (int(v) for v in sys.argv[1:4])
     mode = sys.argv[4] if len(sys.argv) > 4 else "t1"
     z, cb = case(N, K, D, mode)
+    nt = next((int(a.split("=")[1]) for a in sys.argv if a.startswith("--ties=")), 0)
+    if nt:  # nt rows sit (almost) midway between two codes: the fp16 pass cannot certify them
+        g = torch.Generator().manual_seed(1)
+        rows = torch.randperm(N, generator=g)[:nt]
+        a_, b_ = torch.randint(0, K, (nt,), generator=g), torch.randint(0, K, (nt,), generator=g)
+        mid = 0.5 * (cb.cpu()[a_] + cb.cpu()[b_]) + 1e-7 * torch.randn(nt, D, generator=g)
+        z[rows.cuda()] = mid.cuda()
     algo = lipvq.ALGO_TCGEN05
     ws = torch.empty(ops.search_workspace_bytes(N, D, K, lipvq.METRIC_L2, algo), dtype=torch.uint8, device="cuda")
     idx = torch.empty(N, dtype=torch.int64, device="cuda")
+    prepared = "--prepared" in sys.argv  # lipvq_nn_search_prepare_f32 once, then the one-launch search
+    if prepared:
+        ops.nn_search_prepare(cb, ws, lipvq.METRIC_L2, center=z)
+    run = (lambda: ops.nn_search_prepared(z, cb, ws, lipvq.METRIC_L2, out=idx)) if prepared else \
+          (lambda: ops.nn_search(z, cb, lipvq.METRIC_L2, algo, out=idx, workspace=ws))
     for _ in range(3):
-        ops.nn_search(z, cb, lipvq.METRIC_L2, algo, out=idx, workspace=ws)
+        run()
     if "--cold" in sys.argv:  # L2 (data AND the kernel's code) evicted, as between the kernels of a training step
         torch.empty(256 << 20, dtype=torch.uint8, device="cuda").zero_()
-        ops.nn_search(z, cb, lipvq.METRIC_L2, algo, out=idx, workspace=ws)
+        run()
     torch.cuda.synchronize()
     if os.environ.get("LIPVQ_SEARCH_P1", "1") != "0" and hasattr(_cabi.lib, "lipvq_debug_trace_p1"):
         report("lipvq_debug_trace_p1", 16, 4096, {0: "epi g0", 4: "epi g1", 8: "cvt", 12: "mma"})

@@ -41,7 +41,12 @@ def test_tc_search_l2_vs_oracle(N, K, D):
     # tensor-core launch there; longer queues must be thinned by the 3-term pass to a few percent
     lim = 0.02 if D <= 256 else 0.6
     allowed = max(8, lim * N) if int(stats[1]) > N // 8 else max(8, N // 8)
-    assert int(stats[0]) <= allowed, f"{int(stats[0])} of {N} rows went through the exact scan"
+    if L.ops.search_prepared_supported(1 << 22, D, K):
+        # codebooks that stay resident in shared memory: the single-launch pass scans its own uncertified rows exactly
+        # at the end of each CTA -- there is no 3-term pass, both counters are the same number
+        assert int(stats[0]) == int(stats[1])
+    else:
+        assert int(stats[0]) <= allowed, f"{int(stats[0])} of {N} rows went through the exact scan"
 
 
 def test_tc_matches_simt_path_and_other_metrics():
