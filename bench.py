@@ -453,6 +453,7 @@ def run_ours(args):
                              "algorithmic_flops": flops, "algorithmic_bytes": bytes_alg,
                              "hbm_frac": bytes_alg / sd / 1e3 / hbm, "share_of_step": sd / step_us,
                              "rows_rescored_exactly": int(st[0]), "rows_uncertified_by_fp16_pass": int(st[1]),
+                             "codes_evaluated_exactly_for_those_rows": int(st[2]),
                              "l2": "inputs larger than L2 (ten 16.8 MB latent buffers in turn); see timing"}
         # --- the step-dominant kernel: the tensor-core linear layer (11 forward / dX launches + 6 dW launches per step).
         #     Representative launch: encoder.2 (64 -> 128, GELU + derivative), HBM-bound by bytes ---

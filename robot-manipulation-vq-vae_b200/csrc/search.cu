@@ -769,7 +769,7 @@ SearchPlan make_search_plan(int64_t N, int D, int K, int metric, int algo) {
   p.off_work = o;     o = align_up(o + sizeof(int) * (size_t)work_rows, 256);
   if (algo == LIPVQ_ALGO_TCGEN05) {
     const size_t eb = sizeof(uint16_t) * (size_t)p.Kp * p.Dp;
-    p.off_work2 = o; o = align_up(o + sizeof(int) * (size_t)work_rows, 256);
+    p.off_work2 = o; o = align_up(o + sizeof(int) * 2 * (size_t)work_rows, 256);  // (single-launch pass: two floats per queued row)
     p.off_ehi = o;  o = align_up(o + eb, 1024);
     p.off_elo = o;  o = align_up(o + eb, 1024);
     p.off_img = o;  o = align_up(o + (search_p1_fits(N, D, K) ? search_p1_image_bytes(D, K) : 0), 1024);

@@ -88,10 +88,12 @@ struct P1Params {
   int Kp_pub;     // rows of the published arrays (the later passes' padded code count)
   int early_trigger;  // griddepcontrol.launch_dependents right after set-up instead of at the end
   int slab_swap;  // debug: swap LBO/SBO of the no-swizzle descriptors
+  int swap_groups;  // even tiles per block: the two epilogue groups take turns at certifying (opt-in, LIPVQ_P1_SWAP=1)
+  int split_last;   // two tiles per block: group 0 also drains the first columns of the second tile (opt-in, LIPVQ_P1_SPLIT=1)
   int prepared;   // the code image, mu and the code maxima come from a P1State written by search_prep_kernel
   int tail;       // rows this pass cannot certify are settled HERE (exact fp32 scan at the end of the CTA): no later launches
   int qcap;       // tail: queue_out / queue_thr are cut into per-CTA segments of qcap entries
-  float* queue_thr;  // tail: per queued row, the score threshold of the candidate filter
+  float* queue_thr;  // tail: per queued row, the score threshold of the candidate filter and the row's reach (2 floats)
   P1State* st;    // prepared
   int* flagged_ctr;  // tail: grid-wide count of queued rows (statistics only) and the ticket that resets both
   int* done_ctr;
@@ -206,7 +208,7 @@ struct RowBest {  // partial result of one epilogue group for one row, handed to
 // scan, so their loads carry no ordering (volatile loads exposed one shared-memory latency per 16 bytes).
 template <bool ONE>
 __device__ __forceinline__ float tail_score(int k, int NC, uint32_t sB_s, uint32_t sE_s, uint32_t zc_s, const float (&zreg)[64],
-                                            float& en) {
+                                            float& en, float& inv_x) {
   constexpr int b_tile = kBN * kChunk * 2;
   const int jt = k >> 8, r = k & 255;  // kBN = 256
   uint2 nh;
@@ -214,6 +216,7 @@ __device__ __forceinline__ float tail_score(int k, int NC, uint32_t sB_s, uint32
   const float2 n01 = __half22float2(*reinterpret_cast<const __half2*>(&nh.x));
   const float2 n2 = __half22float2(*reinterpret_cast<const __half2*>(&nh.y));
   en = (n01.x + n01.y) + n2.x;
+  inv_x = n2.y;  // excluded codes: 1/||e-mu|| (rounded up)
   float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
   if (ONE) {  // one 64-wide chunk (the tokenizer's own width): the centred row sits in registers
     const uint32_t trow = sB_s + (uint32_t)(jt * b_tile + r * 128);
@@ -328,6 +331,16 @@ __device__ __forceinline__ float tail_exact(int k, const float* __restrict__ cb,
   return (metric == LIPVQ_METRIC_L2) ? sqrtf(av) : (dotm ? -av : av);
 }
 
+// candidate test of the filter.  sc <= thr: the score can belong to the nearest code.  Codes left out of the contraction
+// (sentinel norm 3 x 65504, zero tile row) have no usable score: such a code is a candidate unless it is provably further
+// than the row's best code, ||e-mu|| - ||z-mu|| > d_best, i.e. reach * (1/||e-mu||) < 1 with reach = ||z-mu|| + 1.02 d_best
+// (an EMA codebook early in training holds hundreds of never-hit rows divided by ~eps: evaluating all of them exactly
+// for every queued row cost 45 us per search).
+__device__ __forceinline__ bool tail_is_candidate(float sc, float en, float inv_x, float thr, float reach, bool dotm) {
+  if (en > 1.0e5f) return dotm || !(reach * inv_x < 0.999f);
+  return (sc <= thr) || !(sc == sc);
+}
+
 constexpr int kTailWarps = kThreads / 32;      // 13: every warp of the CTA takes part
 constexpr int kTailCoopRows = 8;               // up to this many queued rows a CTA works on each row with ALL its warps
 constexpr int kTailList = 64;                  // candidate list entries (per warp / per row)
@@ -349,7 +362,7 @@ __device__ __noinline__ void p1_tail_scan(const float* __restrict__ z, const flo
   const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(cb) & 15) == 0);
   for (int w = warp; w < nq; w += kTailWarps) {
     const int64_t row = rows[w];
-    const float thr = thrs[w];
+    const float thr = thrs[2 * w], reach = thrs[2 * w + 1];
     const bool all = !(thr < 3.0e38f);
     const float* zr = z + row * (int64_t)D;
     for (int d = lane; d < Dp; d += 32) {
@@ -386,9 +399,10 @@ __device__ __noinline__ void p1_tail_scan(const float* __restrict__ z, const flo
     for (int k = lane; k < Kp; k += 32) {
       bool cand = all;
       if (!all) {
-        float en;
-        const float sc = (NC == 1) ? tail_score<true>(k, NC, sB_s, sE_s, zc_s, zreg, en) : tail_score<false>(k, NC, sB_s, sE_s, zc_s, zreg, en);
-        cand = (sc <= thr) || (en > 1.0e5f) || !(sc == sc);  // (sentinel norms: 3 x 65504)
+        float en, inv_x;
+        const float sc = (NC == 1) ? tail_score<true>(k, NC, sB_s, sE_s, zc_s, zreg, en, inv_x)
+                                   : tail_score<false>(k, NC, sB_s, sE_s, zc_s, zreg, en, inv_x);
+        cand = tail_is_candidate(sc, en, inv_x, thr, reach, metric == LIPVQ_METRIC_DOT);
       }
       cand = cand && k < K;
       const unsigned m = __ballot_sync(0xffffffffu, cand);
@@ -439,7 +453,7 @@ __device__ __noinline__ void p1_tail_scan(const float* __restrict__ z, const flo
 //   0. the rows are fetched together into CTA-level buffers (one chain of dependent loads for all of them),
 //   1. ALL warps filter every row (warp w takes codes 32 w .., 32 (w + 13) ..; the centred row is read from the shared
 //      buffer into registers), candidates go to the row's list in shared memory -- no barrier between rows,
-//   2. after one barrier warp r evaluates the candidates of row r: the rows' exact evaluations run side by side.
+//   2. after one barrier the candidates of all rows are evaluated exactly, 32 at a time, dealt round-robin to the warps.
 // Called by every thread of the CTA, nq <= kTailCoopRows.  More candidates than a list holds: every code is evaluated.
 __device__ __noinline__ void p1_tail_coop(const float* __restrict__ z, const float* __restrict__ cb, const int* __restrict__ rows,
                                           const float* __restrict__ thrs, int64_t* __restrict__ idx_out, int D, int K, int Kp,
@@ -451,9 +465,13 @@ __device__ __noinline__ void p1_tail_coop(const float* __restrict__ z, const flo
   float* zs_all = zc_all + kTailCoopRows * Dp;      // [kTailCoopRows][Dp] the rows themselves
   int* rlist = reinterpret_cast<int*>(zs_all + kTailCoopRows * Dp);  // [kTailCoopRows][kTailList]
   int* rcnt = rlist + kTailCoopRows * kTailList;                       // [kTailCoopRows]
+  unsigned long long* rkey = reinterpret_cast<unsigned long long*>(rcnt + kTailCoopRows);  // [kTailCoopRows] (8-byte aligned)
   const uint32_t sB_s = smem_u32(sB), sE_s = smem_u32(sE);
   const bool vec = (D % 4 == 0) && ((reinterpret_cast<uintptr_t>(cb) & 15) == 0);
-  if ((int)threadIdx.x < nq) rcnt[threadIdx.x] = 0;
+  if ((int)threadIdx.x < nq) {
+    rcnt[threadIdx.x] = 0;
+    rkey[threadIdx.x] = ~0ull;
+  }
   for (int i = threadIdx.x; i < nq * Dp; i += kThreads) {
     const int w = i / Dp, d = i - w * Dp;
     const float v = (d < D) ? __ldg(z + (int64_t)rows[w] * D + d) : 0.f;
@@ -462,7 +480,7 @@ __device__ __noinline__ void p1_tail_coop(const float* __restrict__ z, const flo
   }
   __syncthreads();
   for (int w = 0; w < nq; ++w) {
-    const float thr = thrs[w];
+    const float thr = thrs[2 * w], reach = thrs[2 * w + 1];
     if (!(thr < 3.0e38f)) continue;  // every code is a candidate: left to the evaluation below
     const uint32_t zc_s = smem_u32(zc_all + w * Dp);
     float zreg[64];
@@ -475,49 +493,59 @@ __device__ __noinline__ void p1_tail_coop(const float* __restrict__ z, const flo
       }
     }
     for (int k = warp * 32 + lane; k < Kp; k += kTailWarps * 32) {
-      float en;
-      const float sc = (NC == 1) ? tail_score<true>(k, NC, sB_s, sE_s, zc_s, zreg, en) : tail_score<false>(k, NC, sB_s, sE_s, zc_s, zreg, en);
-      if (((sc <= thr) || (en > 1.0e5f) || !(sc == sc)) && k < K) {
+      float en, inv_x;
+      const float sc = (NC == 1) ? tail_score<true>(k, NC, sB_s, sE_s, zc_s, zreg, en, inv_x)
+                                 : tail_score<false>(k, NC, sB_s, sE_s, zc_s, zreg, en, inv_x);
+      if (tail_is_candidate(sc, en, inv_x, thr, reach, metric == LIPVQ_METRIC_DOT) && k < K) {
         const int pos = atomicAdd(&rcnt[w], 1);
         if (pos < kTailList) rlist[w * kTailList + pos] = k;
       }
     }
   }
   __syncthreads();
-  if (warp < nq) {
-    const int w = warp;
-    const bool all = !(thrs[w] < 3.0e38f);
-    const int cnt = all ? kTailList + 1 : rcnt[w];
-    const float* zs = zs_all + w * Dp;
-    float bv = INFINITY;
-    int bk = 0x7fffffff;
-    auto evaluate = [&](int k) {
-      const float val = tail_exact(k, cb, zs, D, metric, vec);
-      if (val < bv || (val == bv && k < bk)) {  // lowest index on exact ties, whatever the order of evaluation
-        bv = val;
-        bk = k;
-      }
-    };
-    if (cnt > kTailList) {  // every code (non-finite threshold), or more candidates than the list holds
-      for (int k = lane; k < K; k += 32) evaluate(k);
-    } else {
-      for (int i = lane; i < cnt; i += 32) evaluate(rlist[w * kTailList + i]);
-    }
+  // 2. exact evaluation, batches of 32 candidates dealt round-robin to the warps (a row whose list overflowed, or whose
+  //    threshold is not finite, has every code evaluated: 16 batches at K = 512 -- one warp alone needed 37 000 cycles for
+  //    such a row).  Row results meet in a 64-bit key per row: (order-preserving bits of the value, code index), so the
+  //    minimum is the smallest value and, on exact ties, the lowest index.  NaN values never enter.
+  {
+    int item = 0;
+    for (int w = 0; w < nq; ++w) {
+      const bool all = !(thrs[2 * w] < 3.0e38f);
+      const int cnt = rcnt[w];
+      const bool full = all || cnt > kTailList;
+      const int n = full ? K : cnt;
+      const float* zs = zs_all + w * Dp;
+      for (int b0 = 0; b0 < n; b0 += 32, ++item) {
+        if (item % kTailWarps != warp) continue;
+        const int e = b0 + lane;
+        const int k = (e < n) ? (full ? e : rlist[w * kTailList + e]) : -1;
+        unsigned long long key = ~0ull;
+        if (k >= 0) {
+          const float val = tail_exact(k, cb, zs, D, metric, vec) + 0.f;  // (-0 -> +0)
+          if (val == val) {
+            const uint32_t u = __float_as_uint(val);
+            key = ((unsigned long long)((u & 0x80000000u) ? ~u : (u | 0x80000000u)) << 32) | (uint32_t)k;
+          }
+        }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
-      const int ok = __shfl_xor_sync(0xffffffffu, bk, o);
-      if (ov < bv || (ov == bv && ok < bk)) {
-        bv = ov;
-        bk = ok;
+        for (int o = 16; o > 0; o >>= 1) {
+          const unsigned long long other = __shfl_xor_sync(0xffffffffu, key, o);
+          key = other < key ? other : key;
+        }
+        if (lane == 0 && key != ~0ull) atomicMin(&rkey[w], key);
       }
     }
-    if (lane == 0) {
-      idx_out[rows[w]] = (int64_t)(bk == 0x7fffffff ? 0 : bk);
-      if (ncand_ctr != nullptr) {
-        atomicAdd(ncand_ctr, cnt > kTailList ? K : cnt);
-        if (all) atomicAdd(nall_ctr, 1);
-      }
+  }
+  __syncthreads();
+  if ((int)threadIdx.x < nq) {
+    const int w = threadIdx.x;
+    const unsigned long long key = rkey[w];
+    idx_out[rows[w]] = (key == ~0ull) ? 0 : (int64_t)(uint32_t)(key & 0xffffffffu);  // all-NaN row: index 0 (as the exact-scan kernels)
+    if (ncand_ctr != nullptr) {
+      const bool all = !(thrs[2 * w] < 3.0e38f);
+      const int cnt = rcnt[w];
+      atomicAdd(ncand_ctr, (all || cnt > kTailList) ? K : cnt);
+      if (all) atomicAdd(nall_ctr, 1);
     }
   }
 }
@@ -544,6 +572,10 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
   uint64_t* bars = reinterpret_cast<uint64_t*>(red_s + 32);
   const uint32_t bar_a_full = smem_u32(bars + 0), bar_a_empty = smem_u32(bars + 2);
   const uint32_t bar_acc_full = smem_u32(bars + 4), bar_acc_empty = smem_u32(bars + 6);
+  // "accumulator ab holds a tile for group g": barrier ab of group 0 at bars + 4 + ab, of group 1 at bars + 24 + ab.  One
+  // barrier per (buffer, draining group): every phase of a barrier is then waited for by the same group, in order (a
+  // parity wait only tells phase n from phase n - 1, and with the swapped assignment below a group skips tiles of a buffer)
+  const uint32_t bar_acc_full1 = smem_u32(bars + 24);
   const uint32_t bar_z_full = smem_u32(bars + 8), bar_z_empty = smem_u32(bars + 12);
   const uint32_t bar_x_full = smem_u32(bars + 16), bar_x_empty = smem_u32(bars + 18);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 20);
@@ -565,7 +597,9 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
       mbar_init(bar_a_full + 8 * s, kCvtWarps);
       mbar_init(bar_a_empty + 8 * s, 1);
       mbar_init(bar_acc_full + 8 * s, 1);
-      mbar_init(bar_acc_empty + 8 * s, kEpiWarps / 2);
+      mbar_init(bar_acc_full1 + 8 * s, 1);
+      // (split mode: both groups drain columns of the second tile, which always sits in buffer 1)
+      mbar_init(bar_acc_empty + 8 * s, (s == 1 && p.T == 2 && p.split_last) ? kEpiWarps : kEpiWarps / 2);
       mbar_init(bar_x_full + 8 * s, kEpiWarps / 2);
       mbar_init(bar_x_empty + 8 * s, kEpiWarps / 2);
     }
@@ -619,6 +653,8 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
       }
       mbar_wait(bar_img, 0);  // code tiles + norm slab (bulk copies) are in place (the ones slab: ordered through bar_mu -> bar_a_full)
       fence_after();
+      const uint32_t mma_swap = (p.T % 2 == 0 && p.swap_groups) ? 1u : 0u;
+      const bool mma_split = (p.T == 2 && p.split_last);
       for (int i = 0; i < nblk; ++i) {
         const int buf = i % p.nbufA;
         mbar_wait(bar_a_full + 8 * buf, (uint32_t)(i / p.nbufA) & 1);
@@ -639,7 +675,12 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
 #pragma unroll
             for (int k = 0; k < kChunk / 16; ++k) umma_f16(d_tmem, desc_sw128(aa + 32 * k), desc_sw128(bb + 32 * k), idesc, 1u);
           }
-          umma_commit(bar_acc_full + 8 * ab);
+          if (mma_split && j == 1) {  // both groups drain columns of this tile
+            umma_commit(bar_acc_full + 8 * ab);
+            umma_commit(bar_acc_full1 + 8 * ab);
+          } else {
+            umma_commit((((t + mma_swap * (uint32_t)i) & 1u) ? bar_acc_full1 : bar_acc_full) + 8 * ab);  // (the draining group's)
+          }
           TR(32);
         }
         umma_commit(bar_a_empty + 8 * buf);
@@ -983,7 +1024,12 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
             const float inv = (s < 3.0e38f) ? rsqrtf(s) * 1.0001f : 3.0e38f;  // 1/||e-mu|| rounded up (NaN/inf: unusable)
             excl_inv_loc = fmaxf(excl_inv_loc, inv);
           }
-          const __half2 a = __floats2half2_rn(h0, h1), b = __floats2half2_rn(h2, 0.f);
+          // column 3 (times a zero of the ones slab: no effect on the contraction) tells the in-kernel scan how far an
+          // EXCLUDED code is: 1/||e-mu|| rounded up, finite (0 for ordinary codes and padding)
+          const float inv_x = excluded ? fminf((s < 3.0e38f) ? rsqrtf(s) * 1.0001f : 65504.f, 65504.f) : 0.f;
+          __half2 b = __floats2half2_rn(h2, 0.f);
+          b.y = __float2half_ru(inv_x);
+          const __half2 a = __floats2half2_rn(h0, h1);
           uint8_t* slab = p.img + img_tiles_bytes;
           *reinterpret_cast<uint4*>(slab + slab_off(k, 0)) =
               make_uint4(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b), 0u, 0u);
@@ -1058,7 +1104,7 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
     // chunk (min tree, mask accumulation) are latency- not throughput-bound, the second chunk fills the gaps.
     const int q = warp & 3, g = warp >> 2;
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
-    const uint32_t tbuf = tmem_base + (uint32_t)g * (uint32_t)kBN + lane_off;
+    const uint32_t tbuf0 = tmem_base + lane_off;  // accumulator buffer of tile t: t & 1
     const float emax_g = sqrtf(emax2);
     const bool dotm = (p.metric == LIPVQ_METRIC_DOT);
     // margin(zn) = max(m_alg + m_c, gamma_ref * ref_mag) with every term bounded for ANY candidate code
@@ -1117,10 +1163,42 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
       mb = rec ? xb : mb;
       best = fminf(best, cm);
     };
-    for (int t = g; t < total_tiles; t += 2) {
+    // Which group drains tile t.  The group that drains a block's LAST tile also merges the other group's partial and
+    // certifies the block's rows (~1 300 cycles per block on top of the fold).  With an even number of tiles per block a
+    // fixed assignment t & 1 gives that work to group 1 every time (its period was fold + certification = the kernel's
+    // block period, group 0 had slack); so for even T the assignment is swapped on odd blocks and the two groups take
+    // turns.  Accumulator buffer and barrier parities depend on t only.
+    const int swap = (p.T % 2 == 0 && p.swap_groups) ? 1 : 0;
+    // Split mode (opt-in; two tiles per block, the tokenizer's own shape): with one tile per group, group 1 -- fold +
+    // merge + certification -- sets the block period (4 450 cycles) while group 0 waits ~1 000 cycles per block.  In
+    // split mode group 0 also drains the first kSplitCols columns of the second tile (any warp may read any accumulator
+    // column of its lane quadrant), group 1 the rest.  Measured: no gain (N = 1 M rows: 154-157 us vs 156-162 us) -- the
+    // two groups share the schedulers, group 1's certification stretched from 1 400 to 2 900 cycles: what bounds the block
+    // period is the latency of each warp's dependent chains with three warps per scheduler, not the split of the work.
+    // The swapped assignment above (groups take turns at certifying) was worse: 186-205 us, the certification of block i
+    // and the fold of the first tile of block i + 1 then sit on one serial chain.
+    const bool split = (p.T == 2 && p.split_last);
+    constexpr int kSplitCols = 64;
+    uint32_t acc_par = 0;
+    for (int t = 0; t < total_tiles; ++t) {
       const int i = t / p.T, j = t - i * p.T;
+      int c_lo = 0, c_hi = kBN;
+      if (split) {
+        if (j == 0) {
+          if (g != 0) continue;
+        } else if (g == 0) {
+          c_hi = kSplitCols;
+        } else {
+          c_lo = kSplitCols;
+        }
+      } else if (((t + swap * i) & 1) != g) {
+        continue;
+      }
+      const uint32_t ab = (uint32_t)t & 1u;
+      const uint32_t tbuf = tbuf0 + ab * (uint32_t)kBN;
       TR(10);
-      mbar_wait(bar_acc_full + 8 * g, (uint32_t)(t >> 1) & 1);
+      mbar_wait((g ? bar_acc_full1 : bar_acc_full) + 8 * ab, (acc_par >> ab) & 1u);  // this group's own phase count of buffer ab
+      acc_par ^= 1u << ab;
       fence_after();
       TR(11);
       if (i != cur_blk) {
@@ -1134,15 +1212,15 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
         if (!(margin_row < 3.0e38f)) margin_row = INFINITY;  // non-finite row statistics: nothing can be certified
       }
 #pragma unroll 1
-      for (int c0 = 0; c0 < kBN; c0 += 64) {
+      for (int c0 = c_lo; c0 < c_hi; c0 += 64) {
         uint32_t va[32], vb[32];
         tmem_ld32(tbuf + c0, va);
         tmem_ld32(tbuf + c0 + 32, vb);
         tmem_ld_wait2(va, vb);
-        if (c0 + 64 >= kBN) {  // last load of this accumulator has landed: hand it back to the MMA warp
+        if (c0 + 64 >= c_hi) {  // this group's last load of the accumulator has landed: hand it back to the MMA warp
           fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(bar_acc_empty + 8 * g);
+          if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
           TR(12);
         }
         float cma, xaa, xba, cmb, xab, xbb;
@@ -1152,8 +1230,9 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
         merge_chunk(cmb, xab, xbb, j * kBN + c0 + 32);
       }
       TR(14);
-      const bool last_of_block = (j == p.T - 1);
-      const bool leaves_block = last_of_block || (j + 2 >= p.T);
+      // last_of_block: this group merges the other group's partial and certifies; otherwise it hands its partial over
+      const bool last_of_block = split ? (j == 1 && g == 1) : (j == p.T - 1);
+      const bool leaves_block = split ? (j == 1) : (last_of_block || (j + 2 >= p.T));
       if (!leaves_block) continue;
 
       RowBest* xs = xchg + (i & 1) * kBM + q * 32 + lane;
@@ -1240,7 +1319,14 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
           if (p.tail) {  // this CTA's own segment: scanned at the end of this kernel
             const int pos = atomicAdd(s_qn, 1);
             p.queue_out[(size_t)blockIdx.x * p.qcap + pos] = (int)row;
-            p.queue_thr[(size_t)blockIdx.x * p.qcap + pos] = best + 1.25f * margin_row;  // (NaN / inf: every code is a candidate)
+            // the margin of the codes that can still be the nearest (triangle inequality, as in the refinement above):
+            // with the a-priori margin a few far-away codes (large ||e-mu||) made half the codebook a candidate
+            const float dhat = sqrtf(fmaxf(best + zn * zn, 0.f));
+            const float emax_r = dotm ? emax_g : fminf(emax_g, zn + 1.02f * dhat + 1e-30f);
+            const float m_thr = fminf(margin_of(zn, emax_r, dhat), margin_row);
+            float* qt = p.queue_thr + 2 * ((size_t)blockIdx.x * p.qcap + pos);
+            qt[0] = best + 1.25f * m_thr;  // (NaN / inf: every code is a candidate)
+            qt[1] = zn + 1.02f * dhat;     // how far a code can be from the centre and still be the nearest
           } else {
             const int pos = atomicAdd(p.queue_count, 1);
             p.queue_out[pos] = (int)row;
@@ -1267,7 +1353,7 @@ __global__ void __launch_bounds__(kThreads, 1) search_p1_kernel(const __grid_con
     if (nq > 0) {
       fence_async_smem();  // the A buffers (written by the converters, read by the MMAs) become scratch
       const int* qrows = p.queue_out + (size_t)blockIdx.x * p.qcap;
-      const float* qthr = p.queue_thr + (size_t)blockIdx.x * p.qcap;
+      const float* qthr = p.queue_thr + 2 * (size_t)blockIdx.x * p.qcap;  // (threshold, reach) per queued row
       if (nq <= kTailCoopRows)
         p1_tail_coop(p.z, p.cb, qrows, qthr, p.idx_out, p.D, p.K, p.Kp, p.NC, p.metric, sB, sE, mu_s, reinterpret_cast<float*>(sA),
                      nq, p.stats_out ? p.ncand_ctr : nullptr, p.nall_ctr);
@@ -1418,7 +1504,12 @@ __global__ void __launch_bounds__(256, 1)
         const float inv = (s < 3.0e38f) ? rsqrtf(s) * 1.0001f : 3.0e38f;  // 1/||e-mu|| rounded up (NaN/inf: unusable)
         excl_inv_loc = fmaxf(excl_inv_loc, inv);
       }
-      const __half2 a = __floats2half2_rn(h0, h1), b = __floats2half2_rn(h2, 0.f);
+      // column 3 (times a zero of the ones slab: no effect on the contraction) tells the in-kernel scan how far an
+      // EXCLUDED code is: 1/||e-mu|| rounded up, finite (0 for ordinary codes and padding)
+      const float inv_x = excluded ? fminf((s < 3.0e38f) ? rsqrtf(s) * 1.0001f : 65504.f, 65504.f) : 0.f;
+      __half2 b = __floats2half2_rn(h2, 0.f);
+      b.y = __float2half_ru(inv_x);
+      const __half2 a = __floats2half2_rn(h0, h1);
       uint8_t* slab = img + img_tiles_bytes;
       *reinterpret_cast<uint4*>(slab + slab_off(k, 0)) =
           make_uint4(*reinterpret_cast<const uint32_t*>(&a), *reinterpret_cast<const uint32_t*>(&b), 0u, 0u);
@@ -1586,7 +1677,7 @@ int search_prep_launch(const float* cb, int K, int D, int metric, const float* c
 // The fp16 pass over all rows.  prepared_state == nullptr: ONE launch that also prepares the codebook (cooperatively,
 // in its prologue) and publishes mu / enorm / ehi / elo / hdr for the later passes; otherwise the state written by
 // search_prep_launch for this codebook.  tail != 0: rows the pass cannot certify are settled by the same kernel (exact
-// scan; `queue` and `queue_thr` then hold search_p1_queue_rows(N) entries each and nothing is left for later passes); tail == 0: they are
+// scan; `queue` then holds search_p1_queue_rows(N) ints, `queue_thr` twice as many floats, and nothing is left for later passes); tail == 0: they are
 // appended to `queue` (count at *queue_count, which must be zero on entry).
 int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, int metric, int Kp_pub, float* mu,
                      float* enorm, void* ehi_, void* elo_, void* img, SearchHdr* hdr, int* queue, int* queue_count, int64_t* idx_out,
@@ -1612,6 +1703,11 @@ int search_p1_launch(const float* z, int64_t N, int D, const float* cb, int K, i
   p.early_trigger = 1;
   if (const char* e = getenv("LIPVQ_P1_EARLY_TRIGGER")) p.early_trigger = (e[0] != '0');
   if (const char* e = getenv("LIPVQ_SLAB_DESC_SWAP")) p.slab_swap = (e[0] == '1');
+  p.swap_groups = 0;
+  if (const char* e = getenv("LIPVQ_P1_SWAP")) p.swap_groups = (e[0] == '1');
+  p.split_last = 0;
+  if (const char* e = getenv("LIPVQ_P1_SPLIT")) p.split_last = (e[0] == '1');
+  if (p.swap_groups) p.split_last = 0;
   p.mu_g = mu; p.enorm_g = enorm; p.ehi_g = ehi; p.elo_g = elo; p.hdr = hdr;
   p.img = reinterpret_cast<uint8_t*>(img);
   p.queue_out = queue; p.queue_count = queue_count; p.idx_out = idx_out;

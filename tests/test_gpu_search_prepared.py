@@ -120,6 +120,29 @@ def test_prepared_search_degenerate_codebooks():
     assert int(idx.max()) == 0
 
 
+def test_prepared_search_mostly_dead_ema_codebook():
+    """An EMA codebook early in training: a dozen live codes, every other row divided by ~eps (hq_vae.py:277-279).  The
+    huge rows are left out of the fp16 contraction; rows the pass cannot certify must not pay an exact evaluation of all
+    of them (the per-code triangle-inequality test of the in-kernel scan)."""
+    import lipvq as L
+    N, K, D = 65536, 512, 64
+    g = torch.Generator().manual_seed(3)
+    z = torch.sigmoid(0.2 * torch.randn(N, D, generator=g))
+    cb = torch.randn(K, D, generator=g) * 3e4
+    live = torch.randperm(K, generator=g)[:12]
+    cb[live] = z[torch.randperm(N, generator=g)[:12]] + 0.01 * torch.randn(12, D, generator=g)
+    cb[live[1]] = cb[live[0]] + 1e-6     # a near-duplicate pair: the rows nearest to it cannot be certified in fp16
+    zd, cd = z.to(DEV), cb.to(DEV)
+    ws = _ws(L, N, D, K)
+    L.ops.nn_search_prepare(cd, ws, L.METRIC_L2, center=zd)
+    idx, st = L.ops.nn_search_prepared(zd, cd, ws, L.METRIC_L2, want_stats=True)
+    rows = torch.randperm(N, generator=torch.Generator().manual_seed(0))[:4096]
+    assert_indices(z[rows], cb, idx.cpu()[rows], O.nearest_code_l2(z[rows], cb), max_near_tie_frac=0.5)
+    assert torch.isin(idx.cpu(), live).all()
+    assert int(st[0]) > 0 and int(st[3]) == 0
+    assert int(st[2]) <= 16 * int(st[0]), f"{int(st[2])} exact evaluations for {int(st[0])} queued rows"
+
+
 def test_trainer_steps_and_tokenizes_on_the_prepared_search():
     """TokenizerTrainer prepares the codebook at the end of every step; the indices of a step and of the two tokenize
     modes equal those of the unprepared entry point on the same latents."""
