@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 5
+#define LIPVQ_ABI_VERSION 6
 #define LIPVQ_API __attribute__((visibility("default")))
 
 enum {
@@ -233,6 +233,19 @@ LIPVQ_API int lipvq_linear_fwd_f32(const float* X, int64_t N, int in_dim, int ac
  * nn.Linear -> nn.GELU and its autograd (backbone_lfqvae_v5.py:54-68). */
 LIPVQ_API int lipvq_linear_fwd_dual_f32(const float* X, int64_t N, int in_dim, int act_in, const float* W, const float* bias,
                               int out_dim, int act_out, float* Y, float* dYdpre, void* stream);
+
+/* Three linear layers in ONE launch, for inference (no stored activations):
+ *   Y = act3(act2(act1(X W1^T + b1) W2^T + b2) W3^T + b3),  X [N,d0], Wl [dl, d(l-1)] row-major, bl [dl] or NULL.
+ * The tokenizer's encoder under torch.no_grad -- nn.Linear + GELU, nn.Linear + GELU, the Lipschitz layer's clamped weight
+ * + sigmoid (backbone_lfqvae_v5.py:54-62, 70-76: self.encoder, self.to_latent) -- and, with other widths, its decoder
+ * (:63-68).  Same arithmetic as three lipvq_linear_fwd_f32 calls on the tensor path (three-way bf16 splits, six MMA
+ * chains, fp32 accumulation, fp32 bias + activation); hidden activations stay in shared memory / TMEM.
+ * supported(): 1 when the widths fit (weights of all layers resident in shared memory, N >= 4096), else 0 -- chain three
+ * lipvq_linear_fwd_f32 calls. */
+LIPVQ_API int lipvq_mlp3_fwd_supported(int64_t N, int d0, int d1, int d2, int d3);
+LIPVQ_API int lipvq_mlp3_fwd_f32(const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1,
+                        const float* W2, const float* b2, int d2, int act2, const float* W3, const float* b3, int d3,
+                        int act3, float* Y, void* stream);
 LIPVQ_API int lipvq_linear_bwd_x_f32(const float* dY, int64_t N, int out_dim, const float* W, int in_dim, const float* X,
                            int act_in, float* dX, void* stream);
 LIPVQ_API int lipvq_linear_bwd_w_f32(const float* dY, int64_t N, int out_dim, const float* X, int in_dim, int act_in, float* dW,

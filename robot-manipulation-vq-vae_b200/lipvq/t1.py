@@ -95,14 +95,19 @@ def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: 
     t = b.t
     if not weights_prepared:
         ops.lipschitz_scale_fwd(p["to_latent.W"], p["to_latent.ci"], t["Wn"])
-    if encode_only:
+    fused_enc = encode_only and ops.mlp3_supported(b.N, b.F, 64, b.H, b.D)
+    if fused_enc:  # bulk tokenisation: the three encoder layers in one launch, hidden activations never leave the SM
+        ops.mlp3_fwd(x, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, p["encoder.2.weight"], p["encoder.2.bias"],
+                     A.ACT_GELU, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"])
+    elif encode_only:
         ops.linear_fwd(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, out=t["a1"])
         ops.linear_fwd(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, out=t["a2"])
     else:
         b.alloc_derivatives()
         ops.linear_fwd_dual(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, t["a1"], t["da1_act"])
         ops.linear_fwd_dual(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, t["a2"], t["da2_act"])
-    ops.linear_fwd(t["a2"], A.ACT_NONE, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"])
+    if not fused_enc:
+        ops.linear_fwd(t["a2"], A.ACT_NONE, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"])
     if prepare_search_here:
         prepare_search(p, b, center=t["z_e"])
     if search_prepared or prepare_search_here:

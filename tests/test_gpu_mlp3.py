@@ -1,0 +1,66 @@
+"""-m gpu: lipvq_mlp3_fwd_f32 (three linear layers in one launch, csrc/mlp_chain.cu) through the C-ABI against the CPU
+oracle's encoder / decoder (backbone_lfqvae_v5.py:54-68, 70-76) and against three lipvq_linear_fwd_f32 launches."""
+import pytest
+import torch
+
+import lipvq_oracle as O
+from test_gpu_kernels import DEV
+
+pytestmark = pytest.mark.gpu
+
+
+def _three(L, x, W1, b1, a1, W2, b2, a2, W3, b3, a3):
+    h = L.ops.linear_fwd(x, L.ACT_NONE, W1, b1, a1)
+    h = L.ops.linear_fwd(h, L.ACT_NONE, W2, b2, a2)
+    return L.ops.linear_fwd(h, L.ACT_NONE, W3, b3, a3)
+
+
+@pytest.mark.parametrize("N,dims", [(65536, (12, 64, 128, 64)), (4096, (7, 64, 128, 64)), (9000, (64, 64, 128, 12)),
+                                    (5000, (12, 64, 128, 48)), (4100, (30, 50, 100, 20)), (6000, (100, 64, 72, 16))])
+def test_mlp3_vs_three_launches_and_torch(N, dims):
+    import lipvq as L
+    d0, d1, d2, d3 = dims
+    assert L.ops.mlp3_supported(N, d0, d1, d2, d3)
+    g = torch.Generator().manual_seed(N + d0 + d3)
+    x = torch.rand(N, d0, generator=g) * 2 - 1
+    Ws = [torch.randn(o, i, generator=g) / i ** 0.5 for i, o in ((d0, d1), (d1, d2), (d2, d3))]
+    bs = [torch.randn(o, generator=g) * 0.1 for o in (d1, d2, d3)]
+    acts = (L.ACT_GELU, L.ACT_GELU, L.ACT_SIGMOID)
+    xd = x.to(DEV)
+    Wd, bd = [w.to(DEV) for w in Ws], [b.to(DEV) for b in bs]
+    y = L.ops.mlp3_fwd(xd, Wd[0], bd[0], acts[0], Wd[1], bd[1], acts[1], Wd[2], bd[2], acts[2])
+    y3 = _three(L, xd, Wd[0], bd[0], acts[0], Wd[1], bd[1], acts[1], Wd[2], bd[2], acts[2])
+    torch.cuda.synchronize()
+    h = torch.nn.functional.gelu(x.double() @ Ws[0].double().t() + bs[0].double())
+    h = torch.nn.functional.gelu(h @ Ws[1].double().t() + bs[1].double())
+    ref = torch.sigmoid(h @ Ws[2].double().t() + bs[2].double())
+    assert torch.allclose(y.cpu().double(), ref, rtol=1e-5, atol=2e-6), (y.cpu().double() - ref).abs().max()
+    assert torch.allclose(y, y3, rtol=1e-6, atol=1e-6), (y - y3).abs().max()
+    # no bias, other activations (the decoder ends without one)
+    y = L.ops.mlp3_fwd(xd, Wd[0], None, L.ACT_RELU, Wd[1], bd[1], L.ACT_GELU, Wd[2], None, L.ACT_NONE)
+    h = torch.relu(x.double() @ Ws[0].double().t())
+    h = torch.nn.functional.gelu(h @ Ws[1].double().t() + bs[1].double())
+    ref = h @ Ws[2].double().t()
+    assert torch.allclose(y.cpu().double(), ref, rtol=1e-5, atol=5e-6), (y.cpu().double() - ref).abs().max()
+
+
+def test_tokenize_uses_the_fused_encoder_and_matches_the_oracle():
+    import lipvq as L
+    from lipvq.trainer import TokenizerTrainer
+    torch.manual_seed(1)
+    N = 8192
+    m = L.LLFQVAE_V4(12, 64, 512)
+    m.quantizer = L.LFQQuantizerEMA(512, 64)
+    sd = {k: v.clone() for k, v in m.state_dict().items()}
+    m.to(DEV).train()
+    tr = TokenizerTrainer(m, N)
+    x = torch.rand(N, 12) * 2 - 1
+    c0 = L.launch_count()
+    idx = tr.tokenize(x.to(DEV)).cpu()
+    z_e = tr.bufs.t["z_e"].cpu()
+    p = {k: sd[k] for k in ("encoder.0.weight", "encoder.0.bias", "encoder.2.weight", "encoder.2.bias", "to_latent.W",
+                            "to_latent.b", "to_latent.ci", "quantizer.codebook")}
+    ref_z = O.t1_encode(p, x)
+    assert torch.allclose(z_e, ref_z, rtol=1e-5, atol=2e-6), (z_e - ref_z).abs().max()
+    from test_gpu_kernels import assert_indices
+    assert_indices(ref_z, p["quantizer.codebook"], idx, O.nearest_code_l2(ref_z, p["quantizer.codebook"]), max_near_tie_frac=0.02)
