@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 6
+#define LIPVQ_ABI_VERSION 7
 #define LIPVQ_API __attribute__((visibility("default")))
 
 enum {
@@ -242,7 +242,14 @@ LIPVQ_API int lipvq_linear_fwd_dual_f32(const float* X, int64_t N, int in_dim, i
  * chains, fp32 accumulation, fp32 bias + activation); hidden activations stay in shared memory / TMEM.
  * supported(): 1 when the widths fit (weights of all layers resident in shared memory, N >= 4096), else 0 -- chain three
  * lipvq_linear_fwd_f32 calls. */
+/* lipvq_mlp3_fwd_bf16_f32: the bf16 mode of the same chain (north_star's reduced-precision gate: results within 1e-2
+ * of the fp32 reference).  Inputs, outputs, biases and accumulation stay fp32; activations and weights enter the tensor
+ * core as plain bf16 (one MMA chain instead of six).  No counterpart in the reference, which runs the tokenizer in fp32
+ * (algo/icl.py:788, 976: self.nets.float()); BASELINE config 5 names bf16 for the policy step around it. */
 LIPVQ_API int lipvq_mlp3_fwd_supported(int64_t N, int d0, int d1, int d2, int d3);
+LIPVQ_API int lipvq_mlp3_fwd_bf16_f32(const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1,
+                        const float* W2, const float* b2, int d2, int act2, const float* W3, const float* b3, int d3,
+                        int act3, float* Y, void* stream);
 LIPVQ_API int lipvq_mlp3_fwd_f32(const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1,
                         const float* W2, const float* b2, int d2, int act2, const float* W3, const float* b3, int d3,
                         int act3, float* Y, void* stream);

@@ -65,6 +65,7 @@ struct Mlp3Params {
   float* Y; int64_t ldy;
   uint32_t tmem_cols;
   int fast_gelu;
+  int terms;   // 3: fp32-accurate (three bf16 terms per operand, six MMA chains); 1: plain bf16 operands, one chain
 };
 
 __device__ __forceinline__ uint32_t bf16x2_rn(float lo, float hi) {
@@ -81,11 +82,15 @@ __device__ __forceinline__ void split3_pair(float x0, float x1, uint32_t& h, uin
 }
 // eight consecutive values of tile row r, 16-byte chunk ch of 64-wide chunk c: the three terms of an operand whose
 // terms are `term_stride` bytes apart
-__device__ __forceinline__ void store_split8(uint8_t* base, int term_stride, int r, int ch, const float (&y)[8]) {
+__device__ __forceinline__ void store_split8(uint8_t* base, int term_stride, int r, int ch, const float (&y)[8], int terms = 3) {
+  uint8_t* d = base + (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
+  if (terms == 1) {  // bf16 mode: round to nearest, one term
+    *reinterpret_cast<uint4*>(d) = make_uint4(bf16x2_rn(y[0], y[1]), bf16x2_rn(y[2], y[3]), bf16x2_rn(y[4], y[5]), bf16x2_rn(y[6], y[7]));
+    return;
+  }
   uint32_t hh[4], mm[4], ll[4];
 #pragma unroll
   for (int e = 0; e < 8; e += 2) split3_pair(y[e], y[e + 1], hh[e >> 1], mm[e >> 1], ll[e >> 1]);
-  uint8_t* d = base + (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
   *reinterpret_cast<uint4*>(d) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
   *reinterpret_cast<uint4*>(d + term_stride) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
   *reinterpret_cast<uint4*>(d + 2 * term_stride) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
@@ -219,7 +224,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp3_tc_kernel(const Mlp3Params p
         const int krem = p.din[l] - c * kChunk;
         const int ksteps = krem >= kChunk ? kChunk / 16 : (krem + 15) / 16;
         uint32_t acc_flag = c > 0 ? 1u : 0u;
-        if (ksteps == kChunk / 16) {
+        if (p.terms == 1) {  // bf16 mode: the h x h chain only
+          const uint32_t al = pl ? a_lo[1][0] : a_lo[0][0];
+          for (int k = 0; k < ksteps; ++k) {
+            umma_f16_lo(d_tmem, al + 2 * k, b_lo[0] + 2 * k, kDescSw128Hi, idesc, acc_flag);
+            acc_flag = 1;
+          }
+        } else if (ksteps == kChunk / 16) {
 #pragma unroll
           for (int combo = 0; combo < 6; ++combo) {
             const uint32_t al = pl ? a_lo[1][ta[combo]] : a_lo[0][ta[combo]], bl_ = b_lo[tb[combo]];
@@ -278,7 +289,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp3_tc_kernel(const Mlp3Params p
 #pragma unroll
           for (int e = 0; e < 8; ++e) w[e] = (n < Nb && k0 + e < Ka) ? __ldg(src + e) : 0.f;
         }
-        store_split8(wdst + (kc >> 3) * b_tile, p.NC[l] * b_tile, n, kc & 7, w);
+        store_split8(wdst + (kc >> 3) * b_tile, p.NC[l] * b_tile, n, kc & 7, w, p.terms);
       }
       for (int i = threadIdx.x; i < 256; i += kWorkers * 32)
         bias_s[l * 256 + i] = (p.b[l] != nullptr && i < Nb) ? __ldg(p.b[l] + i) : 0.f;
@@ -325,7 +336,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp3_tc_kernel(const Mlp3Params p
 #pragma unroll
                 for (int e = 0; e < 8; ++e) x[e] = (row < p.N && col + e < p.din[0]) ? __ldg(src + e) : 0.f;
               }
-              store_split8(sA, kTile, rr, ch, x);
+              store_split8(sA, kTile, rr, ch, x, p.terms);
             }
           } else {
             // columns [64 c, 64 c + 64) of the previous layer's accumulator: bias + activation -> bf16 terms
@@ -343,7 +354,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp3_tc_kernel(const Mlp3Params p
                 float y[8];
                 act8<Sel::act, Sel::fast>(v, bl + c0, y);
                 // (columns past dout hold act(0): they meet zero weight columns in this layer)
-                store_split8(sA, kTile, r, (c0 & 63) >> 3, y);
+                store_split8(sA, kTile, r, (c0 & 63) >> 3, y, p.terms);
               }
             });
             fence_before();  // the TMEM reads above are ordered before anything that follows the arrive
@@ -453,9 +464,9 @@ int lipvq_mlp3_fwd_supported(int64_t N, int d0, int d1, int d2, int d3) {
   return mlp3_geom(din, dout).ok ? 1 : 0;
 }
 
-int lipvq_mlp3_fwd_f32(const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1, const float* W2,
-                       const float* b2, int d2, int act2, const float* W3, const float* b3, int d3, int act3, float* Y,
-                       void* stream_) {
+static int mlp3_launch(int terms, const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1,
+                       const float* W2, const float* b2, int d2, int act2, const float* W3, const float* b3, int d3, int act3,
+                       float* Y, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
   LIPVQ_REQUIRE(N >= 0 && d0 > 0 && d1 > 0 && d2 > 0 && d3 > 0, "mlp3_fwd: bad shape");
   if (N == 0) return LIPVQ_OK;
@@ -478,6 +489,7 @@ int lipvq_mlp3_fwd_f32(const float* X, int64_t N, int d0, const float* W1, const
   p.Y = Y; p.ldy = d3;
   p.tmem_cols = g.tmem_cols;
   p.fast_gelu = !(getenv("LIPVQ_EXACT_GELU") != nullptr && getenv("LIPVQ_EXACT_GELU")[0] == '1');
+  p.terms = terms;
   static size_t smem_set[kMaxDevices] = {};  // the attribute is per device
   const int dev_ = current_device();
   if (g.smem > smem_set[dev_]) {
@@ -489,6 +501,18 @@ int lipvq_mlp3_fwd_f32(const float* X, int64_t N, int d0, const float* W1, const
   LIPVQ_CUDA(launch_pdl(mlp3_tc_kernel, dim3(row_blocks < sms ? row_blocks : sms), dim3(kThreads), g.smem, stream, p));
   LIPVQ_LAUNCHED("mlp3_tc_kernel");
   return LIPVQ_OK;
+}
+
+int lipvq_mlp3_fwd_f32(const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1, const float* W2,
+                       const float* b2, int d2, int act2, const float* W3, const float* b3, int d3, int act3, float* Y,
+                       void* stream) {
+  return mlp3_launch(3, X, N, d0, W1, b1, d1, act1, W2, b2, d2, act2, W3, b3, d3, act3, Y, stream);
+}
+
+int lipvq_mlp3_fwd_bf16_f32(const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1, const float* W2,
+                            const float* b2, int d2, int act2, const float* W3, const float* b3, int d3, int act3, float* Y,
+                            void* stream) {
+  return mlp3_launch(1, X, N, d0, W1, b1, d1, act1, W2, b2, d2, act2, W3, b3, d3, act3, Y, stream);
 }
 
 #ifdef LIPVQ_TRACE

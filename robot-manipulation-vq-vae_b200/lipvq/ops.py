@@ -264,15 +264,16 @@ def mlp3_supported(N: int, d0: int, d1: int, d2: int, d3: int) -> bool:
     return bool(lib.lipvq_mlp3_fwd_supported(N, d0, d1, d2, d3))
 
 
-def mlp3_fwd(x, W1, b1, act1: int, W2, b2, act2: int, W3, b3, act3: int, out=None):
-    """act3(act2(act1(x W1^T + b1) W2^T + b2) W3^T + b3) in one launch (inference: no hidden activations are stored)."""
+def mlp3_fwd(x, W1, b1, act1: int, W2, b2, act2: int, W3, b3, act3: int, out=None, bf16: bool = False):
+    """act3(act2(act1(x W1^T + b1) W2^T + b2) W3^T + b3) in one launch (inference: no hidden activations are stored).
+    ``bf16``: activations and weights enter the tensor core as plain bf16 (fp32 accumulation, bias, activation, I/O)."""
     d0 = x.shape[-1]
     N = x.numel() // d0
     d1, d2, d3 = W1.shape[0], W2.shape[0], W3.shape[0]
     if W1.shape[1] != d0 or W2.shape[1] != d1 or W3.shape[1] != d2:
         raise RuntimeError(f"mlp3_fwd: widths do not chain: x {d0}, W1 {tuple(W1.shape)}, W2 {tuple(W2.shape)}, W3 {tuple(W3.shape)}")
     y = out if out is not None else torch.empty(*x.shape[:-1], d3, dtype=F32, device=x.device)
-    _call(lib.lipvq_mlp3_fwd_f32, "mlp3_fwd", _chk(x, F32, "x"), N, d0, _chk(W1, F32, "W1"), _chk(b1, F32, "b1", True), d1, act1,
+    _call(lib.lipvq_mlp3_fwd_bf16_f32 if bf16 else lib.lipvq_mlp3_fwd_f32, "mlp3_fwd", _chk(x, F32, "x"), N, d0, _chk(W1, F32, "W1"), _chk(b1, F32, "b1", True), d1, act1,
           _chk(W2, F32, "W2"), _chk(b2, F32, "b2", True), d2, act2, _chk(W3, F32, "W3"), _chk(b3, F32, "b3", True), d3, act3,
           _chk(y, F32, "y"), _stream())
     return y

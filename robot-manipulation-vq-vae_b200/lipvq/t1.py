@@ -86,19 +86,20 @@ def prepare_search(p: Dict[str, torch.Tensor], b: T1Buffers, center: Optional[to
 
 def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: int = A.ALGO_AUTO,
             encode_only: bool = False, search_prepared: bool = False, weights_prepared: bool = False,
-            prepare_search_here: bool = False) -> None:
+            prepare_search_here: bool = False, encoder_bf16: bool = False) -> None:
     """x [N,F] -> b.t[...]: z_e, idx, z_q, x_recon, losses.  ``encode_only`` stops after the search
     (the bulk-tokenisation path: encode + VQ).  ``search_prepared``: b.t["ws"] was prepared for the current codebook
     (prepare_search); ``weights_prepared``: b.t["Wn"] already holds the clamped to_latent weight of the current
     parameters (bulk tokenisation with fixed weights); ``prepare_search_here``: prepare the codebook inside this call,
-    centred on this batch's latents, right before the search (then ``search_prepared`` applies)."""
+    centred on this batch's latents, right before the search (then ``search_prepared`` applies); ``encoder_bf16``
+    (bulk tokenisation only): the fused encoder in its bf16 mode."""
     t = b.t
     if not weights_prepared:
         ops.lipschitz_scale_fwd(p["to_latent.W"], p["to_latent.ci"], t["Wn"])
     fused_enc = encode_only and ops.mlp3_supported(b.N, b.F, 64, b.H, b.D)
     if fused_enc:  # bulk tokenisation: the three encoder layers in one launch, hidden activations never leave the SM
         ops.mlp3_fwd(x, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, p["encoder.2.weight"], p["encoder.2.bias"],
-                     A.ACT_GELU, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"])
+                     A.ACT_GELU, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"], bf16=encoder_bf16)
     elif encode_only:
         ops.linear_fwd(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, out=t["a1"])
         ops.linear_fwd(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, out=t["a2"])

@@ -124,6 +124,8 @@ class TokenizerTrainer:
         self._graph_full = None  # world > 1: phase a + all-reduce + phase b in one graph
         self._graph_tok = None
         self._graph_tok_fast = None
+        self._graph_tok_bf16 = None
+        self._graph_tok_fast_bf16 = None
         self.graph_collective = os.environ.get("LIPVQ_GRAPH_COLLECTIVE", "1") != "0"
         # input prefetch (step(x, prefetch=x_next)): the next batch's H2D copy runs on its own stream under this step
         self._stage = None
@@ -280,42 +282,44 @@ class TokenizerTrainer:
         return self.bufs.t["idx"]
 
     @torch.no_grad()
-    def tokenize(self, x: torch.Tensor, prepared: bool = False) -> torch.Tensor:
+    def tokenize(self, x: torch.Tensor, prepared: bool = False, bf16: bool = False) -> torch.Tensor:
         """encode + VQ only on x [N,F] (bulk tokenisation) -> int64 [N] (a buffer the next call overwrites).
         ``prepared=True``: the parameters have not changed since the last step() / tokenize() / refresh() of this
         trainer -- the clamped to_latent weight and the prepared codebook of that call are reused (bulk tokenisation
-        of a dataset with fixed weights: three linear layers + one search launch per call)."""
+        of a dataset with fixed weights: one encoder launch + one search launch per call).  ``bf16=True``: the encoder's
+        matrix products take bf16 operands (fp32 accumulation; latents within 1e-2 of the fp32 path, so a token can
+        differ where two codes are about equally near); the search on those latents is exact as always."""
         if tuple(x.shape) != tuple(self.x_static.shape):
             raise RuntimeError(f"expected input of shape {tuple(self.x_static.shape)}, got {tuple(x.shape)}")
         with torch.cuda.device(self.device):
-            return self._tokenize(x, prepared and self.search_prepared and self._tok_ready)
+            return self._tokenize(x, prepared and self.search_prepared and self._tok_ready, bool(bf16))
 
     _tok_ready = False  # Wn and the prepared codebook in bufs are those of the current parameters
 
-    def _tok_forward(self, fast: bool) -> None:
+    def _tok_forward(self, fast: bool, bf16: bool = False) -> None:
         if fast:
             t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True, search_prepared=True,
-                       weights_prepared=True)
+                       weights_prepared=True, encoder_bf16=bf16)
             return
         t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo, encode_only=True,
-                   prepare_search_here=self.search_prepared)
+                   prepare_search_here=self.search_prepared, encoder_bf16=bf16)
 
-    def _tokenize(self, x: torch.Tensor, fast: bool) -> torch.Tensor:
+    def _tokenize(self, x: torch.Tensor, fast: bool, bf16: bool = False) -> torch.Tensor:
         self.x_static.copy_(x, non_blocking=True)
         if not self.use_graph:
-            self._tok_forward(fast)
+            self._tok_forward(fast, bf16)
             self._tok_ready = True
             return self.bufs.t["idx"]
-        attr = "_graph_tok_fast" if fast else "_graph_tok"
+        attr = ("_graph_tok_fast" if fast else "_graph_tok") + ("_bf16" if bf16 else "")
         if getattr(self, attr) is None:
             s = torch.cuda.Stream(device=self.device)
             s.wait_stream(torch.cuda.current_stream(self.device))
             with torch.cuda.stream(s):
-                self._tok_forward(fast)
+                self._tok_forward(fast, bf16)
             torch.cuda.current_stream(self.device).wait_stream(s)
             g = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g):
-                self._tok_forward(fast)
+                self._tok_forward(fast, bf16)
             setattr(self, attr, g)
         getattr(self, attr).replay()
         self._tok_ready = True

@@ -64,3 +64,43 @@ def test_tokenize_uses_the_fused_encoder_and_matches_the_oracle():
     assert torch.allclose(z_e, ref_z, rtol=1e-5, atol=2e-6), (z_e - ref_z).abs().max()
     from test_gpu_kernels import assert_indices
     assert_indices(ref_z, p["quantizer.codebook"], idx, O.nearest_code_l2(ref_z, p["quantizer.codebook"]), max_near_tie_frac=0.02)
+
+
+def test_mlp3_bf16_mode_within_the_reduced_precision_gate():
+    """north_star: losses and reconstructions within 1e-2 for bf16.  The bf16 mode of the fused encoder (plain bf16 operands,
+    fp32 accumulation / bias / activation) against the fp64 evaluation of the same layers, and tokenize(bf16=True) against
+    the fp32 path: same token except where two codes are about equally near."""
+    import lipvq as L
+    from lipvq.trainer import TokenizerTrainer
+    g = torch.Generator().manual_seed(5)
+    N, dims = 16384, (12, 64, 128, 64)
+    x = torch.rand(N, dims[0], generator=g) * 2 - 1
+    Ws = [torch.randn(o, i, generator=g) / i ** 0.5 for i, o in zip(dims[:-1], dims[1:])]
+    bs = [torch.randn(o, generator=g) * 0.1 for o in dims[1:]]
+    y = L.ops.mlp3_fwd(x.to(DEV), Ws[0].to(DEV), bs[0].to(DEV), L.ACT_GELU, Ws[1].to(DEV), bs[1].to(DEV), L.ACT_GELU,
+                       Ws[2].to(DEV), bs[2].to(DEV), L.ACT_SIGMOID, bf16=True).cpu().double()
+    h = torch.nn.functional.gelu(x.double() @ Ws[0].double().t() + bs[0].double())
+    h = torch.nn.functional.gelu(h @ Ws[1].double().t() + bs[1].double())
+    ref = torch.sigmoid(h @ Ws[2].double().t() + bs[2].double())
+    err = (y - ref).abs().max().item()
+    assert 1e-6 < err < 1e-2, err      # (bf16 operands: not the fp32-accurate path, and inside the gate)
+    torch.manual_seed(2)
+    m = L.LLFQVAE_V4(12, 64, 512)
+    m.quantizer = L.LFQQuantizerEMA(512, 64)
+    m.to(DEV).train()
+    tr = TokenizerTrainer(m, 8192)
+    xb = (torch.rand(8192, 12) * 2 - 1).to(DEV)
+    for _ in range(3):
+        tr.step(xb)
+    a = tr.tokenize(xb).clone()
+    z32 = tr.bufs.t["z_e"].clone()
+    b = tr.tokenize(xb, bf16=True).clone()
+    z16 = tr.bufs.t["z_e"].clone()
+    assert (z16 - z32).abs().max().item() < 1e-2
+    cb = tr.p["quantizer.codebook"]
+    diff = (a != b).nonzero().flatten()
+    if diff.numel():   # a different token only where the fp32 latent is about as near to the other code
+        da = (z32[diff] - cb[a[diff]]).norm(dim=-1)
+        db = (z32[diff] - cb[b[diff]]).norm(dim=-1)
+        assert ((db - da) <= 2e-2 * (1 + da)).all()
+    assert diff.numel() <= 0.2 * a.numel()
