@@ -122,6 +122,10 @@ __device__ __forceinline__ void act8(const uint32_t (&v)[8], const float* bl, fl
     if (ACT == LIPVQ_ACT_GELU && FAST) {
       float d;
       gelu_value_grad_fast(pre, y[e], d);
+    } else if (ACT == LIPVQ_ACT_SIGMOID && FAST) {
+      // 1 / (1 + 2^(-x log2 e)) on the approximate ex2 / rcp units (each within 2 ulp: |error| <= 3e-7 on a value in (0, 1));
+      // expf + an IEEE division made the 64-column output pass as long as two 128-column GELU steps
+      y[e] = rcp_approx(1.f + ex2_approx(-1.4426950408889634f * pre));
     } else {
       y[e] = act_apply(ACT, pre);
     }
@@ -137,7 +141,10 @@ __device__ __forceinline__ void dispatch_chain_act(int act, int fast_gelu, F&& b
       if (fast_gelu) body(ActSel<LIPVQ_ACT_GELU, true>{});
       else body(ActSel<LIPVQ_ACT_GELU, false>{});
       break;
-    case LIPVQ_ACT_SIGMOID: body(ActSel<LIPVQ_ACT_SIGMOID, false>{}); break;
+    case LIPVQ_ACT_SIGMOID:
+      if (fast_gelu) body(ActSel<LIPVQ_ACT_SIGMOID, true>{});
+      else body(ActSel<LIPVQ_ACT_SIGMOID, false>{});
+      break;
     default: body(ActSel<LIPVQ_ACT_NONE, false>{}); break;
   }
 }
@@ -264,35 +271,64 @@ __global__ void __launch_bounds__(kThreads, 1) mlp3_tc_kernel(const Mlp3Params p
   } else {
     // ===== workers =====
     // ---- weights of the three layers: (h, m, l) split, swizzled K-major tiles; biases (all sixteen warps) ----
-    for (int l = 0; l < 3; ++l) {
-      const int KC = p.NC[l] * (kChunk / 8);  // 16-byte chunks per tile row
-      const int items = p.Np[l] * KC;
-      const int b_tile = p.Np[l] * 128;
-      uint8_t* wdst = sW + p.wofs[l];
-      const float* W = p.W[l];
-      const int Ka = p.din[l], Nb = p.dout[l];
-      const bool vec = (Ka % 4 == 0) && ((reinterpret_cast<uintptr_t>(W) & 15) == 0);
-      // every CTA starts at a different item: all 148 CTAs stage the SAME 67 KB of weights, and asking for the same lines
-      // at the same moment queues the requests at the L2 slices that own them
-      const int rot = (int)((blockIdx.x * 53u) % (unsigned)items);
-      for (int j = threadIdx.x; j < items; j += kWorkers * 32) {
-        int it = j + rot;
-        if (it >= items) it -= items;
-        const int n = it / KC, kc = it - n * KC;
-        const int k0 = kc * 8;
-        float w[8];
-        const float* src = W + (int64_t)n * Ka + k0;
-        if (n < Nb && vec && k0 + 8 <= Ka) {
-          const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
-          w[0] = a.x; w[1] = a.y; w[2] = a.z; w[3] = a.w; w[4] = b.x; w[5] = b.y; w[6] = b.z; w[7] = b.w;
-        } else {
-#pragma unroll
-          for (int e = 0; e < 8; ++e) w[e] = (n < Nb && k0 + e < Ka) ? __ldg(src + e) : 0.f;
-        }
-        store_split8(wdst + (kc >> 3) * b_tile, p.NC[l] * b_tile, n, kc & 7, w, p.terms);
+    // One index space over the items of all three layers (an item = eight consecutive k of one output row), four items
+    // per thread and pass with ALL their loads in flight before the first conversion: layer by layer, one item at a time,
+    // the staging paid a dependent L2 / DRAM round trip per item and layer (6 600 cycles).
+    {
+      int KCl[3], itemsl[3];
+      for (int l = 0; l < 3; ++l) {
+        KCl[l] = p.NC[l] * (kChunk / 8);
+        itemsl[l] = p.Np[l] * KCl[l];
       }
-      for (int i = threadIdx.x; i < 256; i += kWorkers * 32)
-        bias_s[l * 256 + i] = (p.b[l] != nullptr && i < Nb) ? __ldg(p.b[l] + i) : 0.f;
+      const int total_items = itemsl[0] + itemsl[1] + itemsl[2];
+      for (int base = 0; base < total_items; base += 4 * kWorkers * 32) {
+        float w[4][8];
+        int lay[4], nn[4], kcs[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          int it = base + u * kWorkers * 32 + (int)threadIdx.x;
+          int l = -1;
+          if (it < total_items) {
+            l = 0;
+            if (it >= itemsl[0]) { it -= itemsl[0]; l = 1; }
+            if (l == 1 && it >= itemsl[1]) { it -= itemsl[1]; l = 2; }
+          }
+          lay[u] = l;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) w[u][e] = 0.f;
+          if (l >= 0) {
+            const int KC = l == 0 ? KCl[0] : (l == 1 ? KCl[1] : KCl[2]);
+            const int n = it / KC, kc = it - n * KC;
+            nn[u] = n;
+            kcs[u] = kc;
+            const int Ka = p.din[l], Nb = p.dout[l], k0 = kc * 8;
+            const float* W = p.W[l];
+            const float* src = W + (int64_t)n * Ka + k0;
+            if (n < Nb) {
+              if ((Ka % 4 == 0) && ((reinterpret_cast<uintptr_t>(W) & 15) == 0) && k0 + 8 <= Ka) {
+                const float4 a = __ldg(reinterpret_cast<const float4*>(src)), b = __ldg(reinterpret_cast<const float4*>(src) + 1);
+                w[u][0] = a.x; w[u][1] = a.y; w[u][2] = a.z; w[u][3] = a.w; w[u][4] = b.x; w[u][5] = b.y; w[u][6] = b.z; w[u][7] = b.w;
+              } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                  if (k0 + e < Ka) w[u][e] = __ldg(src + e);
+              }
+            }
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const int l = lay[u];
+          if (l >= 0) {
+            const int b_tile = p.Np[l] * 128;
+            store_split8(sW + p.wofs[l] + (kcs[u] >> 3) * b_tile, p.NC[l] * b_tile, nn[u], kcs[u] & 7, w[u], p.terms);
+          }
+        }
+      }
+      for (int i = threadIdx.x; i < 3 * 256; i += kWorkers * 32) {
+        const int l = i >> 8, c = i & 255;
+        bias_s[i] = (p.b[l] != nullptr && c < p.dout[l]) ? __ldg(p.b[l] + c) : 0.f;
+      }
     }
     fence_async_smem();
     asm volatile("bar.sync 1, %0;" ::"n"(kWorkers * 32) : "memory");  // biases visible to every worker
@@ -374,6 +410,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp3_tc_kernel(const Mlp3Params p
         const uint32_t trow = acc_base + (uint32_t)p.acc[2];
         const float* bl = bias_s + 2 * 256;
         const int act = p.act[2];
+        // A lane holds eight columns of ITS row: stored directly that is one 32-byte piece per lane, 32 different rows
+        // per instruction (the output pass took 7 000 cycles per row block).  The pipeline's region is free now, so the
+        // tile goes through it -- rows padded by 4 floats: the eight lanes of a quarter warp hit distinct banks -- and
+        // leaves in whole rows, consecutive threads writing consecutive 16 bytes.
+        const int ldo = p.Np[2] + 4;
+        const bool staged = (size_t)kBM * ldo * 4 <= (size_t)kRegion && vecY && (p.dout[2] % 4 == 0);
+        float* stile = reinterpret_cast<float*>(sA);
         dispatch_chain_act(act, p.fast_gelu, [&](auto sel) {
           using Sel = decltype(sel);
 #pragma unroll 1
@@ -383,6 +426,12 @@ __global__ void __launch_bounds__(kThreads, 1) mlp3_tc_kernel(const Mlp3Params p
             tmem_ld_wait8(v);
             float y[8];
             act8<Sel::act, Sel::fast>(v, bl + c0, y);
+            if (staged) {
+              float* d = stile + r * ldo + c0;
+              *reinterpret_cast<float4*>(d) = make_float4(y[0], y[1], y[2], y[3]);
+              *reinterpret_cast<float4*>(d + 4) = make_float4(y[4], y[5], y[6], y[7]);
+              continue;
+            }
             const int64_t row = row0 + r;
             if (row < p.N && c0 < p.dout[2]) {
               float* dst = p.Y + row * p.ldy + c0;
@@ -397,6 +446,17 @@ __global__ void __launch_bounds__(kThreads, 1) mlp3_tc_kernel(const Mlp3Params p
             }
           }
         });
+        if (staged) {
+          asm volatile("bar.sync %0, %1;" ::"r"(2 + pl), "n"(kPipeWarps * 32) : "memory");  // the tile is complete
+          const int c4n = p.dout[2] >> 2;  // float4 per output row
+          for (int idx = pt; idx < kBM * c4n; idx += kPipeWarps * 32) {
+            const int rr = idx / c4n, c4 = idx - rr * c4n;
+            const int64_t row = row0 + rr;
+            if (row < p.N)
+              *reinterpret_cast<float4*>(p.Y + row * p.ldy + 4 * c4) = *reinterpret_cast<const float4*>(stile + rr * ldo + 4 * c4);
+          }
+          asm volatile("bar.sync %0, %1;" ::"r"(2 + pl), "n"(kPipeWarps * 32) : "memory");  // read out: the region may be rewritten
+        }
         TR(13);
         fence_before();  // ordered before this warp's next arrive (the next block's first step overwrites nothing it read,
                          // but the MMAs of the next block's last layer overwrite this accumulator)
