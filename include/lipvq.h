@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 7
+#define LIPVQ_ABI_VERSION 8
 #define LIPVQ_API __attribute__((visibility("default")))
 
 enum {
@@ -242,6 +242,14 @@ LIPVQ_API int lipvq_linear_fwd_dual_f32(const float* X, int64_t N, int in_dim, i
  * chains, fp32 accumulation, fp32 bias + activation); hidden activations stay in shared memory / TMEM.
  * supported(): 1 when the widths fit (weights of all layers resident in shared memory, N >= 4096), else 0 -- chain three
  * lipvq_linear_fwd_f32 calls. */
+/* lipvq_mlp3_fwd_train_f32: the same chain as the forward of a TRAINING step -- the two hidden layers also store
+ * their activation H_l = act_l(pre_l) [N, d_l] and its derivative G_l = act_l'(pre_l) (what two
+ * lipvq_linear_fwd_dual_f32 calls store; consumed by lipvq_linear_bwd_x_f32 with LIPVQ_ACT_GIVEN and by
+ * lipvq_linear_bwd_w_f32).  Replaces the encoder / decoder forward of LLFQVAE_V4.forward with autograd's saved
+ * activations (backbone_lfqvae_v5.py:70-84). */
+LIPVQ_API int lipvq_mlp3_fwd_train_f32(const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1,
+                        const float* W2, const float* b2, int d2, int act2, const float* W3, const float* b3, int d3,
+                        int act3, float* Y, float* H1, float* G1, float* H2, float* G2, void* stream);
 /* lipvq_mlp3_fwd_bf16_f32: the bf16 mode of the same chain (north_star's reduced-precision gate: results within 1e-2
  * of the fp32 reference).  Inputs, outputs, biases and accumulation stay fp32; activations and weights enter the tensor
  * core as plain bf16 (one MMA chain instead of six).  No counterpart in the reference, which runs the tokenizer in fp32

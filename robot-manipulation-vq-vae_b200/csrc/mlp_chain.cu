@@ -63,6 +63,8 @@ struct Mlp3Params {
   int acc[3];  // TMEM column of each layer's accumulator (within a pipeline's columns)
   int acc_cols; // TMEM columns per pipeline
   float* Y; int64_t ldy;
+  float* H[2];  // training forward: act_l(pre_l) of the two hidden layers, [N, dout[l]] (NULL: not stored)
+  float* G[2];  // ... and act_l'(pre_l): one evaluation of erf / exp serves the value and the derivative
   uint32_t tmem_cols;
   int fast_gelu;
   int terms;   // 3: fp32-accurate (three bf16 terms per operand, six MMA chains); 1: plain bf16 operands, one chain
@@ -128,6 +130,22 @@ __device__ __forceinline__ void act8(const uint32_t (&v)[8], const float* bl, fl
       y[e] = rcp_approx(1.f + ex2_approx(-1.4426950408889634f * pre));
     } else {
       y[e] = act_apply(ACT, pre);
+    }
+  }
+}
+// the same with the activation's derivative (training forward: the hidden layers store both)
+template <int ACT, bool FAST>
+__device__ __forceinline__ void act8g(const uint32_t (&v)[8], const float* bl, float (&y)[8], float (&d)[8]) {
+  const float4 b0 = *reinterpret_cast<const float4*>(bl), b1 = *reinterpret_cast<const float4*>(bl + 4);
+  const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const float pre = __uint_as_float(v[e]) + bb[e];
+    if (ACT == LIPVQ_ACT_GELU && FAST) {
+      gelu_value_grad_fast(pre, y[e], d[e]);
+    } else {
+      y[e] = act_apply(ACT, pre);
+      d[e] = act_grad(ACT, pre);
     }
   }
 }
@@ -380,6 +398,10 @@ __global__ void __launch_bounds__(kThreads, 1) mlp3_tc_kernel(const Mlp3Params p
             const float* bl = bias_s + (l - 1) * 256;
             const int act = p.act[l - 1];
             const int c_hi = min(p.Np[l - 1], (c + 1) * kChunk);
+            float* Hl = p.H[l - 1];
+            float* Gl = p.G[l - 1];
+            const int dl = p.dout[l - 1];
+            const bool vecH = (dl % 4 == 0) && (((reinterpret_cast<uintptr_t>(Hl) | reinterpret_cast<uintptr_t>(Gl)) & 15) == 0);
             dispatch_chain_act(act, p.fast_gelu, [&](auto sel) {
               using Sel = decltype(sel);
 #pragma unroll 1
@@ -388,7 +410,32 @@ __global__ void __launch_bounds__(kThreads, 1) mlp3_tc_kernel(const Mlp3Params p
                 tmem_ld8(trow + c0, v);
                 tmem_ld_wait8(v);
                 float y[8];
-                act8<Sel::act, Sel::fast>(v, bl + c0, y);
+                if (Hl != nullptr) {
+                  // training forward: the hidden activation and its derivative also go to global memory (one 32-byte
+                  // piece per lane and array: whole sectors)
+                  float d[8];
+                  act8g<Sel::act, Sel::fast>(v, bl + c0, y, d);
+                  const int64_t row = row0 + r;
+                  if (row < p.N && c0 < dl) {
+                    float* hp = Hl + row * dl + c0;
+                    float* gp = Gl + row * dl + c0;
+                    if (vecH && c0 + 8 <= dl) {
+                      *reinterpret_cast<float4*>(hp) = make_float4(y[0], y[1], y[2], y[3]);
+                      *reinterpret_cast<float4*>(hp + 4) = make_float4(y[4], y[5], y[6], y[7]);
+                      *reinterpret_cast<float4*>(gp) = make_float4(d[0], d[1], d[2], d[3]);
+                      *reinterpret_cast<float4*>(gp + 4) = make_float4(d[4], d[5], d[6], d[7]);
+                    } else {
+#pragma unroll
+                      for (int e = 0; e < 8; ++e)
+                        if (c0 + e < dl) {
+                          hp[e] = y[e];
+                          gp[e] = d[e];
+                        }
+                    }
+                  }
+                } else {
+                  act8<Sel::act, Sel::fast>(v, bl + c0, y);
+                }
                 // (columns past dout hold act(0): they meet zero weight columns in this layer)
                 store_split8(sA, kTile, r, (c0 & 63) >> 3, y, p.terms);
               }
@@ -524,7 +571,7 @@ int lipvq_mlp3_fwd_supported(int64_t N, int d0, int d1, int d2, int d3) {
   return mlp3_geom(din, dout).ok ? 1 : 0;
 }
 
-static int mlp3_launch(int terms, const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1,
+static int mlp3_launch(int terms, float* H1, float* G1, float* H2, float* G2, const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1,
                        const float* W2, const float* b2, int d2, int act2, const float* W3, const float* b3, int d3, int act3,
                        float* Y, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -550,6 +597,7 @@ static int mlp3_launch(int terms, const float* X, int64_t N, int d0, const float
   p.tmem_cols = g.tmem_cols;
   p.fast_gelu = !(getenv("LIPVQ_EXACT_GELU") != nullptr && getenv("LIPVQ_EXACT_GELU")[0] == '1');
   p.terms = terms;
+  p.H[0] = H1; p.G[0] = G1; p.H[1] = H2; p.G[1] = G2;
   static size_t smem_set[kMaxDevices] = {};  // the attribute is per device
   const int dev_ = current_device();
   if (g.smem > smem_set[dev_]) {
@@ -566,13 +614,20 @@ static int mlp3_launch(int terms, const float* X, int64_t N, int d0, const float
 int lipvq_mlp3_fwd_f32(const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1, const float* W2,
                        const float* b2, int d2, int act2, const float* W3, const float* b3, int d3, int act3, float* Y,
                        void* stream) {
-  return mlp3_launch(3, X, N, d0, W1, b1, d1, act1, W2, b2, d2, act2, W3, b3, d3, act3, Y, stream);
+  return mlp3_launch(3, nullptr, nullptr, nullptr, nullptr, X, N, d0, W1, b1, d1, act1, W2, b2, d2, act2, W3, b3, d3, act3, Y, stream);
 }
 
 int lipvq_mlp3_fwd_bf16_f32(const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1, const float* W2,
                             const float* b2, int d2, int act2, const float* W3, const float* b3, int d3, int act3, float* Y,
                             void* stream) {
-  return mlp3_launch(1, X, N, d0, W1, b1, d1, act1, W2, b2, d2, act2, W3, b3, d3, act3, Y, stream);
+  return mlp3_launch(1, nullptr, nullptr, nullptr, nullptr, X, N, d0, W1, b1, d1, act1, W2, b2, d2, act2, W3, b3, d3, act3, Y, stream);
+}
+
+int lipvq_mlp3_fwd_train_f32(const float* X, int64_t N, int d0, const float* W1, const float* b1, int d1, int act1,
+                             const float* W2, const float* b2, int d2, int act2, const float* W3, const float* b3, int d3,
+                             int act3, float* Y, float* H1, float* G1, float* H2, float* G2, void* stream) {
+  LIPVQ_REQUIRE(H1 && G1 && H2 && G2, "mlp3_fwd_train: null pointer");
+  return mlp3_launch(3, H1, G1, H2, G2, X, N, d0, W1, b1, d1, act1, W2, b2, d2, act2, W3, b3, d3, act3, Y, stream);
 }
 
 #ifdef LIPVQ_TRACE

@@ -19,7 +19,7 @@ METRIC_L2, METRIC_L2SQ, METRIC_DOT = 0, 1, 2
 ALGO_AUTO, ALGO_SIMT_F32, ALGO_TCGEN05 = 0, 1, 2
 ACT_NONE, ACT_RELU, ACT_GELU, ACT_SIGMOID, ACT_GIVEN = 0, 1, 2, 3, 4
 EMA_SIMPLE, EMA_LAPLACE, EMA_NORMALIZE = 0, 1, 2
-ABI_VERSION = 7
+ABI_VERSION = 8
 
 _p, _i, _i64, _f, _d, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double, C.c_size_t
 
@@ -51,6 +51,7 @@ SIGNATURES = {
     "lipvq_linear_fwd_dual_f32": (_i, [_p, _i64, _i, _i, _p, _p, _i, _i, _p, _p, _p]),
     "lipvq_mlp3_fwd_supported": (_i, [_i64, _i, _i, _i, _i]),
     "lipvq_mlp3_fwd_f32": (_i, [_p, _i64, _i, _p, _p, _i, _i, _p, _p, _i, _i, _p, _p, _i, _i, _p, _p]),
+    "lipvq_mlp3_fwd_train_f32": (_i, [_p, _i64, _i, _p, _p, _i, _i, _p, _p, _i, _i, _p, _p, _i, _i, _p, _p, _p, _p, _p, _p]),
     "lipvq_mlp3_fwd_bf16_f32": (_i, [_p, _i64, _i, _p, _p, _i, _i, _p, _p, _i, _i, _p, _p, _i, _i, _p, _p]),
     "lipvq_linear_bwd_x_f32": (_i, [_p, _i64, _i, _p, _i, _p, _i, _p, _p]),
     "lipvq_linear_bwd_w_f32": (_i, [_p, _i64, _i, _p, _i, _i, _p, _p, _p]),

@@ -279,6 +279,20 @@ def mlp3_fwd(x, W1, b1, act1: int, W2, b2, act2: int, W3, b3, act3: int, out=Non
     return y
 
 
+def mlp3_fwd_train(x, W1, b1, act1: int, W2, b2, act2: int, W3, b3, act3: int, out, h1, g1, h2, g2):
+    """mlp3_fwd as the forward of a training step: the hidden layers also store their activation (h1, h2) and its
+    derivative (g1, g2) -- what two linear_fwd_dual calls store."""
+    d0 = x.shape[-1]
+    N = x.numel() // d0
+    d1, d2, d3 = W1.shape[0], W2.shape[0], W3.shape[0]
+    if W1.shape[1] != d0 or W2.shape[1] != d1 or W3.shape[1] != d2:
+        raise RuntimeError(f"mlp3_fwd_train: widths do not chain: x {d0}, W1 {tuple(W1.shape)}, W2 {tuple(W2.shape)}, W3 {tuple(W3.shape)}")
+    _call(lib.lipvq_mlp3_fwd_train_f32, "mlp3_fwd_train", _chk(x, F32, "x"), N, d0, _chk(W1, F32, "W1"), _chk(b1, F32, "b1", True), d1,
+          act1, _chk(W2, F32, "W2"), _chk(b2, F32, "b2", True), d2, act2, _chk(W3, F32, "W3"), _chk(b3, F32, "b3", True), d3, act3,
+          _chk(out, F32, "y"), _chk(h1, F32, "h1"), _chk(g1, F32, "g1"), _chk(h2, F32, "h2"), _chk(g2, F32, "g2"), _stream())
+    return out
+
+
 def linear_bwd_x(dY, W, Xpre, act_in: int, out=None):
     out_dim, in_dim = W.shape
     N = dY.numel() // out_dim

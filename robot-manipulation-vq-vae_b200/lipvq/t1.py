@@ -79,6 +79,14 @@ class T1Buffers:
                            "scratch": torch.zeros(1, dtype=torch.float64, device=dev)})
 
 
+def _fused_train() -> bool:
+    import os
+    # opt-in: measured SLOWER than the per-layer launches (0.497 vs 0.455 ms per step) -- in the fused kernel the four
+    # hidden tiles of a row block leave as one 32-byte piece per lane and array from the serial chain of a pipeline,
+    # while linear_tc_kernel stores them through TMA under the next block's MMAs
+    return os.environ.get("LIPVQ_MLP3_TRAIN", "0") == "1"
+
+
 def prepare_search(p: Dict[str, torch.Tensor], b: T1Buffers, center: Optional[torch.Tensor] = None) -> None:
     """Codebook-dependent half of the search, once per codebook version (see include/lipvq.h, K3)."""
     ops.nn_search_prepare(p["quantizer.codebook"], b.t["ws"], A.METRIC_L2, center=center)
@@ -96,6 +104,7 @@ def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: 
     t = b.t
     if not weights_prepared:
         ops.lipschitz_scale_fwd(p["to_latent.W"], p["to_latent.ci"], t["Wn"])
+    fused_train = False
     fused_enc = encode_only and ops.mlp3_supported(b.N, b.F, 64, b.H, b.D)
     if fused_enc:  # bulk tokenisation: the three encoder layers in one launch, hidden activations never leave the SM
         ops.mlp3_fwd(x, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, p["encoder.2.weight"], p["encoder.2.bias"],
@@ -105,8 +114,17 @@ def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: 
         ops.linear_fwd(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, out=t["a2"])
     else:
         b.alloc_derivatives()
-        ops.linear_fwd_dual(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, t["a1"], t["da1_act"])
-        ops.linear_fwd_dual(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, t["a2"], t["da2_act"])
+        # training forward: the three encoder layers in one launch that also stores the hidden activations and their
+        # derivatives (opt-in, LIPVQ_MLP3_TRAIN=1; default: three launches per chain)
+        fused_train = _fused_train() and ops.mlp3_supported(b.N, b.F, 64, b.H, b.D) and ops.mlp3_supported(b.N, b.D, 64, b.H, b.F)
+        if fused_train:
+            ops.mlp3_fwd_train(x, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, p["encoder.2.weight"],
+                               p["encoder.2.bias"], A.ACT_GELU, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, t["z_e"],
+                               t["a1"], t["da1_act"], t["a2"], t["da2_act"])
+            fused_enc = True
+        else:
+            ops.linear_fwd_dual(x, A.ACT_NONE, p["encoder.0.weight"], p["encoder.0.bias"], A.ACT_GELU, t["a1"], t["da1_act"])
+            ops.linear_fwd_dual(t["a1"], A.ACT_NONE, p["encoder.2.weight"], p["encoder.2.bias"], A.ACT_GELU, t["a2"], t["da2_act"])
     if not fused_enc:
         ops.linear_fwd(t["a2"], A.ACT_NONE, t["Wn"], p["to_latent.b"], A.ACT_SIGMOID, out=t["z_e"])
     if prepare_search_here:
@@ -121,9 +139,14 @@ def forward(p: Dict[str, torch.Tensor], x: torch.Tensor, b: T1Buffers, *, algo: 
     if not getattr(b, "zeroed_by_caller", False):  # the trainer clears sq and G with one fill at the start of the step
         t["sq"].zero_()
     ops.gather_fwd(t["z_e"], t["idx"], p["quantizer.codebook"], t["sq"][1:], z_q=t["z_q"])
-    ops.linear_fwd_dual(t["z_q"], A.ACT_NONE, p["decoder.0.weight"], p["decoder.0.bias"], A.ACT_GELU, t["c1"], t["dc1_act"])
-    ops.linear_fwd_dual(t["c1"], A.ACT_NONE, p["decoder.2.weight"], p["decoder.2.bias"], A.ACT_GELU, t["c2"], t["dc2_act"])
-    ops.linear_fwd(t["c2"], A.ACT_NONE, p["to_output.weight"], p["to_output.bias"], A.ACT_NONE, out=t["x_recon"])
+    if fused_train:
+        ops.mlp3_fwd_train(t["z_q"], p["decoder.0.weight"], p["decoder.0.bias"], A.ACT_GELU, p["decoder.2.weight"],
+                           p["decoder.2.bias"], A.ACT_GELU, p["to_output.weight"], p["to_output.bias"], A.ACT_NONE,
+                           t["x_recon"], t["c1"], t["dc1_act"], t["c2"], t["dc2_act"])
+    else:
+        ops.linear_fwd_dual(t["z_q"], A.ACT_NONE, p["decoder.0.weight"], p["decoder.0.bias"], A.ACT_GELU, t["c1"], t["dc1_act"])
+        ops.linear_fwd_dual(t["c1"], A.ACT_NONE, p["decoder.2.weight"], p["decoder.2.bias"], A.ACT_GELU, t["c2"], t["dc2_act"])
+        ops.linear_fwd(t["c2"], A.ACT_NONE, p["to_output.weight"], p["to_output.bias"], A.ACT_NONE, out=t["x_recon"])
     # when the backward buffers already exist (a training step) the same pass also writes d recon_loss / d x_recon,
     # which backward() then finds in place as long as the loss gradient is 1 (the trainer's case)
     b.dxr_from_forward = "dxr" in t

@@ -104,3 +104,25 @@ def test_mlp3_bf16_mode_within_the_reduced_precision_gate():
         db = (z32[diff] - cb[b[diff]]).norm(dim=-1)
         assert ((db - da) <= 2e-2 * (1 + da)).all()
     assert diff.numel() <= 0.2 * a.numel()
+
+
+def test_mlp3_train_variant_stores_what_two_dual_layers_store():
+    """lipvq_mlp3_fwd_train_f32 against lipvq_linear_fwd_dual_f32 x 2 + lipvq_linear_fwd_f32: hidden activations, their
+    derivatives and the output, at the encoder's and the decoder's widths."""
+    import lipvq as L
+    for N, dims, act3 in ((65536, (12, 64, 128, 64), L.ACT_SIGMOID), (9000, (64, 64, 128, 12), L.ACT_NONE)):
+        d0, d1, d2, d3 = dims
+        g = torch.Generator().manual_seed(N + d3)
+        x = (torch.rand(N, d0, generator=g) * 2 - 1).to(DEV)
+        Ws = [(torch.randn(o, i, generator=g) / i ** 0.5).to(DEV) for i, o in ((d0, d1), (d1, d2), (d2, d3))]
+        bs = [(torch.randn(o, generator=g) * 0.1).to(DEV) for o in (d1, d2, d3)]
+        e = lambda *s_: torch.empty(*s_, device=DEV)
+        y, h1, g1, h2, g2 = e(N, d3), e(N, d1), e(N, d1), e(N, d2), e(N, d2)
+        L.ops.mlp3_fwd_train(x, Ws[0], bs[0], L.ACT_GELU, Ws[1], bs[1], L.ACT_GELU, Ws[2], bs[2], act3, y, h1, g1, h2, g2)
+        r1, q1, r2, q2 = e(N, d1), e(N, d1), e(N, d2), e(N, d2)
+        L.ops.linear_fwd_dual(x, L.ACT_NONE, Ws[0], bs[0], L.ACT_GELU, r1, q1)
+        L.ops.linear_fwd_dual(r1, L.ACT_NONE, Ws[1], bs[1], L.ACT_GELU, r2, q2)
+        ry = L.ops.linear_fwd(r2, L.ACT_NONE, Ws[2], bs[2], act3)
+        torch.cuda.synchronize()
+        for a, b, what in ((h1, r1, "h1"), (g1, q1, "g1"), (h2, r2, "h2"), (g2, q2, "g2"), (y, ry, "y")):
+            assert torch.allclose(a, b, rtol=1e-6, atol=1e-6), (what, (a - b).abs().max().item())
