@@ -84,3 +84,27 @@ def test_missing_library_fails_loudly(tmp_path):
                PYTHONPATH=os.path.join(ROOT, "robot-manipulation-vq-vae_b200"))
     r = subprocess.run(["python", "-c", "import lipvq"], env=env, capture_output=True, text=True)
     assert r.returncode != 0 and "no CPU fallback" in r.stderr
+
+
+def test_host_side_planning_of_the_round2_entry_points():
+    """No GPU needed: which shapes take the prepared search / the fused encoder, and that the workspace grows with the
+    prepared state (the functions only evaluate geometry)."""
+    import ctypes as C
+    from lipvq import _cabi as A
+    lib = A.lib
+    # the tokenizer's own codebook stays resident in shared memory; big codebooks stream and have no prepared form
+    assert lib.lipvq_nn_search_prepared_supported(65536, 64, 512, A.METRIC_L2) == 1
+    assert lib.lipvq_nn_search_prepared_supported(65536, 64, 65536, A.METRIC_L2) == 0
+    assert lib.lipvq_nn_search_prepared_supported(64, 64, 512, A.METRIC_L2) == 0        # tiny batch: FFMA path
+    assert lib.lipvq_nn_search_prepared_supported(65536, 256, 4096, A.METRIC_L2) == 0
+    ws_tc = lib.lipvq_nn_search_workspace_bytes(65536, 64, 512, A.METRIC_L2, A.ALGO_TCGEN05)
+    img = 512 * 64 * 2 + 512 * 32
+    assert ws_tc >= 2 * img + 3 * 65536 * 4, ws_tc   # two code images (self-contained call + prepared state) + the queues
+    # fused three-layer forward: the encoder's and the decoder's widths fit, a 208-wide output does not (TMEM columns)
+    assert lib.lipvq_mlp3_fwd_supported(65536, 12, 64, 128, 64) == 1
+    assert lib.lipvq_mlp3_fwd_supported(65536, 64, 64, 128, 12) == 1
+    assert lib.lipvq_mlp3_fwd_supported(65536, 12, 64, 128, 208) == 0
+    assert lib.lipvq_mlp3_fwd_supported(1024, 12, 64, 128, 64) == 0                       # small batches: FFMA tiles
+    # error path without a device: a streamed codebook is refused before any launch
+    rc = lib.lipvq_nn_search_prepare_f32(C.c_void_p(16), 65536, 64, A.METRIC_L2, None, 0, C.c_void_p(16), 1 << 30, None)
+    assert rc == A.ERR_UNSUPPORTED and b"resident" in lib.lipvq_last_error()
