@@ -89,12 +89,15 @@ LIPVQ_API uint64_t lipvq_launch_count(void);
  * three-term fp16 split over the rows left, and finally an exact fp32 direct-difference scan
  * (sqrt applied for METRIC_L2, first-min tie rule).  The fp32 FFMA path has two levels (FFMA
  * tiles, exact scan).  Indices therefore equal the reference's except where the reference's
- * own fp32 rounding decides (relative distance gap < 1e-6).
+ * own fp32 rounding decides (relative distance gap < 1e-6).  Codebooks that stay resident in shared memory (every
+ * tokenizer codebook of the reference) take ONE launch: the fp16 pass settles the rows it cannot certify itself -- a
+ * candidate filter on the CUDA cores from the resident fp16 tiles, then the exact fp32 evaluation of the candidates.
  *
  *   z [N,D], codebook [K,D] fp32; idx_out [N] int64; best_out [N] fp32 or NULL (exact winning
  *   distance / squared distance / similarity, as the metric defines).
  *   stats_out: NULL or 4 x int32 on device: {rows decided by the exact scan, rows the first
- *   (fastest) level could not certify, 0, 0}.
+ *   (fastest) level could not certify, and -- when the single-launch pass settles its own rows (codebooks resident in
+ *   shared memory) -- codes evaluated exactly for those rows, rows for which every code was evaluated; else 0, 0}.
  * --------------------------------------------------------------------------------------------- */
 LIPVQ_API size_t lipvq_nn_search_workspace_bytes(int64_t N, int D, int K, int metric, int algo);
 LIPVQ_API int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook, int K, int metric, int algo,
