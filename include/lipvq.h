@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define LIPVQ_ABI_VERSION 8
+#define LIPVQ_ABI_VERSION 9
 #define LIPVQ_API __attribute__((visibility("default")))
 
 enum {
@@ -355,6 +355,15 @@ LIPVQ_API int lipvq_allreduce_oneshot_ctas(void);
 LIPVQ_API size_t lipvq_allreduce_oneshot_flag_bytes(int world);
 LIPVQ_API int lipvq_allreduce_oneshot_f32(const uint64_t* peer_ptrs_dev, int rank, int world, int64_t n,
                                 int64_t flag_offset_bytes, float* out, uint32_t* cta_epoch, void* stream);
+/* The same reduction with its second flag exchange taken off the critical path: ..._deferred_f32 only SIGNALS "I have
+ * read your slab" on its way out, and ..._clear_f32 -- which replaces the memset that clears the slab at the start of
+ * the next step -- waits for the peers' signals of the last reduction (about a step old by then) before it zeroes
+ * slab[0..n).  The pair must be used together: after a deferred reduction the slab may only be written again behind
+ * lipvq_allreduce_oneshot_clear_f32.  Same arguments as above (clear takes no `out`). */
+LIPVQ_API int lipvq_allreduce_oneshot_deferred_f32(const uint64_t* peer_ptrs_dev, int rank, int world, int64_t n,
+                        int64_t flag_offset_bytes, float* out, uint32_t* cta_epoch, void* stream);
+LIPVQ_API int lipvq_allreduce_oneshot_clear_f32(const uint64_t* peer_ptrs_dev, int rank, int world, int64_t n,
+                        int64_t flag_offset_bytes, const uint32_t* cta_epoch, void* stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Callers and data formats either side of the tokenizer.

@@ -36,13 +36,18 @@ __device__ __forceinline__ float4 ld_peer_f4(const float4* p) {  // system-scope
 }
 
 // flags of one rank: [2 phases][world][gridDim.x] uint32 at byte offset flag_off of its symmetric buffer
-__device__ __forceinline__ void exchange(const uint64_t* peer_ptrs, int64_t flag_off, int phase, int rank, int world,
-                                         uint32_t epoch, long long timeout_clocks) {
+__device__ __forceinline__ void signal_peers(const uint64_t* peer_ptrs, int64_t flag_off, int phase, int rank, int world, uint32_t epoch) {
   const int G = gridDim.x, b = blockIdx.x;
   if ((int)threadIdx.x < world) {
     uint32_t* theirs = reinterpret_cast<uint32_t*>(peer_ptrs[threadIdx.x] + flag_off) + ((size_t)phase * world + rank) * G + b;
     __threadfence_system();
     st_release_sys(theirs, epoch);
+  }
+}
+__device__ __forceinline__ void wait_peers(const uint64_t* peer_ptrs, int64_t flag_off, int phase, int rank, int world, uint32_t epoch,
+                                           long long timeout_clocks) {
+  const int G = gridDim.x, b = blockIdx.x;
+  if ((int)threadIdx.x < world) {
     const uint32_t* mine = reinterpret_cast<const uint32_t*>(peer_ptrs[rank] + flag_off) + ((size_t)phase * world + threadIdx.x) * G + b;
     long long t0 = 0;
     uint32_t spins = 0;
@@ -62,11 +67,20 @@ __device__ __forceinline__ void exchange(const uint64_t* peer_ptrs, int64_t flag
   }
   __syncthreads();
 }
+__device__ __forceinline__ void exchange(const uint64_t* peer_ptrs, int64_t flag_off, int phase, int rank, int world,
+                                         uint32_t epoch, long long timeout_clocks) {
+  signal_peers(peer_ptrs, flag_off, phase, rank, world, epoch);
+  wait_peers(peer_ptrs, flag_off, phase, rank, world, epoch, timeout_clocks);
+}
 
+// defer_release != 0: exchange (2) is split -- this kernel only SIGNALS "I have read your slab"; the wait for the peers'
+// signals happens in allreduce_clear_kernel, which the next step runs before it clears the slab (by then the signals are
+// ~a step old: the round trip leaves the critical path).
 __global__ void __launch_bounds__(kArThreads)
     allreduce_oneshot_kernel(const uint64_t* __restrict__ peer_ptrs, int rank, int world, int64_t n4, int64_t flag_off,
-                             float4* __restrict__ out, uint32_t* __restrict__ cta_epoch, long long timeout_clocks) {
+                             float4* __restrict__ out, uint32_t* __restrict__ cta_epoch, long long timeout_clocks, int defer_release) {
   __shared__ uint32_t s_epoch;
+  grid_dep_wait();  // launched as a programmatic dependent: the kernels that filled the slab are complete
   if (threadIdx.x == 0) s_epoch = ++cta_epoch[blockIdx.x];
   __syncthreads();
   const uint32_t epoch = s_epoch;
@@ -80,7 +94,27 @@ __global__ void __launch_bounds__(kArThreads)
     out[i] = acc;
   }
   __syncthreads();
-  exchange(peer_ptrs, flag_off, 1, rank, world, epoch, timeout_clocks);
+  if (defer_release) {
+    signal_peers(peer_ptrs, flag_off, 1, rank, world, epoch);
+  } else {
+    exchange(peer_ptrs, flag_off, 1, rank, world, epoch, timeout_clocks);
+  }
+  grid_dep_launch();
+}
+
+// The other half of the deferred exchange (2), fused with the clear it protects: CTA b waits until every peer has
+// signalled that it has read CTA b's share of this rank's slab in the LAST all-reduce (epoch = the call counter that
+// all-reduce left behind; 0 before the first one: nothing to wait for), then zeroes that share.
+__global__ void __launch_bounds__(kArThreads)
+    allreduce_clear_kernel(const uint64_t* __restrict__ peer_ptrs, int rank, int world, int64_t n4, int64_t flag_off,
+                           const uint32_t* __restrict__ cta_epoch, long long timeout_clocks) {
+  grid_dep_wait();
+  wait_peers(peer_ptrs, flag_off, 1, rank, world, cta_epoch[blockIdx.x], timeout_clocks);
+  float4* mine = reinterpret_cast<float4*>(peer_ptrs[rank]);
+  // (the same index -> CTA mapping as the sums above: a peer's CTA b reads exactly what this CTA clears)
+  for (int64_t i = (int64_t)blockIdx.x * kArThreads + threadIdx.x; i < n4; i += (int64_t)gridDim.x * kArThreads)
+    mine[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+  grid_dep_launch();
 }
 
 }  // namespace
@@ -110,17 +144,40 @@ size_t lipvq_allreduce_oneshot_flag_bytes(int world) {
   return (size_t)2 * (size_t)(world > 0 ? world : 1) * (size_t)lipvq_allreduce_oneshot_ctas() * sizeof(uint32_t);
 }
 
-int lipvq_allreduce_oneshot_f32(const uint64_t* peer_ptrs_dev, int rank, int world, int64_t n, int64_t flag_offset_bytes,
-                                float* out, uint32_t* cta_epoch, void* stream_) {
+static int allreduce_launch(const uint64_t* peer_ptrs_dev, int rank, int world, int64_t n, int64_t flag_offset_bytes, float* out,
+                            uint32_t* cta_epoch, void* stream_, int defer_release) {
   cudaStream_t stream = (cudaStream_t)stream_;
   LIPVQ_REQUIRE(world >= 1 && world <= 64 && rank >= 0 && rank < world, "allreduce_oneshot: bad rank/world %d/%d", rank, world);
   LIPVQ_REQUIRE(n >= 0 && n % 4 == 0, "allreduce_oneshot: length must be a multiple of 4 floats");
   LIPVQ_REQUIRE(flag_offset_bytes >= n * 4 && flag_offset_bytes % 16 == 0, "allreduce_oneshot: flags must follow the slab");
   if (n == 0) return LIPVQ_OK;
   LIPVQ_REQUIRE(peer_ptrs_dev && out && cta_epoch && aligned16(out), "allreduce_oneshot: null or misaligned pointer");
-  allreduce_oneshot_kernel<<<lipvq_allreduce_oneshot_ctas(), kArThreads, 0, stream>>>(
-      peer_ptrs_dev, rank, world, n / 4, flag_offset_bytes, reinterpret_cast<float4*>(out), cta_epoch, peer_timeout_clocks());
+  LIPVQ_CUDA(launch_pdl(allreduce_oneshot_kernel, dim3(lipvq_allreduce_oneshot_ctas()), dim3(kArThreads), 0, stream, peer_ptrs_dev, rank,
+                        world, n / 4, flag_offset_bytes, reinterpret_cast<float4*>(out), cta_epoch, peer_timeout_clocks(), defer_release));
   LIPVQ_LAUNCHED("allreduce_oneshot_kernel");
+  return LIPVQ_OK;
+}
+
+int lipvq_allreduce_oneshot_f32(const uint64_t* peer_ptrs_dev, int rank, int world, int64_t n, int64_t flag_offset_bytes,
+                                float* out, uint32_t* cta_epoch, void* stream) {
+  return allreduce_launch(peer_ptrs_dev, rank, world, n, flag_offset_bytes, out, cta_epoch, stream, 0);
+}
+
+int lipvq_allreduce_oneshot_deferred_f32(const uint64_t* peer_ptrs_dev, int rank, int world, int64_t n, int64_t flag_offset_bytes,
+                                         float* out, uint32_t* cta_epoch, void* stream) {
+  return allreduce_launch(peer_ptrs_dev, rank, world, n, flag_offset_bytes, out, cta_epoch, stream, 1);
+}
+
+int lipvq_allreduce_oneshot_clear_f32(const uint64_t* peer_ptrs_dev, int rank, int world, int64_t n, int64_t flag_offset_bytes,
+                                      const uint32_t* cta_epoch, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  LIPVQ_REQUIRE(world >= 1 && world <= 64 && rank >= 0 && rank < world, "allreduce_clear: bad rank/world %d/%d", rank, world);
+  LIPVQ_REQUIRE(n >= 0 && n % 4 == 0 && flag_offset_bytes >= n * 4 && flag_offset_bytes % 16 == 0, "allreduce_clear: bad layout");
+  if (n == 0) return LIPVQ_OK;
+  LIPVQ_REQUIRE(peer_ptrs_dev && cta_epoch, "allreduce_clear: null pointer");
+  LIPVQ_CUDA(launch_pdl(allreduce_clear_kernel, dim3(lipvq_allreduce_oneshot_ctas()), dim3(kArThreads), 0, stream, peer_ptrs_dev, rank,
+                        world, n / 4, flag_offset_bytes, cta_epoch, peer_timeout_clocks()));
+  LIPVQ_LAUNCHED("allreduce_clear_kernel");
   return LIPVQ_OK;
 }
 

@@ -19,7 +19,7 @@ METRIC_L2, METRIC_L2SQ, METRIC_DOT = 0, 1, 2
 ALGO_AUTO, ALGO_SIMT_F32, ALGO_TCGEN05 = 0, 1, 2
 ACT_NONE, ACT_RELU, ACT_GELU, ACT_SIGMOID, ACT_GIVEN = 0, 1, 2, 3, 4
 EMA_SIMPLE, EMA_LAPLACE, EMA_NORMALIZE = 0, 1, 2
-ABI_VERSION = 8
+ABI_VERSION = 9
 
 _p, _i, _i64, _f, _d, _sz = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_double, C.c_size_t
 
@@ -74,6 +74,8 @@ SIGNATURES = {
     "lipvq_allreduce_oneshot_ctas": (_i, []),
     "lipvq_allreduce_oneshot_flag_bytes": (C.c_size_t, [_i]),
     "lipvq_allreduce_oneshot_f32": (_i, [_p, _i, _i, _i64, _i64, _p, _p, _p]),
+    "lipvq_allreduce_oneshot_deferred_f32": (_i, [_p, _i, _i, _i64, _i64, _p, _p, _p]),
+    "lipvq_allreduce_oneshot_clear_f32": (_i, [_p, _i, _i, _i64, _i64, _p, _p]),
     "lipvq_window_gather_f32": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i, _i, _i, _i, _p, _p, _p, _p, _p]),
     "lipvq_bin_embed_fwd_f32": (_i, [_p, _i64, _i, _i, _i, _i, _p, _p, _p, _p, _p, _p]),
     "lipvq_bin_embed_bwd_f32": (_i, [_p, _p, _i64, _i, _i, _i, _p, _p]),

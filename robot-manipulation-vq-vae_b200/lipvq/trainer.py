@@ -137,7 +137,10 @@ class TokenizerTrainer:
 
     # -- the launch sequence -------------------------------------------------------------------
     def _phase_a(self):
-        self.red.zero_()
+        if self.peer is not None:
+            self.peer.clear()  # (waits for the peers' "slab read" signals of the last reduction, then zeroes)
+        else:
+            self.red.zero_()
         self._arena.zero_()
         t1.forward(self.p, self.x_static, self.bufs, algo=self.search_algo,
                    search_prepared=self.search_prepared and self._centre_ok)
