@@ -366,6 +366,12 @@ inline int live_taps(int T, int dil, int* jlo, int* jhi) {
 
 using namespace lipvq;
 
+namespace lipvq {  // conv_tc.cu
+bool conv_tc_supported(int64_t N, int T, int Ei, int Eo);
+int conv_tc_fwd_launch(const float* X, int64_t N, int T, int E, const float* Wf, const float* bias, int dilation, int jlo, int jhi,
+                       float scale, uint32_t drop_thr, uint32_t seed, float* OUT, uint8_t* mask, cudaStream_t stream);
+}  // namespace lipvq
+
 static inline bool conv_shape_ok(int64_t N, int T, int Ei, int Eo) {
   return N >= 0 && T > 0 && Ei > 0 && Eo > 0 && (N % T) == 0 && (Ei % 4) == 0 && (Eo % 4) == 0;
 }
@@ -415,6 +421,9 @@ int lipvq_dilated_conv_fwd_f32(const float* X, int64_t N, int T, int Ei, const f
   g.scale = 1.f / (1.f - drop_p);
   g.drop_thr = drop_p > 0.f ? (uint32_t)((double)drop_p * 4294967296.0) : 0u;
   g.seed = seed;
+  // wide layers with enough tokens: the contraction on the tensor cores (conv_tc.cu), same values and the same mask
+  if (conv_tc_supported(N, T, Ei, Eo) && ((uintptr_t)mask & 7u) == 0)
+    return conv_tc_fwd_launch(X, N, T, Ei, Wf, bias, dilation, g.jlo, g.jhi, g.scale, g.drop_thr, seed, OUT, mask, stream);
   dim3 grid((unsigned)ceil_div64(N, 128), (unsigned)((Eo + BN - 1) / BN));
   conv_tile_kernel<CONV_FWD, 128><<<grid, NT, 0, stream>>>(g);
   LIPVQ_LAUNCHED("conv_tile_kernel<fwd>");

@@ -1,0 +1,290 @@
+// K8 on the tensor cores: the E -> E dilated convolution of an MS-TCN layer (kernel 3) as ONE contraction
+//   pre[n, o] = sum_{j, c} X[n + (j - 1) d, c] * Wf[o][j][c]          (rows outside the sequence of n read as zero)
+// i.e. a token-major linear layer whose input row is the concatenation of three shifted rows of X and whose weight is
+// the packed [Eo][3 Ei] matrix of lipvq_conv_pack_weights_f32 -- followed by the layer's epilogue
+//   OUT = (keep ? relu(pre + b) / (1 - p) : 0) + X,   mask = keep
+// (reference robomimic/algo/heirarchical_vqvae.py:39-57: Conv1d(E, E, 3, dilation = d, padding = d) -> ReLU -> Dropout
+// -> + x).  At the shipped width E = 512 a layer is 103 GFLOP per 65 536 tokens; the fp32 FFMA tiles of conv.cu need
+// ~3 ms for it.
+//
+// fp32 accuracy as in linear_tc.cu: both operands split into three bf16 terms, six tcgen05.mma chains, fp32 accumulation
+// in TMEM.  Tiles of 128 tokens x 128 outputs; the reduction (3 E, dead taps skipped) streams through a two-stage ring of
+// 64-wide chunks: sixteen converter warps turn fp32 rows of X (shifted per tap, zero outside the sequence) AND fp32 rows
+// of Wf into swizzled K-major bf16 tiles (the weights of a layer are 3 MB and stay in L2: no prepared copy, no workspace),
+// one thread issues the 24 MMAs of a chunk, eight epilogue warps drain one of two accumulators while the next tile's
+// chunks already flow.  Persistent CTAs; consecutive tiles share a row block (its X rows are read from L2, not HBM).
+#include <cuda.h>
+#include <cuda_bf16.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace lipvq {
+namespace {
+
+using namespace tc;
+
+constexpr int kBM = 128, kBN = 128, kChunk = 64;
+constexpr int kTile = kBM * kChunk * 2;      // one term of a 128-row, 64-wide bf16 tile: 16 KB
+constexpr int kStage = 6 * kTile;            // A (h, m, l) + B (h, m, l): 96 KB
+constexpr int kEpiWarps = 8, kCvtWarps = 16;
+constexpr int kWarpMma = kEpiWarps + kCvtWarps;
+constexpr int kThreads = 32 * (kWarpMma + 1);  // 800
+
+struct ConvTcParams {
+  const float* X; int64_t N; int T, E, dil, jlo, jhi;
+  const float* Wf; const float* bias;
+  float* OUT; uint8_t* mask;
+  float scale; uint32_t drop_thr, seed;
+};
+
+__device__ __forceinline__ uint32_t mix32(uint32_t a, uint32_t b) {  // (conv.cu: the same dropout stream)
+  uint32_t h = a * 0x9E3779B1u ^ (b + 0x7F4A7C15u + (a << 6) + (a >> 2));
+  h ^= h >> 16; h *= 0x85EBCA6Bu; h ^= h >> 13; h *= 0xC2B2AE35u; h ^= h >> 16;
+  return h;
+}
+__device__ __forceinline__ uint32_t bf16x2_rn(float lo, float hi) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi), "f"(lo));
+  return r;
+}
+__device__ __forceinline__ void split3_pair(float x0, float x1, uint32_t& h, uint32_t& m, uint32_t& l) {
+  h = bf16x2_rn(x0, x1);
+  const float r0 = x0 - __uint_as_float(h << 16), r1 = x1 - __uint_as_float(h & 0xFFFF0000u);
+  m = bf16x2_rn(r0, r1);
+  l = bf16x2_rn(r0 - __uint_as_float(m << 16), r1 - __uint_as_float(m & 0xFFFF0000u));
+}
+// eight consecutive values of tile row r, 16-byte chunk ch: the three terms, kTile bytes apart
+__device__ __forceinline__ void store_split8(uint8_t* base, int r, int ch, const float4& a, const float4& b) {
+  uint32_t hh[4], mm[4], ll[4];
+  split3_pair(a.x, a.y, hh[0], mm[0], ll[0]);
+  split3_pair(a.z, a.w, hh[1], mm[1], ll[1]);
+  split3_pair(b.x, b.y, hh[2], mm[2], ll[2]);
+  split3_pair(b.z, b.w, hh[3], mm[3], ll[3]);
+  uint8_t* d = base + (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
+  *reinterpret_cast<uint4*>(d) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+  *reinterpret_cast<uint4*>(d + kTile) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+  *reinterpret_cast<uint4*>(d + 2 * kTile) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+}
+
+__global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * kStage);
+  const uint32_t bar_full = smem_u32(bars + 0), bar_empty = smem_u32(bars + 2);
+  const uint32_t bar_acc_full = smem_u32(bars + 4), bar_acc_empty = smem_u32(bars + 6);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row_blocks = (int)((p.N + kBM - 1) / kBM), nct = p.E / kBN;
+  const int tiles = row_blocks * nct;
+  const int ntile = ((int)blockIdx.x < tiles) ? (tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
+  if (ntile == 0) return;
+  const int cpt = p.E / kChunk;               // chunks per tap
+  const int nk = (p.jhi - p.jlo) * cpt;       // chunks per tile (dead taps skipped)
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_full + 8 * s, kCvtWarps);
+      mbar_init(bar_empty + 8 * s, 1);
+      mbar_init(bar_acc_full + 8 * s, 1);
+      mbar_init(bar_acc_empty + 8 * s, kEpiWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), 4 * kBN);
+  grid_dep_wait();
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == kWarpMma) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16(kBM, kBN);
+      const int ta[6] = {1, 2, 0, 1, 0, 0}, tb[6] = {1, 0, 2, 0, 1, 0};  // term 0 = h, 1 = m, 2 = l; smallest products first
+      uint32_t a_lo[2][3], b_lo[2][3];
+      for (int s = 0; s < 2; ++s)
+        for (int t = 0; t < 3; ++t) {
+          a_lo[s][t] = desc_sw128_lo(smem_u32(smem + s * kStage + t * kTile));
+          b_lo[s][t] = desc_sw128_lo(smem_u32(smem + s * kStage + (3 + t) * kTile));
+        }
+      uint32_t g = 0;  // chunks issued (ring position)
+      for (int i = 0; i < ntile; ++i) {
+        const uint32_t ab = (uint32_t)i & 1;
+        mbar_wait(bar_acc_empty + 8 * ab, (((uint32_t)i >> 1) & 1) ^ 1);
+        fence_after();
+        // Two accumulators per tile.  The tensor core TRUNCATES the fp32 accumulator on every accumulating MMA (measured: a
+        // toward-zero bias growing linearly with the number of MMAs, 6.5e-6 at E = 512 with one accumulator), so the h*h
+        // chain, whose partial sums have the result's magnitude, gets an accumulator of its own (a sixth of the truncation
+        // events) and the five small chains (2^-8 and below) share the other, where a truncation is 2^-8 as large.
+        const uint32_t d_hh = tmem_base + ab * (uint32_t)(2 * kBN), d_small = d_hh + (uint32_t)kBN;
+        uint32_t acc_flag = 0, acc_small = 0;
+        for (int kc = 0; kc < nk; ++kc, ++g) {
+          const uint32_t s = g & 1;
+          mbar_wait(bar_full + 8 * s, (g >> 1) & 1);
+          fence_after();
+#pragma unroll
+          for (int combo = 0; combo < 6; ++combo) {
+            const uint32_t al = s ? a_lo[1][ta[combo]] : a_lo[0][ta[combo]];
+            const uint32_t bl = s ? b_lo[1][tb[combo]] : b_lo[0][tb[combo]];
+#pragma unroll
+            for (int k = 0; k < kChunk / 16; ++k) {
+              if (combo < 5) {
+                umma_f16_lo(d_small, al + 2 * k, bl + 2 * k, kDescSw128Hi, idesc, acc_small);
+                acc_small = 1;
+              } else {
+                umma_f16_lo(d_hh, al + 2 * k, bl + 2 * k, kDescSw128Hi, idesc, acc_flag);
+                acc_flag = 1;
+              }
+            }
+          }
+          umma_commit(bar_empty + 8 * s);
+        }
+        umma_commit(bar_acc_full + 8 * ab);
+      }
+    }
+  } else if (warp >= kEpiWarps) {
+    // ===== converters: per chunk 1024 items of A (shifted rows of X) and 1024 of B (rows of Wf), four per thread =====
+    const int tcv = (int)threadIdx.x - kEpiWarps * 32;  // 0..511
+    const int ch = tcv & 7, r0 = tcv >> 3;              // 16-byte chunk of the tile row; rows r0 and r0 + 64
+    uint32_t g = 0;
+    for (int i = 0; i < ntile; ++i) {
+      const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+      const int rb = tile / nct, ct = tile - rb * nct;
+      const int64_t row0 = (int64_t)rb * kBM;
+      int64_t arow[2];
+      int at[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        arow[u] = row0 + r0 + 64 * u;
+        at[u] = (arow[u] < p.N) ? (int)(arow[u] % p.T) : -1;  // time index inside the sequence (-1: no such row)
+      }
+      const float* wrow[2] = {p.Wf + (size_t)(ct * kBN + r0) * 3 * p.E, p.Wf + (size_t)(ct * kBN + r0 + 64) * 3 * p.E};
+      for (int kc = 0; kc < nk; ++kc, ++g) {
+        const int tap = p.jlo + kc / cpt, c0 = (kc % cpt) * kChunk + ch * 8;
+        const int shift = (tap - 1) * p.dil;
+        float4 a[2][2], b[2][2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          const int ts = at[u] + shift;
+          if (at[u] >= 0 && ts >= 0 && ts < p.T) {
+            const float4* src = reinterpret_cast<const float4*>(p.X + (arow[u] + shift) * p.E + c0);
+            a[u][0] = __ldg(src);
+            a[u][1] = __ldg(src + 1);
+          } else {
+            a[u][0] = a[u][1] = make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          const float4* ws = reinterpret_cast<const float4*>(wrow[u] + tap * p.E + c0);
+          b[u][0] = __ldg(ws);
+          b[u][1] = __ldg(ws + 1);
+        }
+        const uint32_t s = g & 1;
+        mbar_wait(bar_empty + 8 * s, ((g >> 1) & 1) ^ 1);  // the loads above are in flight while this waits
+        uint8_t* st = smem + s * kStage;
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+          store_split8(st, r0 + 64 * u, ch, a[u][0], a[u][1]);
+          store_split8(st + 3 * kTile, r0 + 64 * u, ch, b[u][0], b[u][1]);
+        }
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_full + 8 * s);
+      }
+    }
+  } else {
+    // ===== epilogue warps 0-7: TMEM lane quadrant q = warp & 3, 8-column groups part, part + 2, ... =====
+    const int q = warp & 3, part = warp >> 2;
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+    for (int i = 0; i < ntile; ++i) {
+      const int tile = (int)blockIdx.x + i * (int)gridDim.x;
+      const int rb = tile / nct, ct = tile - rb * nct;
+      const int64_t row = (int64_t)rb * kBM + q * 32 + lane;
+      const uint32_t ab = (uint32_t)i & 1;
+      mbar_wait(bar_acc_full + 8 * ab, ((uint32_t)i >> 1) & 1);
+      fence_after();
+      const uint32_t trow = tmem_base + ab * (uint32_t)(2 * kBN) + lane_off;
+#pragma unroll 1
+      for (int c0 = 8 * part; c0 < kBN; c0 += 16) {
+        uint32_t v[8], w[8];
+        tmem_ld8(trow + c0, v);
+        tmem_ld8(trow + kBN + c0, w);
+        tmem_ld_wait8(v);
+        tmem_ld_wait8(w);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) + __uint_as_float(w[e]));
+        if (c0 + 16 >= kBN) {  // this warp's last load of the accumulator: hand it back before the arithmetic
+          fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
+        }
+        if (row < p.N) {
+          const int col = ct * kBN + c0;
+          const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col)), b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col) + 1);
+          const float4 x0 = __ldg(reinterpret_cast<const float4*>(p.X + row * p.E + col));
+          const float4 x1 = __ldg(reinterpret_cast<const float4*>(p.X + row * p.E + col) + 1);
+          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+          const float rr[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+          float o[8];
+          uint32_t kb[2] = {0u, 0u};
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float pre = __uint_as_float(v[e]) + bb[e];
+            bool keep = pre > 0.f;
+            if (p.drop_thr) keep = keep && (mix32(p.seed, (uint32_t)(row * p.E + col + e)) >= p.drop_thr);
+            o[e] = (keep ? pre * p.scale : 0.f) + rr[e];
+            kb[e >> 2] |= (keep ? 1u : 0u) << (8 * (e & 3));
+          }
+          float* dst = p.OUT + row * p.E + col;
+          *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+          *reinterpret_cast<float4*>(dst + 4) = make_float4(o[4], o[5], o[6], o[7]);
+          *reinterpret_cast<uint2*>(p.mask + row * p.E + col) = make_uint2(kb[0], kb[1]);
+        }
+      }
+    }
+  }
+
+  fence_before();
+  __syncthreads();
+  grid_dep_launch();
+  if (warp == kWarpMma) {
+    fence_after();
+    tmem_dealloc(tmem_base, 4 * kBN);
+  }
+}
+
+constexpr size_t kSmem = 1024 + 2 * (size_t)kStage + 128;
+
+}  // namespace
+
+// Shapes the tensor path takes: enough tokens to fill the SMs, widths in whole tiles.  LIPVQ_CONV_ALGO=simt forces the
+// FFMA tiles of conv.cu (A/B runs).
+bool conv_tc_supported(int64_t N, int T, int Ei, int Eo) {
+  if (const char* f = getenv("LIPVQ_CONV_ALGO"))
+    if (f[0] == 's') return false;
+  return N >= 4096 && T >= 1 && Ei == Eo && Ei % kBN == 0 && Ei >= kBN && Ei <= 4096 && N * (int64_t)Ei < ((int64_t)1 << 32);
+}
+
+int conv_tc_fwd_launch(const float* X, int64_t N, int T, int E, const float* Wf, const float* bias, int dilation, int jlo, int jhi,
+                       float scale, uint32_t drop_thr, uint32_t seed, float* OUT, uint8_t* mask, cudaStream_t stream) {
+  ConvTcParams p{};
+  p.X = X; p.N = N; p.T = T; p.E = E; p.dil = dilation; p.jlo = jlo; p.jhi = jhi;
+  p.Wf = Wf; p.bias = bias; p.OUT = OUT; p.mask = mask;
+  p.scale = scale; p.drop_thr = drop_thr; p.seed = seed;
+  static bool smem_set[kMaxDevices] = {};  // the attribute is per device
+  const int dev_ = current_device();
+  if (!smem_set[dev_]) {
+    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    smem_set[dev_] = true;
+  }
+  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN);
+  const int sms = sm_count();
+  LIPVQ_CUDA(launch_pdl(conv_tc_kernel, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
+  LIPVQ_LAUNCHED("conv_tc_kernel");
+  return LIPVQ_OK;
+}
+
+}  // namespace lipvq
