@@ -370,6 +370,10 @@ namespace lipvq {  // conv_tc.cu
 bool conv_tc_supported(int64_t N, int T, int Ei, int Eo);
 int conv_tc_fwd_launch(const float* X, int64_t N, int T, int E, const float* Wf, const float* bias, int dilation, int jlo, int jhi,
                        float scale, uint32_t drop_thr, uint32_t seed, float* OUT, uint8_t* mask, cudaStream_t stream);
+int conv_tc_bwd_x_launch(const float* dOUT, const uint8_t* mask, int64_t N, int T, int E, const float* Wb, int dilation, int jlo,
+                         int jhi, float scale, float* dX, cudaStream_t stream);
+int conv_tc_bwd_w_launch(const float* dOUT, const uint8_t* mask, const float* X, int64_t N, int T, int E, int dilation, int jlo,
+                         int jhi, float scale, float* dWf, float* db, cudaStream_t stream);
 }  // namespace lipvq
 
 static inline bool conv_shape_ok(int64_t N, int T, int Ei, int Eo) {
@@ -443,6 +447,8 @@ int lipvq_dilated_conv_bwd_x_f32(const float* dOUT, const uint8_t* mask, int64_t
   g.N = N; g.T = T; g.Ei = Ei; g.Eo = Eo; g.dil = dilation;
   live_taps(T, dilation, &g.jlo, &g.jhi);
   g.scale = 1.f / (1.f - drop_p);
+  if (conv_tc_supported(N, T, Ei, Eo) && ((uintptr_t)mask & 7u) == 0)
+    return conv_tc_bwd_x_launch(dOUT, mask, N, T, Ei, Wb, dilation, g.jlo, g.jhi, g.scale, dX, stream);
   dim3 grid((unsigned)ceil_div64(N, 128), (unsigned)((Ei + BN - 1) / BN));
   conv_tile_kernel<CONV_BWD_X, 128><<<grid, NT, 0, stream>>>(g);
   LIPVQ_LAUNCHED("conv_tile_kernel<bwd_x>");
@@ -462,6 +468,8 @@ int lipvq_dilated_conv_bwd_w_f32(const float* dOUT, const uint8_t* mask, const f
   g.N = N; g.T = T; g.Ei = Ei; g.Eo = Eo; g.dil = dilation;
   live_taps(T, dilation, &g.jlo, &g.jhi);
   g.scale = 1.f / (1.f - drop_p);
+  if (conv_tc_supported(N, T, Ei, Eo) && aligned16(dWf))
+    return conv_tc_bwd_w_launch(dOUT, mask, X, N, T, Ei, dilation, g.jlo, g.jhi, g.scale, dWf, db, stream);
   const int64_t tiles = ceil_div64(Eo, 64) * ((3 * Ei + BN - 1) / BN);
   int64_t splits = ceil_div64(2 * (int64_t)sm_count(), tiles);
   const int64_t max_splits = ceil_div64(N, 64);

@@ -33,10 +33,13 @@ constexpr int kEpiWarps = 8, kCvtWarps = 16;
 constexpr int kWarpMma = kEpiWarps + kCvtWarps;
 constexpr int kThreads = 32 * (kWarpMma + 1);  // 800
 
+enum { kFwd = 0, kBwdX = 1 };
+
 struct ConvTcParams {
-  const float* X; int64_t N; int T, E, dil, jlo, jhi;
-  const float* Wf; const float* bias;
+  const float* X; int64_t N; int T, E, dil, jlo, jhi;   // kBwdX: X = dOUT (masked by gmask, scaled) and OUT = dX
+  const float* Wf; const float* bias;                   // kBwdX: Wf = Wb [3][Eo][Ei]
   float* OUT; uint8_t* mask;
+  const uint8_t* gmask;
   float scale; uint32_t drop_thr, seed;
 };
 
@@ -69,6 +72,19 @@ __device__ __forceinline__ void store_split8(uint8_t* base, int r, int ch, const
   *reinterpret_cast<uint4*>(d + 2 * kTile) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
 }
 
+__device__ __forceinline__ void mask8(float4& a, float4& b, const uint8_t* m, float scale) {
+  const uint2 k = __ldg(reinterpret_cast<const uint2*>(m));
+  a.x = (k.x & 0xFFu) ? a.x * scale : 0.f; a.y = (k.x & 0xFF00u) ? a.y * scale : 0.f;
+  a.z = (k.x & 0xFF0000u) ? a.z * scale : 0.f; a.w = (k.x & 0xFF000000u) ? a.w * scale : 0.f;
+  b.x = (k.y & 0xFFu) ? b.x * scale : 0.f; b.y = (k.y & 0xFF00u) ? b.y * scale : 0.f;
+  b.z = (k.y & 0xFF0000u) ? b.z * scale : 0.f; b.w = (k.y & 0xFF000000u) ? b.w * scale : 0.f;
+}
+
+// MODE kFwd: the layer forward.  MODE kBwdX: its input gradient
+//   dX[n, i] = dOUT[n, i] + sum_{j, o} masked(dOUT)[n + (1 - j) d, o] * Wb[j][o][i]
+// -- the same contraction with the shifts negated; the B tile (128 inputs i x 64 outputs o, K-major) is gathered from
+// Wb's i-contiguous rows by lanes that run along i (coalesced) and each collect eight consecutive o.
+template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -164,23 +180,33 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
         at[u] = (arow[u] < p.N) ? (int)(arow[u] % p.T) : -1;  // time index inside the sequence (-1: no such row)
       }
       const float* wrow[2] = {p.Wf + (size_t)(ct * kBN + r0) * 3 * p.E, p.Wf + (size_t)(ct * kBN + r0 + 64) * 3 * p.E};
+      const int bn = tcv & 127, bch = tcv >> 7;  // kBwdX: B items (input bn, 16-byte chunks bch and bch + 4)
       for (int kc = 0; kc < nk; ++kc, ++g) {
         const int tap = p.jlo + kc / cpt, c0 = (kc % cpt) * kChunk + ch * 8;
-        const int shift = (tap - 1) * p.dil;
+        const int shift = (MODE == kFwd) ? (tap - 1) * p.dil : (1 - tap) * p.dil;
         float4 a[2][2], b[2][2];
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           const int ts = at[u] + shift;
           if (at[u] >= 0 && ts >= 0 && ts < p.T) {
-            const float4* src = reinterpret_cast<const float4*>(p.X + (arow[u] + shift) * p.E + c0);
+            const int64_t off = (arow[u] + shift) * p.E + c0;
+            const float4* src = reinterpret_cast<const float4*>(p.X + off);
             a[u][0] = __ldg(src);
             a[u][1] = __ldg(src + 1);
+            if (MODE == kBwdX) mask8(a[u][0], a[u][1], p.gmask + off, p.scale);
           } else {
             a[u][0] = a[u][1] = make_float4(0.f, 0.f, 0.f, 0.f);
           }
-          const float4* ws = reinterpret_cast<const float4*>(wrow[u] + tap * p.E + c0);
-          b[u][0] = __ldg(ws);
-          b[u][1] = __ldg(ws + 1);
+          if (MODE == kFwd) {
+            const float4* ws = reinterpret_cast<const float4*>(wrow[u] + tap * p.E + c0);
+            b[u][0] = __ldg(ws);
+            b[u][1] = __ldg(ws + 1);
+          } else {
+            const float* ws = p.Wf + ((size_t)tap * p.E + (kc % cpt) * kChunk + (bch + 4 * u) * 8) * p.E + ct * kBN + bn;
+            b[u][0] = make_float4(__ldg(ws), __ldg(ws + p.E), __ldg(ws + 2 * (size_t)p.E), __ldg(ws + 3 * (size_t)p.E));
+            ws += 4 * (size_t)p.E;
+            b[u][1] = make_float4(__ldg(ws), __ldg(ws + p.E), __ldg(ws + 2 * (size_t)p.E), __ldg(ws + 3 * (size_t)p.E));
+          }
         }
         const uint32_t s = g & 1;
         mbar_wait(bar_empty + 8 * s, ((g >> 1) & 1) ^ 1);  // the loads above are in flight while this waits
@@ -188,7 +214,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
           store_split8(st, r0 + 64 * u, ch, a[u][0], a[u][1]);
-          store_split8(st + 3 * kTile, r0 + 64 * u, ch, b[u][0], b[u][1]);
+          if (MODE == kFwd) store_split8(st + 3 * kTile, r0 + 64 * u, ch, b[u][0], b[u][1]);
+          else store_split8(st + 3 * kTile, bn, bch + 4 * u, b[u][0], b[u][1]);
         }
         fence_async_smem();
         __syncwarp();
@@ -221,7 +248,18 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
         }
-        if (row < p.N) {
+        if (MODE == kBwdX) {
+          if (row < p.N) {
+            const int col = ct * kBN + c0;
+            const float4 x0 = __ldg(reinterpret_cast<const float4*>(p.X + row * p.E + col));  // residual branch of the layer
+            const float4 x1 = __ldg(reinterpret_cast<const float4*>(p.X + row * p.E + col) + 1);
+            float* dst = p.OUT + row * p.E + col;
+            *reinterpret_cast<float4*>(dst) = make_float4(__uint_as_float(v[0]) + x0.x, __uint_as_float(v[1]) + x0.y,
+                                                          __uint_as_float(v[2]) + x0.z, __uint_as_float(v[3]) + x0.w);
+            *reinterpret_cast<float4*>(dst + 4) = make_float4(__uint_as_float(v[4]) + x1.x, __uint_as_float(v[5]) + x1.y,
+                                                              __uint_as_float(v[6]) + x1.z, __uint_as_float(v[7]) + x1.w);
+          }
+        } else if (row < p.N) {
           const int col = ct * kBN + c0;
           const float4 b0 = __ldg(reinterpret_cast<const float4*>(p.bias + col)), b1 = __ldg(reinterpret_cast<const float4*>(p.bias + col) + 1);
           const float4 x0 = __ldg(reinterpret_cast<const float4*>(p.X + row * p.E + col));
@@ -258,6 +296,210 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
 
 constexpr size_t kSmem = 1024 + 2 * (size_t)kStage + 128;
 
+// ---- weight gradient ------------------------------------------------------------------------------------------------
+//   dWf[o][j][i] += sum_tok masked(dOUT)[tok, o] * X[tok + (j - 1) d, i],     db[o] += sum_tok masked(dOUT)[tok, o]
+// The reduction runs over TOKENS, so both operands are gathered into K-major tiles by lanes that run along the channel
+// (coalesced 128-byte rows) and collect eight consecutive tokens each.  One CTA = one 128 x 128 tile of dWf and one slice
+// of the tokens (tiles x slices ~ the SM count); four accumulators: the five small chains in one, the h*h chain dealt over
+// three by chunk (the accumulator truncates per MMA, see above: a long reduction into one accumulator would lose ~2e-5 of
+// the slice's magnitude); the slice's result is added to dWf with vector reductions.
+struct ConvTcWParams {
+  const float* G; const uint8_t* gmask; const float* X;
+  int64_t N; int T, E, dil, jlo, jhi;
+  float scale;
+  float* dWf; float* db;
+  int chunks_per_slice, n_tiles;   // n_tiles = (jhi - jlo) * E / 128 column tiles
+};
+
+__device__ __forceinline__ void red_add_v4(float* dst, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+__global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTcWParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * kStage);
+  const uint32_t bar_full = smem_u32(bars + 0), bar_empty = smem_u32(bars + 2), bar_acc_full = smem_u32(bars + 4);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  float* rs_s = reinterpret_cast<float*>(bars + 10);  // [4][128] bias partial sums (after the ring is idle: in stage 0)
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tile = (int)blockIdx.x, slice = (int)blockIdx.y;
+  const int mt = tile / p.n_tiles, nt = tile - mt * p.n_tiles;
+  const int tpt = p.E / kBN;                       // column tiles per tap
+  const int tap = p.jlo + nt / tpt, i0 = (nt % tpt) * kBN, o0 = mt * kBM;
+  const int64_t total_chunks = (p.N + kChunk - 1) / kChunk;
+  const int64_t cbeg = (int64_t)slice * p.chunks_per_slice;
+  const int nk = (int)((cbeg + p.chunks_per_slice <= total_chunks ? p.chunks_per_slice : total_chunks - cbeg));
+  if (nk <= 0) return;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(bar_full + 8 * s, kCvtWarps);
+      mbar_init(bar_empty + 8 * s, 1);
+    }
+    mbar_init(bar_acc_full, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), 4 * kBN);
+  grid_dep_wait();
+  fence_before();
+  __syncthreads();
+  fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == kWarpMma) {
+    if (lane == 0) {
+      const uint32_t idesc = idesc_bf16(kBM, kBN);
+      const int ta[6] = {1, 2, 0, 1, 0, 0}, tb[6] = {1, 0, 2, 0, 1, 0};
+      uint32_t a_lo[2][3], b_lo[2][3];
+      for (int s = 0; s < 2; ++s)
+        for (int t = 0; t < 3; ++t) {
+          a_lo[s][t] = desc_sw128_lo(smem_u32(smem + s * kStage + t * kTile));
+          b_lo[s][t] = desc_sw128_lo(smem_u32(smem + s * kStage + (3 + t) * kTile));
+        }
+      uint32_t acc_small = 0, hh_used = 0;
+      int rot = 0;
+      for (int kc = 0; kc < nk; ++kc) {
+        const uint32_t s = (uint32_t)kc & 1;
+        mbar_wait(bar_full + 8 * s, ((uint32_t)kc >> 1) & 1);
+        fence_after();
+        const uint32_t d_hh = tmem_base + (uint32_t)((1 + rot) * kBN);
+        uint32_t acc_hh = (hh_used >> rot) & 1u;
+#pragma unroll
+        for (int combo = 0; combo < 6; ++combo) {
+          const uint32_t al = s ? a_lo[1][ta[combo]] : a_lo[0][ta[combo]];
+          const uint32_t bl = s ? b_lo[1][tb[combo]] : b_lo[0][tb[combo]];
+#pragma unroll
+          for (int k = 0; k < kChunk / 16; ++k) {
+            if (combo < 5) {
+              umma_f16_lo(tmem_base, al + 2 * k, bl + 2 * k, kDescSw128Hi, idesc, acc_small);
+              acc_small = 1;
+            } else {
+              umma_f16_lo(d_hh, al + 2 * k, bl + 2 * k, kDescSw128Hi, idesc, acc_hh);
+              acc_hh = 1;
+            }
+          }
+        }
+        hh_used |= 1u << rot;
+        rot = rot == 2 ? 0 : rot + 1;
+        umma_commit(bar_empty + 8 * s);
+      }
+      umma_commit(bar_acc_full);
+    }
+  } else if (warp >= kEpiWarps) {
+    // ===== converters: items (channel n of the tile, eight consecutive tokens of the chunk) =====
+    const int tcv = (int)threadIdx.x - kEpiWarps * 32;
+    const int n = tcv & 127, chb = tcv >> 7;
+    const int sh = (tap - 1) * p.dil;
+    const float* gcol = p.G + o0 + n;
+    const uint8_t* mcol = p.gmask + o0 + n;
+    const float* xcol = p.X + i0 + n;
+    float rsum = 0.f;
+    // time index of the first token of each of this thread's two items, advanced by 64 per chunk
+    int t0[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) t0[u] = (int)((cbeg * kChunk + (chb + 4 * u) * 8) % p.T);
+    const int tstep = kChunk % p.T;
+    for (int kc = 0; kc < nk; ++kc) {
+      const int k0 = (int)(cbeg + kc) * kChunk;   // (N E < 2^32: token indices and element offsets fit 32 bits)
+      // all loads unconditional (addresses clamped into the arrays) and issued before any use: a branch per element would
+      // serialise sixteen round trips to memory per chunk
+      float a[2][8], b[2][8];
+      uint32_t mk[2][8];
+      const int last = (int)p.N - 1;
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int tok0 = k0 + (chb + 4 * u) * 8;
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const int tok = min(tok0 + e, last);
+          const int xr = max(0, min(tok + sh, last));
+          const uint32_t go = (uint32_t)tok * (uint32_t)p.E;
+          a[u][e] = __ldg(gcol + go);
+          mk[u][e] = __ldg(mcol + go);
+          b[u][e] = __ldg(xcol + (uint32_t)xr * (uint32_t)p.E);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        const int tok0 = k0 + (chb + 4 * u) * 8;
+        int tt = t0[u];
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          const bool in = tok0 + e <= last;
+          const int ts = tt + sh;
+          a[u][e] = (in && mk[u][e]) ? a[u][e] * p.scale : 0.f;
+          b[u][e] = (in && ts >= 0 && ts < p.T) ? b[u][e] : 0.f;
+          tt = (tt + 1 == p.T) ? 0 : tt + 1;
+        }
+        t0[u] += tstep;
+        if (t0[u] >= p.T) t0[u] -= p.T;
+      }
+      const uint32_t s = (uint32_t)kc & 1;
+      mbar_wait(bar_empty + 8 * s, (((uint32_t)kc >> 1) & 1) ^ 1);
+      uint8_t* st = smem + s * kStage;
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        store_split8(st, n, chb + 4 * u, make_float4(a[u][0], a[u][1], a[u][2], a[u][3]), make_float4(a[u][4], a[u][5], a[u][6], a[u][7]));
+        store_split8(st + 3 * kTile, n, chb + 4 * u, make_float4(b[u][0], b[u][1], b[u][2], b[u][3]),
+                     make_float4(b[u][4], b[u][5], b[u][6], b[u][7]));
+#pragma unroll
+        for (int e = 0; e < 8; ++e) rsum += a[u][e];
+      }
+      fence_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_full + 8 * s);
+    }
+    if (p.db != nullptr && nt == 0) rs_s[chb * 128 + n] = rsum;
+  } else {
+    // ===== epilogue warps: the slice's tile, summed over the four accumulators, added to dWf =====
+    const int q = warp & 3, part = warp >> 2;
+    const uint32_t lane_off = (uint32_t)(q * 32) << 16;
+    mbar_wait(bar_acc_full, 0);
+    fence_after();
+    const bool three = nk >= 3, two = nk >= 2;   // accumulators that were written at all
+    float* drow = p.dWf + ((size_t)(o0 + q * 32 + lane) * 3 + tap) * p.E + i0;
+#pragma unroll 1
+    for (int c0 = 8 * part; c0 < kBN; c0 += 16) {
+      uint32_t v[8], w[8];
+      float o[8];
+      tmem_ld8(tmem_base + lane_off + c0, v);
+      tmem_ld8(tmem_base + lane_off + kBN + c0, w);
+      tmem_ld_wait8(v);
+      tmem_ld_wait8(w);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) o[e] = __uint_as_float(v[e]) + __uint_as_float(w[e]);
+      if (two) {
+        tmem_ld8(tmem_base + lane_off + 2 * kBN + c0, v);
+        tmem_ld_wait8(v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] += __uint_as_float(v[e]);
+      }
+      if (three) {
+        tmem_ld8(tmem_base + lane_off + 3 * kBN + c0, v);
+        tmem_ld_wait8(v);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] += __uint_as_float(v[e]);
+      }
+      red_add_v4(drow + c0, o[0], o[1], o[2], o[3]);
+      red_add_v4(drow + c0 + 4, o[4], o[5], o[6], o[7]);
+    }
+  }
+
+  fence_before();
+  __syncthreads();
+  grid_dep_launch();
+  if (p.db != nullptr && nt == 0 && threadIdx.x < 128)
+    atomicAdd(p.db + o0 + threadIdx.x, (rs_s[threadIdx.x] + rs_s[128 + threadIdx.x]) + (rs_s[256 + threadIdx.x] + rs_s[384 + threadIdx.x]));
+  if (warp == kWarpMma) {
+    fence_after();
+    tmem_dealloc(tmem_base, 4 * kBN);
+  }
+}
+
+constexpr size_t kSmemW = 1024 + 2 * (size_t)kStage + 128 + 4 * 128 * sizeof(float);
+
 }  // namespace
 
 // Shapes the tensor path takes: enough tokens to fill the SMs, widths in whole tiles.  LIPVQ_CONV_ALGO=simt forces the
@@ -277,13 +519,55 @@ int conv_tc_fwd_launch(const float* X, int64_t N, int T, int E, const float* Wf,
   static bool smem_set[kMaxDevices] = {};  // the attribute is per device
   const int dev_ = current_device();
   if (!smem_set[dev_]) {
-    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel<kFwd>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
     smem_set[dev_] = true;
   }
   const int64_t tiles = ceil_div64(N, kBM) * (E / kBN);
   const int sms = sm_count();
-  LIPVQ_CUDA(launch_pdl(conv_tc_kernel, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
-  LIPVQ_LAUNCHED("conv_tc_kernel");
+  LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kFwd>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
+  LIPVQ_LAUNCHED("conv_tc_kernel<fwd>");
+  return LIPVQ_OK;
+}
+
+int conv_tc_bwd_x_launch(const float* dOUT, const uint8_t* mask, int64_t N, int T, int E, const float* Wb, int dilation, int jlo,
+                         int jhi, float scale, float* dX, cudaStream_t stream) {
+  ConvTcParams p{};
+  p.X = dOUT; p.gmask = mask; p.N = N; p.T = T; p.E = E; p.dil = dilation; p.jlo = jlo; p.jhi = jhi;
+  p.Wf = Wb; p.OUT = dX; p.scale = scale;
+  static bool smem_set[kMaxDevices] = {};
+  const int dev_ = current_device();
+  if (!smem_set[dev_]) {
+    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel<kBwdX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    smem_set[dev_] = true;
+  }
+  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN);
+  const int sms = sm_count();
+  LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kBwdX>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
+  LIPVQ_LAUNCHED("conv_tc_kernel<bwd_x>");
+  return LIPVQ_OK;
+}
+
+int conv_tc_bwd_w_launch(const float* dOUT, const uint8_t* mask, const float* X, int64_t N, int T, int E, int dilation, int jlo,
+                         int jhi, float scale, float* dWf, float* db, cudaStream_t stream) {
+  ConvTcWParams p{};
+  p.G = dOUT; p.gmask = mask; p.X = X; p.N = N; p.T = T; p.E = E; p.dil = dilation; p.jlo = jlo; p.jhi = jhi;
+  p.scale = scale; p.dWf = dWf; p.db = db;
+  p.n_tiles = (jhi - jlo) * (E / kBN);
+  const int tiles = (E / kBM) * p.n_tiles;
+  const int64_t total_chunks = ceil_div64(N, kChunk);
+  int64_t slices = sm_count() / tiles;
+  if (slices < 1) slices = 1;
+  if (slices > total_chunks) slices = total_chunks;
+  p.chunks_per_slice = (int)ceil_div64(total_chunks, slices);
+  slices = ceil_div64(total_chunks, p.chunks_per_slice);
+  static bool smem_set[kMaxDevices] = {};
+  const int dev_ = current_device();
+  if (!smem_set[dev_]) {
+    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_bwd_w_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemW));
+    smem_set[dev_] = true;
+  }
+  LIPVQ_CUDA(launch_pdl(conv_tc_bwd_w_kernel, dim3((unsigned)tiles, (unsigned)slices), dim3(kThreads), kSmemW, stream, p));
+  LIPVQ_LAUNCHED("conv_tc_bwd_w_kernel");
   return LIPVQ_OK;
 }
 

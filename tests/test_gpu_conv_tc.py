@@ -62,3 +62,70 @@ def test_conv_tc_dropout_mask_is_the_ffma_path_s():
     same = (mask == mask2)
     assert torch.allclose(out[same], out2[same], rtol=1e-5, atol=2e-5)
     assert 0.3 < mask.float().mean().item() / (out2 - x != 0).float().mean().item() < 3.0
+
+
+def _simt(fn):
+    os.environ["LIPVQ_CONV_ALGO"] = "simt"
+    try:
+        return fn()
+    finally:
+        del os.environ["LIPVQ_CONV_ALGO"]
+
+
+@pytest.mark.parametrize("B,T,E,dil,drop", [(512, 16, 256, 1, 0.0), (300, 16, 128, 4, 0.0), (1024, 10, 256, 2, 0.25),
+                                            (512, 8, 128, 16, 0.0), (4100, 1, 128, 1, 0.0)])
+def test_conv_tc_backward_vs_autograd_and_ffma(B, T, E, dil, drop):
+    """dX and dWf / db of the layer (heirarchical_vqvae.py:39-57 under autograd) from the tensor-core kernels: against torch
+    autograd in fp64 with the SAME keep-mask, and against the FFMA tiles.  Tolerances: 2e-5 of the gradient's scale (three
+    bf16 terms per operand, fp32 accumulators that truncate per MMA; measured 1e-6 .. 5e-6)."""
+    import lipvq as L
+    g = torch.Generator().manual_seed(B + T + E + dil)
+    x = torch.randn(B, T, E, generator=g)
+    W = torch.randn(E, E, 3, generator=g) / (3 * E) ** 0.5
+    b = torch.randn(E, generator=g) * 0.1
+    go = torch.randn(B, T, E, generator=g)
+    N = B * T
+    Wd = W.to(DEV)
+    Wf, Wb = L.ops.conv_pack_weights(Wd, True, True)
+    xd, god = x.reshape(N, E).to(DEV), go.reshape(N, E).to(DEV)
+    out, mask = L.ops.dilated_conv_fwd(xd, T, Wf, b.to(DEV), dil, drop_p=drop, seed=77)
+    dx = L.ops.dilated_conv_bwd_x(god, mask, T, Wb, dil, drop_p=drop)
+    dWf, db = torch.zeros(E, 3, E, device=DEV), torch.zeros(E, device=DEV)
+    L.ops.dilated_conv_bwd_w(god, mask, xd, T, dil, dWf, db, drop_p=drop)
+    dx2 = _simt(lambda: L.ops.dilated_conv_bwd_x(god, mask, T, Wb, dil, drop_p=drop))
+    dWf2, db2 = torch.zeros(E, 3, E, device=DEV), torch.zeros(E, device=DEV)
+    _simt(lambda: L.ops.dilated_conv_bwd_w(god, mask, xd, T, dil, dWf2, db2, drop_p=drop))
+    torch.cuda.synchronize()
+    # fp64 autograd with the kernel's keep-mask as the ReLU / dropout gate
+    xr = x.double().to(DEV).requires_grad_(True)
+    Wr = W.double().to(DEV).requires_grad_(True)
+    br = b.double().to(DEV).requires_grad_(True)
+    pre = torch.nn.functional.conv1d(xr.transpose(1, 2), Wr, br, dilation=dil, padding=dil).transpose(1, 2)
+    y = pre * mask.reshape(B, T, E).double() / (1.0 - drop) + xr
+    y.backward(go.double().to(DEV))
+    dxr = xr.grad.reshape(N, E)
+    dWr = Wr.grad.permute(0, 2, 1).contiguous()          # [Eo, 3, Ei]
+
+    def close(a, r, what):
+        scale = r.abs().max().item()
+        err = (a.double() - r).abs().max().item()
+        assert err <= 2e-5 * scale, (what, err, scale)
+    close(dx, dxr, "dx"); close(dx2, dxr, "dx ffma")
+    close(dWf, dWr, "dWf"); close(dWf2, dWr, "dWf ffma")
+    close(db, br.grad, "db"); close(db2, br.grad, "db ffma")
+
+
+def test_conv_tc_bwd_w_accumulates_into_dwf():
+    import lipvq as L
+    g = torch.Generator().manual_seed(9)
+    N, T, E = 4096, 16, 128
+    x = torch.randn(N, E, generator=g).to(DEV)
+    go = torch.randn(N, E, generator=g).to(DEV)
+    mask = (torch.rand(N, E, generator=g) > 0.5).to(torch.uint8).to(DEV)
+    base = torch.randn(E, 3, E, generator=g).to(DEV)
+    d0, b0 = torch.zeros(E, 3, E, device=DEV), torch.zeros(E, device=DEV)
+    L.ops.dilated_conv_bwd_w(go, mask, x, T, 2, d0, b0)
+    d1, b1 = base.clone(), torch.ones(E, device=DEV)
+    L.ops.dilated_conv_bwd_w(go, mask, x, T, 2, d1, b1)
+    assert torch.allclose(d1 - base, d0, rtol=1e-4, atol=1e-3 * d0.abs().max().item())
+    assert torch.allclose(b1 - 1.0, b0, rtol=1e-4, atol=1e-3 * b0.abs().max().item())
