@@ -302,26 +302,17 @@ __global__ void __launch_bounds__(256)
 // result is deterministic and does not depend on UN or R.  Winner = smallest value, lowest index on exact ties
 // (torch.argmin's first-min rule).  Every row needs the WHOLE codebook: with one row per CTA the scan was bound by L2
 // bandwidth (3000 queued rows x 128 KB = 393 MB -> 100 us); R rows share each code load.
+#ifndef LIPVQ_RS_UN
+#define LIPVQ_RS_UN 2
+#endif
+constexpr int kRescoreWideR = 16;  // rows per batch of the long-queue form (LIPVQ_RS_UN codes in flight per lane group)
+
 template <int UN, int R>
-__global__ void __launch_bounds__(256)
-    rescore_kernel(const float* __restrict__ z, int D, const float* __restrict__ cb, int K, int metric,
-                   const int* __restrict__ count, const int* __restrict__ first_count, const int* __restrict__ work,
-                   const int* __restrict__ work_first, int skip_rows, int64_t* __restrict__ idx_out, float* __restrict__ best_out, int32_t* __restrict__ stats_out, int vec,
-                   int lpc) {
-  extern __shared__ __align__(16) float zs[];  // [R][D]
-  __shared__ float s_bv[R][8];
-  __shared__ int s_bk[R][8];
+__device__ __forceinline__ void rescore_body(float* zs, float (*s_bv)[8], int (*s_bk)[8], const float* __restrict__ z, int D,
+                                             const float* __restrict__ cb, int K, int metric, int nflag,
+                                             const int* __restrict__ work, int64_t* __restrict__ idx_out,
+                                             float* __restrict__ best_out, int vec, int lpc) {
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  grid_dep_wait();  // launched as a programmatic dependent of the last search pass
-  int nflag = *count;
-  if (work_first != nullptr && *first_count <= skip_rows) {  // the 3-term pass stepped aside: its input queue is ours
-    nflag = *first_count;
-    work = work_first;
-  }
-  if (stats_out && blockIdx.x == 0 && threadIdx.x == 0) {
-    stats_out[0] = nflag;         // rows decided by the exact scan
-    stats_out[1] = *first_count;  // rows the first (fastest) level could not certify
-  }
   const int sub = lane & (lpc - 1), grp = lane / lpc, groups = 32 / lpc;
   for (int w0 = blockIdx.x * R; w0 < nflag; w0 += gridDim.x * R) {
     const int nr = (nflag - w0 < R) ? nflag - w0 : R;
@@ -441,6 +432,36 @@ __global__ void __launch_bounds__(256)
       if (best_out) best_out[row] = (metric == LIPVQ_METRIC_DOT) ? -v : v;
     }
   }
+}
+
+// A long queue (a collapsed codebook: every row a near-tie, e.g. the cosine quantisers of a HierarchicalVQVAE a few steps
+// into training -- 65 536 rows x 1024 codes x 512 took 12 ms with one row per batch, every row re-reading the 2 MB codebook
+// from L2) is scanned sixteen rows per batch: the same sums in the same order (see above), a sixteenth of the L2 traffic.
+// The queue length is only known on the device, so both forms live in one kernel; wide = 0 (host: the rows of a batch do
+// not fit the dynamic shared memory) keeps the one-row form.
+template <int UN, int R>
+__global__ void __launch_bounds__(256)
+    rescore_kernel(const float* __restrict__ z, int D, const float* __restrict__ cb, int K, int metric,
+                   const int* __restrict__ count, const int* __restrict__ first_count, const int* __restrict__ work,
+                   const int* __restrict__ work_first, int skip_rows, int64_t* __restrict__ idx_out, float* __restrict__ best_out, int32_t* __restrict__ stats_out, int vec,
+                   int lpc, int wide) {
+  extern __shared__ __align__(16) float zs[];  // [R][D] ([kRescoreWideR][D] with wide)
+  __shared__ float s_bv[kRescoreWideR][8];
+  __shared__ int s_bk[kRescoreWideR][8];
+  grid_dep_wait();  // launched as a programmatic dependent of the last search pass
+  int nflag = *count;
+  if (work_first != nullptr && *first_count <= skip_rows) {  // the 3-term pass stepped aside: its input queue is ours
+    nflag = *first_count;
+    work = work_first;
+  }
+  if (stats_out && blockIdx.x == 0 && threadIdx.x == 0) {
+    stats_out[0] = nflag;         // rows decided by the exact scan
+    stats_out[1] = *first_count;  // rows the first (fastest) level could not certify
+  }
+  if (wide && nflag >= kRescoreWideR * (int)gridDim.x / 4)
+    rescore_body<LIPVQ_RS_UN, kRescoreWideR>(zs, s_bv, s_bk, z, D, cb, K, metric, nflag, work, idx_out, best_out, vec, lpc);
+  else
+    rescore_body<UN, R>(zs, s_bv, s_bk, z, D, cb, K, metric, nflag, work, idx_out, best_out, vec, lpc);
 }
 
 // Exact scan, small codebooks (D % 4 == 0, D <= 256, K * (D + 4) * 4 bytes <= 200 KB): the fp32 codebook is staged in
@@ -841,7 +862,9 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
   // small codebooks: staged in shared memory, one lane per code (rescore_smem_kernel)
   const size_t rs_wide_smem = ((size_t)K * (D + 4) + D) * sizeof(float);
   const bool rs_wide = vec && D <= 256 && rs_wide_smem <= 200 * 1024;
-  const size_t rs_smem = (size_t)D * sizeof(float);
+  const char* rs_env = getenv("LIPVQ_RESCORE_WIDE");  // =0: one row per batch whatever the queue length (A/B runs)
+  const int rs_multi = ((size_t)kRescoreWideR * D * sizeof(float) <= 48 * 1024 && !(rs_env && rs_env[0] == '0')) ? 1 : 0;
+  const size_t rs_smem = (size_t)(rs_multi ? kRescoreWideR : 1) * D * sizeof(float);
   const bool rs_reg = vec && D <= 64 && K <= 512;  // one code per thread, held in registers (rescore_reg_kernel)
   if (rs_wide) {
     static size_t smem_set[kMaxDevices] = {};  // the attribute is per device
@@ -876,7 +899,7 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
     else
       LIPVQ_CUDA(launch_pdl(rescore_kernel<4, 1>, dim3(rs_blocks), dim3(256), rs_smem, stream, z, D, codebook, K, metric, count,
                             (const int*)&hdr->flagged, queue, (const int*)(queue == work ? nullptr : work),
-                            search_skip_rows(N, D, K), idx_out, (float*)nullptr, stats_out, vec, lpc));
+                            search_skip_rows(N, D, K), idx_out, (float*)nullptr, stats_out, vec, lpc, rs_multi));
     LIPVQ_LAUNCHED("rescore_kernel");
     if (best_out) return search_best_values(z, N, D, codebook, metric, idx_out, best_out, stream);
     return LIPVQ_OK;
@@ -909,7 +932,7 @@ int lipvq_nn_search_f32(const float* z, int64_t N, int D, const float* codebook,
                                                       (const int*)nullptr, 0, idx_out, best_out, stats_out);
   else
     rescore_kernel<4, 1><<<rs_blocks, 256, rs_smem, stream>>>(z, D, codebook, K, metric, &hdr->flagged, &hdr->flagged, work,
-                                                          (const int*)nullptr, 0, idx_out, best_out, stats_out, vec, lpc);
+                                                          (const int*)nullptr, 0, idx_out, best_out, stats_out, vec, lpc, rs_multi);
   LIPVQ_LAUNCHED("rescore_kernel");
   return LIPVQ_OK;
 }

@@ -2,7 +2,7 @@
 decoder; reference robomimic/algo/heirarchical_vqvae.py:8-706), at the shipped config (config/icl_config.py:130-135:
 embed_dim 512, 2 stages x 4 layers, 1024 / 512 codes) -- forward + compute_vqvae_loss + backward + AdamW, CUDA events,
 synthetic action chunks -- next to the oracle port of the same step on the host cores (bounded sample).
-usage: python scripts/bench_t2.py [--steps K] [--no-cpu]      (one JSON line per shape)"""
+usage: python scripts/bench_t2.py [--steps K] [--no-cpu] [--big-only]      (one JSON line per shape)"""
 import json
 import os
 import sys
@@ -79,7 +79,7 @@ def cpu_port(B, T, max_seconds=15.0):
 
 def main():
     steps = int(sys.argv[sys.argv.index("--steps") + 1]) if "--steps" in sys.argv else 20
-    for B, T in ((16, 10), (4096, 16)):
+    for B, T in (((4096, 16),) if "--big-only" in sys.argv else ((16, 10), (4096, 16))):
         ms, ms_fwd, launches, loss = ours(B, T, steps)
         line = {"workload": f"HierarchicalVQVAE training step (fwd + loss + bwd + AdamW), B={B}, T={T}, A={A_DIM}, E=512, "
                             "2x4 MS-TCN layers per side, 1024/512 codes, fp32, eager autograd over liblipvq kernels",
