@@ -307,6 +307,42 @@ __global__ void __launch_bounds__(256)
 #endif
 constexpr int kRescoreWideR = 16;  // rows per batch of the long-queue form (LIPVQ_RS_UN codes in flight per lane group)
 
+// long-queue form at D = 128 NJ with a whole warp per code: every chunk of the UN code rows in flight before the first use
+// (the generic loop exposes one L2 round trip per 128 elements); same sums in the same order as the loop it replaces
+template <int UN, int R, int NJ>
+__device__ __forceinline__ void rescore_unrolled(float (&a)[UN][R], const float* zs, const float* __restrict__ cb, int K, int k0,
+                                                 int lane, int metric) {
+  constexpr int D = 128 * NJ;
+  float4 e4[UN][NJ];
+#pragma unroll
+  for (int u = 0; u < UN; ++u) {
+    const int k = k0 + u * 8;
+#pragma unroll
+    for (int j = 0; j < NJ; ++j)
+      e4[u][j] = (k < K) ? __ldg(reinterpret_cast<const float4*>(cb + (int64_t)k * D + 4 * lane + 128 * j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+#pragma unroll
+  for (int j = 0; j < NJ; ++j) {
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      const float4 z4 = *reinterpret_cast<const float4*>(zs + r * D + 4 * lane + 128 * j);
+#pragma unroll
+      for (int u = 0; u < UN; ++u) {
+        if (metric == LIPVQ_METRIC_DOT) {
+          a[u][r] = fmaf(z4.x, e4[u][j].x, a[u][r]); a[u][r] = fmaf(z4.y, e4[u][j].y, a[u][r]);
+          a[u][r] = fmaf(z4.z, e4[u][j].z, a[u][r]); a[u][r] = fmaf(z4.w, e4[u][j].w, a[u][r]);
+        } else {
+          float df;
+          df = z4.x - e4[u][j].x; a[u][r] = fmaf(df, df, a[u][r]);
+          df = z4.y - e4[u][j].y; a[u][r] = fmaf(df, df, a[u][r]);
+          df = z4.z - e4[u][j].z; a[u][r] = fmaf(df, df, a[u][r]);
+          df = z4.w - e4[u][j].w; a[u][r] = fmaf(df, df, a[u][r]);
+        }
+      }
+    }
+  }
+}
+
 template <int UN, int R>
 __device__ __forceinline__ void rescore_body(float* zs, float (*s_bv)[8], int (*s_bk)[8], const float* __restrict__ z, int D,
                                              const float* __restrict__ cb, int K, int metric, int nflag,
@@ -336,7 +372,11 @@ __device__ __forceinline__ void rescore_body(float* zs, float (*s_bv)[8], int (*
       for (int u = 0; u < UN; ++u)
 #pragma unroll
         for (int r = 0; r < R; ++r) a[u][r] = 0.f;
-      if (vec) {
+      if (R > 1 && vec && lpc == 32 && D == 512) {
+        rescore_unrolled<UN, R, 4>(a, zs, cb, K, k0, lane, metric);
+      } else if (R > 1 && vec && lpc == 32 && D == 256) {
+        rescore_unrolled<UN, R, 2>(a, zs, cb, K, k0, lane, metric);
+      } else if (vec) {
         for (int d = 4 * sub; d < D; d += 4 * lpc) {
           float4 e4[UN];
 #pragma unroll
@@ -434,6 +474,98 @@ __device__ __forceinline__ void rescore_body(float* zs, float (*s_bv)[8], int (*
   }
 }
 
+// Long-queue form proper (D = 128 NJ, a whole warp per code): per iteration a warp holds 2 codes x 16 rows = 32 partial sums
+// per lane.  Reducing each over the warp costs five shuffles and five adds per sum -- more issue slots than the FMAs.  A
+// TRANSPOSED butterfly reduces all 32 at once with 31 shuffles: at the level that pairs lanes (l, l ^ 16) every lane keeps
+// half of its values and sends the other half, and so on; lane l ends with the complete sum number l (code l >> 4, row
+// l & 15).  Every level adds the same two operands as the plain butterfly (16, 8, 4, 2, 1), so the sums are bit-identical.
+template <int NJ>
+__device__ __forceinline__ void rescore_wide32(float* zs, float (*s_bv)[8], int (*s_bk)[8], const float* __restrict__ z,
+                                               const float* __restrict__ cb, int K, int metric, int nflag,
+                                               const int* __restrict__ work, int64_t* __restrict__ idx_out,
+                                               float* __restrict__ best_out) {
+  constexpr int R = kRescoreWideR, D = 128 * NJ;
+  static_assert(R == 16, "the transposed butterfly is written for 2 codes x 16 rows");
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const bool b4 = lane & 16, b3 = lane & 8, b2 = lane & 4, b1 = lane & 2, b0 = lane & 1;
+  for (int w0 = blockIdx.x * R; w0 < nflag; w0 += gridDim.x * R) {
+    const int nr = (nflag - w0 < R) ? nflag - w0 : R;
+    __syncthreads();  // previous batch fully consumed
+    for (int i = threadIdx.x; i < R * (D / 4); i += blockDim.x) {
+      const int r = i / (D / 4), d4 = i - r * (D / 4);
+      reinterpret_cast<float4*>(zs)[i] = (r < nr) ? __ldg(reinterpret_cast<const float4*>(z + (int64_t)work[w0 + r] * D) + d4)
+                                                  : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    __syncthreads();
+    float bv = INFINITY;
+    int bk = 0x7fffffff;
+    for (int k0 = warp; k0 < K; k0 += 16) {
+      float a[2][R];
+#pragma unroll
+      for (int u = 0; u < 2; ++u)
+#pragma unroll
+        for (int r = 0; r < R; ++r) a[u][r] = 0.f;
+      rescore_unrolled<2, R, NJ>(a, zs, cb, K, k0, lane, metric);
+      float w16[16], w8[8], w4[4], w2[2];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const float keep = b4 ? a[1][i] : a[0][i], send = b4 ? a[0][i] : a[1][i];
+        w16[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float keep = b3 ? w16[i + 8] : w16[i], send = b3 ? w16[i] : w16[i + 8];
+        w8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const float keep = b2 ? w8[i + 4] : w8[i], send = b2 ? w8[i] : w8[i + 4];
+        w4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+      }
+#pragma unroll
+      for (int i = 0; i < 2; ++i) {
+        const float keep = b1 ? w4[i + 2] : w4[i], send = b1 ? w4[i] : w4[i + 2];
+        w2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+      }
+      const float keep = b0 ? w2[1] : w2[0], send = b0 ? w2[0] : w2[1];
+      const float av = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+      const int k = k0 + (lane >> 4) * 8;   // ascending per lane: a strict < keeps the lowest index on ties
+      const float val = (metric == LIPVQ_METRIC_L2) ? sqrtf(av) : (metric == LIPVQ_METRIC_DOT ? -av : av);
+      if (k < K && val < bv) {
+        bv = val;
+        bk = k;
+      }
+    }
+    {  // lanes l and l ^ 16 hold the same row, disjoint code sets
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, 16);
+      const int ok = __shfl_xor_sync(0xffffffffu, bk, 16);
+      if (ov < bv || (ov == bv && ok < bk)) {
+        bv = ov;
+        bk = ok;
+      }
+    }
+    if (lane < 16) {
+      s_bv[lane][warp] = bv;
+      s_bk[lane][warp] = bk;
+    }
+    __syncthreads();
+    if (threadIdx.x < nr) {
+      const int r = threadIdx.x;
+      float v = s_bv[r][0];
+      int k = s_bk[r][0];
+      for (int i = 1; i < 8; ++i)
+        if (s_bv[r][i] < v || (s_bv[r][i] == v && s_bk[r][i] < k)) {
+          v = s_bv[r][i];
+          k = s_bk[r][i];
+        }
+      if (k == 0x7fffffff) k = 0;
+      const int64_t row = work[w0 + r];
+      idx_out[row] = (int64_t)k;
+      if (best_out) best_out[row] = (metric == LIPVQ_METRIC_DOT) ? -v : v;
+    }
+  }
+}
+
 // A long queue (a collapsed codebook: every row a near-tie, e.g. the cosine quantisers of a HierarchicalVQVAE a few steps
 // into training -- 65 536 rows x 1024 codes x 512 took 12 ms with one row per batch, every row re-reading the 2 MB codebook
 // from L2) is scanned sixteen rows per batch: the same sums in the same order (see above), a sixteenth of the L2 traffic.
@@ -458,9 +590,11 @@ __global__ void __launch_bounds__(256)
     stats_out[0] = nflag;         // rows decided by the exact scan
     stats_out[1] = *first_count;  // rows the first (fastest) level could not certify
   }
-  if (wide && nflag >= kRescoreWideR * (int)gridDim.x / 4)
-    rescore_body<LIPVQ_RS_UN, kRescoreWideR>(zs, s_bv, s_bk, z, D, cb, K, metric, nflag, work, idx_out, best_out, vec, lpc);
-  else
+  if (wide && nflag >= kRescoreWideR * (int)gridDim.x / 4) {
+    if (vec && D == 512) rescore_wide32<4>(zs, s_bv, s_bk, z, cb, K, metric, nflag, work, idx_out, best_out);
+    else if (vec && D == 256) rescore_wide32<2>(zs, s_bv, s_bk, z, cb, K, metric, nflag, work, idx_out, best_out);
+    else rescore_body<LIPVQ_RS_UN, kRescoreWideR>(zs, s_bv, s_bk, z, D, cb, K, metric, nflag, work, idx_out, best_out, vec, lpc);
+  } else
     rescore_body<UN, R>(zs, s_bv, s_bk, z, D, cb, K, metric, nflag, work, idx_out, best_out, vec, lpc);
 }
 

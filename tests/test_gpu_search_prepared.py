@@ -174,30 +174,33 @@ def test_trainer_steps_and_tokenizes_on_the_prepared_search():
     assert_indices(tr.bufs.t["z_e"], tr.p["quantizer.codebook"], d, ref.cpu())
 
 
-def test_long_queue_exact_scan_wide_batches_equal_one_row_batches():
+@pytest.mark.parametrize("K,D,metric", [(1024, 512, "dot"), (2048, 256, "l2"), (1024, 384, "dot")])
+def test_long_queue_exact_scan_wide_batches_equal_one_row_batches(K, D, metric):
     """A collapsed codebook (the cosine quantisers of a HierarchicalVQVAE a few steps into training: codes with mutual cosine
     0.9999, exact duplicates) leaves EVERY row to the exact scan; its long-queue form (sixteen rows per batch) must give the
     one-row form's indices bit for bit, and the fp64 winner wherever the fp64 gap is above fp32 rounding of the scores."""
     import os
     import lipvq as L
     g = torch.Generator().manual_seed(5)
-    N, K, D = 8192, 1024, 512
+    N = 8192
     base = torch.nn.functional.normalize(torch.randn(1, D, generator=g), dim=1)
     cb = torch.nn.functional.normalize(base + 0.01 * torch.randn(K, D, generator=g) / D ** 0.5, dim=1)
-    cb[100] = cb[7]                                          # exact duplicates: the lower index must win
+    cb[K // 2:] = cb[:K // 2]      # every code twice: each row's winner is an exact tie (never certifiable); lower index wins
     z = torch.nn.functional.normalize(base + 0.3 * torch.randn(N, D, generator=g) / D ** 0.5, dim=1)
     zd, cd = z.to(DEV), cb.to(DEV)
-    idx, st = L.ops.nn_search(zd, cd, L.METRIC_DOT, L.ALGO_TCGEN05, want_stats=True)
+    M = L.METRIC_DOT if metric == "dot" else L.METRIC_L2
+    idx, st = L.ops.nn_search(zd, cd, M, L.ALGO_TCGEN05, want_stats=True)
     os.environ["LIPVQ_RESCORE_WIDE"] = "0"
     try:
-        idx1 = L.ops.nn_search(zd, cd, L.METRIC_DOT, L.ALGO_TCGEN05)
+        idx1 = L.ops.nn_search(zd, cd, M, L.ALGO_TCGEN05)
     finally:
         del os.environ["LIPVQ_RESCORE_WIDE"]
     torch.cuda.synchronize()
     assert st[0].item() > N // 2, st.tolist()              # the regime this test is about
     assert torch.equal(idx, idx1)
-    assert (idx == 100).sum().item() == 0
-    s = z.double() @ cb.double().T
+    assert (idx >= K // 2).sum().item() == 0
+    h = cb[:K // 2].double()
+    s = z.double() @ h.T if metric == "dot" else -torch.cdist(z.double(), h)
     top = s.topk(2, dim=1)
     clear = (top.values[:, 0] - top.values[:, 1]) > 1e-5
     assert torch.equal(idx.cpu()[clear], top.indices[:, 0][clear])
