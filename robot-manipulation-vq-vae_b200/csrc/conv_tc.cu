@@ -502,12 +502,15 @@ constexpr size_t kSmemW = 1024 + 2 * (size_t)kStage + 128 + 4 * 128 * sizeof(flo
 
 }  // namespace
 
-// Shapes the tensor path takes: enough tokens to fill the SMs, widths in whole tiles.  LIPVQ_CONV_ALGO=simt forces the
-// FFMA tiles of conv.cu (A/B runs).
+// Shapes the tensor path takes: widths in whole tiles, any number of tokens from LIPVQ_CONV_TC_MIN_TOKENS (default 32) up --
+// with a few hundred tokens only a handful of CTAs have work, but each walks its K = 3E in ~25 us where the FFMA tiles (as
+// few CTAs, one 16-wide step at a time) need 140-190 us.  LIPVQ_CONV_ALGO=simt forces the FFMA tiles of conv.cu (A/B runs).
 bool conv_tc_supported(int64_t N, int T, int Ei, int Eo) {
   if (const char* f = getenv("LIPVQ_CONV_ALGO"))
     if (f[0] == 's') return false;
-  return N >= 4096 && T >= 1 && Ei == Eo && Ei % kBN == 0 && Ei >= kBN && Ei <= 4096 && N * (int64_t)Ei < ((int64_t)1 << 32);
+  int64_t min_tokens = 32;
+  if (const char* f = getenv("LIPVQ_CONV_TC_MIN_TOKENS")) min_tokens = atoll(f);
+  return N >= min_tokens && T >= 1 && Ei == Eo && Ei % kBN == 0 && Ei >= kBN && Ei <= 4096 && N * (int64_t)Ei < ((int64_t)1 << 32);
 }
 
 int conv_tc_fwd_launch(const float* X, int64_t N, int T, int E, const float* Wf, const float* bias, int dilation, int jlo, int jhi,

@@ -9,11 +9,12 @@ from . import ops
 from .modules import LFQQuantizer, LFQQuantizerEMA, LipschitzMLP, LLFQVAE_V4
 from .classic import VQVAE
 from .hvq import (ActionDecoder, ActionEncoder, DilatedTemporalConvLayer, HierarchicalVQVAE, MSTCNStage)
+from .hvq_trainer import HvqTrainer
 from .hq import HierarchicalLFQHVQVAE, LFQQuantizerEMA_KMeans
 from .bin_action import AdaptiveBinActionEmbedding
 from .dataset import ActionSequenceDataset
 from . import icrt, icl_algo
 
 __all__ = ["ops", "LLFQVAE_V4", "LipschitzMLP", "LFQQuantizer", "LFQQuantizerEMA", "LFQQuantizerEMA_KMeans",
-           "HierarchicalLFQHVQVAE", "VQVAE", "HierarchicalVQVAE", "ActionEncoder", "ActionDecoder", "MSTCNStage",
+           "HierarchicalLFQHVQVAE", "VQVAE", "HierarchicalVQVAE", "HvqTrainer", "ActionEncoder", "ActionDecoder", "MSTCNStage",
            "DilatedTemporalConvLayer", "AdaptiveBinActionEmbedding", "ActionSequenceDataset", "icrt", "icl_algo", "launch_count"]

@@ -436,9 +436,32 @@ class HierarchicalVQVAE(nn.Module):
             avg[dead_mask] = repl
             size[dead_mask] = 1.0
 
+    @torch.no_grad()
+    def replace_dead_codes_static(self, embeddings, subclusters):
+        """replace_dead_codes without a device-to-host copy and with shapes that do not depend on the data (CUDA-graph
+        capture, HvqTrainer): EVERY code draws a candidate row, dead codes take theirs.  Same law as the reference's
+        (each dead code gets an independent uniform row of the batch, heirarchical_vqvae.py:543-588), not the same
+        random stream: the reference draws num_dead indices, this draws K."""
+        for size, thr, cb, avg, src in ((self.cluster_size_z, self.replace_threshold_z, self.codebook_z, self.embed_avg_z,
+                                         embeddings),
+                                        (self.cluster_size_q, self.replace_threshold_q, self.codebook_q, self.embed_avg_q,
+                                         subclusters)):
+            flat = src.reshape(-1, src.shape[-1]).detach()
+            if flat.size(0) == 0:
+                return
+            dead = size < thr
+            idx = torch.randint(0, flat.size(0), (size.numel(),), device=flat.device)
+            repl = flat[idx].contiguous()
+            if self.use_cosine:
+                repl = ops.l2_normalize_rows(repl)
+            cb.copy_(torch.where(dead[:, None], repl, cb))
+            avg.copy_(torch.where(dead[:, None], repl, avg))
+            size.copy_(torch.where(dead, torch.ones_like(size), size))
+
     def forward(self, actions, training=True):
         embeddings = self.encoder(actions)
-        if not self.codebooks_initialized:
+        graph_safe = getattr(self, "_graph_safe", False)  # HvqTrainer: initialised beforehand, no host round trips
+        if not graph_safe and not self.codebooks_initialized:
             self.initialize_codebooks_with_current_batch(embeddings)
         B, T, D = embeddings.shape
         quantized_z, z_indices, z_ops = self._quantize(embeddings, self.codebook_z)
@@ -454,7 +477,10 @@ class HierarchicalVQVAE(nn.Module):
                              self.codebook_z)
             self._ema_update(quantized_z.reshape(-1, D), q_indices.reshape(-1), self.embed_avg_q, self.cluster_size_q,
                              self.codebook_q)
-            self.replace_dead_codes(embeddings, quantized_z)
+            if graph_safe:
+                self.replace_dead_codes_static(embeddings, quantized_z)
+            else:
+                self.replace_dead_codes(embeddings, quantized_z)
         return out
 
     # -- losses --------------------------------------------------------------------------------

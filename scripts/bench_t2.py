@@ -62,6 +62,25 @@ def ours(B, T, steps):
     return ms, ms_fwd, launches, float(loss)
 
 
+def ours_graph(B, T, steps):
+    """the same step through lipvq.HvqTrainer (one CUDA graph per step; dead codes replaced with static shapes)"""
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(0)
+    m = lipvq.HierarchicalVQVAE(A_DIM, **CFG).to(dev).train()
+    tr = lipvq.HvqTrainer(m, lr=1e-3, weight_decay=1e-4, lambda_rec=0.002)
+    xs = [torch.rand(B, T, A_DIM, device=dev) * 2 - 1 for _ in range(4)]
+    for i in range(3):
+        tr.step(xs[i % 4])
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(steps):
+        losses = tr.step(xs[i % 4])
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / steps, float(losses["vqvae_loss"])
+
+
 def cpu_port(B, T, max_seconds=15.0):
     import lipvq_oracle as O
     torch.manual_seed(0)
@@ -85,6 +104,10 @@ def main():
                             "2x4 MS-TCN layers per side, 1024/512 codes, fp32, eager autograd over liblipvq kernels",
                 "ms_per_step": ms, "chunks_per_s": B / (ms * 1e-3), "ms_forward_eval": ms_fwd,
                 "chunks_per_s_forward_eval": B / (ms_fwd * 1e-3), "own_kernel_launches_per_step": launches, "final_loss": loss}
+        if "--no-graph" not in sys.argv:
+            ms_g, loss_g = ours_graph(B, T, steps)
+            line["graph_step"] = {"ms_per_step": ms_g, "chunks_per_s": B / (ms_g * 1e-3), "final_loss": loss_g,
+                                  "how": "lipvq.HvqTrainer: the whole step as one CUDA graph"}
         if "--no-cpu" not in sys.argv:
             Bc = min(B, 256)
             cpu_ms = cpu_port(Bc, T)

@@ -315,3 +315,51 @@ def test_kmeans_init_vs_reference_fixture(L):
     _close(cb[perm], g["hq_codebook"], rtol=1e-4, atol=1e-5, what="hq kmeans centres")
     z_q, idx = q(g["z"].to(DEV))  # forward after init: every blob owns exactly one code
     assert torch.equal(torch.bincount(idx.cpu(), minlength=8), torch.full((8,), 32))
+
+
+def test_hvq_trainer_graph_step_equals_eager_step():
+    """lipvq.HvqTrainer: the captured step (one CUDA graph) against the same step run eagerly, from the same initial state on
+    the same batches, with the dead-code thresholds at zero (no random replacement: the two runs are then deterministic up to
+    the order of the atomic adds of the per-code sums)."""
+    import copy
+    import lipvq as L
+    torch.manual_seed(0)
+    cfg = dict(embed_dim=128, num_subclusters=64, num_clusters=32, num_stages=2, num_layers_per_stage=2, dropout=0.0,
+               kmeans_init=False, replace_threshold_z=0.0, replace_threshold_q=0.0)
+    m1 = L.HierarchicalVQVAE(7, **cfg).to(DEV).train()
+    xs = [torch.rand(8, 10, 7, device=DEV) * 2 - 1 for _ in range(6)]
+    with torch.no_grad():
+        m1.initialize_codebooks_with_current_batch(m1.encoder(xs[0]))
+    m2 = copy.deepcopy(m1)
+    t1 = L.HvqTrainer(m1, lr=1e-3, weight_decay=1e-4, lambda_rec=0.5, graph=True, warmup=3)
+    t2 = L.HvqTrainer(m2, lr=1e-3, weight_decay=1e-4, lambda_rec=0.5, graph=False)
+    # the capture's warm-up steps are real steps on the first batch: give the eager trainer the same three
+    l1 = t1.step(xs[0])
+    for _ in range(3):
+        t2.step(xs[0])
+    l2 = t2.step(xs[0])
+    assert torch.allclose(l1["vqvae_loss"], l2["vqvae_loss"], rtol=1e-4, atol=1e-7), (l1["vqvae_loss"], l2["vqvae_loss"])
+    for x in xs[1:]:
+        l1, l2 = t1.step(x), t2.step(x)
+        assert torch.allclose(l1["vqvae_loss"], l2["vqvae_loss"], rtol=2e-3, atol=1e-6), (l1["vqvae_loss"], l2["vqvae_loss"])
+    for (n, a), (_, b) in zip(m1.named_parameters(), m2.named_parameters()):
+        assert torch.allclose(a, b, rtol=1e-2, atol=2e-4), n
+    assert torch.allclose(m1.cluster_size_z, m2.cluster_size_z, rtol=1e-3, atol=1e-3)
+
+
+def test_replace_dead_codes_static_replaces_exactly_the_dead_codes():
+    import lipvq as L
+    torch.manual_seed(1)
+    m = L.HierarchicalVQVAE(7, embed_dim=64, num_subclusters=32, num_clusters=16, num_stages=1, num_layers_per_stage=1,
+                            kmeans_init=False).to(DEV)
+    emb = torch.randn(4, 10, 64, device=DEV)
+    m.cluster_size_z.copy_(torch.arange(32, device=DEV).float() % 2)       # every second code dead
+    m.cluster_size_q.fill_(5.0)
+    cz, cq = m.codebook_z.clone(), m.codebook_q.clone()
+    m.replace_dead_codes_static(emb, emb)
+    dead = torch.arange(32, device=DEV) % 2 == 0
+    assert torch.equal(m.codebook_z[~dead], cz[~dead]) and torch.equal(m.codebook_q, cq)
+    rows = torch.nn.functional.normalize(emb.reshape(-1, 64), dim=-1)
+    hit = (m.codebook_z[dead] @ rows.T).max(dim=1).values                    # each replacement is a (normalised) batch row
+    assert torch.all(hit > 1 - 1e-5)
+    assert torch.all(m.cluster_size_z[dead] == 1.0) and torch.equal(m.embed_avg_z[dead], m.codebook_z[dead])
