@@ -72,6 +72,26 @@ __device__ __forceinline__ void store_split8(uint8_t* base, int r, int ch, const
   *reinterpret_cast<uint4*>(d + 2 * kTile) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
 }
 
+// MN-major, SWIZZLE_128B: LBO = distance between 64-element blocks of the M/N dimension, SBO = between 8-token groups
+__device__ __forceinline__ uint64_t desc_mn_sw128(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) | ((uint64_t)((sbo >> 4) & 0x3FFF) << 32) |
+         (1ull << 46) | (2ull << 61);
+}
+constexpr int kWBlk = 64 * 128;  // one 64-channel block of one term of a 64-token chunk: 8 KB
+
+// eight consecutive channels (16-byte chunk c of 16) of token tk of the chunk: the three terms, kTile bytes apart
+__device__ __forceinline__ void store_split8_mn(uint8_t* base, int tk, int c, const float4& a, const float4& b) {
+  uint32_t hh[4], mm[4], ll[4];
+  split3_pair(a.x, a.y, hh[0], mm[0], ll[0]);
+  split3_pair(a.z, a.w, hh[1], mm[1], ll[1]);
+  split3_pair(b.x, b.y, hh[2], mm[2], ll[2]);
+  split3_pair(b.z, b.w, hh[3], mm[3], ll[3]);
+  uint8_t* d = base + (uint32_t)((c >> 3) * kWBlk + (tk >> 3) * 1024 + (tk & 7) * 128 + (((c & 7) ^ (tk & 7)) << 4));
+  *reinterpret_cast<uint4*>(d) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
+  *reinterpret_cast<uint4*>(d + kTile) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
+  *reinterpret_cast<uint4*>(d + 2 * kTile) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
+}
+
 __device__ __forceinline__ void mask8(float4& a, float4& b, const uint8_t* m, float scale) {
   const uint2 k = __ldg(reinterpret_cast<const uint2*>(m));
   a.x = (k.x & 0xFFu) ? a.x * scale : 0.f; a.y = (k.x & 0xFF00u) ? a.y * scale : 0.f;
@@ -82,8 +102,8 @@ __device__ __forceinline__ void mask8(float4& a, float4& b, const uint8_t* m, fl
 
 // MODE kFwd: the layer forward.  MODE kBwdX: its input gradient
 //   dX[n, i] = dOUT[n, i] + sum_{j, o} masked(dOUT)[n + (1 - j) d, o] * Wb[j][o][i]
-// -- the same contraction with the shifts negated; the B tile (128 inputs i x 64 outputs o, K-major) is gathered from
-// Wb's i-contiguous rows by lanes that run along i (coalesced) and each collect eight consecutive o.
+// -- the same contraction with the shifts negated; the B tile (64 outputs o of the reduction x 128 inputs i) keeps Wb's
+// i-contiguous rows: an MN-major operand (layout of the weight-gradient kernel below), read with coalesced float4 loads.
 template <int MODE>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -120,13 +140,16 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
   if (warp == kWarpMma) {
     // ===== MMA issuer =====
     if (lane == 0) {
-      const uint32_t idesc = idesc_bf16(kBM, kBN);
+      // kBwdX: the weight tile is MN-major (input channels contiguous, see the converters), A stays K-major
+      const uint32_t idesc = idesc_bf16(kBM, kBN) | (MODE == kBwdX ? (1u << 16) : 0u);
       const int ta[6] = {1, 2, 0, 1, 0, 0}, tb[6] = {1, 0, 2, 0, 1, 0};  // term 0 = h, 1 = m, 2 = l; smallest products first
       uint32_t a_lo[2][3], b_lo[2][3];
+      uint64_t b_mn[2][3];
       for (int s = 0; s < 2; ++s)
         for (int t = 0; t < 3; ++t) {
           a_lo[s][t] = desc_sw128_lo(smem_u32(smem + s * kStage + t * kTile));
           b_lo[s][t] = desc_sw128_lo(smem_u32(smem + s * kStage + (3 + t) * kTile));
+          b_mn[s][t] = desc_mn_sw128(smem_u32(smem + s * kStage + (3 + t) * kTile), kWBlk, 1024);
         }
       uint32_t g = 0;  // chunks issued (ring position)
       for (int i = 0; i < ntile; ++i) {
@@ -149,13 +172,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
             const uint32_t bl = s ? b_lo[1][tb[combo]] : b_lo[0][tb[combo]];
 #pragma unroll
             for (int k = 0; k < kChunk / 16; ++k) {
-              if (combo < 5) {
-                umma_f16_lo(d_small, al + 2 * k, bl + 2 * k, kDescSw128Hi, idesc, acc_small);
-                acc_small = 1;
+              const uint32_t dst = combo < 5 ? d_small : d_hh;
+              const uint32_t fl = combo < 5 ? acc_small : acc_flag;
+              if (MODE == kBwdX) {  // 16 outputs o of the reduction = two 8-row atoms of the MN-major tile
+                const uint64_t bm = s ? b_mn[1][tb[combo]] : b_mn[0][tb[combo]];
+                umma_f16(dst, (((uint64_t)kDescSw128Hi) << 32 | (uint64_t)al) + (uint64_t)(2 * k), bm + (uint64_t)(128 * k), idesc, fl);
               } else {
-                umma_f16_lo(d_hh, al + 2 * k, bl + 2 * k, kDescSw128Hi, idesc, acc_flag);
-                acc_flag = 1;
+                umma_f16_lo(dst, al + 2 * k, bl + 2 * k, kDescSw128Hi, idesc, fl);
               }
+              if (combo < 5) acc_small = 1; else acc_flag = 1;
             }
           }
           umma_commit(bar_empty + 8 * s);
@@ -180,7 +205,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
         at[u] = (arow[u] < p.N) ? (int)(arow[u] % p.T) : -1;  // time index inside the sequence (-1: no such row)
       }
       const float* wrow[2] = {p.Wf + (size_t)(ct * kBN + r0) * 3 * p.E, p.Wf + (size_t)(ct * kBN + r0 + 64) * 3 * p.E};
-      const int bn = tcv & 127, bch = tcv >> 7;  // kBwdX: B items (input bn, 16-byte chunks bch and bch + 4)
+      const int bc = tcv & 15, bo = tcv >> 4;  // kBwdX: B items (16-byte chunk bc of a Wb row, rows bo and bo + 32 of the chunk)
       for (int kc = 0; kc < nk; ++kc, ++g) {
         const int tap = p.jlo + kc / cpt, c0 = (kc % cpt) * kChunk + ch * 8;
         const int shift = (MODE == kFwd) ? (tap - 1) * p.dil : (1 - tap) * p.dil;
@@ -201,11 +226,11 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
             const float4* ws = reinterpret_cast<const float4*>(wrow[u] + tap * p.E + c0);
             b[u][0] = __ldg(ws);
             b[u][1] = __ldg(ws + 1);
-          } else {
-            const float* ws = p.Wf + ((size_t)tap * p.E + (kc % cpt) * kChunk + (bch + 4 * u) * 8) * p.E + ct * kBN + bn;
-            b[u][0] = make_float4(__ldg(ws), __ldg(ws + p.E), __ldg(ws + 2 * (size_t)p.E), __ldg(ws + 3 * (size_t)p.E));
-            ws += 4 * (size_t)p.E;
-            b[u][1] = make_float4(__ldg(ws), __ldg(ws + p.E), __ldg(ws + 2 * (size_t)p.E), __ldg(ws + 3 * (size_t)p.E));
+          } else {  // row o = bo + 32 u of the chunk of Wb[tap], input channels 8 bc .. 8 bc + 7 of the column tile
+            const float4* ws = reinterpret_cast<const float4*>(p.Wf + ((size_t)tap * p.E + (kc % cpt) * kChunk + bo + 32 * u) * p.E +
+                                                               ct * kBN + 8 * bc);
+            b[u][0] = __ldg(ws);
+            b[u][1] = __ldg(ws + 1);
           }
         }
         const uint32_t s = g & 1;
@@ -215,7 +240,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
         for (int u = 0; u < 2; ++u) {
           store_split8(st, r0 + 64 * u, ch, a[u][0], a[u][1]);
           if (MODE == kFwd) store_split8(st + 3 * kTile, r0 + 64 * u, ch, b[u][0], b[u][1]);
-          else store_split8(st + 3 * kTile, bn, bch + 4 * u, b[u][0], b[u][1]);
+          else store_split8_mn(st + 3 * kTile, bo + 32 * u, bc, b[u][0], b[u][1]);
         }
         fence_async_smem();
         __syncwarp();
@@ -298,11 +323,15 @@ constexpr size_t kSmem = 1024 + 2 * (size_t)kStage + 128;
 
 // ---- weight gradient ------------------------------------------------------------------------------------------------
 //   dWf[o][j][i] += sum_tok masked(dOUT)[tok, o] * X[tok + (j - 1) d, i],     db[o] += sum_tok masked(dOUT)[tok, o]
-// The reduction runs over TOKENS, so both operands are gathered into K-major tiles by lanes that run along the channel
-// (coalesced 128-byte rows) and collect eight consecutive tokens each.  One CTA = one 128 x 128 tile of dWf and one slice
-// of the tokens (tiles x slices ~ the SM count); four accumulators: the five small chains in one, the h*h chain dealt over
-// three by chunk (the accumulator truncates per MMA, see above: a long reduction into one accumulator would lose ~2e-5 of
-// the slice's magnitude); the slice's result is added to dWf with vector reductions.
+// The reduction runs over TOKENS while both operands are stored channel-contiguous: they go into MN-major tiles (canonical
+// SWIZZLE_128B layout: 8 tokens x 128 bytes = one 1024-byte atom, 16-byte chunk ^= token & 7; atoms of consecutive 8-token
+// groups SBO = 1024 bytes apart, the two 64-channel blocks LBO = 8 KB apart -- the layout of linear_tc_bwd_w_kernel), so the
+// converters read rows with the same coalesced float4 loads as the forward and nothing is transposed.  (A first version
+// gathered K-major tiles with scalar loads: 0.99 ms per layer; with a branch per element even 3.09 ms, the sixteen round
+// trips of a chunk serialised.)  One CTA = one 128 x 128 tile of dWf and one slice of the tokens (tiles x slices ~ the SM
+// count); four accumulators: the five small chains in one, the h*h chain dealt over three by chunk (the accumulator
+// truncates per MMA, see above: a long reduction into one accumulator would lose ~2e-5 of the slice's magnitude); the
+// slice's result is added to dWf with vector reductions.
 struct ConvTcWParams {
   const float* G; const uint8_t* gmask; const float* X;
   int64_t N; int T, E, dil, jlo, jhi;
@@ -321,7 +350,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTc
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * kStage);
   const uint32_t bar_full = smem_u32(bars + 0), bar_empty = smem_u32(bars + 2), bar_acc_full = smem_u32(bars + 4);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
-  float* rs_s = reinterpret_cast<float*>(bars + 10);  // [4][128] bias partial sums (after the ring is idle: in stage 0)
+  float* rs_s = reinterpret_cast<float*>(bars + 10);  // [128] bias gradient of the slice
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int tile = (int)blockIdx.x, slice = (int)blockIdx.y;
@@ -342,6 +371,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTc
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), 4 * kBN);
+  if (threadIdx.x < 128) rs_s[threadIdx.x] = 0.f;
   grid_dep_wait();
   fence_before();
   __syncthreads();
@@ -350,13 +380,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTc
 
   if (warp == kWarpMma) {
     if (lane == 0) {
-      const uint32_t idesc = idesc_bf16(kBM, kBN);
+      const uint32_t idesc = idesc_bf16(kBM, kBN) | (1u << 15) | (1u << 16);  // A and B MN-major
       const int ta[6] = {1, 2, 0, 1, 0, 0}, tb[6] = {1, 0, 2, 0, 1, 0};
-      uint32_t a_lo[2][3], b_lo[2][3];
+      uint64_t da[2][3], db_[2][3];  // descriptors of (stage, term) at token 0; a 16-token step = two atoms = 2048 bytes
       for (int s = 0; s < 2; ++s)
         for (int t = 0; t < 3; ++t) {
-          a_lo[s][t] = desc_sw128_lo(smem_u32(smem + s * kStage + t * kTile));
-          b_lo[s][t] = desc_sw128_lo(smem_u32(smem + s * kStage + (3 + t) * kTile));
+          da[s][t] = desc_mn_sw128(smem_u32(smem + s * kStage + t * kTile), kWBlk, 1024);
+          db_[s][t] = desc_mn_sw128(smem_u32(smem + s * kStage + (3 + t) * kTile), kWBlk, 1024);
         }
       uint32_t acc_small = 0, hh_used = 0;
       int rot = 0;
@@ -368,15 +398,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTc
         uint32_t acc_hh = (hh_used >> rot) & 1u;
 #pragma unroll
         for (int combo = 0; combo < 6; ++combo) {
-          const uint32_t al = s ? a_lo[1][ta[combo]] : a_lo[0][ta[combo]];
-          const uint32_t bl = s ? b_lo[1][tb[combo]] : b_lo[0][tb[combo]];
+          const uint64_t ad = s ? da[1][ta[combo]] : da[0][ta[combo]];
+          const uint64_t bd = s ? db_[1][tb[combo]] : db_[0][tb[combo]];
 #pragma unroll
           for (int k = 0; k < kChunk / 16; ++k) {
             if (combo < 5) {
-              umma_f16_lo(tmem_base, al + 2 * k, bl + 2 * k, kDescSw128Hi, idesc, acc_small);
+              umma_f16(tmem_base, ad + (uint64_t)(128 * k), bd + (uint64_t)(128 * k), idesc, acc_small);
               acc_small = 1;
             } else {
-              umma_f16_lo(d_hh, al + 2 * k, bl + 2 * k, kDescSw128Hi, idesc, acc_hh);
+              umma_f16(d_hh, ad + (uint64_t)(128 * k), bd + (uint64_t)(128 * k), idesc, acc_hh);
               acc_hh = 1;
             }
           }
@@ -388,51 +418,41 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTc
       umma_commit(bar_acc_full);
     }
   } else if (warp >= kEpiWarps) {
-    // ===== converters: items (channel n of the tile, eight consecutive tokens of the chunk) =====
+    // ===== converters: item = (token of the chunk, 16-byte chunk of eight channels); a warp covers two token rows =====
     const int tcv = (int)threadIdx.x - kEpiWarps * 32;
-    const int n = tcv & 127, chb = tcv >> 7;
+    const int c = tcv & 15, tkb = tcv >> 4;          // channels 8c .. 8c+7 of the tile; tokens tkb and tkb + 32 of the chunk
     const int sh = (tap - 1) * p.dil;
-    const float* gcol = p.G + o0 + n;
-    const uint8_t* mcol = p.gmask + o0 + n;
-    const float* xcol = p.X + i0 + n;
-    float rsum = 0.f;
-    // time index of the first token of each of this thread's two items, advanced by 64 per chunk
-    int t0[2];
+    const float* gcol = p.G + o0 + 8 * c;
+    const uint8_t* mcol = p.gmask + o0 + 8 * c;
+    const float* xcol = p.X + i0 + 8 * c;
+    float rsum[8];
 #pragma unroll
-    for (int u = 0; u < 2; ++u) t0[u] = (int)((cbeg * kChunk + (chb + 4 * u) * 8) % p.T);
+    for (int e = 0; e < 8; ++e) rsum[e] = 0.f;
+    int t0[2];  // time index of this thread's two tokens, advanced by 64 per chunk
+#pragma unroll
+    for (int u = 0; u < 2; ++u) t0[u] = (int)((cbeg * kChunk + tkb + 32 * u) % p.T);
     const int tstep = kChunk % p.T;
+    const int last = (int)p.N - 1;
     for (int kc = 0; kc < nk; ++kc) {
       const int k0 = (int)(cbeg + kc) * kChunk;   // (N E < 2^32: token indices and element offsets fit 32 bits)
-      // all loads unconditional (addresses clamped into the arrays) and issued before any use: a branch per element would
-      // serialise sixteen round trips to memory per chunk
-      float a[2][8], b[2][8];
-      uint32_t mk[2][8];
-      const int last = (int)p.N - 1;
+      // loads unconditional (rows clamped into the arrays), conditions applied afterwards as selects
+      float4 a[2][2], b[2][2];
+      uint2 mk[2];
+      bool live[2], inx[2];
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
-        const int tok0 = k0 + (chb + 4 * u) * 8;
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const int tok = min(tok0 + e, last);
-          const int xr = max(0, min(tok + sh, last));
-          const uint32_t go = (uint32_t)tok * (uint32_t)p.E;
-          a[u][e] = __ldg(gcol + go);
-          mk[u][e] = __ldg(mcol + go);
-          b[u][e] = __ldg(xcol + (uint32_t)xr * (uint32_t)p.E);
-        }
-      }
-#pragma unroll
-      for (int u = 0; u < 2; ++u) {
-        const int tok0 = k0 + (chb + 4 * u) * 8;
-        int tt = t0[u];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const bool in = tok0 + e <= last;
-          const int ts = tt + sh;
-          a[u][e] = (in && mk[u][e]) ? a[u][e] * p.scale : 0.f;
-          b[u][e] = (in && ts >= 0 && ts < p.T) ? b[u][e] : 0.f;
-          tt = (tt + 1 == p.T) ? 0 : tt + 1;
-        }
+        const int tok = k0 + tkb + 32 * u;
+        const int tc = min(tok, last), xr = max(0, min(tc + sh, last));
+        const uint32_t go = (uint32_t)tc * (uint32_t)p.E;
+        a[u][0] = __ldg(reinterpret_cast<const float4*>(gcol + go));
+        a[u][1] = __ldg(reinterpret_cast<const float4*>(gcol + go) + 1);
+        mk[u] = __ldg(reinterpret_cast<const uint2*>(mcol + go));
+        const float4* xs = reinterpret_cast<const float4*>(xcol + (uint32_t)xr * (uint32_t)p.E);
+        b[u][0] = __ldg(xs);
+        b[u][1] = __ldg(xs + 1);
+        live[u] = tok <= last;
+        const int ts = t0[u] + sh;
+        inx[u] = live[u] && ts >= 0 && ts < p.T;
         t0[u] += tstep;
         if (t0[u] >= p.T) t0[u] -= p.T;
       }
@@ -441,17 +461,27 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTc
       uint8_t* st = smem + s * kStage;
 #pragma unroll
       for (int u = 0; u < 2; ++u) {
-        store_split8(st, n, chb + 4 * u, make_float4(a[u][0], a[u][1], a[u][2], a[u][3]), make_float4(a[u][4], a[u][5], a[u][6], a[u][7]));
-        store_split8(st + 3 * kTile, n, chb + 4 * u, make_float4(b[u][0], b[u][1], b[u][2], b[u][3]),
-                     make_float4(b[u][4], b[u][5], b[u][6], b[u][7]));
-#pragma unroll
-        for (int e = 0; e < 8; ++e) rsum += a[u][e];
+        const float sc = live[u] ? p.scale : 0.f;
+        float4 g0 = a[u][0], g1 = a[u][1];
+        g0.x = (mk[u].x & 0xFFu) ? g0.x * sc : 0.f; g0.y = (mk[u].x & 0xFF00u) ? g0.y * sc : 0.f;
+        g0.z = (mk[u].x & 0xFF0000u) ? g0.z * sc : 0.f; g0.w = (mk[u].x & 0xFF000000u) ? g0.w * sc : 0.f;
+        g1.x = (mk[u].y & 0xFFu) ? g1.x * sc : 0.f; g1.y = (mk[u].y & 0xFF00u) ? g1.y * sc : 0.f;
+        g1.z = (mk[u].y & 0xFF0000u) ? g1.z * sc : 0.f; g1.w = (mk[u].y & 0xFF000000u) ? g1.w * sc : 0.f;
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int tk = tkb + 32 * u;
+        store_split8_mn(st, tk, c, g0, g1);
+        store_split8_mn(st + 3 * kTile, tk, c, inx[u] ? b[u][0] : z4, inx[u] ? b[u][1] : z4);
+        rsum[0] += g0.x; rsum[1] += g0.y; rsum[2] += g0.z; rsum[3] += g0.w;
+        rsum[4] += g1.x; rsum[5] += g1.y; rsum[6] += g1.z; rsum[7] += g1.w;
       }
       fence_async_smem();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_full + 8 * s);
     }
-    if (p.db != nullptr && nt == 0) rs_s[chb * 128 + n] = rsum;
+    if (p.db != nullptr && nt == 0) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) atomicAdd(rs_s + 8 * c + e, rsum[e]);
+    }
   } else {
     // ===== epilogue warps: the slice's tile, summed over the four accumulators, added to dWf =====
     const int q = warp & 3, part = warp >> 2;
@@ -491,7 +521,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTc
   __syncthreads();
   grid_dep_launch();
   if (p.db != nullptr && nt == 0 && threadIdx.x < 128)
-    atomicAdd(p.db + o0 + threadIdx.x, (rs_s[threadIdx.x] + rs_s[128 + threadIdx.x]) + (rs_s[256 + threadIdx.x] + rs_s[384 + threadIdx.x]));
+    atomicAdd(p.db + o0 + threadIdx.x, rs_s[threadIdx.x]);
   if (warp == kWarpMma) {
     fence_after();
     tmem_dealloc(tmem_base, 4 * kBN);
