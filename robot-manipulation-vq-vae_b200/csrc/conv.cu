@@ -468,7 +468,7 @@ int lipvq_dilated_conv_bwd_w_f32(const float* dOUT, const uint8_t* mask, const f
   g.N = N; g.T = T; g.Ei = Ei; g.Eo = Eo; g.dil = dilation;
   live_taps(T, dilation, &g.jlo, &g.jhi);
   g.scale = 1.f / (1.f - drop_p);
-  if (conv_tc_supported(N, T, Ei, Eo) && aligned16(dWf))
+  if (conv_tc_supported(N, T, Ei, Eo) && aligned16(dWf) && ((uintptr_t)mask & 7u) == 0)
     return conv_tc_bwd_w_launch(dOUT, mask, X, N, T, Ei, dilation, g.jlo, g.jhi, g.scale, dWf, db, stream);
   const int64_t tiles = ceil_div64(Eo, 64) * ((3 * Ei + BN - 1) / BN);
   int64_t splits = ceil_div64(2 * (int64_t)sm_count(), tiles);

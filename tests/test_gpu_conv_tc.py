@@ -129,3 +129,31 @@ def test_conv_tc_bwd_w_accumulates_into_dwf():
     L.ops.dilated_conv_bwd_w(go, mask, x, T, 2, d1, b1)
     assert torch.allclose(d1 - base, d0, rtol=1e-4, atol=1e-3 * d0.abs().max().item())
     assert torch.allclose(b1 - 1.0, b0, rtol=1e-4, atol=1e-3 * b0.abs().max().item())
+
+
+def test_conv_misaligned_mask_takes_the_ffma_tiles():
+    """A keep-mask that is only 4-byte aligned (all the C-ABI asks for) cannot be read in 8-byte words: the entry points must
+    fall back to the FFMA tiles instead of faulting, with the same results."""
+    import lipvq as L
+    g = torch.Generator().manual_seed(11)
+    N, T, E = 2048, 16, 128
+    x = torch.randn(N, E, generator=g).to(DEV)
+    go = torch.randn(N, E, generator=g).to(DEV)
+    W = (torch.randn(E, E, 3, generator=g) / (3 * E) ** 0.5).to(DEV)
+    b = torch.zeros(E, device=DEV)
+    Wf, Wb = L.ops.conv_pack_weights(W, True, True)
+    _, mask = L.ops.dilated_conv_fwd(x, T, Wf, b, 2)
+    store = torch.zeros(N * E + 16, dtype=torch.uint8, device=DEV)
+    m4 = store[4:4 + N * E].view(N, E)
+    assert m4.data_ptr() % 8 == 4
+    m4.copy_(mask)
+    dx = L.ops.dilated_conv_bwd_x(go, m4, T, Wb, 2)
+    dx0 = L.ops.dilated_conv_bwd_x(go, mask, T, Wb, 2)
+    d1, d0 = torch.zeros(E, 3, E, device=DEV), torch.zeros(E, 3, E, device=DEV)
+    b1, b0 = torch.zeros(E, device=DEV), torch.zeros(E, device=DEV)
+    L.ops.dilated_conv_bwd_w(go, m4, x, T, 2, d1, b1)
+    L.ops.dilated_conv_bwd_w(go, mask, x, T, 2, d0, b0)
+    torch.cuda.synchronize()
+    assert torch.allclose(dx, dx0, rtol=1e-5, atol=2e-5 * dx0.abs().max().item())
+    assert torch.allclose(d1, d0, rtol=1e-5, atol=2e-5 * d0.abs().max().item())
+    assert torch.allclose(b1, b0, rtol=1e-5, atol=2e-5 * b0.abs().max().item())
