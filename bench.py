@@ -239,6 +239,48 @@ def _time_rotating(fn, bufs, iters, streamed=False):
     return statistics.mean(durs), min(durs)
 
 
+def t2_leg(dev, B=4096, T=16, steps=5):
+    """The fork's live tokenizer (HierarchicalVQVAE, SURVEY section 8 'next' row) at its shipped config: training step through
+    lipvq.HvqTrainer (one CUDA graph) and eval forward, synthetic chunks resident in HBM.  Not the headline; an extra key."""
+    import lipvq
+    cfg = dict(embed_dim=512, num_subclusters=1024, num_clusters=512, num_stages=2, num_layers_per_stage=4, dropout=0.0,
+               kmeans_init=False)
+    torch.manual_seed(0)
+    m = lipvq.HierarchicalVQVAE(12, **cfg).to(dev).train()
+    tr = lipvq.HvqTrainer(m, lr=1e-3, weight_decay=1e-4, lambda_rec=0.002)
+    xs = [torch.rand(B, T, 12, device=dev) * 2 - 1 for _ in range(4)]
+    for i in range(3):
+        tr.step(xs[i % 4])
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    for i in range(steps):
+        losses = tr.step(xs[i % 4])
+    b.record()
+    torch.cuda.synchronize()
+    ms = a.elapsed_time(b) / steps
+    with torch.no_grad():
+        m.eval()
+        for i in range(2):
+            m(xs[i % 4], training=False)
+        torch.cuda.synchronize()
+        a.record()
+        for i in range(steps):
+            m(xs[i % 4], training=False)
+        b.record()
+        torch.cuda.synchronize()
+    ms_f = a.elapsed_time(b) / steps
+    out = {"workload": f"HierarchicalVQVAE (heirarchical_vqvae.py:8-706) E=512, 2x4 MS-TCN layers per side, 1024/512 codes, "
+                       f"B={B}, T={T}, fp32; 4 input batches rotate (activations >> L2)",
+           "train_step": {"ms_per_step": ms, "chunks_per_s": B / (ms * 1e-3), "how": "lipvq.HvqTrainer, one CUDA graph per step",
+                          "final_loss": float(losses["vqvae_loss"])},
+           "forward_eval": {"ms": ms_f, "chunks_per_s": B / (ms_f * 1e-3)},
+           "see": "scripts/bench_t2.py (eager step, B=16 shape, oracle port on the host cores), DESIGN.md section 7"}
+    del tr, m, xs
+    torch.cuda.empty_cache()
+    return out
+
+
 def search_sweep(dev, hbm, tf_burst, flush, cpu_rows=256):
     """BASELINE config 3: K in {512, 4096, 65536} x D in {64, 256}, N = 65536, raw latents z ~ U(0,1), with the
     two baselines the config names: torch.cdist + argmin on the host cores and eager on the same B200."""
@@ -482,6 +524,8 @@ def run_ours(args):
         if not args.no_sweep:
             extra["sweep"] = search_sweep(dev, hbm, tf_burst, flush)
         del flush
+        if not args.no_t2 and world == 1:
+            extra["t2"] = t2_leg(dev)
 
     if world > 1:
         dist.barrier()
@@ -698,6 +742,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the timed CPU leg (profiling runs only)")
     ap.add_argument("--no-sweep", action="store_true", help="skip the codebook-size sweep (BASELINE config 3) in the line")
+    ap.add_argument("--no-t2", action="store_true", help="skip the HierarchicalVQVAE leg (extra key t2) in the line")
     ap.add_argument("--config", default="c2", choices=["c2", "c5"],
                     help="c2: tokenizer training step (default, the headline); c5: ICRT+LipVQ-VAE policy training step")
     args = ap.parse_args()

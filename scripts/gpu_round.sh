@@ -15,13 +15,13 @@ timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "s
 timeout 600 python bench.py --steps 30 --warmup 5 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench exit $?"
 cat gpurun_out/bench.json; tail -n 5 gpurun_out/bench.err
 if [ "${1:-}" != "noncu" ]; then
-  timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 &&
+  timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-t2 > gpurun_out/plain.log 2>&1 &&
   timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
-      python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_launches.log 2>&1
+      python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-t2 > gpurun_out/ncu_launches.log 2>&1
   echo "ncu launches exit $?"
-  timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/plain2.log 2>&1 &&
+  timeout 300 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-t2 > gpurun_out/plain2.log 2>&1 &&
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:"${NCU_KERNEL:-search_p1}" -s 6 -c 3 \
-      -f -o gpurun_out/prof_search python bench.py --steps 2 --warmup 3 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1
+      -f -o gpurun_out/prof_search python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-t2 > gpurun_out/ncu_full.log 2>&1
   echo "ncu full exit $?"
 fi
 ls -la gpurun_out | head -30
