@@ -79,6 +79,15 @@ def test_cpu_tensors_are_refused():
         lipvq.ops.nn_search(torch.zeros(4, 16), torch.zeros(32, 16))
 
 
+def test_hvq_trainer_has_no_cpu_path():
+    import lipvq
+    m = lipvq.HierarchicalVQVAE(7, embed_dim=32, num_subclusters=8, num_clusters=4, num_stages=1, num_layers_per_stage=1,
+                                kmeans_init=False)
+    assert not getattr(m, "_graph_safe", False)      # the module's own forward keeps the reference's host-driven behaviour
+    with pytest.raises(RuntimeError, match="CUDA"):
+        lipvq.HvqTrainer(m)
+
+
 def test_missing_library_fails_loudly(tmp_path):
     env = dict(os.environ, LIPVQ_LIB=str(tmp_path / "nope.so"),
                PYTHONPATH=os.path.join(ROOT, "robot-manipulation-vq-vae_b200"))
