@@ -582,7 +582,25 @@ __device__ __forceinline__ uint64_t desc_mn_sw128(uint32_t smem_addr, uint32_t l
          (1ull << 46) | (2ull << 61);
 }
 
-__global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinTcWParams p) {
+// Roles of the weight-gradient kernel: the epilogue runs once, at the very end, so four warps (one per TMEM lane quadrant) are
+// enough (21 warps instead of 25).  Measured at the bench shape (step time): 8 epilogue warps 0.4549 ms, 4 epilogue warps
+// 0.4531 ms; THREE converter register sets (two units in flight; 15 converter warps = 640 threads for 96 registers, or 16
+// with 80) 0.480 / 0.492 ms, 15 converter warps with two sets 0.461 ms: the converters are bound by their issue rate, not
+// by the bytes in flight -- the macros keep those variants buildable (-DLIPVQ_W_CVT / _SETS / _EPI).
+#ifndef LIPVQ_W_CVT
+#define LIPVQ_W_CVT 16
+#endif
+#ifndef LIPVQ_W_SETS
+#define LIPVQ_W_SETS 2
+#endif
+#ifndef LIPVQ_W_EPI
+#define LIPVQ_W_EPI 4
+#endif
+constexpr int kWEpi = LIPVQ_W_EPI, kWCvt = LIPVQ_W_CVT;  // (registers are allocated per four warps: 20 warps -> 96 per thread, 21 -> 80)
+constexpr int kWMma = kWEpi + kWCvt;
+constexpr int kWThreads = 32 * (kWMma + 1);  // 640
+
+__global__ void __launch_bounds__(kWThreads, 1) linear_tc_bwd_w_kernel(const LinTcWParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   const int a_term = p.nbA * kWBlk, b_term = p.nbB * kWBlk;   // one term of one buffer
@@ -603,15 +621,15 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < 2; ++s) {
-      mbar_init(bar_full + 8 * s, kCvtWarps);
+      mbar_init(bar_full + 8 * s, kWCvt);
       mbar_init(bar_empty + 8 * s, 1);
     }
     mbar_init(bar_done, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == kWarpMma) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
+  if (warp == kWMma) tmem_alloc(smem_u32(tmem_slot), p.tmem_cols);
   // chunks the converters never write (columns past out_dim / in_dim + 1) must read as zero
-  for (int i = threadIdx.x; i < (2 * buf_bytes + kWBlk) / 16; i += kThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < (2 * buf_bytes + kWBlk) / 16; i += kWThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
   if (p.ones_sep) {  // constant chunk (1, 0, ..., 0) of every token, h term, both buffers: never touched again
     __syncthreads();
     if (threadIdx.x < 2 * kWTok) {
@@ -628,7 +646,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
   const uint32_t tmem_base = *tmem_slot;
   TR(1);
 
-  if (warp == kWarpMma) {
+  if (warp == kWMma) {
     if (lane == 0) {
       const uint32_t idesc = idesc_bf16(kBM, p.Np) | (1u << 15) | (1u << 16);  // A and B MN-major
       const uint32_t zero_addr = smem_u32(zero_blk);
@@ -665,14 +683,14 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
       }
       umma_commit(bar_done);
     }
-  } else if (warp >= kEpiWarps) {
+  } else if (warp >= kWEpi) {
     // ===== converters: item = (token, 16-byte chunk); consecutive threads take consecutive chunks of one token row =====
-    const int tcv = (int)threadIdx.x - kEpiWarps * 32;
+    const int tcv = (int)threadIdx.x - kWEpi * 32;
     const int CT = p.CA + p.CB;
     const int items = kWTok * CT;
     const bool vecY = (p.out_dim % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.dY) & 15) == 0);
     const bool vecX = (p.in_dim % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.X) & 15) == 0);
-    constexpr int kCT = kCvtWarps * 32;
+    constexpr int kCT = kWCvt * 32;
     const float rcpCT = 1.f / (float)CT;
     const int nbatch = (items + 2 * kCT - 1) / (2 * kCT);  // batches of two items per thread and block
     const int total_units = nblk * nbatch;
@@ -757,7 +775,21 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
         TR(23);
       }
     };
-    // two register sets in ping-pong (a copy at the end of the iteration would wait for the loads it is meant to hide)
+#if LIPVQ_W_SETS == 3
+    // three register sets in rotation, two units in flight (a copy at the end of the iteration would wait for the loads it
+    // is meant to hide)
+    float w0[2][8], w1[2][8], w2[2][8];
+    load_unit(0, w0);
+    load_unit(1, w1);
+    for (int unit = 0; unit < total_units; unit += 3) {
+      load_unit(unit + 2, w2);
+      convert_unit(unit, w0);
+      load_unit(unit + 3, w0);
+      convert_unit(unit + 1, w1);
+      load_unit(unit + 4, w1);
+      convert_unit(unit + 2, w2);
+    }
+#else
     float w0[2][8], w1[2][8];
     load_unit(0, w0);
     for (int unit = 0; unit < total_units; unit += 2) {
@@ -766,9 +798,10 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
       load_unit(unit + 2, w0);
       convert_unit(unit + 1, w1);
     }
+#endif
   } else {
-    // ===== epilogue warps 0-7: TMEM lane = output row o; every second 16-column group; one pass at the very end =====
-    const int q = warp & 3, half = warp >> 2;
+    // ===== epilogue warps 0-3: TMEM lane = output row o; one pass over the 16-column groups at the very end =====
+    const int q = warp & 3, half = (kWEpi == 8) ? (warp >> 2) : 0;
     const int o = q * 32 + lane;
     TR(10);
     mbar_wait(bar_done, 0);
@@ -778,9 +811,9 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
     // 16-byte vector reductions (four columns per request); every CTA starts at a different column group so the 148
     // CTAs do not walk the same addresses in lock step
     const bool vec = (p.in_dim % 4 == 0) && ((reinterpret_cast<uintptr_t>(p.dW) & 15) == 0);
-    const int ngroups = p.Np / 16, mine = (ngroups - half + 1) / 2;  // groups half, half + 2, ...
+    const int ngroups = p.Np / 16, mine = (kWEpi == 8) ? (ngroups - half + 1) / 2 : ngroups;
     for (int g = 0; g < mine; ++g) {
-      const int c0 = 16 * (half + 2 * ((g + (int)blockIdx.x) % mine));
+      const int c0 = 16 * (half + (kWEpi == 8 ? 2 : 1) * ((g + (int)blockIdx.x) % mine));
       uint32_t v[16];
       tmem_ld16(trow + c0, v);
       tmem_ld_wait16(v);
@@ -809,7 +842,7 @@ __global__ void __launch_bounds__(kThreads, 1) linear_tc_bwd_w_kernel(const LinT
   fence_before();
   __syncthreads();
   grid_dep_launch();  // every role of this CTA is done: the next kernel may be scheduled (a waiting dependent polls, so not earlier)
-  if (warp == kWarpMma) {
+  if (warp == kWMma) {
     fence_after();
     tmem_dealloc(tmem_base, p.tmem_cols);
   }
@@ -952,7 +985,7 @@ int linear_tc_bwd_w_launch(const float* dY, int64_t N, int out_dim, const float*
   }
   const int blocks = (int)ceil_div64(N, kWTok);
   const int sms = sm_count();
-  LIPVQ_CUDA(launch_pdl(linear_tc_bwd_w_kernel, dim3(blocks < sms ? blocks : sms), dim3(kThreads), smem, stream, p));
+  LIPVQ_CUDA(launch_pdl(linear_tc_bwd_w_kernel, dim3(blocks < sms ? blocks : sms), dim3(kWThreads), smem, stream, p));
   LIPVQ_LAUNCHED("linear_tc_bwd_w_kernel");
   return LIPVQ_OK;
 }
