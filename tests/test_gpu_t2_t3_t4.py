@@ -363,3 +363,29 @@ def test_replace_dead_codes_static_replaces_exactly_the_dead_codes():
     hit = (m.codebook_z[dead] @ rows.T).max(dim=1).values                    # each replacement is a (normalised) batch row
     assert torch.all(hit > 1 - 1e-5)
     assert torch.all(m.cluster_size_z[dead] == 1.0) and torch.equal(m.embed_avg_z[dead], m.codebook_z[dead])
+
+
+def test_t2_shipped_width_vs_oracle(L):
+    """HierarchicalVQVAE at the fork's shipped config (config/icl_config.py:130-135: embed_dim 512, 2 x 4 MS-TCN layers per
+    side, 1024 / 512 codes) against the oracle port, forward in eval mode: the E = 512 convolutions run on the tensor cores
+    (conv_tc.cu, 160 tokens >= its gate), the searches on the streamed tcgen05 pass + exact scan.  Embeddings within 2e-4
+    (eight layers of three-term bf16 contractions against fp32 torch); indices equal except cosine near-ties inside the
+    reference matmul's own rounding, which at random initialisation (gaps of 1e-3 between codes) means equal."""
+    import lipvq_oracle as O
+    torch.manual_seed(5)
+    cfg = dict(embed_dim=512, num_subclusters=1024, num_clusters=512, num_stages=2, num_layers_per_stage=4)
+    p = O.t2_init(12, **cfg)
+    m = L.HierarchicalVQVAE(12, dropout=0.0, kmeans_init=False, **cfg)
+    sd = dict(p)
+    sd["codebooks_initialized"] = torch.tensor(True)
+    m.load_state_dict(sd, strict=True)
+    m.to(DEV).eval()
+    actions = torch.rand(16, 10, 12) * 2 - 1
+    out = m(actions.to(DEV), training=False)
+    ref = O.t2_forward({k: v.clone() for k, v in p.items()}, actions, training=False, num_stages=2, num_layers=4)
+    _close(out["embeddings"], ref["embeddings"], rtol=2e-4, atol=2e-5)
+    mz = int((out["z_indices"].cpu() != ref["z_indices"]).sum())
+    mq = int((out["q_indices"].cpu() != ref["q_indices"]).sum())
+    assert mz <= 2 and mq <= 2, (mz, mq)
+    if mz == 0 and mq == 0:
+        _close(out["reconstructed_actions"], ref["reconstructed_actions"], rtol=1e-3, atol=2e-5)
