@@ -41,6 +41,7 @@ struct ConvTcParams {
   float* OUT; uint8_t* mask;
   const uint8_t* gmask;
   float scale; uint32_t drop_thr, seed;
+  int split;   // 1: one tile = (row block, column tile, TAP); raw partial sums are added into OUT (see conv_tc_*_launch)
 };
 
 __device__ __forceinline__ uint32_t mix32(uint32_t a, uint32_t b) {  // (conv.cu: the same dropout stream)
@@ -115,11 +116,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row_blocks = (int)((p.N + kBM - 1) / kBM), nct = p.E / kBN;
-  const int tiles = row_blocks * nct;
+  const int ntap = p.split ? p.jhi - p.jlo : 1;  // split: the live taps of a tile go to different CTAs
+  const int tiles = row_blocks * nct * ntap;
   const int ntile = ((int)blockIdx.x < tiles) ? (tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   if (ntile == 0) return;
   const int cpt = p.E / kChunk;               // chunks per tap
-  const int nk = (p.jhi - p.jlo) * cpt;       // chunks per tile (dead taps skipped)
+  const int nk = p.split ? cpt : (p.jhi - p.jlo) * cpt;  // chunks per tile (dead taps skipped)
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < 2; ++s) {
@@ -195,7 +197,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
     uint32_t g = 0;
     for (int i = 0; i < ntile; ++i) {
       const int tile = (int)blockIdx.x + i * (int)gridDim.x;
-      const int rb = tile / nct, ct = tile - rb * nct;
+      const int t2 = tile / ntap, jbase = p.jlo + (tile - t2 * ntap);
+      const int rb = t2 / nct, ct = t2 - rb * nct;
       const int64_t row0 = (int64_t)rb * kBM;
       int64_t arow[2];
       int at[2];
@@ -207,7 +210,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
       const float* wrow[2] = {p.Wf + (size_t)(ct * kBN + r0) * 3 * p.E, p.Wf + (size_t)(ct * kBN + r0 + 64) * 3 * p.E};
       const int bc = tcv & 15, bo = tcv >> 4;  // kBwdX: B items (16-byte chunk bc of a Wb row, rows bo and bo + 32 of the chunk)
       for (int kc = 0; kc < nk; ++kc, ++g) {
-        const int tap = p.jlo + kc / cpt, c0 = (kc % cpt) * kChunk + ch * 8;
+        const int tap = jbase + kc / cpt, c0 = (kc % cpt) * kChunk + ch * 8;
         const int shift = (MODE == kFwd) ? (tap - 1) * p.dil : (1 - tap) * p.dil;
         float4 a[2][2], b[2][2];
 #pragma unroll
@@ -253,7 +256,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
     const uint32_t lane_off = (uint32_t)(q * 32) << 16;
     for (int i = 0; i < ntile; ++i) {
       const int tile = (int)blockIdx.x + i * (int)gridDim.x;
-      const int rb = tile / nct, ct = tile - rb * nct;
+      const int t2 = tile / ntap;
+      const int rb = t2 / nct, ct = t2 - rb * nct;
       const int64_t row = (int64_t)rb * kBM + q * 32 + lane;
       const uint32_t ab = (uint32_t)i & 1;
       mbar_wait(bar_acc_full + 8 * ab, ((uint32_t)i >> 1) & 1);
@@ -273,7 +277,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
           __syncwarp();
           if (lane == 0) mbar_arrive(bar_acc_empty + 8 * ab);
         }
-        if (MODE == kBwdX) {
+        if (p.split) {  // a tap's share of the sums: added to OUT, which the host side initialised
+          if (row < p.N) {
+            float* dst = p.OUT + row * p.E + ct * kBN + c0;
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(__uint_as_float(v[0])),
+                         "f"(__uint_as_float(v[1])), "f"(__uint_as_float(v[2])), "f"(__uint_as_float(v[3])) : "memory");
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + 4), "f"(__uint_as_float(v[4])),
+                         "f"(__uint_as_float(v[5])), "f"(__uint_as_float(v[6])), "f"(__uint_as_float(v[7])) : "memory");
+          }
+        } else if (MODE == kBwdX) {
           if (row < p.N) {
             const int col = ct * kBN + c0;
             const float4 x0 = __ldg(reinterpret_cast<const float4*>(p.X + row * p.E + col));  // residual branch of the layer
@@ -320,6 +332,43 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
 }
 
 constexpr size_t kSmem = 1024 + 2 * (size_t)kStage + 128;
+
+// Few tokens (a grid far below the SM count, e.g. the 160 tokens of the reference's own batch: 8 tiles, each a chain of 24
+// chunks ~ 50 us): the live taps of a tile go to different CTAs (a third of the chain), which add their partial sums into
+// OUT -- zeroed beforehand (forward; this kernel then applies the layer's epilogue in place) or preset to dOUT (input
+// gradient: nothing left to do).
+__global__ void __launch_bounds__(256) conv_split_epilogue_kernel(const ConvTcParams p) {
+  grid_dep_wait();
+  const int64_t n4 = p.N * p.E / 4;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t o = 4 * i;
+    const int col = (int)(o % p.E);
+    const float4 a = *reinterpret_cast<const float4*>(p.OUT + o);
+    const float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+    const float4 x = __ldg(reinterpret_cast<const float4*>(p.X + o));
+    const float pre[4] = {a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w};
+    const float rr[4] = {x.x, x.y, x.z, x.w};
+    float out[4];
+    uint32_t kb = 0;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      bool keep = pre[e] > 0.f;
+      if (p.drop_thr) keep = keep && (mix32(p.seed, (uint32_t)(o + e)) >= p.drop_thr);
+      out[e] = (keep ? pre[e] * p.scale : 0.f) + rr[e];
+      kb |= (keep ? 1u : 0u) << (8 * e);
+    }
+    *reinterpret_cast<float4*>(p.OUT + o) = make_float4(out[0], out[1], out[2], out[3]);
+    *reinterpret_cast<uint32_t*>(p.mask + o) = kb;
+  }
+}
+
+// split by tap when that still leaves the grid inside one wave (LIPVQ_CONV_SPLIT=0: never)
+inline int conv_split(int64_t N, int E, int jlo, int jhi) {
+  if (const char* f = getenv("LIPVQ_CONV_SPLIT"))
+    if (f[0] == '0') return 0;
+  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN);
+  return (jhi - jlo > 1 && tiles * (jhi - jlo) <= sm_count()) ? 1 : 0;
+}
 
 // ---- weight gradient ------------------------------------------------------------------------------------------------
 //   dWf[o][j][i] += sum_tok masked(dOUT)[tok, o] * X[tok + (j - 1) d, i],     db[o] += sum_tok masked(dOUT)[tok, o]
@@ -555,10 +604,18 @@ int conv_tc_fwd_launch(const float* X, int64_t N, int T, int E, const float* Wf,
     LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel<kFwd>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
     smem_set[dev_] = true;
   }
-  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN);
+  p.split = conv_split(N, E, jlo, jhi);
+  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN) * (p.split ? jhi - jlo : 1);
   const int sms = sm_count();
+  if (p.split) LIPVQ_CUDA(cudaMemsetAsync(OUT, 0, (size_t)N * E * sizeof(float), stream));
   LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kFwd>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
   LIPVQ_LAUNCHED("conv_tc_kernel<fwd>");
+  if (p.split) {
+    int64_t blocks = ceil_div64(N * E / 4, 256);
+    if (blocks > 4 * sms) blocks = 4 * sms;
+    LIPVQ_CUDA(launch_pdl(conv_split_epilogue_kernel, dim3((unsigned)blocks), dim3(256), 0, stream, p));
+    LIPVQ_LAUNCHED("conv_split_epilogue_kernel");
+  }
   return LIPVQ_OK;
 }
 
@@ -573,8 +630,10 @@ int conv_tc_bwd_x_launch(const float* dOUT, const uint8_t* mask, int64_t N, int 
     LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel<kBwdX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
     smem_set[dev_] = true;
   }
-  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN);
+  p.split = conv_split(N, E, jlo, jhi);
+  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN) * (p.split ? jhi - jlo : 1);
   const int sms = sm_count();
+  if (p.split) LIPVQ_CUDA(cudaMemcpyAsync(dX, dOUT, (size_t)N * E * sizeof(float), cudaMemcpyDeviceToDevice, stream));
   LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kBwdX>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
   LIPVQ_LAUNCHED("conv_tc_kernel<bwd_x>");
   return LIPVQ_OK;

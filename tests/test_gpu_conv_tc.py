@@ -157,3 +157,40 @@ def test_conv_misaligned_mask_takes_the_ffma_tiles():
     assert torch.allclose(dx, dx0, rtol=1e-5, atol=2e-5 * dx0.abs().max().item())
     assert torch.allclose(d1, d0, rtol=1e-5, atol=2e-5 * d0.abs().max().item())
     assert torch.allclose(b1, b0, rtol=1e-5, atol=2e-5 * b0.abs().max().item())
+
+
+@pytest.mark.parametrize("drop", [0.0, 0.2])
+def test_conv_tc_few_tokens_split_by_tap(drop):
+    """160 tokens (the reference's own batch: 16 chunks of 10) at E = 512: the live taps of a tile run in different CTAs and add
+    their partial sums into OUT / dX.  Same values (fp32 atomic order aside) and the same mask as the unsplit tensor path and
+    as the FFMA tiles."""
+    import lipvq as L
+    g = torch.Generator().manual_seed(21)
+    B, T, E, dil = 16, 10, 512, 2
+    N = B * T
+    x = torch.randn(N, E, generator=g).to(DEV)
+    go = torch.randn(N, E, generator=g).to(DEV)
+    W = (torch.randn(E, E, 3, generator=g) / (3 * E) ** 0.5).to(DEV)
+    b = (torch.randn(E, generator=g) * 0.1).to(DEV)
+    Wf, Wb = L.ops.conv_pack_weights(W, True, True)
+
+    def run():
+        out, mask = L.ops.dilated_conv_fwd(x, T, Wf, b, dil, drop_p=drop, seed=99)
+        return out, mask, L.ops.dilated_conv_bwd_x(go, mask, T, Wb, dil, drop_p=drop)
+    out, mask, dx = run()
+    os.environ["LIPVQ_CONV_SPLIT"] = "0"
+    try:
+        out1, mask1, dx1 = run()
+    finally:
+        del os.environ["LIPVQ_CONV_SPLIT"]
+    out2, mask2, dx2 = _simt(run)
+    torch.cuda.synchronize()
+    for o, m_, d in ((out1, mask1, dx1), (out2, mask2, dx2)):
+        assert (mask != m_).float().mean().item() < 1e-4
+        same = mask == m_
+        assert torch.allclose(out[same], o[same], rtol=1e-5, atol=2e-5)
+    # the gradients use their own run's mask: compare where the masks agree everywhere on the rows involved
+    if torch.equal(mask, mask1):
+        assert torch.allclose(dx, dx1, rtol=1e-5, atol=2e-5 * dx1.abs().max().item())
+    if torch.equal(mask, mask2):
+        assert torch.allclose(dx, dx2, rtol=1e-5, atol=2e-5 * dx2.abs().max().item())
