@@ -41,7 +41,8 @@ struct ConvTcParams {
   float* OUT; uint8_t* mask;
   const uint8_t* gmask;
   float scale; uint32_t drop_thr, seed;
-  int split;   // 1: one tile = (row block, column tile, TAP); raw partial sums are added into OUT (see conv_tc_*_launch)
+  int split;   // s > 0: one tile = (row block, column tile, tap, one of s ranges of the tap's chunks); raw partial sums are
+               // added into OUT (see conv_tc_*_launch)
 };
 
 __device__ __forceinline__ uint32_t mix32(uint32_t a, uint32_t b) {  // (conv.cu: the same dropout stream)
@@ -116,12 +117,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int row_blocks = (int)((p.N + kBM - 1) / kBM), nct = p.E / kBN;
-  const int ntap = p.split ? p.jhi - p.jlo : 1;  // split: the live taps of a tile go to different CTAs
+  const int ntap = p.split ? (p.jhi - p.jlo) * p.split : 1;  // split: the live taps (and ranges of their chunks) of a tile go to different CTAs
   const int tiles = row_blocks * nct * ntap;
   const int ntile = ((int)blockIdx.x < tiles) ? (tiles - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x : 0;
   if (ntile == 0) return;
   const int cpt = p.E / kChunk;               // chunks per tap
-  const int nk = p.split ? cpt : (p.jhi - p.jlo) * cpt;  // chunks per tile (dead taps skipped)
+  const int nk = p.split ? cpt / p.split : (p.jhi - p.jlo) * cpt;  // chunks per tile (dead taps skipped)
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < 2; ++s) {
@@ -197,7 +198,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
     uint32_t g = 0;
     for (int i = 0; i < ntile; ++i) {
       const int tile = (int)blockIdx.x + i * (int)gridDim.x;
-      const int t2 = tile / ntap, jbase = p.jlo + (tile - t2 * ntap);
+      const int t2 = tile / ntap, part = tile - t2 * ntap;
+      const int jbase = p.jlo + (p.split ? part / p.split : 0), cbase = p.split ? (part % p.split) * nk : 0;
       const int rb = t2 / nct, ct = t2 - rb * nct;
       const int64_t row0 = (int64_t)rb * kBM;
       int64_t arow[2];
@@ -210,7 +212,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
       const float* wrow[2] = {p.Wf + (size_t)(ct * kBN + r0) * 3 * p.E, p.Wf + (size_t)(ct * kBN + r0 + 64) * 3 * p.E};
       const int bc = tcv & 15, bo = tcv >> 4;  // kBwdX: B items (16-byte chunk bc of a Wb row, rows bo and bo + 32 of the chunk)
       for (int kc = 0; kc < nk; ++kc, ++g) {
-        const int tap = jbase + kc / cpt, c0 = (kc % cpt) * kChunk + ch * 8;
+        const int kq = kc + cbase;  // position in the tile's full chunk sequence (tap-major)
+        const int tap = jbase + kq / cpt, c0 = (kq % cpt) * kChunk + ch * 8;
         const int shift = (MODE == kFwd) ? (tap - 1) * p.dil : (1 - tap) * p.dil;
         float4 a[2][2], b[2][2];
 #pragma unroll
@@ -230,7 +233,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
             b[u][0] = __ldg(ws);
             b[u][1] = __ldg(ws + 1);
           } else {  // row o = bo + 32 u of the chunk of Wb[tap], input channels 8 bc .. 8 bc + 7 of the column tile
-            const float4* ws = reinterpret_cast<const float4*>(p.Wf + ((size_t)tap * p.E + (kc % cpt) * kChunk + bo + 32 * u) * p.E +
+            const float4* ws = reinterpret_cast<const float4*>(p.Wf + ((size_t)tap * p.E + (kq % cpt) * kChunk + bo + 32 * u) * p.E +
                                                                ct * kBN + 8 * bc);
             b[u][0] = __ldg(ws);
             b[u][1] = __ldg(ws + 1);
@@ -366,8 +369,12 @@ __global__ void __launch_bounds__(256) conv_split_epilogue_kernel(const ConvTcPa
 inline int conv_split(int64_t N, int E, int jlo, int jhi) {
   if (const char* f = getenv("LIPVQ_CONV_SPLIT"))
     if (f[0] == '0') return 0;
-  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN);
-  return (jhi - jlo > 1 && tiles * (jhi - jlo) <= sm_count()) ? 1 : 0;
+  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN) * (jhi - jlo);
+  const int cpt = E / kChunk;
+  if (jhi - jlo <= 1 && tiles * 2 > sm_count()) return 0;
+  for (int s = 4; s >= 1; s >>= 1)  // each tap's chunks in s ranges while the grid stays inside one wave
+    if (cpt % s == 0 && tiles * s <= sm_count() && (s > 1 || jhi - jlo > 1)) return s;
+  return 0;
 }
 
 // ---- weight gradient ------------------------------------------------------------------------------------------------
@@ -605,7 +612,7 @@ int conv_tc_fwd_launch(const float* X, int64_t N, int T, int E, const float* Wf,
     smem_set[dev_] = true;
   }
   p.split = conv_split(N, E, jlo, jhi);
-  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN) * (p.split ? jhi - jlo : 1);
+  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN) * (p.split ? (jhi - jlo) * p.split : 1);
   const int sms = sm_count();
   if (p.split) LIPVQ_CUDA(cudaMemsetAsync(OUT, 0, (size_t)N * E * sizeof(float), stream));
   LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kFwd>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
@@ -631,7 +638,7 @@ int conv_tc_bwd_x_launch(const float* dOUT, const uint8_t* mask, int64_t N, int 
     smem_set[dev_] = true;
   }
   p.split = conv_split(N, E, jlo, jhi);
-  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN) * (p.split ? jhi - jlo : 1);
+  const int64_t tiles = ceil_div64(N, kBM) * (E / kBN) * (p.split ? (jhi - jlo) * p.split : 1);
   const int sms = sm_count();
   if (p.split) LIPVQ_CUDA(cudaMemcpyAsync(dX, dOUT, (size_t)N * E * sizeof(float), cudaMemcpyDeviceToDevice, stream));
   LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kBwdX>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
