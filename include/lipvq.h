@@ -297,7 +297,8 @@ LIPVQ_API int lipvq_lipschitz_scale_bwd_f32(const float* G, const float* W, cons
  *   unpack: dW [Eo][Ei][3] += dWf
  * E % 128 == 0 with at least 32 tokens: the three entry points run on the tensor cores (csrc/conv_tc.cu: three bf16
  * terms per operand, fp32 accumulation; values within 1e-5 of the fp32 FFMA tiles, same keep-mask and dropout stream;
- * needs N * E < 2^32 and an 8-byte-aligned mask, else -- or with LIPVQ_CONV_ALGO=simt -- the FFMA tiles run).
+ * needs N * E < 2^32 and an 8-byte-aligned mask, else -- or with LIPVQ_CONV_ALGO=simt -- the FFMA tiles run;
+ * LIPVQ_CONV_PRECISION=bf16: plain bf16 operands and one MMA chain, values within 1e-2).
  * --------------------------------------------------------------------------------------------- */
 LIPVQ_API int lipvq_conv_pack_weights_f32(const float* W, int Eo, int Ei, float* Wf, float* Wb, void* stream);
 LIPVQ_API int lipvq_conv_unpack_grad_f32(const float* dWf, int Eo, int Ei, float* dW, void* stream);

@@ -41,6 +41,7 @@ struct ConvTcParams {
   float* OUT; uint8_t* mask;
   const uint8_t* gmask;
   float scale; uint32_t drop_thr, seed;
+  int terms;   // 3: fp32 accuracy (three bf16 terms per operand, six chains); 1: bf16 mode (plain bf16 operands, one chain)
   int split;   // s > 0: one tile = (row block, column tile, tap, one of s ranges of the tap's chunks); raw partial sums are
                // added into OUT (see conv_tc_*_launch)
 };
@@ -62,13 +63,17 @@ __device__ __forceinline__ void split3_pair(float x0, float x1, uint32_t& h, uin
   l = bf16x2_rn(r0 - __uint_as_float(m << 16), r1 - __uint_as_float(m & 0xFFFF0000u));
 }
 // eight consecutive values of tile row r, 16-byte chunk ch: the three terms, kTile bytes apart
-__device__ __forceinline__ void store_split8(uint8_t* base, int r, int ch, const float4& a, const float4& b) {
+__device__ __forceinline__ void store_split8(uint8_t* base, int r, int ch, const float4& a, const float4& b, int terms = 3) {
+  uint8_t* d = base + (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
+  if (terms == 1) {  // bf16 mode: the rounded value alone
+    *reinterpret_cast<uint4*>(d) = make_uint4(bf16x2_rn(a.x, a.y), bf16x2_rn(a.z, a.w), bf16x2_rn(b.x, b.y), bf16x2_rn(b.z, b.w));
+    return;
+  }
   uint32_t hh[4], mm[4], ll[4];
   split3_pair(a.x, a.y, hh[0], mm[0], ll[0]);
   split3_pair(a.z, a.w, hh[1], mm[1], ll[1]);
   split3_pair(b.x, b.y, hh[2], mm[2], ll[2]);
   split3_pair(b.z, b.w, hh[3], mm[3], ll[3]);
-  uint8_t* d = base + (uint32_t)(r * 128 + ((ch ^ (r & 7)) << 4));
   *reinterpret_cast<uint4*>(d) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
   *reinterpret_cast<uint4*>(d + kTile) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
   *reinterpret_cast<uint4*>(d + 2 * kTile) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
@@ -82,13 +87,17 @@ __device__ __forceinline__ uint64_t desc_mn_sw128(uint32_t smem_addr, uint32_t l
 constexpr int kWBlk = 64 * 128;  // one 64-channel block of one term of a 64-token chunk: 8 KB
 
 // eight consecutive channels (16-byte chunk c of 16) of token tk of the chunk: the three terms, kTile bytes apart
-__device__ __forceinline__ void store_split8_mn(uint8_t* base, int tk, int c, const float4& a, const float4& b) {
+__device__ __forceinline__ void store_split8_mn(uint8_t* base, int tk, int c, const float4& a, const float4& b, int terms = 3) {
+  uint8_t* d = base + (uint32_t)((c >> 3) * kWBlk + (tk >> 3) * 1024 + (tk & 7) * 128 + (((c & 7) ^ (tk & 7)) << 4));
+  if (terms == 1) {
+    *reinterpret_cast<uint4*>(d) = make_uint4(bf16x2_rn(a.x, a.y), bf16x2_rn(a.z, a.w), bf16x2_rn(b.x, b.y), bf16x2_rn(b.z, b.w));
+    return;
+  }
   uint32_t hh[4], mm[4], ll[4];
   split3_pair(a.x, a.y, hh[0], mm[0], ll[0]);
   split3_pair(a.z, a.w, hh[1], mm[1], ll[1]);
   split3_pair(b.x, b.y, hh[2], mm[2], ll[2]);
   split3_pair(b.z, b.w, hh[3], mm[3], ll[3]);
-  uint8_t* d = base + (uint32_t)((c >> 3) * kWBlk + (tk >> 3) * 1024 + (tk & 7) * 128 + (((c & 7) ^ (tk & 7)) << 4));
   *reinterpret_cast<uint4*>(d) = make_uint4(hh[0], hh[1], hh[2], hh[3]);
   *reinterpret_cast<uint4*>(d + kTile) = make_uint4(mm[0], mm[1], mm[2], mm[3]);
   *reinterpret_cast<uint4*>(d + 2 * kTile) = make_uint4(ll[0], ll[1], ll[2], ll[3]);
@@ -106,7 +115,7 @@ __device__ __forceinline__ void mask8(float4& a, float4& b, const uint8_t* m, fl
 //   dX[n, i] = dOUT[n, i] + sum_{j, o} masked(dOUT)[n + (1 - j) d, o] * Wb[j][o][i]
 // -- the same contraction with the shifts negated; the B tile (64 outputs o of the reduction x 128 inputs i) keeps Wb's
 // i-contiguous rows: an MN-major operand (layout of the weight-gradient kernel below), read with coalesced float4 loads.
-template <int MODE>
+template <int MODE, int TERMS>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -171,6 +180,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
           fence_after();
 #pragma unroll
           for (int combo = 0; combo < 6; ++combo) {
+            if (TERMS == 1 && combo < 5) continue;  // bf16 mode: the h * h chain alone
             const uint32_t al = s ? a_lo[1][ta[combo]] : a_lo[0][ta[combo]];
             const uint32_t bl = s ? b_lo[1][tb[combo]] : b_lo[0][tb[combo]];
 #pragma unroll
@@ -244,9 +254,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
         uint8_t* st = smem + s * kStage;
 #pragma unroll
         for (int u = 0; u < 2; ++u) {
-          store_split8(st, r0 + 64 * u, ch, a[u][0], a[u][1]);
-          if (MODE == kFwd) store_split8(st + 3 * kTile, r0 + 64 * u, ch, b[u][0], b[u][1]);
-          else store_split8_mn(st + 3 * kTile, bo + 32 * u, bc, b[u][0], b[u][1]);
+          store_split8(st, r0 + 64 * u, ch, a[u][0], a[u][1], TERMS);
+          if (MODE == kFwd) store_split8(st + 3 * kTile, r0 + 64 * u, ch, b[u][0], b[u][1], TERMS);
+          else store_split8_mn(st + 3 * kTile, bo + 32 * u, bc, b[u][0], b[u][1], TERMS);
         }
         fence_async_smem();
         __syncwarp();
@@ -270,11 +280,13 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_kernel(const ConvTcParams
       for (int c0 = 8 * part; c0 < kBN; c0 += 16) {
         uint32_t v[8], w[8];
         tmem_ld8(trow + c0, v);
-        tmem_ld8(trow + kBN + c0, w);
+        if (TERMS == 3) tmem_ld8(trow + kBN + c0, w);
         tmem_ld_wait8(v);
-        tmem_ld_wait8(w);
+        if (TERMS == 3) {
+          tmem_ld_wait8(w);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) + __uint_as_float(w[e]));
+          for (int e = 0; e < 8; ++e) v[e] = __float_as_uint(__uint_as_float(v[e]) + __uint_as_float(w[e]));
+        }
         if (c0 + 16 >= kBN) {  // this warp's last load of the accumulator: hand it back before the arithmetic
           fence_before();
           __syncwarp();
@@ -365,6 +377,13 @@ __global__ void __launch_bounds__(256) conv_split_epilogue_kernel(const ConvTcPa
   }
 }
 
+// LIPVQ_CONV_PRECISION=bf16: the bf16 mode of the three kernels (plain bf16 operands, ONE MMA chain, fp32 accumulation /
+// bias / activation / I/O) -- values within 1e-2 of the fp32 evaluation (north_star's bf16 gate); default: fp32 accuracy
+inline int conv_terms() {
+  const char* f = getenv("LIPVQ_CONV_PRECISION");
+  return (f && f[0] == 'b') ? 1 : 3;
+}
+
 // split by tap when that still leaves the grid inside one wave (LIPVQ_CONV_SPLIT=0: never)
 inline int conv_split(int64_t N, int E, int jlo, int jhi) {
   if (const char* f = getenv("LIPVQ_CONV_SPLIT"))
@@ -394,12 +413,14 @@ struct ConvTcWParams {
   float scale;
   float* dWf; float* db;
   int chunks_per_slice, n_tiles;   // n_tiles = (jhi - jlo) * E / 128 column tiles
+  int terms;                       // 3 / 1 as in ConvTcParams
 };
 
 __device__ __forceinline__ void red_add_v4(float* dst, float a, float b, float c, float d) {
   asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
+template <int TERMS>
 __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTcWParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -454,6 +475,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTc
         uint32_t acc_hh = (hh_used >> rot) & 1u;
 #pragma unroll
         for (int combo = 0; combo < 6; ++combo) {
+          if (TERMS == 1 && combo < 5) continue;
           const uint64_t ad = s ? da[1][ta[combo]] : da[0][ta[combo]];
           const uint64_t bd = s ? db_[1][tb[combo]] : db_[0][tb[combo]];
 #pragma unroll
@@ -525,8 +547,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTc
         g1.z = (mk[u].y & 0xFF0000u) ? g1.z * sc : 0.f; g1.w = (mk[u].y & 0xFF000000u) ? g1.w * sc : 0.f;
         const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
         const int tk = tkb + 32 * u;
-        store_split8_mn(st, tk, c, g0, g1);
-        store_split8_mn(st + 3 * kTile, tk, c, inx[u] ? b[u][0] : z4, inx[u] ? b[u][1] : z4);
+        store_split8_mn(st, tk, c, g0, g1, TERMS);
+        store_split8_mn(st + 3 * kTile, tk, c, inx[u] ? b[u][0] : z4, inx[u] ? b[u][1] : z4, TERMS);
         rsum[0] += g0.x; rsum[1] += g0.y; rsum[2] += g0.z; rsum[3] += g0.w;
         rsum[4] += g1.x; rsum[5] += g1.y; rsum[6] += g1.z; rsum[7] += g1.w;
       }
@@ -550,12 +572,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv_tc_bwd_w_kernel(const ConvTc
     for (int c0 = 8 * part; c0 < kBN; c0 += 16) {
       uint32_t v[8], w[8];
       float o[8];
-      tmem_ld8(tmem_base + lane_off + c0, v);
+      if (TERMS == 3) tmem_ld8(tmem_base + lane_off + c0, v);   // (bf16 mode: the small-chain accumulator was never written)
       tmem_ld8(tmem_base + lane_off + kBN + c0, w);
-      tmem_ld_wait8(v);
+      if (TERMS == 3) tmem_ld_wait8(v);
       tmem_ld_wait8(w);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) o[e] = __uint_as_float(v[e]) + __uint_as_float(w[e]);
+      for (int e = 0; e < 8; ++e) o[e] = (TERMS == 3 ? __uint_as_float(v[e]) : 0.f) + __uint_as_float(w[e]);
       if (two) {
         tmem_ld8(tmem_base + lane_off + 2 * kBN + c0, v);
         tmem_ld_wait8(v);
@@ -608,14 +630,17 @@ int conv_tc_fwd_launch(const float* X, int64_t N, int T, int E, const float* Wf,
   static bool smem_set[kMaxDevices] = {};  // the attribute is per device
   const int dev_ = current_device();
   if (!smem_set[dev_]) {
-    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel<kFwd>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel<kFwd, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel<kFwd, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
     smem_set[dev_] = true;
   }
   p.split = conv_split(N, E, jlo, jhi);
+  p.terms = conv_terms();
   const int64_t tiles = ceil_div64(N, kBM) * (E / kBN) * (p.split ? (jhi - jlo) * p.split : 1);
   const int sms = sm_count();
   if (p.split) LIPVQ_CUDA(cudaMemsetAsync(OUT, 0, (size_t)N * E * sizeof(float), stream));
-  LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kFwd>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
+  if (p.terms == 1) LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kFwd, 1>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
+  else LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kFwd, 3>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
   LIPVQ_LAUNCHED("conv_tc_kernel<fwd>");
   if (p.split) {
     int64_t blocks = ceil_div64(N * E / 4, 256);
@@ -634,14 +659,17 @@ int conv_tc_bwd_x_launch(const float* dOUT, const uint8_t* mask, int64_t N, int 
   static bool smem_set[kMaxDevices] = {};
   const int dev_ = current_device();
   if (!smem_set[dev_]) {
-    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel<kBwdX>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel<kBwdX, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
+    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_kernel<kBwdX, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem));
     smem_set[dev_] = true;
   }
   p.split = conv_split(N, E, jlo, jhi);
+  p.terms = conv_terms();
   const int64_t tiles = ceil_div64(N, kBM) * (E / kBN) * (p.split ? (jhi - jlo) * p.split : 1);
   const int sms = sm_count();
   if (p.split) LIPVQ_CUDA(cudaMemcpyAsync(dX, dOUT, (size_t)N * E * sizeof(float), cudaMemcpyDeviceToDevice, stream));
-  LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kBwdX>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
+  if (p.terms == 1) LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kBwdX, 1>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
+  else LIPVQ_CUDA(launch_pdl(conv_tc_kernel<kBwdX, 3>, dim3((unsigned)(tiles < sms ? tiles : sms)), dim3(kThreads), kSmem, stream, p));
   LIPVQ_LAUNCHED("conv_tc_kernel<bwd_x>");
   return LIPVQ_OK;
 }
@@ -652,6 +680,7 @@ int conv_tc_bwd_w_launch(const float* dOUT, const uint8_t* mask, const float* X,
   p.G = dOUT; p.gmask = mask; p.X = X; p.N = N; p.T = T; p.E = E; p.dil = dilation; p.jlo = jlo; p.jhi = jhi;
   p.scale = scale; p.dWf = dWf; p.db = db;
   p.n_tiles = (jhi - jlo) * (E / kBN);
+  p.terms = conv_terms();
   const int tiles = (E / kBM) * p.n_tiles;
   const int64_t total_chunks = ceil_div64(N, kChunk);
   int64_t slices = sm_count() / tiles;
@@ -662,10 +691,12 @@ int conv_tc_bwd_w_launch(const float* dOUT, const uint8_t* mask, const float* X,
   static bool smem_set[kMaxDevices] = {};
   const int dev_ = current_device();
   if (!smem_set[dev_]) {
-    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_bwd_w_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemW));
+    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_bwd_w_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemW));
+    LIPVQ_CUDA(cudaFuncSetAttribute(conv_tc_bwd_w_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemW));
     smem_set[dev_] = true;
   }
-  LIPVQ_CUDA(launch_pdl(conv_tc_bwd_w_kernel, dim3((unsigned)tiles, (unsigned)slices), dim3(kThreads), kSmemW, stream, p));
+  if (p.terms == 1) LIPVQ_CUDA(launch_pdl(conv_tc_bwd_w_kernel<1>, dim3((unsigned)tiles, (unsigned)slices), dim3(kThreads), kSmemW, stream, p));
+  else LIPVQ_CUDA(launch_pdl(conv_tc_bwd_w_kernel<3>, dim3((unsigned)tiles, (unsigned)slices), dim3(kThreads), kSmemW, stream, p));
   LIPVQ_LAUNCHED("conv_tc_bwd_w_kernel");
   return LIPVQ_OK;
 }

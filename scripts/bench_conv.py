@@ -15,7 +15,10 @@ Wf, Wb = ops.conv_pack_weights(W, True, True)
 go = torch.randn(B * T, E, generator=g).cuda()
 _, mask = ops.dilated_conv_fwd(x, T, Wf, b, 2)
 dWf, db = torch.zeros(E, 3, E).cuda(), torch.zeros(E).cuda()
-for algo in ("tc", "simt"):
+for algo in ("tc", "tc-bf16", "simt"):
+    os.environ.pop("LIPVQ_CONV_PRECISION", None)
+    if algo == "tc-bf16":
+        os.environ["LIPVQ_CONV_PRECISION"] = "bf16"
     if algo == "simt":
         os.environ["LIPVQ_CONV_ALGO"] = "simt"
     for name, fn in (("forward", lambda: ops.dilated_conv_fwd(x, T, Wf, b, 2)),

@@ -194,3 +194,56 @@ def test_conv_tc_few_tokens_split_by_tap(drop):
         assert torch.allclose(dx, dx1, rtol=1e-5, atol=2e-5 * dx1.abs().max().item())
     if torch.equal(mask, mask2):
         assert torch.allclose(dx, dx2, rtol=1e-5, atol=2e-5 * dx2.abs().max().item())
+
+
+def _bf16(fn):
+    os.environ["LIPVQ_CONV_PRECISION"] = "bf16"
+    try:
+        return fn()
+    finally:
+        del os.environ["LIPVQ_CONV_PRECISION"]
+
+
+@pytest.mark.parametrize("B,T,E", [(512, 16, 512), (16, 10, 512)])
+def test_conv_bf16_mode_within_the_bf16_gate(B, T, E):
+    """LIPVQ_CONV_PRECISION=bf16: plain bf16 operands, one MMA chain, fp32 accumulation and epilogue.  north_star's gate for
+    bf16 is 1e-2: forward values and both gradients within 1e-2 of the fp32-accurate path, relative to the tensor's scale."""
+    import lipvq as L
+    g = torch.Generator().manual_seed(31)
+    N = B * T
+    x = torch.randn(N, E, generator=g).to(DEV)
+    go = torch.randn(N, E, generator=g).to(DEV)
+    W = (torch.randn(E, E, 3, generator=g) / (3 * E) ** 0.5).to(DEV)
+    b = (torch.randn(E, generator=g) * 0.1).to(DEV)
+    Wf, Wb = L.ops.conv_pack_weights(W, True, True)
+    out, mask = L.ops.dilated_conv_fwd(x, T, Wf, b, 2)
+
+    def grads():
+        dx = L.ops.dilated_conv_bwd_x(go, mask, T, Wb, 2)
+        dW, db = torch.zeros(E, 3, E, device=DEV), torch.zeros(E, device=DEV)
+        L.ops.dilated_conv_bwd_w(go, mask, x, T, 2, dW, db)
+        return dx, dW, db
+    dx, dW, db = grads()
+    out_b, mask_b = _bf16(lambda: L.ops.dilated_conv_fwd(x, T, Wf, b, 2))
+    dx_b, dW_b, db_b = _bf16(grads)
+    torch.cuda.synchronize()
+
+    def gate(a, r, what):
+        err = (a - r).abs().max().item() / r.abs().max().item()
+        assert err < 1e-2, (what, err)
+        assert err > 1e-6 or what == "db", (what, err, "the bf16 mode did not run")   # (db is summed in fp32 in both modes)
+    gate(out_b, out, "out"); gate(dx_b, dx, "dx"); gate(dW_b, dW, "dW"); gate(db_b, db, "db")
+    assert (mask_b != mask).float().mean().item() < 5e-3     # keep-mask flips only where the pre-activation is ~0
+
+
+def test_t2_embeddings_in_bf16_conv_mode_within_gate():
+    import lipvq as L
+    torch.manual_seed(7)
+    m = L.HierarchicalVQVAE(12, embed_dim=512, num_subclusters=1024, num_clusters=512, num_stages=2, num_layers_per_stage=4,
+                            dropout=0.0, kmeans_init=False).to(DEV).eval()
+    x = torch.rand(64, 16, 12, device=DEV) * 2 - 1
+    with torch.no_grad():
+        e32 = m.encoder(x)
+        e16 = _bf16(lambda: m.encoder(x))
+    err = (e16 - e32).abs().max().item() / e32.abs().max().item()
+    assert 1e-6 < err < 1e-2, err
